@@ -1,0 +1,129 @@
+/*
+ * b200_paged.h -- C ABI of libb200_paged.so: the B200 (sm_100a) replacement for the
+ * opaque device call on vllm-neuron's decode hot path.
+ *
+ * What it replaces.  In the reference every numeric op of a step happens inside ONE call,
+ *   self.model(input_ids, position_ids, input_block_ids, slot_mapping, block_tables,
+ *              full_context_lens, computed_context_lens, sampling_params, ...)
+ *   vllm_neuron/worker/neuronx_distributed_model_runner.py:517-530
+ *   -> vllm_neuron/worker/neuronx_distributed_model_loader.py:336-348  (NxDI forward)
+ * The entry points below are the pieces of that call, plus the device-side version of the
+ * host index construction that feeds it (model_runner.py:739-763, 798-832, 848-936).
+ *
+ * Conventions.  Plain pointers and sizes only (no torch types).  Every pointer is a DEVICE
+ * pointer unless named host_*.  `stream` is a cudaStream_t passed as void*.  No entry point
+ * allocates device memory or synchronises the device: scratch is passed in as `workspace`
+ * (size from the matching *_workspace_bytes).  Return value 0 = ok; otherwise a B200_ERR_*
+ * code (or a cudaError_t for launch failures) and b200_last_error() holds a message.
+ * There is no CPU fallback: without an sm_100 device every compute call fails.
+ *
+ * Block-KV contract (reference: model_runner.py:76-81, platform.py:149-159):
+ *   slot = block_id * block_size + offset;  slot == -1 is padding (never written);
+ *   block 0 is vLLM's null block;  block tables are right-padded with 0.
+ * Device pool layout (ours; NxDI's is not observable): K and V pools are separate arrays
+ *   [num_blocks][Hkv][block_size][D] bf16, so one (block, kv head) tile is contiguous.
+ */
+#ifndef B200_PAGED_H_
+#define B200_PAGED_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_ABI_VERSION 1
+
+enum {
+  B200_OK = 0,
+  B200_ERR_INVALID_ARG = -1,
+  B200_ERR_NO_DEVICE = -2,      /* no CUDA device with compute capability 10.x */
+  B200_ERR_WORKSPACE = -3,      /* workspace too small */
+  B200_ERR_UNSUPPORTED = -4,    /* shape outside what the kernels cover */
+  B200_ERR_DRIVER = -5          /* cuTensorMapEncodeTiled / driver entry point failure */
+};
+
+enum { B200_BF16 = 0, B200_FP8_E4M3 = 1, B200_INT8 = 2, B200_F32 = 3 };
+
+int b200_abi_version(void);
+const char* b200_last_error(void);
+/* 0 iff `device` is an sm_100 part (reference analogue: /dev/neuron* probe, vllm_neuron/__init__.py:8-23) */
+int b200_device_check(int device);
+
+/* ---------------------------------------------------------------- index construction on device
+ * Replaces model_runner.py:765-832 (+ :887-917): per decode row b (persistent row r = row_ids[b]):
+ *   position = num_tokens[r] - 1; full_ctx = position + 1;
+ *   slot = block_table[r][position / bs] * bs + position % bs.
+ * Outputs are int64 like the reference's tensors (ctx_lens int32 for the kernels). */
+int b200_build_decode_meta(const int32_t* block_table, int64_t bt_row_stride, const int32_t* row_ids,
+                           const int32_t* num_tokens, int64_t* slot_mapping, int64_t* positions, int32_t* ctx_lens,
+                           int B, int max_blocks, int block_size, void* stream);
+/* Replaces model_runner.py:739-763 (+ :853-885): batch-1 prefill with a prefix-cache hit.
+ * slot_mapping_out[i] for i in [0, max_model_len): slot of token (num_computed + i) while that
+ * token < prompt_len, else -1 (the reference's slice [num_computed:] right-padded with -1).
+ * positions_out[i] = num_computed + i for the same range, else 0. */
+int b200_build_prefill_meta(const int32_t* block_table_row, int prompt_len, int num_computed, int64_t* slot_mapping_out,
+                            int64_t* positions_out, int max_model_len, int block_size, void* stream);
+/* Mirror of InputBatch.block_table.append_row / add_row (model_runner.py:461-471, 484-486):
+ * updates = n packed (row, col, block_id) int32 triples already on the device. */
+int b200_block_table_scatter(int32_t* block_table, int64_t bt_row_stride, const int32_t* updates, int n, int rows,
+                             int max_blocks, void* stream);
+/* End of a decode step on device: tokens_io[b] = sampled[b]; num_tokens[row_ids[b]] += 1
+ * (the device-side twin of model_runner.py:325-339, so a captured step can be replayed). */
+int b200_advance_decode(const int64_t* sampled, int64_t* tokens_io, int32_t* num_tokens, const int32_t* row_ids, int B,
+                        void* stream);
+
+/* ---------------------------------------------------------------- KV-cache write
+ * Scatter k, v [T][Hkv][D] (token stride in elements) into the pools by slot_mapping; slot < 0 skipped. */
+int b200_kv_write(const void* k, const void* v, int64_t k_token_stride, int64_t v_token_stride, void* k_pool, void* v_pool,
+                  const int64_t* slot_mapping, int T, int Hkv, int D, int block_size, int num_blocks, void* stream);
+/* Fused: rotate q and k of a packed qkv row [T][(Hq+2Hkv)*D] (rotate-half RoPE, fp32 cos/sin tables
+ * [max_pos][D/2]), write roped q back in place, and scatter roped k and v into the pools. */
+int b200_rope_kv_write(void* qkv, const int64_t* positions, const float* cos_table, const float* sin_table, int max_pos,
+                       void* k_pool, void* v_pool, const int64_t* slot_mapping, int T, int Hq, int Hkv, int D,
+                       int block_size, int num_blocks, void* stream);
+
+/* ---------------------------------------------------------------- paged attention
+ * Decode (q_len = 1): out[b][h][:] = softmax(q K^T scale) V over ctx_lens[b] tokens gathered through
+ * block_table[row_ids ? row_ids[b] : b].  Split along the context in chunks of `chunk_blocks` blocks
+ * (flash-decoding); partials live in `workspace`.  chunk_blocks = 0 picks a default. */
+size_t b200_paged_attn_decode_workspace_bytes(int B, int Hq, int Hkv, int D, int max_blocks, int chunk_blocks);
+int b200_paged_attn_decode(const void* q, int64_t q_token_stride, const void* k_pool, const void* v_pool, int num_blocks,
+                           const int32_t* block_table, int64_t bt_row_stride, const int32_t* row_ids,
+                           const int32_t* ctx_lens, void* out, void* workspace, size_t workspace_bytes, int B, int Hq,
+                           int Hkv, int D, int block_size, int max_blocks, int chunk_blocks, float scale, void* stream);
+/* Prefix-cached prefill, one sequence: queries for absolute positions computed_len .. computed_len+S_new-1,
+ * causal over cached prefix + new tokens, all K/V already in the pools. */
+int b200_paged_attn_prefill(const void* q, int64_t q_token_stride, const void* k_pool, const void* v_pool, int num_blocks,
+                            const int32_t* block_table_row, void* out, int S_new, int computed_len, int Hq, int Hkv,
+                            int D, int block_size, float scale, void* stream);
+
+/* ---------------------------------------------------------------- per-channel-scaled GEMM (tcgen05 / TMEM / TMA)
+ * out[M][N] = (sum_k a[m][k] * w[n][k]) * a_scale[m] * w_scale[n] + bias[n] + residual[m][n]
+ * a: [M][K], w: [N][K], both `ab_dtype` (BF16 | FP8_E4M3 | INT8); scales fp32 (NULL = 1), bias bf16 [N] or NULL,
+ * residual bf16 [M][N] or NULL; out_dtype BF16 | F32.  split_k = 0 picks one. */
+size_t b200_gemm_workspace_bytes(int M, int N, int K, int ab_dtype, int split_k);
+int b200_gemm(const void* a, const void* w, void* out, const float* a_scale, const float* w_scale, const void* bias,
+              const void* residual, int M, int N, int K, int ab_dtype, int out_dtype, int split_k, void* workspace,
+              size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------- glue kernels of the decoder step */
+/* y = x * rsqrt(mean(x^2)+eps) * w (fp32 math).  Writes any of: out_bf16 [T][H]; out_q [T][H] (q_dtype FP8/INT8)
+ * with dynamic per-token scale out_scale [T] (scale = amax/qmax, q = rn(y_bf16 / scale)). */
+int b200_rmsnorm(const void* x, const void* w, void* out_bf16, void* out_q, float* out_scale, int T, int H, float eps,
+                 int q_dtype, void* stream);
+/* act = silu(gate) * up from gate_up [T][2I] (gate columns first); same output options as rmsnorm. */
+int b200_silu_mul(const void* gate_up, void* out_bf16, void* out_q, float* out_scale, int T, int I, int q_dtype,
+                  void* stream);
+int b200_quantize_per_token(const void* x, void* out_q, float* out_scale, int T, int K, int q_dtype, void* stream);
+int b200_embedding(const int64_t* tokens, const void* table, void* out, int T, int H, int V, void* stream);
+/* Greedy sampling (reference: top_k=1, temperature=1.0 for temperature 0, model_runner.py:1126-1128).
+ * out_idx[t] = idx_offset + first index of the row maximum; out_val[t] = that maximum (for TP merges). */
+int b200_argmax(const float* logits, int64_t row_stride, float* out_val, int64_t* out_idx, int T, int V,
+                int64_t idx_offset, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_PAGED_H_ */

@@ -1,0 +1,115 @@
+#!/usr/bin/env python
+"""Kernel-level micro-benchmarks (CUDA events, inputs rotated through > L2-size working sets).
+
+    python tools/microbench.py attn|gemm|all [--json out.json]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from vllm_neuron_b200 import ops  # noqa: E402
+
+PEAKS = {}
+try:
+    PEAKS = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))
+except Exception:
+    pass
+HBM = PEAKS.get("hbm_gbs", 6650.0)
+
+
+def time_calls(fns, iters=3, warmup=1):
+    """fns: list of closures run back to back (one 'round'); returns avg ms per closure."""
+    for _ in range(warmup):
+        for f in fns:
+            f()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        for f in fns:
+            f()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / (iters * len(fns))
+
+
+def bench_attn(b=64, hq=32, hkv=8, d=128, ctx=2048, layers=8, chunks=(0, 4, 8, 16, 32)):
+    bs = 32
+    nblk = ctx // bs
+    nb = b * nblk + 1
+    g = torch.Generator(device="cuda").manual_seed(11)
+    pools = [
+        (torch.randn(nb, hkv, bs, d, generator=g, device="cuda", dtype=torch.bfloat16),
+         torch.randn(nb, hkv, bs, d, generator=g, device="cuda", dtype=torch.bfloat16))
+        for _ in range(layers)
+    ]
+    perm = torch.randperm(nb - 1, generator=torch.Generator().manual_seed(7)) + 1
+    bt = perm[: b * nblk].reshape(b, nblk).to(torch.int32).cuda()
+    ctxl = torch.full((b,), ctx, dtype=torch.int32, device="cuda")
+    q = torch.randn(b, hq, d, generator=g, device="cuda", dtype=torch.bfloat16)
+    out = torch.empty_like(q)
+    ws = torch.empty(ops.paged_attn_decode_workspace_bytes(b, hq, hkv, d, nblk, 0), dtype=torch.uint8, device="cuda")
+    alg = b * ctx * 2 * hkv * d * 2 + 2 * b * hq * d * 2 + b * nblk * 4
+    res = []
+    for cb in chunks:
+        fns = [
+            (lambda kp=kp, vp=vp: ops.paged_attn_decode(q, kp, vp, bt, ctxl, d**-0.5, out=out, workspace=ws, chunk_blocks=cb))
+            for kp, vp in pools
+        ]
+        ms = time_calls(fns)
+        gbs = alg / ms / 1e6
+        res.append({"kernel": "paged_attn_decode", "B": b, "Hq": hq, "Hkv": hkv, "D": d, "ctx": ctx, "chunk_blocks": cb,
+                    "ms": ms, "GBps": gbs, "frac_hbm": gbs / HBM})
+        print(res[-1], flush=True)
+    return res
+
+
+def bench_gemm(shapes=None, kinds=("fp8", "bf16")):
+    shapes = shapes or [(64, 6144, 4096), (64, 4096, 4096), (64, 28672, 4096), (64, 4096, 14336), (64, 128256, 4096)]
+    res = []
+    for kind in kinds:
+        for m, n, k in shapes:
+            eb = 2 if kind == "bf16" else 1
+            copies = max(2, int(300e6 // (n * k * eb)) + 1)
+            if kind == "bf16":
+                ws_ = [torch.randn(n, k, device="cuda", dtype=torch.bfloat16) for _ in range(copies)]
+                a = torch.randn(m, k, device="cuda", dtype=torch.bfloat16)
+                sa = sw = None
+            else:
+                ws_ = [torch.randn(n, k, device="cuda", dtype=torch.bfloat16).to(torch.float8_e4m3fn) for _ in range(copies)]
+                a = torch.randn(m, k, device="cuda", dtype=torch.bfloat16).to(torch.float8_e4m3fn)
+                sa = torch.ones(m, device="cuda")
+                sw = torch.ones(n, device="cuda")
+            out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+            nbytes = ops.gemm_workspace_bytes(m, n, k, 0 if kind == "bf16" else 1, 0)
+            wsp = torch.empty(max(nbytes, 16), dtype=torch.uint8, device="cuda")
+            fns = [(lambda w=w: ops.gemm(a, w, sa, sw, out=out, workspace=wsp)) for w in ws_]
+            ms = time_calls(fns, iters=5)
+            alg = n * k * eb + n * 4 + m * k * eb + m * 4 + 2 * m * n
+            gbs = alg / ms / 1e6
+            res.append({"kernel": f"gemm_{kind}", "M": m, "N": n, "K": k, "ms": ms, "GBps": gbs, "frac_hbm": gbs / HBM,
+                        "TFLOPs": 2 * m * n * k / ms / 1e9})
+            print(res[-1], flush=True)
+            del ws_
+    return res
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("what", nargs="?", default="all")
+    ap.add_argument("--json", default=None)
+    a = ap.parse_args()
+    ops.device_check(0)
+    out = []
+    if a.what in ("attn", "all"):
+        out += bench_attn()
+    if a.what in ("gemm", "all"):
+        out += bench_gemm()
+    if a.json:
+        json.dump(out, open(a.json, "w"), indent=1)

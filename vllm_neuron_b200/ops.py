@@ -1,0 +1,274 @@
+"""Tensor-level wrappers over the C ABI: validate, take raw pointers and the current CUDA stream, call.
+
+Torch is plumbing here (device memory + streams); every op below runs one of the hand-written
+sm_100a kernels in libb200_paged.so.  Nothing in this file computes on the host.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _cabi
+from ._cabi import BF16, F32, FP8_E4M3, INT8, check
+
+_QDT = {None: BF16, "bf16": BF16, "fp8": FP8_E4M3, "int8": INT8}
+_TORCH_Q = {FP8_E4M3: torch.float8_e4m3fn, INT8: torch.int8}
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return 0 if t is None else t.data_ptr()
+
+
+def _cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _cabi.B200Error("b200 ops need CUDA tensors (no CPU fallback)")
+
+
+def device_check(device: int = 0):
+    check(_cabi.load().b200_device_check(device), "b200_device_check")
+
+
+# ------------------------------------------------------------------ index construction
+def build_decode_meta(block_table, row_ids, num_tokens, slot_mapping, positions, ctx_lens, block_size: int):
+    """block_table int32 [rows, max_blocks]; row_ids int32 [B] or None; num_tokens int32 [rows];
+    outputs: slot_mapping int64 [B], positions int64 [B], ctx_lens int32 [B]."""
+    _cuda(block_table, num_tokens, slot_mapping)
+    assert block_table.dtype == torch.int32 and num_tokens.dtype == torch.int32
+    assert slot_mapping.dtype == torch.int64 and positions.dtype == torch.int64 and ctx_lens.dtype == torch.int32
+    b = slot_mapping.numel()
+    check(
+        _cabi.load().b200_build_decode_meta(
+            _ptr(block_table), block_table.stride(0), _ptr(row_ids), _ptr(num_tokens), _ptr(slot_mapping),
+            _ptr(positions), _ptr(ctx_lens), b, block_table.shape[1], block_size, _stream(),
+        ),
+        "b200_build_decode_meta",
+    )
+
+
+def build_prefill_meta(block_table_row, prompt_len: int, num_computed: int, slot_mapping, positions, block_size: int):
+    _cuda(block_table_row, slot_mapping, positions)
+    assert block_table_row.dtype == torch.int32 and slot_mapping.dtype == torch.int64 and positions.dtype == torch.int64
+    check(
+        _cabi.load().b200_build_prefill_meta(
+            _ptr(block_table_row), prompt_len, num_computed, _ptr(slot_mapping), _ptr(positions),
+            slot_mapping.numel(), block_size, _stream(),
+        ),
+        "b200_build_prefill_meta",
+    )
+
+
+def block_table_scatter(block_table, updates):
+    """updates int32 [n, 3] = (row, col, block_id) on the device."""
+    _cuda(block_table, updates)
+    assert block_table.dtype == torch.int32 and updates.dtype == torch.int32 and updates.is_contiguous()
+    n = updates.shape[0]
+    check(
+        _cabi.load().b200_block_table_scatter(
+            _ptr(block_table), block_table.stride(0), _ptr(updates), n, block_table.shape[0], block_table.shape[1], _stream()
+        ),
+        "b200_block_table_scatter",
+    )
+
+
+def advance_decode(sampled, tokens_io, num_tokens, row_ids):
+    _cuda(sampled, tokens_io, num_tokens)
+    check(
+        _cabi.load().b200_advance_decode(
+            _ptr(sampled), _ptr(tokens_io), _ptr(num_tokens), _ptr(row_ids), sampled.numel(), _stream()
+        ),
+        "b200_advance_decode",
+    )
+
+
+# ------------------------------------------------------------------ KV cache
+def kv_write(k, v, k_pool, v_pool, slot_mapping):
+    """k, v [T, Hkv, D] bf16 (last two dims contiguous); pools [num_blocks, Hkv, bs, D]."""
+    _cuda(k, v, k_pool, v_pool, slot_mapping)
+    t, hkv, d = k.shape
+    nb, hkv2, bs, d2 = k_pool.shape
+    assert (hkv, d) == (hkv2, d2) and k.stride(2) == 1 and k.stride(1) == d and v.stride(1) == d
+    assert k_pool.is_contiguous() and v_pool.is_contiguous() and slot_mapping.dtype == torch.int64
+    check(
+        _cabi.load().b200_kv_write(
+            _ptr(k), _ptr(v), k.stride(0), v.stride(0), _ptr(k_pool), _ptr(v_pool), _ptr(slot_mapping),
+            t, hkv, d, bs, nb, _stream(),
+        ),
+        "b200_kv_write",
+    )
+
+
+def rope_kv_write(qkv, positions, cos, sin, k_pool, v_pool, slot_mapping, num_q_heads: int):
+    """qkv [T, (Hq+2Hkv)*D] bf16 contiguous; q is rotated in place, roped k and v go to the pools."""
+    _cuda(qkv, positions, cos, sin, k_pool, v_pool, slot_mapping)
+    nb, hkv, bs, d = k_pool.shape
+    t = qkv.shape[0]
+    assert qkv.is_contiguous() and qkv.shape[1] == (num_q_heads + 2 * hkv) * d and qkv.dtype == torch.bfloat16
+    assert cos.dtype == torch.float32 and cos.shape[1] == d // 2 and cos.is_contiguous() and sin.is_contiguous()
+    assert positions.dtype == torch.int64 and slot_mapping.dtype == torch.int64
+    check(
+        _cabi.load().b200_rope_kv_write(
+            _ptr(qkv), _ptr(positions), _ptr(cos), _ptr(sin), cos.shape[0], _ptr(k_pool), _ptr(v_pool),
+            _ptr(slot_mapping), t, num_q_heads, hkv, d, bs, nb, _stream(),
+        ),
+        "b200_rope_kv_write",
+    )
+
+
+# ------------------------------------------------------------------ paged attention
+def paged_attn_decode_workspace_bytes(b, hq, hkv, d, max_blocks, chunk_blocks=0) -> int:
+    return int(_cabi.load().b200_paged_attn_decode_workspace_bytes(b, hq, hkv, d, max_blocks, chunk_blocks))
+
+
+def paged_attn_decode(q, k_pool, v_pool, block_table, ctx_lens, scale, out=None, workspace=None, row_ids=None,
+                      max_blocks=None, chunk_blocks=0):
+    """q [B, Hq, D] bf16 (token stride arbitrary); block_table int32 [rows, max_blocks]; ctx_lens int32 [B]."""
+    _cuda(q, k_pool, v_pool, block_table, ctx_lens)
+    b, hq, d = q.shape
+    nb, hkv, bs, d2 = k_pool.shape
+    assert d == d2 and q.stride(2) == 1 and q.stride(1) == d and q.dtype == torch.bfloat16
+    assert block_table.dtype == torch.int32 and ctx_lens.dtype == torch.int32
+    mb = block_table.shape[1] if max_blocks is None else min(max_blocks, block_table.shape[1])
+    if out is None:
+        out = torch.empty((b, hq, d), dtype=q.dtype, device=q.device)
+    assert out.is_contiguous()
+    if workspace is None:
+        workspace = torch.empty(paged_attn_decode_workspace_bytes(b, hq, hkv, d, mb, chunk_blocks), dtype=torch.uint8, device=q.device)
+    check(
+        _cabi.load().b200_paged_attn_decode(
+            _ptr(q), q.stride(0), _ptr(k_pool), _ptr(v_pool), nb, _ptr(block_table), block_table.stride(0),
+            _ptr(row_ids), _ptr(ctx_lens), _ptr(out), _ptr(workspace), workspace.numel() * workspace.element_size(),
+            b, hq, hkv, d, bs, mb, chunk_blocks, float(scale), _stream(),
+        ),
+        "b200_paged_attn_decode",
+    )
+    return out
+
+
+def paged_attn_prefill(q, k_pool, v_pool, block_table_row, computed_len: int, scale, out=None):
+    """q [S_new, Hq, D] bf16; one sequence; K/V of all computed_len + S_new tokens already in the pools."""
+    _cuda(q, k_pool, v_pool, block_table_row)
+    s_new, hq, d = q.shape
+    nb, hkv, bs, _ = k_pool.shape
+    assert q.stride(2) == 1 and q.stride(1) == d and block_table_row.dtype == torch.int32
+    if out is None:
+        out = torch.empty((s_new, hq, d), dtype=q.dtype, device=q.device)
+    check(
+        _cabi.load().b200_paged_attn_prefill(
+            _ptr(q), q.stride(0), _ptr(k_pool), _ptr(v_pool), nb, _ptr(block_table_row), _ptr(out), s_new,
+            computed_len, hq, hkv, d, bs, float(scale), _stream(),
+        ),
+        "b200_paged_attn_prefill",
+    )
+    return out
+
+
+# ------------------------------------------------------------------ GEMM
+def _ab_dtype(t):
+    if t.dtype == torch.bfloat16:
+        return BF16
+    if t.dtype == torch.float8_e4m3fn:
+        return FP8_E4M3
+    if t.dtype == torch.int8:
+        return INT8
+    raise _cabi.B200Error(f"unsupported GEMM operand dtype {t.dtype}")
+
+
+def gemm_workspace_bytes(m, n, k, ab_dtype, split_k=0) -> int:
+    return int(_cabi.load().b200_gemm_workspace_bytes(m, n, k, ab_dtype, split_k))
+
+
+def gemm(a, w, a_scale=None, w_scale=None, bias=None, residual=None, out=None, out_dtype=torch.bfloat16, split_k=0,
+         workspace=None):
+    """out[M,N] = (a[M,K] @ w[N,K]^T) * a_scale[m] * w_scale[n] + bias[n] + residual[m,n]."""
+    _cuda(a, w, a_scale, w_scale, bias, residual)
+    m, k = a.shape
+    n, k2 = w.shape
+    assert k == k2 and a.is_contiguous() and w.is_contiguous() and a.dtype == w.dtype
+    dt = _ab_dtype(a)
+    if out is None:
+        out = torch.empty((m, n), dtype=out_dtype, device=a.device)
+    assert out.is_contiguous() and out.shape == (m, n)
+    odt = F32 if out.dtype == torch.float32 else BF16
+    if residual is not None:
+        assert residual.dtype == torch.bfloat16 and residual.is_contiguous() and residual.shape == (m, n)
+    if workspace is None:
+        nbytes = gemm_workspace_bytes(m, n, k, dt, split_k)
+        workspace = torch.empty(nbytes, dtype=torch.uint8, device=a.device) if nbytes else None
+    check(
+        _cabi.load().b200_gemm(
+            _ptr(a), _ptr(w), _ptr(out), _ptr(a_scale), _ptr(w_scale), _ptr(bias), _ptr(residual), m, n, k, dt, odt,
+            split_k, _ptr(workspace), 0 if workspace is None else workspace.numel() * workspace.element_size(), _stream(),
+        ),
+        "b200_gemm",
+    )
+    return out
+
+
+# ------------------------------------------------------------------ glue
+def rmsnorm(x, w, eps, quant=None, out_bf16=None, want_bf16=None):
+    """Returns bf16 y, or (q, scale) for quant in {"fp8","int8"} (plus y when want_bf16)."""
+    _cuda(x, w)
+    t, h = x.shape
+    assert x.is_contiguous() and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
+    qd = _QDT[quant]
+    if qd == BF16:
+        y = out_bf16 if out_bf16 is not None else torch.empty_like(x)
+        check(_cabi.load().b200_rmsnorm(_ptr(x), _ptr(w), _ptr(y), 0, 0, t, h, float(eps), qd, _stream()), "b200_rmsnorm")
+        return y
+    q = torch.empty((t, h), dtype=_TORCH_Q[qd], device=x.device)
+    s = torch.empty((t,), dtype=torch.float32, device=x.device)
+    y = (out_bf16 if out_bf16 is not None else torch.empty_like(x)) if want_bf16 else None
+    check(_cabi.load().b200_rmsnorm(_ptr(x), _ptr(w), _ptr(y), _ptr(q), _ptr(s), t, h, float(eps), qd, _stream()), "b200_rmsnorm")
+    return (q, s, y) if want_bf16 else (q, s)
+
+
+def silu_mul(gate_up, quant=None):
+    _cuda(gate_up)
+    t, i2 = gate_up.shape
+    i = i2 // 2
+    assert gate_up.is_contiguous() and gate_up.dtype == torch.bfloat16
+    qd = _QDT[quant]
+    if qd == BF16:
+        y = torch.empty((t, i), dtype=torch.bfloat16, device=gate_up.device)
+        check(_cabi.load().b200_silu_mul(_ptr(gate_up), _ptr(y), 0, 0, t, i, qd, _stream()), "b200_silu_mul")
+        return y
+    q = torch.empty((t, i), dtype=_TORCH_Q[qd], device=gate_up.device)
+    s = torch.empty((t,), dtype=torch.float32, device=gate_up.device)
+    check(_cabi.load().b200_silu_mul(_ptr(gate_up), 0, _ptr(q), _ptr(s), t, i, qd, _stream()), "b200_silu_mul")
+    return q, s
+
+
+def quantize_per_token(x, quant: str):
+    _cuda(x)
+    t, k = x.shape
+    assert x.is_contiguous() and x.dtype == torch.bfloat16
+    qd = _QDT[quant]
+    q = torch.empty((t, k), dtype=_TORCH_Q[qd], device=x.device)
+    s = torch.empty((t,), dtype=torch.float32, device=x.device)
+    check(_cabi.load().b200_quantize_per_token(_ptr(x), _ptr(q), _ptr(s), t, k, qd, _stream()), "b200_quantize_per_token")
+    return q, s
+
+
+def embedding(tokens, table, out=None):
+    _cuda(tokens, table)
+    v, h = table.shape
+    t = tokens.numel()
+    assert tokens.dtype == torch.int64 and table.is_contiguous()
+    if out is None:
+        out = torch.empty((t, h), dtype=table.dtype, device=table.device)
+    check(_cabi.load().b200_embedding(_ptr(tokens), _ptr(table), _ptr(out), t, h, v, _stream()), "b200_embedding")
+    return out
+
+
+def argmax(logits, idx_offset: int = 0, want_val: bool = False):
+    _cuda(logits)
+    t, v = logits.shape
+    assert logits.dtype == torch.float32 and logits.stride(1) == 1
+    idx = torch.empty((t,), dtype=torch.int64, device=logits.device)
+    val = torch.empty((t,), dtype=torch.float32, device=logits.device) if want_val else None
+    check(_cabi.load().b200_argmax(_ptr(logits), logits.stride(0), _ptr(val), _ptr(idx), t, v, idx_offset, _stream()), "b200_argmax")
+    return (val, idx) if want_val else idx
