@@ -6,7 +6,7 @@ import pytest
 import torch
 
 from oracle import attn_ref
-from tests.util import logical_to_device_pool, make_block_tables, rel_err
+from parity_util import logical_to_device_pool, make_block_tables, rel_err
 
 pytestmark = pytest.mark.gpu
 TOL = 2e-2

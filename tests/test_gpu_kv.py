@@ -5,7 +5,7 @@ import pytest
 import torch
 
 from oracle import index_ref, kv_ref
-from tests.util import device_to_logical_pool
+from parity_util import device_to_logical_pool
 
 pytestmark = pytest.mark.gpu
 
@@ -28,7 +28,7 @@ def test_decode_meta_matches_golden(ops, golden_index):
         b = len(c["reqs"])
         mb = mml // bs
         bt = torch.zeros((b + 3, mb), dtype=torch.int32)
-        rows = torch.tensor([(i * 2 + 1) % (b + 3) for i in range(b)], dtype=torch.int32)  # scattered persistent rows
+        rows = torch.randperm(b + 3, generator=torch.Generator().manual_seed(b))[:b].to(torch.int32)  # scattered persistent rows
         assert len(set(rows.tolist())) == b
         ntok = torch.zeros(b + 3, dtype=torch.int32)
         for i, q in enumerate(c["reqs"]):
