@@ -50,6 +50,8 @@ int b200_abi_version(void);
 const char* b200_last_error(void);
 /* 0 iff `device` is an sm_100 part (reference analogue: /dev/neuron* probe, vllm_neuron/__init__.py:8-23) */
 int b200_device_check(int device);
+/* number of kernel launches issued through this library by the calling process (bench.py's gpu_launches) */
+uint64_t b200_launch_count(void);
 
 /* ---------------------------------------------------------------- index construction on device
  * Replaces model_runner.py:765-832 (+ :887-917): per decode row b (persistent row r = row_ids[b]):

@@ -32,3 +32,56 @@ def rel_err(got, want):
 def max_rel_err(got, want, floor):
     got, want = got.float(), want.float()
     return ((got - want).abs() / want.abs().clamp_min(floor)).max().item()
+
+
+# ---------------------------------------------------------------- duck-typed vLLM config / scheduler output
+from types import SimpleNamespace  # noqa: E402
+
+
+def hf_config_from_shape(shape):
+    return SimpleNamespace(
+        hidden_size=shape.hidden, num_hidden_layers=shape.layers, num_attention_heads=shape.num_q_heads,
+        num_key_value_heads=shape.num_kv_heads, head_dim=shape.head_dim, intermediate_size=shape.intermediate,
+        vocab_size=shape.vocab, rope_theta=shape.rope_theta, rope_scaling=shape.rope_scaling,
+        rms_norm_eps=shape.rms_eps, attention_bias=shape.qkv_bias, architectures=["LlamaForCausalLM"],
+        _name_or_path=shape.name,
+    )
+
+
+def make_vllm_config(shape, *, max_num_seqs, max_model_len, block_size=32, num_gpu_blocks_override=None,
+                     prefix_caching=True, tp=1, override=None, enforce_eager=False):
+    """The attributes of VllmConfig the runner reads (the reference's unit tests use Mock configs the same way,
+    test/unit/conftest.py:104-145)."""
+    return SimpleNamespace(
+        model_config=SimpleNamespace(hf_config=hf_config_from_shape(shape), max_model_len=max_model_len, seed=0,
+                                     enforce_eager=enforce_eager, dtype=torch.bfloat16),
+        cache_config=SimpleNamespace(block_size=block_size, enable_prefix_caching=prefix_caching,
+                                     num_gpu_blocks_override=num_gpu_blocks_override),
+        parallel_config=SimpleNamespace(tensor_parallel_size=tp, world_size=tp),
+        scheduler_config=SimpleNamespace(max_num_seqs=max_num_seqs, max_model_len=max_model_len,
+                                         max_num_batched_tokens=131072),
+        load_config=SimpleNamespace(load_format="dummy"),
+        additional_config={"override_neuron_config": override or {}},
+    )
+
+
+def sched_output(new_reqs=(), cached=(), finished=()):
+    """new_reqs: (req_id, prompt_ids, block_ids, num_computed); cached: (req_id, new_block_ids or None)."""
+    num_sched = {}
+    news = []
+    for rid, prompt, blocks, ncomp in new_reqs:
+        news.append(SimpleNamespace(req_id=rid, prompt_token_ids=list(prompt), block_ids=(list(blocks),),
+                                    num_computed_tokens=ncomp, sampling_params=None, mm_features=[], lora_request=None))
+        num_sched[rid] = len(prompt) - ncomp
+    for rid, _ in cached:
+        num_sched[rid] = 1
+    c = SimpleNamespace(
+        req_ids=[r for r, _ in cached], resumed_req_ids=set(),
+        new_block_ids=[None if nb is None else (list(nb),) for _, nb in cached],
+        num_computed_tokens=[0] * len(cached), new_token_ids=[], num_output_tokens=[0] * len(cached),
+    )
+    return SimpleNamespace(
+        scheduled_new_reqs=news, scheduled_cached_reqs=c, num_scheduled_tokens=num_sched,
+        total_num_scheduled_tokens=sum(num_sched.values()), finished_req_ids=set(finished),
+        scheduled_spec_decode_tokens={}, free_encoder_mm_hashes=[],
+    )

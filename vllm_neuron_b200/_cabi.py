@@ -25,6 +25,7 @@ SIGNATURES = {
     "b200_abi_version": (_i, []),
     "b200_last_error": (C.c_char_p, []),
     "b200_device_check": (_i, [_i]),
+    "b200_launch_count": (C.c_uint64, []),
     "b200_build_decode_meta": (_i, [_p, _i64, _p, _p, _p, _p, _p, _i, _i, _i, _p]),
     "b200_build_prefill_meta": (_i, [_p, _i, _i, _p, _p, _i, _i, _p]),
     "b200_block_table_scatter": (_i, [_p, _i64, _p, _i, _i, _i, _p]),

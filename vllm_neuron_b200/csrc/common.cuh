@@ -15,6 +15,7 @@ namespace b200 {
 // ---------------------------------------------------------------- host error plumbing
 void set_last_error(const char* fmt, ...);
 int check_cuda(cudaError_t e, const char* what);
+#define B200_LAUNCHED(n) ::b200::count_launch(n)
 #define B200_CUDA_OK(expr)                         \
   do {                                             \
     int _rc = ::b200::check_cuda((expr), #expr);   \
@@ -33,6 +34,7 @@ int check_cuda(cudaError_t e, const char* what);
 int make_tmap_2d(CUtensorMap* out, const void* base, CUtensorMapDataType dt, uint32_t elem_bytes, uint64_t cols,
                  uint64_t rows, uint64_t row_pitch_bytes, uint32_t box_cols, uint32_t box_rows);
 int sm_count();
+void count_launch(int n = 1);
 
 // ---------------------------------------------------------------- device helpers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }

@@ -225,6 +225,7 @@ int launch_gemm(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilogue
   dim3 grid(p.n_tiles, p.m_tiles, p.splits);
   kern<<<grid, GEMM_THREADS, smem, stream>>>(wm, am, ep, partial, M, N, p.num_kb, p.kb_per_split);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -292,6 +293,7 @@ int b200_gemm(const void* a, const void* w, void* out, const float* a_scale, con
     int64_t total = (int64_t)M * N;
     splitk_reduce_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(partial, ep, M, N, p.splits);
     B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   }
   return B200_OK;
 }

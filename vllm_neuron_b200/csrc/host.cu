@@ -2,6 +2,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 
+#include <atomic>
 #include <mutex>
 
 #include "common.cuh"
@@ -9,6 +10,8 @@
 namespace b200 {
 
 static thread_local char g_err[512] = "";
+static std::atomic<uint64_t> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 
 void set_last_error(const char* fmt, ...) {
   va_list ap;
@@ -87,6 +90,8 @@ extern "C" {
 int b200_abi_version(void) { return B200_ABI_VERSION; }
 
 const char* b200_last_error(void) { return b200::g_err; }
+
+uint64_t b200_launch_count(void) { return b200::g_launches.load(); }
 
 int b200_device_check(int device) {
   int n = 0;

@@ -383,6 +383,7 @@ int b200_build_decode_meta(const int32_t* block_table, int64_t bt_row_stride, co
   build_decode_meta_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
       block_table, bt_row_stride, row_ids, num_tokens, slot_mapping, positions, ctx_lens, B, max_blocks, block_size);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -393,6 +394,7 @@ int b200_build_prefill_meta(const int32_t* block_table_row, int prompt_len, int 
   build_prefill_meta_kernel<<<(max_model_len + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
       block_table_row, prompt_len, num_computed, slot_mapping_out, positions_out, max_model_len, block_size);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -403,6 +405,7 @@ int b200_block_table_scatter(int32_t* block_table, int64_t bt_row_stride, const 
   block_table_scatter_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(block_table, bt_row_stride, updates, n,
                                                                                  rows, max_blocks);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -412,6 +415,7 @@ int b200_advance_decode(const int64_t* sampled, int64_t* tokens_io, int32_t* num
   if (B <= 0) return B200_OK;
   advance_decode_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(sampled, tokens_io, num_tokens, row_ids, B);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -425,6 +429,7 @@ int b200_kv_write(const void* k, const void* v, int64_t k_token_stride, int64_t 
                                                        v_token_stride / 8, (uint4*)k_pool, (uint4*)v_pool, slot_mapping,
                                                        Hkv, D / 8, block_size, (int64_t)num_blocks * block_size);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -438,6 +443,7 @@ int b200_rope_kv_write(void* qkv, const int64_t* positions, const float* cos_tab
                                                             (uint4*)k_pool, (uint4*)v_pool, slot_mapping, Hq, Hkv, D,
                                                             block_size, (int64_t)num_blocks * block_size);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -461,6 +467,7 @@ int b200_rmsnorm(const void* x, const void* w, void* out_bf16, void* out_q, floa
     B200_REQUIRE(false, "rmsnorm: bad q_dtype %d", q_dtype);
   }
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -483,6 +490,7 @@ int b200_silu_mul(const void* gate_up, void* out_bf16, void* out_q, float* out_s
     B200_REQUIRE(false, "silu_mul: bad q_dtype %d", q_dtype);
   }
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -498,6 +506,7 @@ int b200_quantize_per_token(const void* x, void* out_q, float* out_scale, int T,
   else
     B200_REQUIRE(false, "quantize_per_token: bad q_dtype %d", q_dtype);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -507,6 +516,7 @@ int b200_embedding(const int64_t* tokens, const void* table, void* out, int T, i
   if (T <= 0) return B200_OK;
   embedding_kernel<<<T, 256, 0, (cudaStream_t)stream>>>(tokens, (const uint4*)table, (uint4*)out, H / 8, V);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -517,6 +527,7 @@ int b200_argmax(const float* logits, int64_t row_stride, float* out_val, int64_t
   if (T <= 0) return B200_OK;
   argmax_kernel<<<T, 1024, 0, (cudaStream_t)stream>>>(logits, row_stride, out_val, out_idx, V, idx_offset);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 

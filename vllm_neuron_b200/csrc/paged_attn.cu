@@ -478,9 +478,11 @@ int launch_decode(const CUtensorMap& km, const CUtensorMap& vm, const void* q, i
                                                part_o, part_ml, B, Hq, Hkv, max_chunks, chunk_blocks,
                                                scale * 1.4426950408889634f);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   paged_attn_combine_kernel<D><<<B * Hq, D, 0, stream>>>(part_o, part_ml, ctx_lens, (__nv_bfloat16*)out, Hq, max_chunks,
                                                         chunk_blocks);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -498,6 +500,7 @@ int launch_prefill(const CUtensorMap& km, const CUtensorMap& vm, const void* q, 
   kern<<<grid, 128, smem, stream>>>(km, vm, (const __nv_bfloat16*)q, q_stride, bt_row, (__nv_bfloat16*)out, S_new,
                                     computed_len, Hq, Hkv, scale * 1.4426950408889634f);
   B200_CUDA_OK(cudaGetLastError());
+  B200_LAUNCHED(1);
   return B200_OK;
 }
 

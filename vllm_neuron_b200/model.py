@@ -1,0 +1,389 @@
+"""Llama / Qwen2 decoder over the block-KV cache, wired on the C-ABI kernels.
+
+This is the B200 replacement for what the reference obtains from NxDI behind
+`NeuronCausalLM.forward` (vllm_neuron/worker/neuronx_distributed_model_loader.py:336-365): given the
+index tensors of a step it runs embedding -> L x (RMSNorm -> qkv GEMM -> RoPE + KV write by slot ->
+paged attention through the block table -> o GEMM (+residual) [all-reduce] -> RMSNorm -> gate/up GEMM ->
+SiLU*mul -> down GEMM (+residual) [all-reduce]) -> RMSNorm -> lm_head GEMM -> greedy argmax.
+Host code only sequences kernel launches on the current CUDA stream; the decode step is captured into a
+CUDA graph.  Tensor parallelism: q/kv heads and MLP columns are sharded, one NCCL all-reduce after o_proj and
+after down_proj.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+
+import torch
+
+from . import ops
+from .config import ModelShape
+
+_QKIND = {"bf16": None, "fp8": "fp8", "int8": "int8"}
+
+
+def rope_tables(head_dim: int, max_pos: int, theta: float, scaling: dict | None, device):
+    """fp32 cos/sin tables [max_pos, head_dim/2]; 'llama3' frequency scaling as published by Meta."""
+    inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.float64) / head_dim))
+    if scaling and scaling.get("rope_type", scaling.get("type")) == "llama3":
+        factor, lo, hi = scaling["factor"], scaling["low_freq_factor"], scaling["high_freq_factor"]
+        old = scaling["original_max_position_embeddings"]
+        wavelen = 2 * math.pi / inv_freq
+        smooth = (old / wavelen - lo) / (hi - lo)
+        scaled = torch.where(wavelen > old / lo, inv_freq / factor, inv_freq)
+        mid = (1 - smooth) * inv_freq / factor + smooth * inv_freq
+        inv_freq = torch.where((wavelen <= old / lo) & (wavelen >= old / hi), mid, scaled)
+    ang = torch.outer(torch.arange(max_pos, dtype=torch.float64), inv_freq)
+    return ang.cos().float().contiguous().to(device), ang.sin().float().contiguous().to(device)
+
+
+def quantize_weight(w: torch.Tensor, kind: str):
+    """Offline symmetric per-output-channel quantisation (load time, not the hot path).
+    scale[n] = amax|W[n,:]| / qmax;  fp8: cast RNE saturating to e4m3fn (qmax 448);  int8: round-half-even, clamp 127."""
+    w32 = w.float()
+    amax = w32.abs().amax(dim=-1)
+    qmax = 448.0 if kind == "fp8" else 127.0
+    scale = torch.where(amax > 0, amax / qmax, torch.ones_like(amax)).float()
+    y = w32 / scale.unsqueeze(-1)
+    if kind == "fp8":
+        q = y.clamp(-448.0, 448.0).to(torch.float8_e4m3fn)
+    else:
+        q = torch.round(y).clamp(-127, 127).to(torch.int8)
+    return q.contiguous(), scale.contiguous()
+
+
+def random_init_full_weights(shape: ModelShape, seed: int = 0, device="cpu", std: float = 0.02):
+    """Random-init weights of the architecture (HF init: N(0, 0.02^2), norms = 1), full (un-sharded), bf16.
+    Generated on CPU with a seeded generator so every rank / the oracle sees identical values."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+
+    def rnd(*s):
+        return (torch.randn(*s, generator=g, dtype=torch.float32) * std).to(torch.bfloat16).to(device)
+
+    qd, kd = shape.num_q_heads * shape.head_dim, shape.num_kv_heads * shape.head_dim
+    w = {"embed": rnd(shape.vocab, shape.hidden), "lm_head": rnd(shape.vocab, shape.hidden),
+         "final_norm": torch.ones(shape.hidden, dtype=torch.bfloat16, device=device), "layers": []}
+    for _ in range(shape.layers):
+        lw = {
+            "input_norm": torch.ones(shape.hidden, dtype=torch.bfloat16, device=device),
+            "post_norm": torch.ones(shape.hidden, dtype=torch.bfloat16, device=device),
+            "wqkv": rnd(qd + 2 * kd, shape.hidden),
+            "wo": rnd(shape.hidden, qd),
+            "wgu": rnd(2 * shape.intermediate, shape.hidden),
+            "wdown": rnd(shape.hidden, shape.intermediate),
+        }
+        if shape.qkv_bias:
+            lw["bqkv"] = rnd(qd + 2 * kd)
+        w["layers"].append(lw)
+    return w
+
+
+class _Linear:
+    """One (possibly TP-sharded, possibly quantised) weight with its per-channel scale."""
+
+    def __init__(self, w_full: torch.Tensor, quant: str, device, row_slices=None, col_slice=None, bias=None):
+        # quantise the FULL weight first (per-channel scales are properties of the un-sharded matrix), then shard
+        if quant in ("fp8", "int8"):
+            wq, ws = quantize_weight(w_full.to(device), quant)
+        else:
+            wq, ws = w_full.to(device), None
+        if row_slices is not None:
+            wq = torch.cat([wq[a:b] for a, b in row_slices], dim=0)
+            if ws is not None:
+                ws = torch.cat([ws[a:b] for a, b in row_slices], dim=0)
+            if bias is not None:
+                bias = torch.cat([bias[a:b] for a, b in row_slices], dim=0)
+        if col_slice is not None:
+            wq = wq[:, col_slice[0] : col_slice[1]]
+        self.w = wq.contiguous()
+        self.scale = None if ws is None else ws.contiguous()
+        self.bias = None if bias is None else bias.to(device).contiguous()
+        self.quant = quant
+        self.n, self.k = self.w.shape
+
+
+@dataclass
+class StepBuffers:
+    tokens: torch.Tensor
+    row_ids: torch.Tensor
+    slot_mapping: torch.Tensor
+    positions: torch.Tensor
+    ctx_lens: torch.Tensor
+    sampled: torch.Tensor
+
+
+class B200CausalLM:
+    def __init__(self, shape: ModelShape, full_weights: dict | None, *, quant: str = "bf16", num_blocks: int,
+                 max_num_seqs: int, max_model_len: int, block_size: int = 32, device="cuda", tp_rank: int = 0,
+                 tp_size: int = 1, tp_group=None, quant_lm_head: bool = True, seed: int = 0):
+        assert quant in ("bf16", "fp8", "int8"), f"quant mode {quant!r} not built yet"
+        assert shape.num_q_heads % tp_size == 0 and shape.num_kv_heads % tp_size == 0, "heads must divide TP"
+        assert shape.intermediate % tp_size == 0 and shape.vocab % tp_size == 0
+        ops.device_check(torch.device(device).index or 0)
+        self.shape, self.quant, self.device = shape, quant, torch.device(device)
+        self.tp_rank, self.tp_size, self.tp_group = tp_rank, tp_size, tp_group
+        self.block_size, self.num_blocks = block_size, num_blocks
+        self.max_num_seqs, self.max_model_len = max_num_seqs, max_model_len
+        self.max_blocks = max_model_len // block_size
+        self.hq = shape.num_q_heads // tp_size
+        self.hkv = shape.num_kv_heads // tp_size
+        self.d = shape.head_dim
+        self.inter = shape.intermediate // tp_size
+        self.vocab_local = shape.vocab // tp_size
+        self.scale = self.d**-0.5
+        dev = self.device
+        if full_weights is None:
+            full_weights = _LazyRandomWeights(shape, seed)
+        r, t, d = tp_rank, tp_size, self.d
+        Hq, Hkv, I = shape.num_q_heads, shape.num_kv_heads, shape.intermediate
+        qd, kd = Hq * d, Hkv * d
+        qkv_rows = [(r * qd // t, (r + 1) * qd // t), (qd + r * kd // t, qd + (r + 1) * kd // t),
+                    (qd + kd + r * kd // t, qd + kd + (r + 1) * kd // t)]
+        gu_rows = [(r * I // t, (r + 1) * I // t), (I + r * I // t, I + (r + 1) * I // t)]
+        self.embed = full_weights["embed"].to(dev).contiguous()
+        self.final_norm = full_weights["final_norm"].to(dev).contiguous()
+        v0, v1 = r * shape.vocab // t, (r + 1) * shape.vocab // t
+        self.lm_head = _Linear(full_weights["lm_head"], quant if quant_lm_head else "bf16", dev, row_slices=[(v0, v1)])
+        self.vocab_offset = v0
+        self.layers = []
+        for li in range(shape.layers):
+            lw = full_weights["layers"][li]
+            self.layers.append(
+                {
+                    "input_norm": lw["input_norm"].to(dev).contiguous(),
+                    "post_norm": lw["post_norm"].to(dev).contiguous(),
+                    "qkv": _Linear(lw["wqkv"], quant, dev, row_slices=qkv_rows, bias=lw.get("bqkv")),
+                    "o": _Linear(lw["wo"], quant, dev, col_slice=(r * qd // t, (r + 1) * qd // t)),
+                    "gu": _Linear(lw["wgu"], quant, dev, row_slices=gu_rows),
+                    "down": _Linear(lw["wdown"], quant, dev, col_slice=(r * I // t, (r + 1) * I // t)),
+                }
+            )
+            if isinstance(full_weights, _LazyRandomWeights):
+                full_weights.drop(li)
+        self.cos, self.sin = rope_tables(d, max_model_len, shape.rope_theta, shape.rope_scaling, dev)
+        # ---- KV pools: per layer [2(K,V)][num_blocks][Hkv_local][bs][D] bf16; block 0 is vLLM's null block
+        self.kv = [torch.zeros((2, num_blocks, self.hkv, block_size, d), dtype=torch.bfloat16, device=dev)
+                   for _ in range(shape.layers)]
+        # ---- persistent per-sequence state (rows = the reference's seq-id slots, RUNNER:130-136)
+        self.block_table = torch.zeros((max_num_seqs, self.max_blocks), dtype=torch.int32, device=dev)
+        self.num_tokens = torch.zeros((max_num_seqs,), dtype=torch.int32, device=dev)
+        self._decode_bufs: dict[int, StepBuffers] = {}
+        self._graphs: dict[int, torch.cuda.CUDAGraph] = {}
+        self._alloc_workspaces()
+
+    # ------------------------------------------------------------------ workspaces
+    def _linears(self):
+        for L in self.layers[:1]:
+            yield from (L["qkv"], L["o"], L["gu"], L["down"])
+        yield self.lm_head
+
+    def _alloc_workspaces(self):
+        dev = self.device
+        nbytes = 16
+        for m in {self.max_num_seqs, min(self.max_model_len, 4096)}:
+            for lin in self._linears():
+                dt = {"bf16": 0, "fp8": 1, "int8": 2}[lin.quant]
+                nbytes = max(nbytes, ops.gemm_workspace_bytes(m, lin.n, lin.k, dt, 0))
+        self.gemm_ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        self.attn_ws = torch.empty(
+            max(16, ops.paged_attn_decode_workspace_bytes(self.max_num_seqs, self.hq, self.hkv, self.d, self.max_blocks, 0)),
+            dtype=torch.uint8, device=dev)
+
+    # ------------------------------------------------------------------ building blocks
+    def _linear(self, lin: _Linear, x, xs=None, residual=None, out_dtype=torch.bfloat16):
+        return ops.gemm(x, lin.w, xs, lin.scale, lin.bias, residual, out_dtype=out_dtype, workspace=self.gemm_ws)
+
+    def _norm(self, x, w):
+        q = _QKIND[self.quant]
+        if q is None:
+            return ops.rmsnorm(x, w, self.shape.rms_eps), None
+        return ops.rmsnorm(x, w, self.shape.rms_eps, quant=q)
+
+    def _all_reduce(self, x):
+        if self.tp_size > 1:
+            torch.distributed.all_reduce(x, group=self.tp_group)
+        return x
+
+    def _layers(self, x, positions, slot_mapping, attn_fn):
+        t = x.shape[0]
+        q = _QKIND[self.quant]
+        qd = self.hq * self.d
+        first = self.tp_rank == 0  # the residual is folded into rank 0's GEMM epilogue; the all-reduce sums it in once
+        for li, L in enumerate(self.layers):
+            h, hs = self._norm(x, L["input_norm"])
+            qkv = self._linear(L["qkv"], h, hs)
+            kp, vp = self.kv[li][0], self.kv[li][1]
+            ops.rope_kv_write(qkv, positions, self.cos, self.sin, kp, vp, slot_mapping, self.hq)
+            a = attn_fn(qkv[:, :qd].unflatten(1, (self.hq, self.d)), kp, vp).reshape(t, qd)
+            if q is None:
+                x = self._all_reduce(self._linear(L["o"], a, None, x if first else None))
+            else:
+                aq, a_s = ops.quantize_per_token(a, q)
+                x = self._all_reduce(self._linear(L["o"], aq, a_s, x if first else None))
+            h2, h2s = self._norm(x, L["post_norm"])
+            gu = self._linear(L["gu"], h2, h2s)
+            if q is None:
+                x = self._all_reduce(self._linear(L["down"], ops.silu_mul(gu), None, x if first else None))
+            else:
+                act, act_s = ops.silu_mul(gu, quant=q)
+                x = self._all_reduce(self._linear(L["down"], act, act_s, x if first else None))
+        return x
+
+    def _sample(self, x_rows):
+        """final norm -> lm_head (fp32 logits of the local vocab shard) -> greedy argmax (TP: merge (val, idx))."""
+        lm_q = _QKIND[self.lm_head.quant]
+        if lm_q is None:
+            h, hs = ops.rmsnorm(x_rows, self.final_norm, self.shape.rms_eps), None
+        else:
+            h, hs = ops.rmsnorm(x_rows, self.final_norm, self.shape.rms_eps, quant=lm_q)
+        logits = self._linear(self.lm_head, h, hs, out_dtype=torch.float32)
+        if self.tp_size == 1:
+            return ops.argmax(logits), logits
+        val, idx = ops.argmax(logits, idx_offset=self.vocab_offset, want_val=True)
+        vals = torch.empty((self.tp_size, val.numel()), dtype=val.dtype, device=val.device)
+        idxs = torch.empty((self.tp_size, idx.numel()), dtype=idx.dtype, device=idx.device)
+        torch.distributed.all_gather_into_tensor(vals, val, group=self.tp_group)
+        torch.distributed.all_gather_into_tensor(idxs, idx, group=self.tp_group)
+        best = vals.max(dim=0, keepdim=True).values
+        cand = torch.where(vals == best, idxs, torch.full_like(idxs, self.shape.vocab))
+        return cand.min(dim=0).values, logits
+
+    # ------------------------------------------------------------------ decode
+    def decode_buffers(self, b: int) -> StepBuffers:
+        if b not in self._decode_bufs:
+            dev = self.device
+            self._decode_bufs[b] = StepBuffers(
+                tokens=torch.zeros(b, dtype=torch.int64, device=dev),
+                row_ids=torch.arange(b, dtype=torch.int32, device=dev),
+                slot_mapping=torch.zeros(b, dtype=torch.int64, device=dev),
+                positions=torch.zeros(b, dtype=torch.int64, device=dev),
+                ctx_lens=torch.zeros(b, dtype=torch.int32, device=dev),
+                sampled=torch.zeros(b, dtype=torch.int64, device=dev),
+            )
+        return self._decode_bufs[b]
+
+    def _decode_body(self, bufs: StepBuffers, max_ctx_blocks: int, advance: bool):
+        b = bufs.tokens.numel()
+        # index construction on device (RUNNER:765-832): positions, slot_mapping, context lengths
+        ops.build_decode_meta(self.block_table, bufs.row_ids, self.num_tokens, bufs.slot_mapping, bufs.positions,
+                              bufs.ctx_lens, self.block_size)
+        x = ops.embedding(bufs.tokens, self.embed)
+
+        def attn(qv, kp, vp):
+            return ops.paged_attn_decode(qv, kp, vp, self.block_table, bufs.ctx_lens, self.scale, workspace=self.attn_ws,
+                                         row_ids=bufs.row_ids, max_blocks=max_ctx_blocks)
+
+        x = self._layers(x, bufs.positions, bufs.slot_mapping, attn)
+        ids, _ = self._sample(x)
+        bufs.sampled.copy_(ids)
+        if advance:  # device-side twin of RUNNER:325-339 so the captured step can be replayed back to back
+            ops.advance_decode(bufs.sampled, bufs.tokens, self.num_tokens, bufs.row_ids)
+        return bufs.sampled
+
+    def decode_step(self, b: int, *, max_ctx_blocks: int | None = None, advance: bool = False, use_graph: bool = False):
+        """One decode step for the `b` rows in decode_buffers(b).row_ids; inputs already on the device:
+        bufs.tokens (last sampled token per row), self.num_tokens[row] (= prompt + outputs incl. that token)."""
+        bufs = self.decode_buffers(b)
+        mcb = self.max_blocks if max_ctx_blocks is None else max_ctx_blocks
+        if not use_graph:
+            return self._decode_body(bufs, mcb, advance)
+        key = (b, mcb, advance)
+        if key not in self._graphs:
+            nt = self.num_tokens.clone()
+            tk = bufs.tokens.clone()
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):  # warm-up outside capture (function attributes, NCCL channels)
+                self._decode_body(bufs, mcb, advance)
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            self.num_tokens.copy_(nt)
+            bufs.tokens.copy_(tk)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._decode_body(bufs, mcb, advance)
+            self.num_tokens.copy_(nt)
+            bufs.tokens.copy_(tk)
+            self._graphs[key] = g
+        self._graphs[key].replay()
+        return bufs.sampled
+
+    # ------------------------------------------------------------------ prefill (batch 1, prefix-cached)
+    def prefill(self, row: int, new_tokens: torch.Tensor, prompt_len: int, computed_len: int):
+        """Compute the uncached suffix `new_tokens` (device int64 [prompt_len - computed_len]) of one request whose
+        block ids are already in block_table[row]; returns the sampled next token (device int64 [1])."""
+        s_new = prompt_len - computed_len
+        assert new_tokens.numel() == s_new and s_new > 0
+        dev = self.device
+        slot_full = torch.empty(self.max_model_len, dtype=torch.int64, device=dev)
+        pos_full = torch.empty(self.max_model_len, dtype=torch.int64, device=dev)
+        bt_row = self.block_table[row]
+        ops.build_prefill_meta(bt_row, prompt_len, computed_len, slot_full, pos_full, self.block_size)
+        slots, positions = slot_full[:s_new], pos_full[:s_new]
+        x = ops.embedding(new_tokens, self.embed)
+
+        def attn(qv, kp, vp):
+            return ops.paged_attn_prefill(qv, kp, vp, bt_row, computed_len, self.scale)
+
+        x = self._layers(x, positions, slots, attn)
+        ids, _ = self._sample(x[-1:].contiguous())
+        self.num_tokens[row] = prompt_len
+        return ids
+
+    def kv_bytes_per_block(self) -> int:
+        return 2 * self.hkv * self.block_size * self.d * 2 * self.shape.layers
+
+
+class _LazyRandomWeights:
+    """Generates random-init weights layer by layer (8B+ models do not fit a full CPU copy comfortably).
+    Values depend only on (seed, tensor name, layer), never on the TP rank."""
+
+    def __init__(self, shape: ModelShape, seed: int, std: float = 0.02):
+        self.shape, self.seed, self.std = shape, seed, std
+        self._cache: dict = {}
+        self.layers = _LazyLayers(self)
+
+    def _gen(self, tag: int, *s):
+        dev = "cuda" if torch.cuda.is_available() else "cpu"
+        g = torch.Generator(device=dev).manual_seed(self.seed * 1000003 + tag)
+        return (torch.randn(*s, generator=g, dtype=torch.float32, device=dev) * self.std).to(torch.bfloat16)
+
+    def __getitem__(self, k):
+        sh = self.shape
+        if k == "layers":
+            return self.layers
+        if k == "embed":
+            return self._gen(1, sh.vocab, sh.hidden)
+        if k == "lm_head":
+            return self._gen(2, sh.vocab, sh.hidden)
+        if k == "final_norm":
+            return torch.ones(sh.hidden, dtype=torch.bfloat16)
+        raise KeyError(k)
+
+    def layer(self, li: int):
+        if li not in self._cache:
+            sh = self.shape
+            qd, kd = sh.num_q_heads * sh.head_dim, sh.num_kv_heads * sh.head_dim
+            lw = {
+                "input_norm": torch.ones(sh.hidden, dtype=torch.bfloat16),
+                "post_norm": torch.ones(sh.hidden, dtype=torch.bfloat16),
+                "wqkv": self._gen(100 + li * 8, qd + 2 * kd, sh.hidden),
+                "wo": self._gen(101 + li * 8, sh.hidden, qd),
+                "wgu": self._gen(102 + li * 8, 2 * sh.intermediate, sh.hidden),
+                "wdown": self._gen(103 + li * 8, sh.hidden, sh.intermediate),
+            }
+            if sh.qkv_bias:
+                lw["bqkv"] = self._gen(104 + li * 8, qd + 2 * kd)
+            self._cache[li] = lw
+        return self._cache[li]
+
+    def drop(self, li: int):
+        self._cache.pop(li, None)
+
+
+class _LazyLayers:
+    def __init__(self, parent):
+        self.parent = parent
+
+    def __getitem__(self, li):
+        return self.parent.layer(li)

@@ -32,6 +32,11 @@ def device_check(device: int = 0):
     check(_cabi.load().b200_device_check(device), "b200_device_check")
 
 
+def launch_count() -> int:
+    """Kernel launches issued through libb200_paged.so by this process so far."""
+    return int(_cabi.load().b200_launch_count())
+
+
 # ------------------------------------------------------------------ index construction
 def build_decode_meta(block_table, row_ids, num_tokens, slot_mapping, positions, ctx_lens, block_size: int):
     """block_table int32 [rows, max_blocks]; row_ids int32 [B] or None; num_tokens int32 [rows];

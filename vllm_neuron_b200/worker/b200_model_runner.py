@@ -1,0 +1,264 @@
+"""B200 model runner: vllm-neuron's `execute_model(scheduler_output) -> ModelRunnerOutput` contract on B200.
+
+Reference: vllm_neuron/worker/neuronx_distributed_model_runner.py
+  * execute_model                       :252-291
+  * _update_states                      :381-510   (request cache, block-id append / replace)
+  * seq-id slot map                     :130-136, 263-268, 714-717
+  * prefill / decode index construction :704-832   -> here: block ids are scattered into a persistent DEVICE
+    block table and positions / slot_mapping / context lengths are derived ON DEVICE by
+    b200_build_decode_meta / b200_build_prefill_meta (no per-step Python list building, no deepcopy).
+  * _generate_model_runner_output       :293-359
+  * get_kv_cache_spec                   :361-379
+  * initialize_kv_cache                 :142-150   (no-op in the reference; here it allocates the pools)
+
+The runner keeps its own light request cache instead of vLLM's InputBatch; the scheduler's block-id lists
+stay owned by vLLM's KV manager and are only mirrored (host list + device table).
+"""
+from __future__ import annotations
+
+import logging
+from dataclasses import dataclass, field
+
+import torch
+
+from .. import ops
+from ..config import B200Config, ModelShape, build_config
+from ..model import B200CausalLM
+
+logger = logging.getLogger(__name__)
+
+_SLOT_MAPPING_PAD = -1  # RUNNER:80
+_BLOCK_TABLE_PAD = 0  # RUNNER:81
+
+
+@dataclass
+class CachedRequest:
+    req_id: str
+    prompt_token_ids: list[int]
+    output_token_ids: list[int] = field(default_factory=list)
+    block_ids: list[int] = field(default_factory=list)
+    num_computed_tokens: int = 0
+    row: int = -1  # persistent block-table row (the reference's "neuron seq id")
+    sampling_params: object = None
+
+    @property
+    def num_tokens(self) -> int:
+        return len(self.prompt_token_ids) + len(self.output_token_ids)
+
+
+def _first_group(block_ids):
+    """vLLM passes block ids per KV-cache group; this path has exactly one group (RUNNER:743)."""
+    if block_ids is None:
+        return None
+    if isinstance(block_ids, (tuple, list)) and block_ids and isinstance(block_ids[0], (list, tuple)):
+        assert len(block_ids) == 1, "exactly one KV cache group is supported"
+        return list(block_ids[0])
+    return list(block_ids)
+
+
+class B200ModelRunner:
+    def __init__(self, vllm_config, device: torch.device, *, model: B200CausalLM | None = None,
+                 tp_rank: int = 0, tp_size: int = 1, tp_group=None):
+        self.vllm_config = vllm_config
+        self.model_config = vllm_config.model_config
+        self.cache_config = vllm_config.cache_config
+        self.parallel_config = vllm_config.parallel_config
+        self.scheduler_config = vllm_config.scheduler_config
+        self.device = device
+        self.block_size = self.cache_config.block_size
+        self.max_num_reqs = self.scheduler_config.max_num_seqs
+        self.max_model_len = self.model_config.max_model_len
+        self.tp_rank, self.tp_size, self.tp_group = tp_rank, tp_size, tp_group
+        self.requests: dict[str, CachedRequest] = {}
+        # request id -> persistent row; free rows (RUNNER:130-136)
+        self.req_to_row: dict[str, int] = {}
+        self.free_rows = set(range(self.max_num_reqs))
+        self.model = model
+        self.b200_config: B200Config | None = None
+        self.num_blocks: int | None = None
+        self.use_cuda_graph = not getattr(self.model_config, "enforce_eager", False)
+        self._stage = None
+        self.h2d_bytes_last = 0
+        self.d2h_bytes_last = 0
+
+    # ------------------------------------------------------------------ config / load / KV allocation
+    def build_b200_config(self) -> B200Config:
+        add = getattr(self.vllm_config, "additional_config", None) or {}
+        override = add.get("override_neuron_config") or add.get("override_b200_config") or {}
+        self.b200_config = build_config(
+            tensor_parallel_size=self.parallel_config.tensor_parallel_size,
+            max_num_seqs=self.max_num_reqs,
+            max_model_len=self.max_model_len,
+            block_size=self.block_size,
+            enable_prefix_caching=bool(self.cache_config.enable_prefix_caching),
+            num_gpu_blocks_override=self.cache_config.num_gpu_blocks_override,
+            override=override,
+        )
+        return self.b200_config
+
+    def model_shape(self) -> ModelShape:
+        return ModelShape.from_hf(self.model_config.hf_config)
+
+    def load_model(self, *, load_dummy_weights: bool = False) -> None:
+        """Weights are materialised in initialize_kv_cache (the model object owns weights + pools); this
+        validates the config exactly where the reference does (get_neuron_model, LOADER:662-721)."""
+        cfg = self.build_b200_config()
+        self.shape = self.model_shape()
+        self.is_block_kv_layout = cfg.is_block_kv_layout
+        self.is_prefix_caching = cfg.is_prefix_caching
+        self._load_dummy = True if load_dummy_weights else getattr(self.vllm_config.load_config, "load_format", "dummy") == "dummy"
+        if not self._load_dummy:
+            raise NotImplementedError(
+                "checkpoint loading is not built yet (SURVEY 8(f)-4); run with load_format='dummy' (random-init weights)")
+
+    def get_kv_cache_spec(self):
+        """RUNNER:361-379 hands vLLM ONE spec under 'layer'; we register one per decoder layer with the per-rank
+        kv-head count so vLLM's block budget is right without --num-gpu-blocks-override (documented deviation)."""
+        from vllm.v1.kv_cache_interface import FullAttentionSpec
+
+        shape = self.model_shape()
+        spec = FullAttentionSpec(block_size=self.block_size, num_kv_heads=shape.num_kv_heads // self.tp_size,
+                                 head_size=shape.head_dim, dtype=torch.bfloat16, sliding_window=None)
+        return {f"layers.{i}.attn": spec for i in range(shape.layers)}
+
+    def initialize_kv_cache(self, kv_cache_config=None, num_blocks: int | None = None) -> None:
+        """The reference's is a no-op (NxDI allocates pa_num_blocks x pa_block_size itself, LOADER:775-778).
+        Here the pools are ours: [layers][2][num_blocks][Hkv/TP][block_size][D] bf16, block 0 = null block."""
+        if num_blocks is None:
+            num_blocks = getattr(kv_cache_config, "num_blocks", None) or self.b200_config.pa_num_blocks
+        self.num_blocks = int(num_blocks)
+        if self.model is None:
+            self.model = B200CausalLM(
+                self.shape, None, quant=self.b200_config.quant_mode, num_blocks=self.num_blocks,
+                max_num_seqs=self.max_num_reqs, max_model_len=self.max_model_len, block_size=self.block_size,
+                device=self.device, tp_rank=self.tp_rank, tp_size=self.tp_size, tp_group=self.tp_group,
+                seed=getattr(self.model_config, "seed", 0) or 0,
+            )
+        self._init_staging()
+
+    def _init_staging(self):
+        n = self.max_num_reqs
+        self._pin_tokens = torch.zeros(n, dtype=torch.int64).pin_memory()
+        self._pin_rows = torch.zeros(n, dtype=torch.int32).pin_memory()
+        self._pin_ntok = torch.zeros(n, dtype=torch.int32).pin_memory()
+        self._pin_upd = torch.zeros((max(64, 4 * n), 3), dtype=torch.int32).pin_memory()
+        self._dev_upd = torch.zeros_like(self._pin_upd, device=self.device)
+        self._pin_out = torch.zeros(n, dtype=torch.int64).pin_memory()
+
+    # ------------------------------------------------------------------ state tracking (RUNNER:381-510)
+    def _update_states(self, so) -> list[tuple[int, int, int]]:
+        """Returns the (row, col, block_id) triples to scatter into the device block table."""
+        updates: list[tuple[int, int, int]] = []
+        for req_id in so.finished_req_ids:
+            self.requests.pop(req_id, None)
+            row = self.req_to_row.pop(req_id, None)
+            if row is not None:
+                self.free_rows.add(row)  # RUNNER:263-268
+        for nr in so.scheduled_new_reqs:
+            assert nr.req_id not in self.req_to_row, "Encountered an existing request ID while prefilling a new request"
+            assert self.free_rows, "No free sequence ID available!"
+            row = min(self.free_rows)
+            self.free_rows.discard(row)
+            self.req_to_row[nr.req_id] = row
+            blocks = _first_group(nr.block_ids) or []
+            st = CachedRequest(nr.req_id, list(nr.prompt_token_ids), [], blocks, nr.num_computed_tokens, row,
+                               getattr(nr, "sampling_params", None))
+            self.requests[nr.req_id] = st
+            updates += [(row, c, b) for c, b in enumerate(blocks)]
+        cached = so.scheduled_cached_reqs
+        resumed = getattr(cached, "resumed_req_ids", None)
+        legacy_resumed = getattr(cached, "resumed_from_preemption", None)
+        for i, req_id in enumerate(cached.req_ids):
+            st = self.requests[req_id]
+            new_blocks = _first_group(cached.new_block_ids[i]) if cached.new_block_ids else None
+            is_resumed = (req_id in resumed) if resumed is not None else bool(legacy_resumed and legacy_resumed[i])
+            if not is_resumed:
+                if new_blocks:
+                    start = len(st.block_ids)
+                    st.block_ids.extend(new_blocks)  # RUNNER:461-466
+                    updates += [(st.row, start + c, b) for c, b in enumerate(new_blocks)]
+            else:
+                assert new_blocks is not None
+                st.block_ids = list(new_blocks)  # RUNNER:467-471: replace after preemption
+                updates += [(st.row, c, b) for c, b in enumerate(st.block_ids)]
+            st.num_computed_tokens = st.num_tokens - 1
+        return updates
+
+    def _push_block_updates(self, updates):
+        if not updates:
+            return
+        n = len(updates)
+        if n > self._pin_upd.shape[0]:
+            self._pin_upd = torch.zeros((2 * n, 3), dtype=torch.int32).pin_memory()
+            self._dev_upd = torch.zeros_like(self._pin_upd, device=self.device)
+        self._pin_upd[:n] = torch.tensor(updates, dtype=torch.int32)
+        self._dev_upd[:n].copy_(self._pin_upd[:n], non_blocking=True)
+        ops.block_table_scatter(self.model.block_table, self._dev_upd[:n])
+        self.h2d_bytes_last += n * 12
+
+    # ------------------------------------------------------------------ the step
+    @torch.inference_mode()
+    def execute_model(self, scheduler_output, intermediate_tensors=None):
+        from vllm.v1.outputs import EMPTY_MODEL_RUNNER_OUTPUT, ModelRunnerOutput
+
+        self.h2d_bytes_last = self.d2h_bytes_last = 0
+        updates = self._update_states(scheduler_output)
+        if not scheduler_output.total_num_scheduled_tokens:
+            return EMPTY_MODEL_RUNNER_OUTPUT  # RUNNER:272-274
+        self._push_block_updates(updates)
+
+        req_ids: list[str] = []
+        pending: list[torch.Tensor] = []
+        # ---- prefill: one request at a time (SCHED:116 guarantees batch 1; several are processed in turn)
+        for nr in scheduler_output.scheduled_new_reqs:
+            st = self.requests[nr.req_id]
+            n_sched = scheduler_output.num_scheduled_tokens[nr.req_id]
+            plen = len(st.prompt_token_ids)
+            if st.num_computed_tokens + n_sched != plen:
+                raise NotImplementedError("chunked prefill is not on the B200 hot path yet (SURVEY 8(f)-3)")
+            assert plen <= self.max_model_len
+            new = torch.tensor(st.prompt_token_ids[st.num_computed_tokens:], dtype=torch.int64).pin_memory()
+            new_d = new.to(self.device, non_blocking=True)
+            self.h2d_bytes_last += new.numel() * 8
+            pending.append(self.model.prefill(st.row, new_d, plen, st.num_computed_tokens))
+            req_ids.append(nr.req_id)
+        # ---- decode batch (RUNNER:765-832)
+        dec_ids = list(scheduler_output.scheduled_cached_reqs.req_ids)
+        if dec_ids:
+            b = len(dec_ids)
+            max_ctx = 0
+            for i, rid in enumerate(dec_ids):
+                st = self.requests[rid]
+                self._pin_tokens[i] = st.output_token_ids[-1] if st.output_token_ids else st.prompt_token_ids[-1]
+                self._pin_rows[i] = st.row
+                self._pin_ntok[st.row] = st.num_tokens
+                max_ctx = max(max_ctx, st.num_tokens)
+            bufs = self.model.decode_buffers(b)
+            bufs.tokens.copy_(self._pin_tokens[:b], non_blocking=True)
+            bufs.row_ids.copy_(self._pin_rows[:b], non_blocking=True)
+            self.model.num_tokens.copy_(self._pin_ntok, non_blocking=True)
+            self.h2d_bytes_last += b * 12 + self._pin_ntok.numel() * 4
+            # bound the context split by the longest live context, rounded to 8 blocks so few graphs are captured
+            mcb = min(self.model.max_blocks, -(-(-(-max_ctx // self.block_size)) // 8) * 8)
+            pending.append(self.model.decode_step(b, max_ctx_blocks=mcb, use_graph=self.use_cuda_graph))
+            req_ids += dec_ids
+        # ---- one D2H read of all sampled ids (the step's only sync point; RUNNER:304-306 `.tolist()`)
+        ids = torch.cat(pending) if len(pending) > 1 else pending[0]
+        n = ids.numel()
+        self._pin_out[:n].copy_(ids, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        self.d2h_bytes_last += n * 8
+        sampled = [[int(x)] for x in self._pin_out[:n].tolist()]
+        sampled = [[x for x in row if x != -1] for row in sampled]  # RUNNER:304-306
+        for rid, row in zip(req_ids, sampled):
+            self.requests[rid].output_token_ids.extend(row)  # RUNNER:325-339
+        if self.tp_rank != 0 and self.tp_size > 1:
+            pass  # every rank tracks state; only the driver's output is used (WORKER:65-69)
+        return ModelRunnerOutput(
+            req_ids=req_ids,
+            req_id_to_index={r: i for i, r in enumerate(req_ids)},
+            sampled_token_ids=sampled,
+            logprobs=None,
+            prompt_logprobs_dict={},
+            pooler_output=[],
+        )
