@@ -22,7 +22,7 @@ INT8_MAX = 127.0
 def _quant_rows(x32, kind: str):
     amax = x32.abs().amax(dim=-1)
     qmax = FP8_MAX if kind == "fp8" else INT8_MAX
-    scale = (amax / qmax).float()
+    scale = torch.div(amax, torch.full_like(amax, qmax)).float()  # tensor/tensor: true IEEE division
     scale = torch.where(amax > 0, scale, torch.ones_like(scale))
     y = x32 / scale.unsqueeze(-1)
     if kind == "fp8":

@@ -43,15 +43,33 @@ def _run(quant, steps=12, use_graph=True):
                "b": torch.randint(0, shape.vocab, (33,), generator=g).tolist(),
                "c": torch.randint(0, shape.vocab, (5,), generator=g).tolist()}
     prompts["d"] = prompts["a"][:64] + torch.randint(0, shape.vocab, (9,), generator=g).tolist()  # shares 2 blocks with "a"
-    blocks, outs, ref_outs, margins = {}, {k: [] for k in prompts}, {k: [] for k in prompts}, []
+    blocks, outs, ref_outs, margins = {}, {k: [] for k in prompts}, {k: [] for k in prompts}, {k: [] for k in prompts}
+    stats = {"gpu": [], "ref": [], "hp": []}  # logits of the CUDA path, the oracle, and the unquantised (bf16) oracle
+    ref_hp = None
+    if quant != "bf16":  # second oracle without quantisation: measures the quantisation noise itself
+        ref_hp = llama_ref.RefLlama(
+            llama_ref.RefConfig(shape.hidden, shape.layers, shape.num_q_heads, shape.num_kv_heads, shape.head_dim,
+                                shape.intermediate, shape.vocab, shape.rope_theta, shape.rope_scaling, shape.rms_eps,
+                                shape.qkv_bias, "bf16", mml, bs),
+            weights, nb + 1)
+
+    def record(logits, hp_logits):
+        stats["gpu"].append(model.last_logits.float().cpu().clone())
+        stats["ref"].append(logits.float().clone())
+        if hp_logits is not None:
+            stats["hp"].append(hp_logits.float().clone())
 
     def ref_prefill(rid, ncomp):
         p = prompts[rid]
         row = index_ref.prefill_index(len(p), blocks[rid], ncomp, bs, mml)
         tok, logits = ref.prefill(torch.tensor(p), torch.tensor(row["block_table"]), torch.tensor(row["slot_mapping"]), ncomp)
         top2 = logits.float().topk(2, dim=-1).values
-        margins.append((top2[:, 0] - top2[:, 1]).min().item())
+        margins[rid].append((top2[:, 0] - top2[:, 1]).min().item())
         ref_outs[rid].append(int(tok))
+        hp = None
+        if ref_hp is not None:
+            _, hp = ref_hp.prefill(torch.tensor(p), torch.tensor(row["block_table"]), torch.tensor(row["slot_mapping"]), ncomp)
+        record(logits, hp)
 
     # prefill a, b, c (no cache hit)
     for rid in ["a", "b", "c"]:
@@ -82,30 +100,62 @@ def _run(quant, steps=12, use_graph=True):
         out = runner.execute_model(sched_output(cached=cached))
         rows = [index_ref.decode_index(len(prompts[r]), len(ref_outs[r]), blocks[r], bs, mml) for r in live]
         fin = index_ref.finalize_inputs(rows, [[ref_outs[r][-1]] for r in live], False, mml)
-        tok, logits = ref.decode(torch.tensor(fin["input_tokens"][:, 0]), torch.tensor(fin["position_ids"][:, 0]),
-                                 torch.tensor(fin["slot_mapping"][:, 0]), torch.tensor(fin["block_tables"]),
-                                 torch.tensor(fin["full_context_lens"][:, 0]))
+        args = (torch.tensor(fin["input_tokens"][:, 0]), torch.tensor(fin["position_ids"][:, 0]),
+                torch.tensor(fin["slot_mapping"][:, 0]), torch.tensor(fin["block_tables"]),
+                torch.tensor(fin["full_context_lens"][:, 0]))
+        tok, logits = ref.decode(*args)
         top2 = logits.float().topk(2, dim=-1).values
+        record(logits, ref_hp.decode(*args)[1] if ref_hp is not None else None)
         for i, rid in enumerate(live):
             outs[rid] += out.sampled_token_ids[out.req_id_to_index[rid]]
             ref_outs[rid].append(int(tok[i]))
-            margins.append((top2[i, 0] - top2[i, 1]).item())
+            margins[rid].append((top2[i, 0] - top2[i, 1]).item())
         if step == 5:  # finish "b" mid-run: its row is freed and the batch shrinks (continuous batching)
             runner.execute_model(sched_output(finished=["b"]))
             live.remove("b")
+    model.stats = {k: torch.cat(v) for k, v in stats.items() if v}
     return runner, model, ref, outs, ref_outs, margins, live, blocks
+
+
+def _rms(x):
+    return x.float().pow(2).mean().sqrt().item()
 
 
 @pytest.mark.parametrize("quant", ["bf16", "fp8", "int8"])
 def test_greedy_tokens_match_oracle(quant):
     runner, model, ref, outs, ref_outs, margins, live, blocks = _run(quant)
-    flat_got = [t for k in sorted(outs) for t in outs[k]]
-    flat_ref = [t for k in sorted(ref_outs) for t in ref_outs[k]]
-    assert len(flat_got) == len(flat_ref) and len(flat_got) > 40
+    keys = sorted(outs)
+    flat_got = [t for k in keys for t in outs[k]]
+    flat_ref = [t for k in keys for t in ref_outs[k]]
+    flat_margin = [m for k in keys for m in margins[k]]
+    assert len(flat_got) == len(flat_ref) == len(flat_margin) and len(flat_got) > 40
     mism = [i for i, (a, b) in enumerate(zip(flat_got, flat_ref)) if a != b]
-    # a mismatch is only tolerated at a near-tie of the oracle's own logits (random-init weights)
-    assert not mism or min(margins) < 2e-3, f"{len(mism)} mismatches, min oracle top-2 margin {min(margins)}"
-    assert len(mism) <= 1
+    st = model.stats
+    std = _rms(st["ref"] - st["ref"].mean())
+    e_g = _rms(st["gpu"] - st["ref"])            # CUDA path vs oracle
+    e_max = (st["gpu"] - st["ref"]).abs().max().item()
+    msg = f"[{quant}] logits: rms err {e_g:.3e} max err {e_max:.3e} std {std:.3f}; mismatches {len(mism)}/{len(flat_got)}"
+    if quant == "bf16":
+        print(msg)
+        # north_star: bf16 within 2e-2 relative; every logit (1.5M values) within 5% of the logit spread
+        assert e_g < 1e-2 * std and e_max < 5e-2 * std, msg
+    else:
+        # W8A8 with dynamic per-token scales: a 1-ulp bf16 difference upstream (accumulation order, bf16 P in the
+        # attention MMA) flips 8-bit activation codes downstream, so the two quantised models decorrelate at the
+        # level of the quantisation noise itself.  The bar is therefore stated against that noise, measured as
+        # oracle(quantised) - oracle(bf16): the CUDA path must be as close to the unquantised model as the oracle's
+        # quantised model is, and no further from the quantised oracle than two independent draws of that noise.
+        e_q = _rms(st["ref"] - st["hp"])
+        e_gh = _rms(st["gpu"] - st["hp"])
+        msg += f"; quantisation noise {e_q:.3e}, CUDA-vs-bf16-oracle {e_gh:.3e}"
+        print(msg)
+        assert e_gh < 1.15 * e_q, msg
+        assert e_g < 1.5 * e_q, msg
+        assert e_q < (0.15 if quant == "fp8" else 0.05) * std, msg
+    # greedy tokens: identical except where the oracle's own top-2 margin is inside the logit error band
+    bad = [i for i in mism if flat_margin[i] > 6 * e_g]
+    assert not bad, msg + f"; mismatches outside the error band at {bad}: margins {[flat_margin[i] for i in bad]}"
+    assert len(mism) <= sum(1 for m in flat_margin if m <= 6 * e_g), msg
 
 
 def test_kv_cache_contents_bit_exact_bf16():

@@ -43,7 +43,8 @@ def quantize_weight(w: torch.Tensor, kind: str):
     w32 = w.float()
     amax = w32.abs().amax(dim=-1)
     qmax = 448.0 if kind == "fp8" else 127.0
-    scale = torch.where(amax > 0, amax / qmax, torch.ones_like(amax)).float()
+    # tensor / tensor is a true IEEE division on both CPU and CUDA (tensor / python-scalar may become a reciprocal multiply)
+    scale = torch.where(amax > 0, torch.div(amax, torch.full_like(amax, qmax)), torch.ones_like(amax)).float()
     y = w32 / scale.unsqueeze(-1)
     if kind == "fp8":
         q = y.clamp(-448.0, 448.0).to(torch.float8_e4m3fn)
@@ -84,7 +85,8 @@ class _Linear:
     def __init__(self, w_full: torch.Tensor, quant: str, device, row_slices=None, col_slice=None, bias=None):
         # quantise the FULL weight first (per-channel scales are properties of the un-sharded matrix), then shard
         if quant in ("fp8", "int8"):
-            wq, ws = quantize_weight(w_full.to(device), quant)
+            wq, ws = quantize_weight(w_full, quant)  # on whatever device the master weight lives
+            wq, ws = wq.to(device), ws.to(device)
         else:
             wq, ws = w_full.to(device), None
         if row_slices is not None:
@@ -168,7 +170,7 @@ class B200CausalLM:
         self.block_table = torch.zeros((max_num_seqs, self.max_blocks), dtype=torch.int32, device=dev)
         self.num_tokens = torch.zeros((max_num_seqs,), dtype=torch.int32, device=dev)
         self._decode_bufs: dict[int, StepBuffers] = {}
-        self._graphs: dict[int, torch.cuda.CUDAGraph] = {}
+        self._graphs: dict[tuple, tuple] = {}
         self._alloc_workspaces()
 
     # ------------------------------------------------------------------ workspaces
@@ -237,6 +239,7 @@ class B200CausalLM:
         else:
             h, hs = ops.rmsnorm(x_rows, self.final_norm, self.shape.rms_eps, quant=lm_q)
         logits = self._linear(self.lm_head, h, hs, out_dtype=torch.float32)
+        self.last_logits = logits  # kept for parity tests (a reference, no copy)
         if self.tp_size == 1:
             return ops.argmax(logits), logits
         val, idx = ops.argmax(logits, idx_offset=self.vocab_offset, want_val=True)
@@ -304,8 +307,9 @@ class B200CausalLM:
                 self._decode_body(bufs, mcb, advance)
             self.num_tokens.copy_(nt)
             bufs.tokens.copy_(tk)
-            self._graphs[key] = g
-        self._graphs[key].replay()
+            self._graphs[key] = (g, self.last_logits)
+        g, self.last_logits = self._graphs[key]
+        g.replay()
         return bufs.sampled
 
     # ------------------------------------------------------------------ prefill (batch 1, prefix-cached)
