@@ -1,0 +1,443 @@
+#!/usr/bin/env python
+"""Headline benchmark: Llama-3.1-8B FP8 (per-channel W8A8) block-KV paged decode, batch 64, block_size 32, 2k context.
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched by torchrun, one rank per GPU, TP=N)
+    python bench.py --impl reference --gpus N --steps K --warmup W   (the CPU restatement of the reference path)
+
+One "step" = one decode step of the whole batch (embedding -> 32 x [norm, qkv GEMM, RoPE + KV write by slot, paged
+attention through the block table, o GEMM, norm, gate/up GEMM, SiLU*mul, down GEMM] -> norm -> lm_head -> greedy).
+  value : tokens/s, inputs resident in HBM, CUDA-graph replay, device-timed with CUDA events, max over ranks.
+  e2e   : the same metric through the plugin's `execute_model(scheduler_output)` with HOST inputs: every step
+          copies token ids / rows / lengths from pinned host memory and reads the sampled ids back.
+  roofline : paged-attention decode kernel, algorithmic bytes / CUDA-event time per launch vs measured HBM peak.
+  cpu_baseline : oracle/ (torch-CPU restatement) timed on the host cores on a bounded sample (N=1, rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "decode_tokens_per_s"
+UNIT = "tokens/s"
+BS = 32
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def attn_algorithmic_bytes(ctx_lens, hq, hkv, d, kv_bytes=2):
+    """sum_seq ctx*2*Hkv*D*sizeof(kv) + 2*B*Hq*D*2 (q in, out) + B*ceil(ctx/bs)*4 (int32 block table)."""
+    b = len(ctx_lens)
+    return (sum(int(c) * 2 * hkv * d * kv_bytes for c in ctx_lens) + 2 * b * hq * d * 2
+            + sum(-(-int(c) // BS) * 4 for c in ctx_lens))
+
+
+def step_algorithmic_bytes(shape, quant, b, ctx, tp=1):
+    """Weights + KV that one decode step must stream from HBM per GPU (lower bound used for the step roofline)."""
+    wb = 1 if quant in ("fp8", "int8") else 2
+    qd, kd = shape.num_q_heads * shape.head_dim, shape.num_kv_heads * shape.head_dim
+    per_layer = ((qd + 2 * kd) * shape.hidden + shape.hidden * qd + 2 * shape.intermediate * shape.hidden
+                 + shape.hidden * shape.intermediate) * wb
+    weights = (per_layer * shape.layers + shape.vocab * shape.hidden * wb) // tp
+    kv = shape.layers * b * ctx * 2 * (shape.num_kv_heads // tp) * shape.head_dim * 2
+    return weights, kv
+
+
+# ---------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.idx)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+        return self
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------- CPU leg (oracle)
+def cpu_sample(shape, quant, b, ctx, threads, seed=0):
+    """Builds ONE decoder layer + lm_head of the oracle with random-init weights and a KV pool holding `ctx` tokens per
+    sequence.  Returns a closure that runs one sample (B tokens through 1 layer) and one that runs norm+lm_head+argmax."""
+    import torch
+
+    from oracle import llama_ref
+
+    torch.set_num_threads(threads)
+    g = torch.Generator().manual_seed(seed)
+
+    def rnd(*s):
+        return (torch.randn(*s, generator=g, dtype=torch.float32) * 0.02).to(torch.bfloat16)
+
+    qd, kd = shape.num_q_heads * shape.head_dim, shape.num_kv_heads * shape.head_dim
+    ones = torch.ones(shape.hidden, dtype=torch.bfloat16)
+    w = {"embed": rnd(1024, shape.hidden), "lm_head": rnd(shape.vocab, shape.hidden), "final_norm": ones,
+         "layers": [{"input_norm": ones, "post_norm": ones, "wqkv": rnd(qd + 2 * kd, shape.hidden), "wo": rnd(shape.hidden, qd),
+                     "wgu": rnd(2 * shape.intermediate, shape.hidden), "wdown": rnd(shape.hidden, shape.intermediate)}]}
+    nblk = -(-(ctx + 1) // BS)
+    nb = b * nblk + 1
+    cfg = llama_ref.RefConfig(shape.hidden, 1, shape.num_q_heads, shape.num_kv_heads, shape.head_dim, shape.intermediate,
+                              shape.vocab, shape.rope_theta, shape.rope_scaling, shape.rms_eps, shape.qkv_bias, quant,
+                              max_pos=nblk * BS, block_size=BS)
+    ref = llama_ref.RefLlama(cfg, w, nb)
+    for lin in (ref.lm_head, *[ref.layers[0][k] for k in ("qkv", "o", "gate_up", "down")]):
+        lin.prepare_f64()
+    ref.k_pools[0].copy_(torch.randn(ref.k_pools[0].shape, generator=g).to(torch.bfloat16))
+    ref.v_pools[0].copy_(torch.randn(ref.v_pools[0].shape, generator=g).to(torch.bfloat16))
+    perm = torch.randperm(nb - 1, generator=torch.Generator().manual_seed(7)) + 1
+    bt = perm[: b * nblk].reshape(b, nblk)
+    tokens = torch.randint(0, 1024, (b,), generator=g)
+    pos = torch.full((b,), ctx - 1, dtype=torch.int64)
+    slots = bt[:, (ctx - 1) // BS] * BS + (ctx - 1) % BS
+    ctxl = torch.full((b,), ctx, dtype=torch.int64)
+    from oracle import attn_ref, kv_ref
+
+    def layer_once():
+        def attn(q, kp, vp, scale):
+            return attn_ref.paged_attention_decode_ref(q, kp, vp, bt, ctxl, scale)
+
+        return ref._forward(tokens, pos, slots, attn)
+
+    def head_once(x):
+        return kv_ref.argmax_ref(ref._logits(x))
+
+    return layer_once, head_once
+
+
+def time_cpu_step(shape, quant, b, ctx, threads, reps):
+    """Returns (list of extrapolated full-step seconds per rep, description).  One rep = 1 decoder layer on the full
+    batch + lm_head/argmax; full step = L x layer + head ('1 layer x L extrapolation')."""
+    layer_once, head_once = cpu_sample(shape, quant, b, ctx, threads)
+    x = layer_once()  # warm-up (also first-touch of the widened weights)
+    head_once(x)
+    out = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        x = layer_once()
+        t1 = time.perf_counter()
+        head_once(x)
+        t2 = time.perf_counter()
+        out.append(shape.layers * (t1 - t0) + (t2 - t1))
+    desc = (f"1 of {shape.layers} decoder layers (batch {b}, ctx {ctx}) + lm_head/argmax per rep, extrapolated "
+            f"x{shape.layers}; {reps} reps; torch-CPU oracle, fp64-accumulate GEMMs, {threads} threads")
+    return out, desc
+
+
+# ---------------------------------------------------------------------------------------------- reference arm
+def run_reference(args, shape):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # only rank 0 runs the CPU arm
+    threads = os.cpu_count() or 1
+    layer_once, head_once = cpu_sample(shape, args.quant, args.batch, args.ctx, threads)
+    x = None
+    for _ in range(max(1, min(args.warmup, 2))):  # CPU warm-up is capped: each rep is seconds, not microseconds
+        x = layer_once()
+        head_once(x)
+    # bounded sample: each "step" runs 1 of L layers (+ the head); steps beyond the time budget reuse the running mean
+    budget_s, t_layer, t_head, done = args.cpu_budget_s, [], [], 0
+    t_start = time.perf_counter()
+    for _ in range(args.steps):
+        if done >= 3 and time.perf_counter() - t_start > budget_s:
+            break
+        t0 = time.perf_counter()
+        x = layer_once()
+        t1 = time.perf_counter()
+        head_once(x)
+        t2 = time.perf_counter()
+        t_layer.append(t1 - t0)
+        t_head.append(t2 - t1)
+        done += 1
+    step_s = shape.layers * statistics.mean(t_layer) + statistics.mean(t_head)
+    value = args.batch / step_s
+    sample = (f"each step = 1 of {shape.layers} decoder layers on the full batch ({args.batch} seqs, ctx {args.ctx}) + "
+              f"lm_head/argmax, extrapolated x{shape.layers}; {done} of {args.steps} steps timed inside a "
+              f"{budget_s:.0f} s budget (mean used); torch-CPU oracle (oracle/llama_ref.py), fp64-accumulate GEMMs")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": args.quant, "data": "synthetic (random-init weights, random KV, random tokens)",
+        "config": workload_config(args, shape, 1),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, shape, tp):
+    return {
+        "workload": f"{shape.name} {args.quant} per-channel W8A8 block-KV paged decode" if args.quant != "bf16"
+        else f"{shape.name} bf16 block-KV paged decode",
+        "global_batch": args.batch, "context": args.ctx, "block_size": BS, "parallelism": f"tp{tp}",
+        "kv_dtype": "bf16", "l2": "inputs larger than L2 (weights + KV streamed per step >> 126 MB)",
+    }
+
+
+# ---------------------------------------------------------------------------------------------- B200 arm
+def run_b200(args, shape):
+    import torch
+    import torch.distributed as dist
+
+    from vllm_neuron_b200 import ops
+    from vllm_neuron_b200.model import B200CausalLM
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch N>1 with torchrun (one rank per GPU)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    group = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        group = dist.group.WORLD
+    ops.device_check(local)  # fails loudly without an sm_100 device / the CUDA library
+
+    b, k_steps, w_steps, e_steps, p_steps = args.batch, args.steps, args.warmup, args.e2e_steps, 2
+    n0 = args.ctx - w_steps  # tokens per sequence before the first warm-up step; first timed step has ctx = args.ctx
+    assert n0 >= 1
+    n_end = args.ctx + k_steps + w_steps + e_steps + p_steps + 2
+    max_model_len = -(-n_end // BS) * BS
+    max_blocks = max_model_len // BS
+    num_blocks = b * max_blocks + 1
+    model = B200CausalLM(shape, None, quant=args.quant, num_blocks=num_blocks, max_num_seqs=b, max_model_len=max_model_len,
+                         block_size=BS, device=dev, tp_rank=rank, tp_size=world, tp_group=group, seed=0)
+    # synthetic state: block ids = random permutation of [1, num_blocks) (seed 7), KV ~ N(0,1) (seed 11)
+    perm = torch.randperm(num_blocks - 1, generator=torch.Generator().manual_seed(7)) + 1
+    bt_host = perm.reshape(b, max_blocks).to(torch.int32)
+    model.block_table.copy_(bt_host)
+    g = torch.Generator(device=dev).manual_seed(11)
+    for kv in model.kv:
+        kv.normal_(generator=g)
+        kv[:, 0].zero_()  # null block
+    tok_host = torch.randint(0, shape.vocab, (b,), generator=torch.Generator().manual_seed(1234))
+    bufs = model.decode_buffers(b)
+    bufs.tokens.copy_(tok_host)
+    model.num_tokens.fill_(n0)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident decode: CUDA-graph replay, the sampled token and the length advance on the device
+    l0 = ops.launch_count()
+    model.decode_step(b, advance=True, use_graph=True)  # captures (one eager warm-up pass + one capture pass) and replays
+    launches_per_step = (ops.launch_count() - l0) // 2
+    model.num_tokens.fill_(n0)
+    for _ in range(w_steps):
+        model.decode_step(b, advance=True, use_graph=True)
+    barrier()
+    clocks = ClockSampler(local).start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(k_steps):
+        model.decode_step(b, advance=True, use_graph=True)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop()
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / k_steps
+    value = b * k_steps / (ms * 1e-3)
+    mean_ctx = args.ctx + (k_steps - 1) / 2
+
+    # ---- end to end through execute_model (host inputs each step, sampled ids read back each step)
+    e2e = run_e2e(args, shape, model, bt_host, dev, rank, world, group, barrier, n_start=args.ctx + k_steps)
+
+    # ---- per-kernel device times (eager, CUDA events around every launch) for the roofline of the dominant kernel
+    n_prof = int(model.num_tokens[0].item())
+    with ops.kernel_timer() as kt:
+        for _ in range(p_steps):
+            model.decode_step(b, advance=True, use_graph=False)
+    ksum = kt.summary()
+    hbm_peak, peak_src = load_peaks()
+    attn_cnt, attn_ms = ksum["paged_attn_decode"]
+    ctxs = [n_prof + (p_steps - 1) / 2] * b
+    attn_bytes = attn_algorithmic_bytes(ctxs, model.hq, model.hkv, model.d)
+    achieved = attn_bytes / (attn_ms * 1e-3) / 1e9
+    kernels = {}
+    per_step_ms = 0.0
+    for name, (cnt, mean_ms) in sorted(ksum.items(), key=lambda kv: -kv[1][0] * kv[1][1]):
+        kernels[name] = {"launches_per_step": cnt / p_steps, "mean_us": round(mean_ms * 1e3, 2),
+                         "us_per_step": round(cnt * mean_ms * 1e3 / p_steps, 1)}
+        per_step_ms += cnt * mean_ms / p_steps
+    wbytes, kvbytes = step_algorithmic_bytes(shape, args.quant, b, mean_ctx, world)
+    roofline = {
+        "bound": "hbm", "kernel": "paged_attn_decode_kernel (+ split combine)", "achieved": round(achieved, 1),
+        "peak": hbm_peak, "unit": "GB/s", "frac": round(achieved / hbm_peak, 4), "traffic": args.attn_traffic,
+        "peak_source": peak_src, "algorithmic_bytes_per_launch": int(attn_bytes), "mean_us_per_launch": round(attn_ms * 1e3, 2),
+        "share_of_step": round(attn_cnt * attn_ms / p_steps / per_step_ms, 4),
+        "step": {"weights_bytes": int(wbytes), "kv_bytes": int(kvbytes),
+                 "min_ms_at_peak": round((wbytes + kvbytes) / hbm_peak / 1e6, 4),
+                 "frac_of_step_roofline": round((wbytes + kvbytes) / hbm_peak / 1e6 / ms_per_step, 4)},
+    }
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        steps_s, desc = time_cpu_step(shape, args.quant, b, args.ctx, threads, reps=args.cpu_reps)
+        cpu = {"value": b / statistics.median(steps_s), "unit": UNIT, "cores": threads, "kind": "port", "sample": desc}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": k_steps, "warmup": w_steps,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": args.quant, "data": "synthetic (random-init weights, N(0,1) KV pool, random tokens, permuted block ids)",
+            "config": dict(workload_config(args, shape, world), mean_context_in_timed_region=mean_ctx,
+                           max_model_len=max_model_len, num_blocks=num_blocks, cuda_graph=True),
+            "clocks": clk, "e2e": e2e, "gpu_launches": launches_per_step * k_steps,
+            "launches_per_step": launches_per_step, "roofline": roofline, "cpu_baseline": cpu, "kernels": kernels,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_e2e(args, shape, model, bt_host, dev, rank, world, group, barrier, n_start):
+    """Decode steps through B200ModelRunner.execute_model: the call vLLM's worker makes (reference WORKER:65-69 ->
+    RUNNER:252-291).  Host state in, sampled ids out; H2D/D2H bytes counted by the runner from the tensors it copies."""
+    import torch
+
+    from tests_support import make_vllm_config, sched_output
+    from vllm_neuron_b200.worker.b200_model_runner import B200ModelRunner, CachedRequest
+
+    b = args.batch
+    override = {} if args.quant == "bf16" else {
+        "quantized": True, "quantization_dtype": "f8e4m3" if args.quant == "fp8" else "int8",
+        "quantization_type": "per_channel_symmetric"}
+    cfg = make_vllm_config(shape, max_num_seqs=b, max_model_len=model.max_model_len,
+                           num_gpu_blocks_override=model.num_blocks, tp=world, override=override)
+    runner = B200ModelRunner(cfg, dev, model=model, tp_rank=rank, tp_size=world, tp_group=group)
+    runner.load_model(load_dummy_weights=True)
+    runner.initialize_kv_cache(num_blocks=model.num_blocks)
+    # requests already mid-generation: n_start tokens each (synthetic prompt ids), every block pre-assigned
+    gen = torch.Generator().manual_seed(1234)
+    for i in range(b):
+        rid = f"req-{i}"
+        prompt = torch.randint(0, shape.vocab, (n_start,), generator=gen).tolist()
+        runner.requests[rid] = CachedRequest(rid, prompt, [], bt_host[i].tolist(), n_start - 1, i, None)
+        runner.req_to_row[rid] = i
+    runner.free_rows.clear()
+    so = sched_output(cached=[(f"req-{i}", None) for i in range(b)])
+    for _ in range(3):
+        runner.execute_model(so)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    h2d = d2h = 0
+    for _ in range(args.e2e_steps):
+        out = runner.execute_model(so)
+        h2d += runner.h2d_bytes_last
+        d2h += runner.d2h_bytes_last
+    e1.record()
+    barrier()
+    assert len(out.sampled_token_ids) == b
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        import torch.distributed as dist
+
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return {"value": b * args.e2e_steps / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d // args.e2e_steps,
+            "d2h_bytes_per_step": d2h // args.e2e_steps, "steps": args.e2e_steps, "ms_per_step": ms / args.e2e_steps,
+            "api": "B200ModelRunner.execute_model(scheduler_output)"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--model", default="llama-3.1-8b")
+    ap.add_argument("--quant", default="fp8", choices=["bf16", "fp8", "int8"])
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--ctx", type=int, default=2048)
+    ap.add_argument("--e2e-steps", type=int, default=32)
+    ap.add_argument("--cpu-reps", type=int, default=3)
+    ap.add_argument("--cpu-budget-s", type=float, default=150.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--layers", type=int, default=0, help="debug: override the layer count (result is then NOT the headline)")
+    ap.add_argument("--attn-traffic", type=float, default=None,
+                    help="dram bytes read+written per attention launch from the committed ncu --set full capture")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    from dataclasses import replace
+
+    from vllm_neuron_b200.config import PRESETS
+
+    shape = PRESETS[args.model]
+    if args.layers:
+        shape = replace(shape, layers=args.layers, name=f"{shape.name}[{args.layers} layers, DEBUG]")
+    if args.attn_traffic is None:
+        try:
+            with open(os.path.join(ROOT, "profiles", "attn_traffic.json")) as f:
+                args.attn_traffic = json.load(f).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+    if args.impl == "reference":
+        run_reference(args, shape)
+    else:
+        run_b200(args, shape)
+
+
+if __name__ == "__main__":
+    main()

@@ -49,6 +49,14 @@ class RefLinear:
         else:
             raise ValueError(quant)
 
+    def prepare_f64(self):
+        """Widen the stored weight once (values unchanged) so repeated calls skip the per-call conversion."""
+        if self.quant == "bf16":
+            self.w = self.w.to(torch.float64)
+        else:
+            self.wq = self.wq.to(torch.float64)
+        return self
+
     def __call__(self, x, residual=None, out_dtype=torch.bfloat16):
         if self.quant == "bf16":
             return quant_ref.gemm_ref(x, self.w, self.bias, residual, out_dtype)

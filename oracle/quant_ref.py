@@ -44,9 +44,15 @@ def quantize_act_per_token(x, kind: str):
     return _quant_rows(x.float(), kind)
 
 
+def _f64(w):
+    """Weights may be handed over already widened (RefLinear.prepare_f64: the timed CPU baseline converts once,
+    outside the timed region, like any CPU runtime would keep its weights in the compute dtype)."""
+    return w if w.dtype == torch.float64 else w.to(torch.float64)
+
+
 def qgemm_ref(xq, x_scale, wq, w_scale, bias=None, residual=None, out_dtype=torch.bfloat16):
     """W8A8: exact integer / fp8 products accumulated in fp64, scaled in fp32."""
-    acc = (xq.to(torch.float64) @ wq.to(torch.float64).t()).float()
+    acc = (xq.to(torch.float64) @ _f64(wq).t()).float()
     y = acc * x_scale.view(-1, 1) * w_scale.view(1, -1)
     if bias is not None:
         y = y + bias.float().view(1, -1)
@@ -57,7 +63,7 @@ def qgemm_ref(xq, x_scale, wq, w_scale, bias=None, residual=None, out_dtype=torc
 
 def gemm_ref(x, w, bias=None, residual=None, out_dtype=torch.bfloat16):
     """Plain bf16 GEMM: out = x @ w^T (+bias)(+residual), fp32+ accumulate, one rounding."""
-    y = (x.to(torch.float64) @ w.to(torch.float64).t()).float()
+    y = (x.to(torch.float64) @ _f64(w).t()).float()
     if bias is not None:
         y = y + bias.float().view(1, -1)
     if residual is not None:
@@ -67,7 +73,7 @@ def gemm_ref(x, w, bias=None, residual=None, out_dtype=torch.bfloat16):
 
 def wo_gemm_ref(x, wq, w_scale, bias=None, residual=None, out_dtype=torch.bfloat16):
     """Weight-only int8: bf16 activations x (int8 weights dequantised per channel)."""
-    acc = (x.to(torch.float64) @ wq.to(torch.float64).t()).float()
+    acc = (x.to(torch.float64) @ _f64(wq).t()).float()
     y = acc * w_scale.view(1, -1)
     if bias is not None:
         y = y + bias.float().view(1, -1)

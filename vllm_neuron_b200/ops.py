@@ -12,10 +12,57 @@ from ._cabi import BF16, F32, FP8_E4M3, INT8, check
 
 _QDT = {None: BF16, "bf16": BF16, "fp8": FP8_E4M3, "int8": INT8}
 _TORCH_Q = {FP8_E4M3: torch.float8_e4m3fn, INT8: torch.int8}
+_DTN = {BF16: "bf16", FP8_E4M3: "fp8", INT8: "int8"}
 
 
 def _stream():
     return torch.cuda.current_stream().cuda_stream
+
+
+# ------------------------------------------------------------------ per-launch device timing (bench.py roofline leg)
+_PROF: list | None = None
+
+
+class kernel_timer:
+    """with ops.kernel_timer() as t: ...eager calls...; t.summary() -> {name: (count, mean_ms)}.
+    CUDA events are recorded on the launching stream right around each C-ABI call (not usable under graph capture)."""
+
+    def __enter__(self):
+        global _PROF
+        self.records = _PROF = []
+        return self
+
+    def __exit__(self, *exc):
+        global _PROF
+        _PROF = None
+        return False
+
+    def summary(self):
+        torch.cuda.synchronize()
+        acc: dict[str, list] = {}
+        for name, e0, e1 in self.records:
+            acc.setdefault(name, []).append(e0.elapsed_time(e1))
+        return {k: (len(v), sum(v) / len(v)) for k, v in acc.items()}
+
+
+class _k:
+    __slots__ = ("name", "e0")
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if _PROF is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *exc):
+        if _PROF is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            _PROF.append((self.name, self.e0, e1))
+        return False
 
 
 def _ptr(t):
@@ -45,13 +92,14 @@ def build_decode_meta(block_table, row_ids, num_tokens, slot_mapping, positions,
     assert block_table.dtype == torch.int32 and num_tokens.dtype == torch.int32
     assert slot_mapping.dtype == torch.int64 and positions.dtype == torch.int64 and ctx_lens.dtype == torch.int32
     b = slot_mapping.numel()
-    check(
-        _cabi.load().b200_build_decode_meta(
-            _ptr(block_table), block_table.stride(0), _ptr(row_ids), _ptr(num_tokens), _ptr(slot_mapping),
-            _ptr(positions), _ptr(ctx_lens), b, block_table.shape[1], block_size, _stream(),
-        ),
-        "b200_build_decode_meta",
-    )
+    with _k("build_decode_meta"):
+        check(
+            _cabi.load().b200_build_decode_meta(
+                _ptr(block_table), block_table.stride(0), _ptr(row_ids), _ptr(num_tokens), _ptr(slot_mapping),
+                _ptr(positions), _ptr(ctx_lens), b, block_table.shape[1], block_size, _stream(),
+            ),
+            "b200_build_decode_meta",
+        )
 
 
 def build_prefill_meta(block_table_row, prompt_len: int, num_computed: int, slot_mapping, positions, block_size: int):
@@ -114,13 +162,14 @@ def rope_kv_write(qkv, positions, cos, sin, k_pool, v_pool, slot_mapping, num_q_
     assert qkv.is_contiguous() and qkv.shape[1] == (num_q_heads + 2 * hkv) * d and qkv.dtype == torch.bfloat16
     assert cos.dtype == torch.float32 and cos.shape[1] == d // 2 and cos.is_contiguous() and sin.is_contiguous()
     assert positions.dtype == torch.int64 and slot_mapping.dtype == torch.int64
-    check(
-        _cabi.load().b200_rope_kv_write(
-            _ptr(qkv), _ptr(positions), _ptr(cos), _ptr(sin), cos.shape[0], _ptr(k_pool), _ptr(v_pool),
-            _ptr(slot_mapping), t, num_q_heads, hkv, d, bs, nb, _stream(),
-        ),
-        "b200_rope_kv_write",
-    )
+    with _k("rope_kv_write"):
+        check(
+            _cabi.load().b200_rope_kv_write(
+                _ptr(qkv), _ptr(positions), _ptr(cos), _ptr(sin), cos.shape[0], _ptr(k_pool), _ptr(v_pool),
+                _ptr(slot_mapping), t, num_q_heads, hkv, d, bs, nb, _stream(),
+            ),
+            "b200_rope_kv_write",
+        )
 
 
 # ------------------------------------------------------------------ paged attention
@@ -142,14 +191,15 @@ def paged_attn_decode(q, k_pool, v_pool, block_table, ctx_lens, scale, out=None,
     assert out.is_contiguous()
     if workspace is None:
         workspace = torch.empty(paged_attn_decode_workspace_bytes(b, hq, hkv, d, mb, chunk_blocks), dtype=torch.uint8, device=q.device)
-    check(
-        _cabi.load().b200_paged_attn_decode(
-            _ptr(q), q.stride(0), _ptr(k_pool), _ptr(v_pool), nb, _ptr(block_table), block_table.stride(0),
-            _ptr(row_ids), _ptr(ctx_lens), _ptr(out), _ptr(workspace), workspace.numel() * workspace.element_size(),
-            b, hq, hkv, d, bs, mb, chunk_blocks, float(scale), _stream(),
-        ),
-        "b200_paged_attn_decode",
-    )
+    with _k("paged_attn_decode"):
+        check(
+            _cabi.load().b200_paged_attn_decode(
+                _ptr(q), q.stride(0), _ptr(k_pool), _ptr(v_pool), nb, _ptr(block_table), block_table.stride(0),
+                _ptr(row_ids), _ptr(ctx_lens), _ptr(out), _ptr(workspace), workspace.numel() * workspace.element_size(),
+                b, hq, hkv, d, bs, mb, chunk_blocks, float(scale), _stream(),
+            ),
+            "b200_paged_attn_decode",
+        )
     return out
 
 
@@ -161,13 +211,14 @@ def paged_attn_prefill(q, k_pool, v_pool, block_table_row, computed_len: int, sc
     assert q.stride(2) == 1 and q.stride(1) == d and block_table_row.dtype == torch.int32
     if out is None:
         out = torch.empty((s_new, hq, d), dtype=q.dtype, device=q.device)
-    check(
-        _cabi.load().b200_paged_attn_prefill(
-            _ptr(q), q.stride(0), _ptr(k_pool), _ptr(v_pool), nb, _ptr(block_table_row), _ptr(out), s_new,
-            computed_len, hq, hkv, d, bs, float(scale), _stream(),
-        ),
-        "b200_paged_attn_prefill",
-    )
+    with _k("paged_attn_prefill"):
+        check(
+            _cabi.load().b200_paged_attn_prefill(
+                _ptr(q), q.stride(0), _ptr(k_pool), _ptr(v_pool), nb, _ptr(block_table_row), _ptr(out), s_new,
+                computed_len, hq, hkv, d, bs, float(scale), _stream(),
+            ),
+            "b200_paged_attn_prefill",
+        )
     return out
 
 
@@ -203,13 +254,14 @@ def gemm(a, w, a_scale=None, w_scale=None, bias=None, residual=None, out=None, o
     if workspace is None:
         nbytes = gemm_workspace_bytes(m, n, k, dt, split_k)
         workspace = torch.empty(nbytes, dtype=torch.uint8, device=a.device) if nbytes else None
-    check(
-        _cabi.load().b200_gemm(
-            _ptr(a), _ptr(w), _ptr(out), _ptr(a_scale), _ptr(w_scale), _ptr(bias), _ptr(residual), m, n, k, dt, odt,
-            split_k, _ptr(workspace), 0 if workspace is None else workspace.numel() * workspace.element_size(), _stream(),
-        ),
-        "b200_gemm",
-    )
+    with _k(f"gemm_{_DTN[dt]}[{m}x{n}x{k}]"):
+        check(
+            _cabi.load().b200_gemm(
+                _ptr(a), _ptr(w), _ptr(out), _ptr(a_scale), _ptr(w_scale), _ptr(bias), _ptr(residual), m, n, k, dt, odt,
+                split_k, _ptr(workspace), 0 if workspace is None else workspace.numel() * workspace.element_size(), _stream(),
+            ),
+            "b200_gemm",
+        )
     return out
 
 
@@ -222,12 +274,14 @@ def rmsnorm(x, w, eps, quant=None, out_bf16=None, want_bf16=None):
     qd = _QDT[quant]
     if qd == BF16:
         y = out_bf16 if out_bf16 is not None else torch.empty_like(x)
-        check(_cabi.load().b200_rmsnorm(_ptr(x), _ptr(w), _ptr(y), 0, 0, t, h, float(eps), qd, _stream()), "b200_rmsnorm")
+        with _k("rmsnorm"):
+            check(_cabi.load().b200_rmsnorm(_ptr(x), _ptr(w), _ptr(y), 0, 0, t, h, float(eps), qd, _stream()), "b200_rmsnorm")
         return y
     q = torch.empty((t, h), dtype=_TORCH_Q[qd], device=x.device)
     s = torch.empty((t,), dtype=torch.float32, device=x.device)
     y = (out_bf16 if out_bf16 is not None else torch.empty_like(x)) if want_bf16 else None
-    check(_cabi.load().b200_rmsnorm(_ptr(x), _ptr(w), _ptr(y), _ptr(q), _ptr(s), t, h, float(eps), qd, _stream()), "b200_rmsnorm")
+    with _k("rmsnorm_quant"):
+        check(_cabi.load().b200_rmsnorm(_ptr(x), _ptr(w), _ptr(y), _ptr(q), _ptr(s), t, h, float(eps), qd, _stream()), "b200_rmsnorm")
     return (q, s, y) if want_bf16 else (q, s)
 
 
@@ -239,11 +293,13 @@ def silu_mul(gate_up, quant=None):
     qd = _QDT[quant]
     if qd == BF16:
         y = torch.empty((t, i), dtype=torch.bfloat16, device=gate_up.device)
-        check(_cabi.load().b200_silu_mul(_ptr(gate_up), _ptr(y), 0, 0, t, i, qd, _stream()), "b200_silu_mul")
+        with _k("silu_mul"):
+            check(_cabi.load().b200_silu_mul(_ptr(gate_up), _ptr(y), 0, 0, t, i, qd, _stream()), "b200_silu_mul")
         return y
     q = torch.empty((t, i), dtype=_TORCH_Q[qd], device=gate_up.device)
     s = torch.empty((t,), dtype=torch.float32, device=gate_up.device)
-    check(_cabi.load().b200_silu_mul(_ptr(gate_up), 0, _ptr(q), _ptr(s), t, i, qd, _stream()), "b200_silu_mul")
+    with _k("silu_mul_quant"):
+        check(_cabi.load().b200_silu_mul(_ptr(gate_up), 0, _ptr(q), _ptr(s), t, i, qd, _stream()), "b200_silu_mul")
     return q, s
 
 
@@ -254,7 +310,8 @@ def quantize_per_token(x, quant: str):
     qd = _QDT[quant]
     q = torch.empty((t, k), dtype=_TORCH_Q[qd], device=x.device)
     s = torch.empty((t,), dtype=torch.float32, device=x.device)
-    check(_cabi.load().b200_quantize_per_token(_ptr(x), _ptr(q), _ptr(s), t, k, qd, _stream()), "b200_quantize_per_token")
+    with _k("quantize_per_token"):
+        check(_cabi.load().b200_quantize_per_token(_ptr(x), _ptr(q), _ptr(s), t, k, qd, _stream()), "b200_quantize_per_token")
     return q, s
 
 
@@ -265,7 +322,8 @@ def embedding(tokens, table, out=None):
     assert tokens.dtype == torch.int64 and table.is_contiguous()
     if out is None:
         out = torch.empty((t, h), dtype=table.dtype, device=table.device)
-    check(_cabi.load().b200_embedding(_ptr(tokens), _ptr(table), _ptr(out), t, h, v, _stream()), "b200_embedding")
+    with _k("embedding"):
+        check(_cabi.load().b200_embedding(_ptr(tokens), _ptr(table), _ptr(out), t, h, v, _stream()), "b200_embedding")
     return out
 
 
@@ -275,5 +333,6 @@ def argmax(logits, idx_offset: int = 0, want_val: bool = False):
     assert logits.dtype == torch.float32 and logits.stride(1) == 1
     idx = torch.empty((t,), dtype=torch.int64, device=logits.device)
     val = torch.empty((t,), dtype=torch.float32, device=logits.device) if want_val else None
-    check(_cabi.load().b200_argmax(_ptr(logits), logits.stride(0), _ptr(val), _ptr(idx), t, v, idx_offset, _stream()), "b200_argmax")
+    with _k("argmax"):
+        check(_cabi.load().b200_argmax(_ptr(logits), logits.stride(0), _ptr(val), _ptr(idx), t, v, idx_offset, _stream()), "b200_argmax")
     return (val, idx) if want_val else idx

@@ -111,6 +111,25 @@ class B200ModelRunner:
             raise NotImplementedError(
                 "checkpoint loading is not built yet (SURVEY 8(f)-4); run with load_format='dummy' (random-init weights)")
 
+    def weight_bytes_estimate(self) -> int:
+        """Per-rank bytes of the weights that initialize_kv_cache will materialise (used to size the KV budget)."""
+        sh, tp = self.model_shape(), self.tp_size
+        cfg = self.b200_config or self.build_b200_config()
+        wb = 2 if cfg.quant_mode == "bf16" else 1
+        qd, kd = sh.num_q_heads * sh.head_dim, sh.num_kv_heads * sh.head_dim
+        per_layer = ((qd + 2 * kd) * sh.hidden + sh.hidden * qd + 3 * sh.intermediate * sh.hidden) * wb
+        return (per_layer * sh.layers + sh.vocab * sh.hidden * wb) // tp + sh.vocab * sh.hidden * 2
+
+    def warm_up(self) -> None:
+        """Capture the full-batch decode graph ahead of the first request (reference: compile/warm-up is NxDI's)."""
+        if self.model is None or not self.use_cuda_graph:
+            return
+        saved = self.model.num_tokens.clone()
+        self.model.num_tokens.fill_(0)  # pos = -1 -> slot -1: nothing is written
+        self.model.decode_step(self.max_num_reqs, use_graph=True)
+        self.model.num_tokens.copy_(saved)
+        torch.cuda.synchronize()
+
     def get_kv_cache_spec(self):
         """RUNNER:361-379 hands vLLM ONE spec under 'layer'; we register one per decoder layer with the per-rank
         kv-head count so vLLM's block budget is right without --num-gpu-blocks-override (documented deviation)."""
