@@ -1,0 +1,70 @@
+"""CPU tests of the model runner's host-side state tracking (no GPU, no kernels): request cache, persistent rows,
+block-id append / replace -- the behaviours the reference pins in test/unit/worker/test_model_runner.py:984-1018,
+1124-1161 -- and the (row, col, block) triples handed to the device block table."""
+import pytest
+import torch
+
+from parity_util import make_vllm_config, sched_output
+from vllm_neuron_b200.config import PRESETS
+from vllm_neuron_b200.worker.b200_model_runner import B200ModelRunner
+
+
+def _runner(mns=4):
+    cfg = make_vllm_config(PRESETS["tiny-test"], max_num_seqs=mns, max_model_len=256, num_gpu_blocks_override=41)
+    return B200ModelRunner(cfg, torch.device("cpu"))
+
+
+def test_new_request_takes_lowest_free_row_and_mirrors_blocks():
+    r = _runner()
+    upd = r._update_states(sched_output(new_reqs=[("a", list(range(40)), [7, 3], 0)]))
+    assert r.req_to_row == {"a": 0} and r.requests["a"].block_ids == [7, 3]
+    assert upd == [(0, 0, 7), (0, 1, 3)]
+    upd = r._update_states(sched_output(new_reqs=[("b", list(range(5)), [9], 0)]))
+    assert r.req_to_row["b"] == 1 and upd == [(1, 0, 9)]
+
+
+def test_cached_request_block_append_and_resume_replace():
+    r = _runner()
+    r._update_states(sched_output(new_reqs=[("a", list(range(40)), [7, 3], 0)]))
+    r.requests["a"].output_token_ids.append(11)
+    upd = r._update_states(sched_output(cached=[("a", [5])]))
+    assert r.requests["a"].block_ids == [7, 3, 5] and upd == [(0, 2, 5)]          # RUNNER:461-466
+    assert r.requests["a"].num_computed_tokens == 40                                # num_tokens - 1
+    upd = r._update_states(sched_output(cached=[("a", None)]))
+    assert upd == [] and r.requests["a"].block_ids == [7, 3, 5]
+    so = sched_output(cached=[("a", [20, 21])])
+    so.scheduled_cached_reqs.resumed_req_ids = {"a"}
+    upd = r._update_states(so)
+    assert r.requests["a"].block_ids == [20, 21] and upd == [(0, 0, 20), (0, 1, 21)]  # RUNNER:467-471 (replace)
+
+
+def test_finished_request_frees_its_row():
+    r = _runner(mns=2)
+    r._update_states(sched_output(new_reqs=[("a", [1, 2, 3], [4], 0)]))
+    r._update_states(sched_output(new_reqs=[("b", [1, 2, 3], [5], 0)]))
+    assert not r.free_rows
+    with pytest.raises(AssertionError, match="No free sequence ID"):
+        r._update_states(sched_output(new_reqs=[("c", [1], [6], 0)]))
+    r._update_states(sched_output(finished=["a"]))
+    assert r.free_rows == {0} and "a" not in r.requests
+    r._update_states(sched_output(new_reqs=[("c", [1], [6], 0)]))
+    assert r.req_to_row["c"] == 0
+    with pytest.raises(AssertionError, match="existing request ID"):
+        r._update_states(sched_output(new_reqs=[("c", [1], [6], 0)]))
+
+
+def test_empty_step_returns_empty_output():
+    from vllm.v1.outputs import EMPTY_MODEL_RUNNER_OUTPUT
+
+    r = _runner()
+    assert r.execute_model(sched_output()) is EMPTY_MODEL_RUNNER_OUTPUT  # RUNNER:272-274
+
+
+def test_config_and_kv_spec_follow_the_reference_keys():
+    r = _runner()
+    cfg = r.build_b200_config()
+    assert cfg.pa_block_size == 32 and cfg.pa_num_blocks == 41 and cfg.is_block_kv_layout and cfg.is_prefix_caching
+    spec = r.get_kv_cache_spec()
+    assert len(spec) == PRESETS["tiny-test"].layers
+    s0 = next(iter(spec.values()))
+    assert s0.block_size == 32 and s0.num_kv_heads == 2 and s0.head_size == 64 and s0.dtype == torch.bfloat16

@@ -1,0 +1,39 @@
+"""CPU tests of the continuous-batching policy (reference behaviours: test/unit/core/test_scheduler.py:147-164,
+404-422 for admission; :430-663 for the min_tokens stop rules)."""
+import pytest
+
+from vllm_neuron_b200.core.scheduler import admit_count, stop_reason
+
+
+@pytest.mark.parametrize("running,pending,cap,want", [
+    (0, 0, 4, 0),
+    (0, 1, 4, 1),   # empty engine: start a new batch
+    (0, 3, 4, 1),   # prefill batch is 1 (SCHED:116)
+    (2, 3, 4, 1),   # a free decode line: one more prefill
+    (4, 3, 4, 0),   # decode batch full: nothing admitted
+    (3, 1, 4, 1),
+    (0, 2, 1, 1),
+])
+def test_admit_count(running, pending, cap, want):
+    assert admit_count(running, pending, cap) == want
+
+
+def _stop(**kw):
+    base = dict(num_tokens=10, num_output_tokens=3, max_tokens=16, max_model_len=2048, min_tokens=0, last_token_id=5,
+                eos_token_id=2, ignore_eos=False, stop_token_ids=())
+    base.update(kw)
+    return stop_reason(**base)
+
+
+def test_stop_rules():
+    assert _stop() is None
+    assert _stop(last_token_id=2) == "stop"
+    assert _stop(last_token_id=2, ignore_eos=True) is None
+    assert _stop(last_token_id=2, min_tokens=5) is None            # EOS suppressed until min_tokens reached
+    assert _stop(last_token_id=2, min_tokens=3) == "stop"
+    assert _stop(last_token_id=7, stop_token_ids=(7,)) == ("stop", 7)
+    assert _stop(last_token_id=7, stop_token_ids=(7,), min_tokens=9) is None
+    assert _stop(num_output_tokens=16) == "length"                 # max_tokens wins over min_tokens
+    assert _stop(num_output_tokens=16, min_tokens=32) == "length"
+    assert _stop(num_tokens=2048) == "length"
+    assert _stop(pooling=True) is None and _stop(pooling=True, has_pooler_output=True) == "stop"

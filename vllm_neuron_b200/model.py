@@ -79,6 +79,30 @@ def random_init_full_weights(shape: ModelShape, seed: int = 0, device="cpu", std
     return w
 
 
+def tp_shard_plan(shape: ModelShape, rank: int, size: int) -> dict:
+    """Row/column ranges of every weight owned by TP rank `rank`: q/kv heads and MLP columns are
+    column-parallel (rows of W[N,K]), o_proj/down_proj are row-parallel (columns of W[N,K]), lm_head by vocab rows."""
+    d = shape.head_dim
+    qd, kd, I = shape.num_q_heads * d, shape.num_kv_heads * d, shape.intermediate
+    r, t = rank, size
+    return {
+        "qkv_rows": [(r * qd // t, (r + 1) * qd // t), (qd + r * kd // t, qd + (r + 1) * kd // t),
+                     (qd + kd + r * kd // t, qd + kd + (r + 1) * kd // t)],
+        "o_cols": (r * qd // t, (r + 1) * qd // t),
+        "gu_rows": [(r * I // t, (r + 1) * I // t), (I + r * I // t, I + (r + 1) * I // t)],
+        "down_cols": (r * I // t, (r + 1) * I // t),
+        "vocab_rows": (r * shape.vocab // t, (r + 1) * shape.vocab // t),
+    }
+
+
+def merge_sharded_argmax(vals: torch.Tensor, idxs: torch.Tensor, vocab: int) -> torch.Tensor:
+    """vals/idxs [tp, B]: each rank's local (max, global index).  Global greedy token = lowest index among the
+    ranks holding the global maximum (same tie rule as the single-GPU argmax kernel)."""
+    best = vals.max(dim=0, keepdim=True).values
+    cand = torch.where(vals == best, idxs, torch.full_like(idxs, vocab))
+    return cand.min(dim=0).values
+
+
 class _Linear:
     """One (possibly TP-sharded, possibly quantised) weight with its per-channel scale."""
 
@@ -136,15 +160,11 @@ class B200CausalLM:
         dev = self.device
         if full_weights is None:
             full_weights = _LazyRandomWeights(shape, seed)
-        r, t, d = tp_rank, tp_size, self.d
-        Hq, Hkv, I = shape.num_q_heads, shape.num_kv_heads, shape.intermediate
-        qd, kd = Hq * d, Hkv * d
-        qkv_rows = [(r * qd // t, (r + 1) * qd // t), (qd + r * kd // t, qd + (r + 1) * kd // t),
-                    (qd + kd + r * kd // t, qd + kd + (r + 1) * kd // t)]
-        gu_rows = [(r * I // t, (r + 1) * I // t), (I + r * I // t, I + (r + 1) * I // t)]
+        plan = tp_shard_plan(shape, tp_rank, tp_size)
+        qkv_rows, gu_rows = plan["qkv_rows"], plan["gu_rows"]
         self.embed = full_weights["embed"].to(dev).contiguous()
         self.final_norm = full_weights["final_norm"].to(dev).contiguous()
-        v0, v1 = r * shape.vocab // t, (r + 1) * shape.vocab // t
+        v0, v1 = plan["vocab_rows"]
         self.lm_head = _Linear(full_weights["lm_head"], quant if quant_lm_head else "bf16", dev, row_slices=[(v0, v1)])
         self.vocab_offset = v0
         self.layers = []
@@ -155,9 +175,9 @@ class B200CausalLM:
                     "input_norm": lw["input_norm"].to(dev).contiguous(),
                     "post_norm": lw["post_norm"].to(dev).contiguous(),
                     "qkv": _Linear(lw["wqkv"], quant, dev, row_slices=qkv_rows, bias=lw.get("bqkv")),
-                    "o": _Linear(lw["wo"], quant, dev, col_slice=(r * qd // t, (r + 1) * qd // t)),
+                    "o": _Linear(lw["wo"], quant, dev, col_slice=plan["o_cols"]),
                     "gu": _Linear(lw["wgu"], quant, dev, row_slices=gu_rows),
-                    "down": _Linear(lw["wdown"], quant, dev, col_slice=(r * I // t, (r + 1) * I // t)),
+                    "down": _Linear(lw["wdown"], quant, dev, col_slice=plan["down_cols"]),
                 }
             )
             if isinstance(full_weights, _LazyRandomWeights):
@@ -247,9 +267,7 @@ class B200CausalLM:
         idxs = torch.empty((self.tp_size, idx.numel()), dtype=idx.dtype, device=idx.device)
         torch.distributed.all_gather_into_tensor(vals, val, group=self.tp_group)
         torch.distributed.all_gather_into_tensor(idxs, idx, group=self.tp_group)
-        best = vals.max(dim=0, keepdim=True).values
-        cand = torch.where(vals == best, idxs, torch.full_like(idxs, self.shape.vocab))
-        return cand.min(dim=0).values, logits
+        return merge_sharded_argmax(vals, idxs, self.shape.vocab), logits
 
     # ------------------------------------------------------------------ decode
     def decode_buffers(self, b: int) -> StepBuffers:
