@@ -25,7 +25,7 @@ fi
 SHORT="python bench.py --steps 3 --warmup 3 --e2e-steps 2 --no-cpu-baseline"
 if [[ "$ARGS" == *" launches "* ]]; then
   timeout 600 $SHORT > gpurun_out/plain.log 2>&1 &&
-  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 2000 -c 1500 --csv \
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -k regex:b200:: -s ${LAUNCH_SKIP:-454} -c ${LAUNCH_COUNT:-1362} --csv \
       --log-file gpurun_out/launches.csv $SHORT > gpurun_out/ncu_launches.log 2>&1
   echo "launches exit=$?" | tee -a gpurun_out/summary.txt
 fi

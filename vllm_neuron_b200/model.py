@@ -182,9 +182,9 @@ class B200CausalLM:
             )
             if isinstance(full_weights, _LazyRandomWeights):
                 full_weights.drop(li)
-        self.cos, self.sin = rope_tables(d, max_model_len, shape.rope_theta, shape.rope_scaling, dev)
+        self.cos, self.sin = rope_tables(self.d, max_model_len, shape.rope_theta, shape.rope_scaling, dev)
         # ---- KV pools: per layer [2(K,V)][num_blocks][Hkv_local][bs][D] bf16; block 0 is vLLM's null block
-        self.kv = [torch.zeros((2, num_blocks, self.hkv, block_size, d), dtype=torch.bfloat16, device=dev)
+        self.kv = [torch.zeros((2, num_blocks, self.hkv, block_size, self.d), dtype=torch.bfloat16, device=dev)
                    for _ in range(shape.layers)]
         # ---- persistent per-sequence state (rows = the reference's seq-id slots, RUNNER:130-136)
         self.block_table = torch.zeros((max_num_seqs, self.max_blocks), dtype=torch.int32, device=dev)
