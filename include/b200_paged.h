@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 1
+#define B200_ABI_VERSION 2
 
 enum {
   B200_OK = 0,
@@ -52,6 +52,9 @@ const char* b200_last_error(void);
 int b200_device_check(int device);
 /* number of kernel launches issued through this library by the calling process (bench.py's gpu_launches) */
 uint64_t b200_launch_count(void);
+/* Programmatic dependent launch for every kernel of the library (default on): a kernel may become resident while its
+ * predecessor on the stream drains; the GEMM uses that window to prefetch weight tiles.  Returns the previous setting. */
+int b200_set_pdl(int enabled);
 
 /* ---------------------------------------------------------------- index construction on device
  * Replaces model_runner.py:765-832 (+ :887-917): per decode row b (persistent row r = row_ids[b]):
@@ -88,13 +91,18 @@ int b200_rope_kv_write(void* qkv, const int64_t* positions, const float* cos_tab
 
 /* ---------------------------------------------------------------- paged attention
  * Decode (q_len = 1): out[b][h][:] = softmax(q K^T scale) V over ctx_lens[b] tokens gathered through
- * block_table[row_ids ? row_ids[b] : b].  Split along the context in chunks of `chunk_blocks` blocks
- * (flash-decoding); partials live in `workspace`.  chunk_blocks = 0 picks a default. */
-size_t b200_paged_attn_decode_workspace_bytes(int B, int Hq, int Hkv, int D, int max_blocks, int chunk_blocks);
+ * block_table[row_ids ? row_ids[b] : b].  Flash-decoding with a BALANCED split: all (sequence, kv head) pairs are laid
+ * end to end as one list of 32-token blocks and every warp takes an equal contiguous share (>= min_quota blocks; 0 picks
+ * the default), so ragged context lengths cost nothing; per-share partials live in `workspace` and a second kernel merges
+ * them.  Outputs: q_dtype == B200_BF16 -> out [B][Hq][D] bf16;  FP8_E4M3 / INT8 -> out_q [B][Hq*D] with the dynamic
+ * per-token scale out_scale [B] (same arithmetic as b200_quantize_per_token on the bf16 result), out optional.
+ * ctx_lens[b] must be <= max_blocks * 32. */
+size_t b200_paged_attn_decode_workspace_bytes(int B, int Hq, int Hkv, int D, int max_blocks, int min_quota);
 int b200_paged_attn_decode(const void* q, int64_t q_token_stride, const void* k_pool, const void* v_pool, int num_blocks,
                            const int32_t* block_table, int64_t bt_row_stride, const int32_t* row_ids,
-                           const int32_t* ctx_lens, void* out, void* workspace, size_t workspace_bytes, int B, int Hq,
-                           int Hkv, int D, int block_size, int max_blocks, int chunk_blocks, float scale, void* stream);
+                           const int32_t* ctx_lens, void* out, void* out_q, float* out_scale, int q_dtype, void* workspace,
+                           size_t workspace_bytes, int B, int Hq, int Hkv, int D, int block_size, int max_blocks,
+                           int min_quota, float scale, void* stream);
 /* Prefix-cached prefill, one sequence: queries for absolute positions computed_len .. computed_len+S_new-1,
  * causal over cached prefix + new tokens, all K/V already in the pools. */
 int b200_paged_attn_prefill(const void* q, int64_t q_token_stride, const void* k_pool, const void* v_pool, int num_blocks,
@@ -104,11 +112,22 @@ int b200_paged_attn_prefill(const void* q, int64_t q_token_stride, const void* k
 /* ---------------------------------------------------------------- per-channel-scaled GEMM (tcgen05 / TMEM / TMA)
  * out[M][N] = (sum_k a[m][k] * w[n][k]) * a_scale[m] * w_scale[n] + bias[n] + residual[m][n]
  * a: [M][K], w: [N][K], both `ab_dtype` (BF16 | FP8_E4M3 | INT8); scales fp32 (NULL = 1), bias bf16 [N] or NULL,
- * residual bf16 [M][N] or NULL; out_dtype BF16 | F32.  split_k = 0 picks one. */
-size_t b200_gemm_workspace_bytes(int M, int N, int K, int ab_dtype, int split_k);
+ * residual bf16 [M][N] or NULL; out_dtype BF16 | F32.
+ * Persistent stream-K: max_ctas CTAs (0 = one per SM) each take an equal share of the (tile, k-block) space; tiles cut
+ * by a share boundary are summed in fixed order by the last contributor.  `workspace` (b200_gemm_workspace_bytes) holds
+ * the fix-up counters in its first 4 KiB: it must be ZERO-FILLED before its first use and is left zeroed by every call;
+ * one workspace may serve all GEMMs issued on one stream. */
+size_t b200_gemm_workspace_bytes(int M, int N, int K, int ab_dtype, int max_ctas);
 int b200_gemm(const void* a, const void* w, void* out, const float* a_scale, const float* w_scale, const void* bias,
-              const void* residual, int M, int N, int K, int ab_dtype, int out_dtype, int split_k, void* workspace,
+              const void* residual, int M, int N, int K, int ab_dtype, int out_dtype, int max_ctas, void* workspace,
               size_t workspace_bytes, void* stream);
+/* gate/up projection with SiLU(gate)*up fused into the epilogue.  w_gu [2I][K] holds, per group of 32 rows, 16 gate rows
+ * followed by the 16 up rows of the same channels (w_scale / bias permuted alike); out_act [M][I] bf16 =
+ * bf16(silu(bf16(gate)) * bf16(up)) exactly as b200_gemm + b200_silu_mul produce; tile_amax [ceil(2I/128)][M] fp32
+ * receives max|act| per 64-channel tile for the per-token quantisation that follows (b200_quantize_per_token). */
+int b200_gemm_silu_mul(const void* a, const void* w_gu, void* out_act, const float* a_scale, const float* w_scale,
+                       const void* bias, float* tile_amax, int M, int N2, int K, int ab_dtype, int max_ctas,
+                       void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------- glue kernels of the decoder step */
 /* y = x * rsqrt(mean(x^2)+eps) * w (fp32 math).  Writes any of: out_bf16 [T][H]; out_q [T][H] (q_dtype FP8/INT8)
@@ -118,7 +137,10 @@ int b200_rmsnorm(const void* x, const void* w, void* out_bf16, void* out_q, floa
 /* act = silu(gate) * up from gate_up [T][2I] (gate columns first); same output options as rmsnorm. */
 int b200_silu_mul(const void* gate_up, void* out_bf16, void* out_q, float* out_scale, int T, int I, int q_dtype,
                   void* stream);
-int b200_quantize_per_token(const void* x, void* out_q, float* out_scale, int T, int K, int q_dtype, void* stream);
+/* Dynamic per-token quantisation of x [T][K] bf16.  tile_amax [n_tiles][T] (optional, from b200_gemm_silu_mul) supplies
+ * the row maxima so rows can be cut across CTAs; NULL = scan the row. */
+int b200_quantize_per_token(const void* x, void* out_q, float* out_scale, const float* tile_amax, int n_tiles, int T, int K,
+                            int q_dtype, void* stream);
 int b200_embedding(const int64_t* tokens, const void* table, void* out, int T, int H, int V, void* stream);
 /* Greedy sampling (reference: top_k=1, temperature=1.0 for temperature 0, model_runner.py:1126-1128).
  * out_idx[t] = idx_offset + first index of the row maximum; out_val[t] = that maximum (for TP merges). */

@@ -33,7 +33,7 @@ def test_header_and_binding_agree(lib):
 
 
 def test_abi_version(lib):
-    assert lib.b200_abi_version() == 1
+    assert lib.b200_abi_version() == 2
 
 
 def test_no_device_is_an_error_not_a_fallback(lib):
@@ -49,8 +49,9 @@ def test_no_device_is_an_error_not_a_fallback(lib):
 def test_argument_validation_without_gpu(lib):
     # null pointers / bad shapes are rejected before any launch
     assert lib.b200_gemm(None, None, None, None, None, None, None, 1, 1, 16, 0, 0, 0, None, 0, None) == -1
-    assert lib.b200_paged_attn_decode(None, 0, None, None, 0, None, 0, None, None, None, None, 0, 1, 8, 8, 128, 32, 4, 0, 1.0, None) == -1
-    assert lib.b200_paged_attn_decode_workspace_bytes(64, 32, 8, 128, 64, 8) == 64 * 32 * 8 * 130 * 4
+    assert lib.b200_paged_attn_decode(None, 0, None, None, 0, None, 0, None, None, None, None, None, 0, None, 0, 1, 8, 8, 128, 32, 4, 0, 1.0, None) == -1
+    # balanced split: at most ceil(max_blocks / min_quota) + 1 partials per (sequence, head)
+    assert lib.b200_paged_attn_decode_workspace_bytes(64, 32, 8, 128, 64, 8) == 64 * 32 * 9 * 130 * 4
 
 
 def test_ops_refuse_cpu_tensors():

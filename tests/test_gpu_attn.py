@@ -33,17 +33,19 @@ def _check(got, want):
 
 
 @pytest.mark.parametrize(
-    "b,hq,hkv,d,ctxs,chunk",
+    "b,hq,hkv,d,ctxs,quota",
     [
         (4, 32, 8, 128, [1, 31, 32, 33], 0),          # block-boundary edge cases
         (8, 32, 8, 128, [2048, 100, 777, 1024, 5, 64, 1999, 300], 0),  # ragged, cfg2 heads
-        (3, 32, 4, 64, [500, 2048, 17], 4),           # TinyLlama heads (G=8, D=64)
+        (3, 32, 4, 64, [500, 2048, 17], 4),           # TinyLlama heads (G=8, D=64), 4-block minimum share
         (5, 5, 1, 128, [96, 640, 33, 1, 250], 2),     # Qwen2.5-32B @ TP=8 (G=5)
-        (2, 8, 1, 128, [4096, 3000], 32),             # 70B @ TP=8 (G=8), long context, 32-block chunks
-        (6, 4, 4, 128, [128] * 6, 1),                 # MHA (G=1), 1-block chunks
+        (2, 8, 1, 128, [4096, 3000], 32),             # 70B @ TP=8 (G=8), long context, 32-block minimum share
+        (6, 4, 4, 128, [128] * 6, 1),                 # MHA (G=1), 1-block shares (every block its own partial)
+        (64, 32, 8, 128, [2048 + 7 * i for i in range(64)], 0),  # cfg2/cfg3 batch: shares cut (sequence, head) pairs mid-way
+        (7, 8, 2, 64, [0, 33, 0, 0, 1000, 64, 0], 3),  # empty sequences inside and at both ends of the batch
     ],
 )
-def test_decode_matches_oracle(ops, b, hq, hkv, d, ctxs, chunk):
+def test_decode_matches_oracle(ops, b, hq, hkv, d, ctxs, quota):
     g = torch.Generator().manual_seed(13)
     bs = 32
     max_blocks = max(-(-c // bs) for c in ctxs)
@@ -56,7 +58,7 @@ def test_decode_matches_oracle(ops, b, hq, hkv, d, ctxs, chunk):
     want = attn_ref.paged_attention_decode_ref(q, kp, vp, bt, ctx, scale)
     got = ops.paged_attn_decode(
         q.cuda(), logical_to_device_pool(kp).cuda(), logical_to_device_pool(vp).cuda(), bt.cuda(), ctx.cuda(), scale,
-        chunk_blocks=chunk,
+        min_quota=quota,
     )
     torch.cuda.synchronize()
     _check(got.cpu(), want)
@@ -81,6 +83,47 @@ def test_decode_row_ids_and_strided_q(ops):
     got = ops.paged_attn_decode(qd, logical_to_device_pool(kp).cuda(), logical_to_device_pool(vp).cuda(), bt.cuda(),
                                 ctx.cuda(), 0.1, row_ids=rows.cuda())
     _check(got.cpu(), want)
+
+
+@pytest.mark.parametrize("kind", ["fp8", "int8"])
+def test_decode_fused_per_token_quantisation_is_bit_exact(ops, kind):
+    """The merge kernel's quantised output == the oracle's per-token quantiser applied to the kernel's own bf16 output."""
+    from oracle import quant_ref
+
+    g = torch.Generator().manual_seed(29)
+    b, hq, hkv, d, bs = 9, 32, 8, 128, 32
+    ctxs = [700, 1, 64, 2048, 333, 0, 95, 1500, 32]
+    nb = sum(-(-c // bs) for c in ctxs) + 2
+    kp, vp = _pools(nb, bs, hkv, d, g)
+    bt = make_block_tables(b, ctxs, bs, nb, 64, g).cuda()
+    q = torch.randn(b, hq, d, generator=g).bfloat16().cuda()
+    ctx = torch.tensor(ctxs, dtype=torch.int32).cuda()
+    kd, vd = logical_to_device_pool(kp).cuda(), logical_to_device_pool(vp).cuda()
+    y = ops.paged_attn_decode(q, kd, vd, bt, ctx, 0.09)
+    yq, ys = ops.paged_attn_decode(q, kd, vd, bt, ctx, 0.09, quant=kind)
+    qw, sw = quant_ref.quantize_act_per_token(y.cpu().reshape(b, hq * d), kind)
+    assert torch.equal(ys.cpu(), sw)
+    assert torch.equal(yq.cpu().view(torch.uint8), qw.view(torch.uint8))
+
+
+def test_decode_is_deterministic_and_pdl_invariant(ops):
+    """Same bits with programmatic dependent launch on and off (the partition does not depend on timing)."""
+    g = torch.Generator().manual_seed(31)
+    b, hq, hkv, d, bs = 16, 32, 8, 128, 32
+    ctxs = [100 * (i + 1) for i in range(b)]
+    nb = sum(-(-c // bs) for c in ctxs) + 2
+    kp, vp = _pools(nb, bs, hkv, d, g)
+    bt = make_block_tables(b, ctxs, bs, nb, 50, g).cuda()
+    q = torch.randn(b, hq, d, generator=g).bfloat16().cuda()
+    ctx = torch.tensor(ctxs, dtype=torch.int32).cuda()
+    kd, vd = logical_to_device_pool(kp).cuda(), logical_to_device_pool(vp).cuda()
+    a = ops.paged_attn_decode(q, kd, vd, bt, ctx, 0.09)
+    old = ops.set_pdl(False)
+    try:
+        c = ops.paged_attn_decode(q, kd, vd, bt, ctx, 0.09)
+    finally:
+        ops.set_pdl(old)
+    assert torch.equal(a, c)
 
 
 def test_decode_zero_context_row_is_zero(ops):

@@ -31,12 +31,14 @@ def _assert_close(got, want, exact_int=False):
     assert not bad.any(), f"{bad.sum().item()} / {bad.numel()} outside tolerance; max err {(got - want).abs().max().item()} rms {rms}"
 
 
+# last column = max_ctas of the persistent stream-K schedule (0 = one CTA per SM)
 SHAPES = [
     (64, 6144, 4096, 0),     # cfg3 qkv
-    (64, 4096, 4096, 0),     # o_proj (auto split-K)
-    (64, 4096, 14336, 0),    # down_proj (auto split-K, long K)
-    (64, 1024, 512, 1),      # no split
-    (64, 1024, 512, 4),      # explicit split, 1 k-block each (fp8)
+    (64, 4096, 4096, 0),     # o_proj (32 tiles cut over 148 CTAs)
+    (64, 4096, 14336, 0),    # down_proj (long K)
+    (64, 1024, 512, 1),      # one CTA walks every tile: no fix-up
+    (64, 1024, 512, 5),      # 8 tiles x 4 k-blocks over 5 CTAs: spans start and end mid-tile
+    (64, 1024, 512, 32),     # one k-block per CTA: every tile has 4 contributors
     (4, 2048, 2048, 0),      # TinyLlama decode batch
     (1, 256, 128, 0),        # single row, single k-block
     (128, 640, 1152, 0),     # Qwen TP=8 o-proj-like, M=128
@@ -45,9 +47,9 @@ SHAPES = [
 ]
 
 
-@pytest.mark.parametrize("m,n,k,split", SHAPES)
+@pytest.mark.parametrize("m,n,k,ctas", SHAPES)
 @pytest.mark.parametrize("kind", ["fp8", "int8"])
-def test_w8a8_gemm(ops, m, n, k, split, kind):
+def test_w8a8_gemm(ops, m, n, k, ctas, kind):
     g = torch.Generator().manual_seed(m * 7 + n + k)
     x = torch.randn(m, k, generator=g).bfloat16()
     w = (torch.randn(n, k, generator=g) * 0.02).bfloat16()
@@ -57,18 +59,18 @@ def test_w8a8_gemm(ops, m, n, k, split, kind):
     res = torch.randn(m, n, generator=g).bfloat16() if k % 1024 == 0 else None
     want = quant_ref.qgemm_ref(xq, xs, wq, ws, bias, res)
     got = ops.gemm(xq.cuda(), wq.cuda(), xs.cuda(), ws.cuda(), None if bias is None else bias.cuda(),
-                   None if res is None else res.cuda(), split_k=split)
+                   None if res is None else res.cuda(), max_ctas=ctas)
     torch.cuda.synchronize()
     _assert_close(got, want, exact_int=(kind == "int8"))
 
 
-@pytest.mark.parametrize("m,n,k,split", SHAPES[:4] + SHAPES[5:8])
-def test_bf16_gemm(ops, m, n, k, split):
+@pytest.mark.parametrize("m,n,k,ctas", SHAPES[:5] + SHAPES[6:9])
+def test_bf16_gemm(ops, m, n, k, ctas):
     g = torch.Generator().manual_seed(m + n + k)
     x = torch.randn(m, k, generator=g).bfloat16()
     w = (torch.randn(n, k, generator=g) * 0.02).bfloat16()
     want = quant_ref.gemm_ref(x, w)
-    got = ops.gemm(x.cuda(), w.cuda(), split_k=split)
+    got = ops.gemm(x.cuda(), w.cuda(), max_ctas=ctas)
     torch.cuda.synchronize()
     _assert_close(got, want)
 
@@ -89,10 +91,62 @@ def test_fp32_out_and_linearity(ops):
     assert torch.equal(o1[:8].cpu(), want)
 
 
-def test_gemm_split_k_is_deterministic(ops):
+def test_gemm_stream_k_is_deterministic_and_leaves_workspace_clean(ops):
+    """Fix-up sums run in fixed contributor order -> same bits every launch, with PDL on or off; the counters at the head
+    of a shared workspace are zero again after every call (that is what lets one workspace serve a whole step)."""
     g = torch.Generator().manual_seed(2)
     x = torch.randn(64, 4096, generator=g).bfloat16().cuda()
     w = torch.randn(4096, 4096, generator=g).bfloat16().cuda()
-    a = ops.gemm(x, w, split_k=4)
-    b = ops.gemm(x, w, split_k=4)
-    assert torch.equal(a, b)
+    ws = ops.gemm_workspace(64, 4096, 4096, 0, x.device)
+    a = ops.gemm(x, w, workspace=ws)
+    assert int(ws[:4096].view(torch.int32).abs().sum()) == 0
+    b = ops.gemm(x, w, workspace=ws)
+    old = ops.set_pdl(False)
+    try:
+        c = ops.gemm(x, w, workspace=ws)
+    finally:
+        ops.set_pdl(old)
+    assert torch.equal(a, b) and torch.equal(a, c)
+    assert int(ws[:4096].view(torch.int32).abs().sum()) == 0
+
+
+@pytest.mark.parametrize("kind", ["bf16", "fp8", "int8"])
+@pytest.mark.parametrize("m,i,k,ctas", [(64, 14336, 4096, 0), (4, 5632, 2048, 0), (100, 96, 256, 3), (300, 1792, 512, 0)])
+def test_gemm_silu_mul_matches_unfused(ops, kind, m, i, k, ctas):
+    """gate/up GEMM with SiLU*mul in the epilogue == b200_gemm (on the same interleaved rows) followed by b200_silu_mul,
+    bit for bit (same tiles, same stream-K cuts, fixed fix-up order), and within the GEMM tolerance of the oracle.  The per-tile
+    maxima it emits give exactly the per-token scale of the oracle's quantiser."""
+    from oracle import kv_ref
+
+    g = torch.Generator().manual_seed(m + i + k)
+    x = torch.randn(m, k, generator=g).bfloat16()
+    w = (torch.randn(2 * i, k, generator=g) * 0.03).bfloat16()
+    if kind == "bf16":
+        xq, xs, wq, ws = x, None, w, None
+        want_gu = quant_ref.gemm_ref(x, w)
+    else:
+        xq, xs = quant_ref.quantize_act_per_token(x, kind)
+        wq, ws = quant_ref.quantize_weight_per_channel(w, kind)
+        want_gu = quant_ref.qgemm_ref(xq, xs, wq, ws)
+    want = kv_ref.silu_mul_ref(want_gu)
+    dev = lambda t: None if t is None else t.cuda()  # noqa: E731
+    wi, si = ops.interleave_gate_up(dev(wq), dev(ws))
+    # unfused twin on the SAME row order (same tiles, same stream-K cuts), de-interleaved before SiLU*mul
+    gu_i = ops.gemm(dev(xq), wi, dev(xs), si, max_ctas=ctas)
+    idx = torch.arange(i).view(-1, 16)
+    perm = torch.cat([idx, idx + i], dim=1).reshape(-1).cuda()
+    gu = torch.empty_like(gu_i)
+    gu[:, perm] = gu_i
+    unfused = ops.silu_mul(gu)
+    act, tile_amax = ops.gemm_silu_mul(dev(xq), wi, dev(xs), si, max_ctas=ctas)
+    torch.cuda.synchronize()
+    assert torch.equal(act, unfused)
+    got, wantf = act.float().cpu(), want.float()
+    rms = wantf.pow(2).mean().sqrt().item()
+    assert ((got - wantf).abs() <= 2e-2 * rms + wantf.abs() * 2.0**-6 + 1e-6).all()
+    assert torch.equal(tile_amax.max(dim=0).values.cpu(), act.float().abs().max(dim=1).values.cpu())
+    for qk in ("fp8", "int8"):
+        q1, s1 = ops.quantize_per_token(act, qk, tile_amax=tile_amax)
+        qw, sw = quant_ref.quantize_act_per_token(act.cpu(), qk)
+        assert torch.equal(s1.cpu(), sw)
+        assert torch.equal(q1.cpu().view(torch.uint8), qw.view(torch.uint8))

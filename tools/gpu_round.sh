@@ -1,6 +1,6 @@
 #!/bin/bash
 # One gpurun call: GPU parity tests, smoke, the headline bench, then (only if the bench exited 0) the ncu launch list.
-# usage: tools/gpu_round.sh [tests] [bench] [launches] [ncufull]
+# usage: tools/gpu_round.sh [tests] [micro] [bench] [launches] [ncufull]
 mkdir -p gpurun_out
 : > gpurun_out/summary.txt
 want() { [[ " $* " == *" $1 "* ]] ; }
@@ -9,11 +9,16 @@ if [[ "$ARGS" == *" tests "* ]]; then
   for f in test_gpu_kv test_gpu_glue test_gpu_attn test_gpu_gemm test_gpu_model; do
     timeout 600 python -m pytest tests/$f.py -q -m gpu --timeout 300 -s > gpurun_out/$f.log 2>&1
     echo "$f exit=$?" | tee -a gpurun_out/summary.txt
-    tail -4 gpurun_out/$f.log
+    tail -15 gpurun_out/$f.log
   done
   timeout 300 python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1
   echo "smoke exit=$?" | tee -a gpurun_out/summary.txt
   tail -2 gpurun_out/smoke.log
+fi
+if [[ "$ARGS" == *" micro "* ]]; then
+  timeout 600 python tools/microbench.py ${MICRO_WHAT:-all} --json gpurun_out/microbench.json > gpurun_out/microbench.log 2>&1
+  echo "micro exit=$?" | tee -a gpurun_out/summary.txt
+  tail -30 gpurun_out/microbench.log
 fi
 BENCH="python bench.py --steps ${BENCH_STEPS:-64} --warmup 5 ${BENCH_EXTRA}"
 if [[ "$ARGS" == *" bench "* ]]; then

@@ -39,7 +39,7 @@ def time_calls(fns, iters=3, warmup=1):
     return e0.elapsed_time(e1) / (iters * len(fns))
 
 
-def bench_attn(b=64, hq=32, hkv=8, d=128, ctx=2048, layers=8, chunks=(0, 4, 8, 16, 32)):
+def bench_attn(b=64, hq=32, hkv=8, d=128, ctx=2048, layers=8, quotas=(0, 8, 16)):
     bs = 32
     nblk = ctx // bs
     nb = b * nblk + 1
@@ -57,21 +57,22 @@ def bench_attn(b=64, hq=32, hkv=8, d=128, ctx=2048, layers=8, chunks=(0, 4, 8, 1
     ws = torch.empty(ops.paged_attn_decode_workspace_bytes(b, hq, hkv, d, nblk, 0), dtype=torch.uint8, device="cuda")
     alg = b * ctx * 2 * hkv * d * 2 + 2 * b * hq * d * 2 + b * nblk * 4
     res = []
-    for cb in chunks:
+    for cb in quotas:
         fns = [
-            (lambda kp=kp, vp=vp: ops.paged_attn_decode(q, kp, vp, bt, ctxl, d**-0.5, out=out, workspace=ws, chunk_blocks=cb))
+            (lambda kp=kp, vp=vp: ops.paged_attn_decode(q, kp, vp, bt, ctxl, d**-0.5, out=out, workspace=ws, min_quota=cb))
             for kp, vp in pools
         ]
         ms = time_calls(fns)
         gbs = alg / ms / 1e6
-        res.append({"kernel": "paged_attn_decode", "B": b, "Hq": hq, "Hkv": hkv, "D": d, "ctx": ctx, "chunk_blocks": cb,
+        res.append({"kernel": "paged_attn_decode", "B": b, "Hq": hq, "Hkv": hkv, "D": d, "ctx": ctx, "min_quota": cb,
                     "ms": ms, "GBps": gbs, "frac_hbm": gbs / HBM})
         print(res[-1], flush=True)
     return res
 
 
-def bench_gemm(shapes=None, kinds=("fp8", "bf16")):
+def bench_gemm(shapes=None, kinds=("fp8", "bf16"), pdl=True):
     shapes = shapes or [(64, 6144, 4096), (64, 4096, 4096), (64, 28672, 4096), (64, 4096, 14336), (64, 128256, 4096)]
+    ops.set_pdl(pdl)
     res = []
     for kind in kinds:
         for m, n, k in shapes:
@@ -88,12 +89,12 @@ def bench_gemm(shapes=None, kinds=("fp8", "bf16")):
                 sw = torch.ones(n, device="cuda")
             out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
             nbytes = ops.gemm_workspace_bytes(m, n, k, 0 if kind == "bf16" else 1, 0)
-            wsp = torch.empty(max(nbytes, 16), dtype=torch.uint8, device="cuda")
+            wsp = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device="cuda")  # stream-K counters start at zero
             fns = [(lambda w=w: ops.gemm(a, w, sa, sw, out=out, workspace=wsp)) for w in ws_]
             ms = time_calls(fns, iters=5)
             alg = n * k * eb + n * 4 + m * k * eb + m * 4 + 2 * m * n
             gbs = alg / ms / 1e6
-            res.append({"kernel": f"gemm_{kind}", "M": m, "N": n, "K": k, "ms": ms, "GBps": gbs, "frac_hbm": gbs / HBM,
+            res.append({"kernel": f"gemm_{kind}", "pdl": pdl, "M": m, "N": n, "K": k, "ms": ms, "GBps": gbs, "frac_hbm": gbs / HBM,
                         "TFLOPs": 2 * m * n * k / ms / 1e9})
             print(res[-1], flush=True)
             del ws_
@@ -111,5 +112,7 @@ if __name__ == "__main__":
         out += bench_attn()
     if a.what in ("gemm", "all"):
         out += bench_gemm()
+        out += bench_gemm(kinds=("fp8",), pdl=False)
+        ops.set_pdl(True)
     if a.json:
         json.dump(out, open(a.json, "w"), indent=1)

@@ -12,6 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200_paged.so")
 
 OK = 0
+ABI_VERSION = 2
 BF16, FP8_E4M3, INT8, F32 = 0, 1, 2, 3
 
 _p = C.c_void_p
@@ -26,6 +27,7 @@ SIGNATURES = {
     "b200_last_error": (C.c_char_p, []),
     "b200_device_check": (_i, [_i]),
     "b200_launch_count": (C.c_uint64, []),
+    "b200_set_pdl": (_i, [_i]),
     "b200_build_decode_meta": (_i, [_p, _i64, _p, _p, _p, _p, _p, _i, _i, _i, _p]),
     "b200_build_prefill_meta": (_i, [_p, _i, _i, _p, _p, _i, _i, _p]),
     "b200_block_table_scatter": (_i, [_p, _i64, _p, _i, _i, _i, _p]),
@@ -35,14 +37,15 @@ SIGNATURES = {
     "b200_paged_attn_decode_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
     "b200_paged_attn_decode": (
         _i,
-        [_p, _i64, _p, _p, _i, _p, _i64, _p, _p, _p, _p, _sz, _i, _i, _i, _i, _i, _i, _i, _f, _p],
+        [_p, _i64, _p, _p, _i, _p, _i64, _p, _p, _p, _p, _p, _i, _p, _sz, _i, _i, _i, _i, _i, _i, _i, _f, _p],
     ),
     "b200_paged_attn_prefill": (_i, [_p, _i64, _p, _p, _i, _p, _p, _i, _i, _i, _i, _i, _i, _f, _p]),
     "b200_gemm_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "b200_gemm": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _sz, _p]),
+    "b200_gemm_silu_mul": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _sz, _p]),
     "b200_rmsnorm": (_i, [_p, _p, _p, _p, _p, _i, _i, _f, _i, _p]),
     "b200_silu_mul": (_i, [_p, _p, _p, _p, _i, _i, _i, _p]),
-    "b200_quantize_per_token": (_i, [_p, _p, _p, _i, _i, _i, _p]),
+    "b200_quantize_per_token": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _p]),
     "b200_embedding": (_i, [_p, _p, _p, _i, _i, _i, _p]),
     "b200_argmax": (_i, [_p, _i64, _p, _p, _i, _i, _i64, _p]),
 }
@@ -69,8 +72,8 @@ def load():
         fn = getattr(lib, name)  # AttributeError if the header and the library disagree
         fn.restype = res
         fn.argtypes = args
-    if lib.b200_abi_version() != 1:
-        raise B200Error(f"ABI version mismatch: library {lib.b200_abi_version()} != binding 1")
+    if lib.b200_abi_version() != ABI_VERSION:
+        raise B200Error(f"ABI version mismatch: library {lib.b200_abi_version()} != binding {ABI_VERSION}")
     _lib = lib
     return lib
 

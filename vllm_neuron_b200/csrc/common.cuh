@@ -35,6 +35,28 @@ int make_tmap_2d(CUtensorMap* out, const void* base, CUtensorMapDataType dt, uin
                  uint64_t rows, uint64_t row_pitch_bytes, uint32_t box_cols, uint32_t box_rows);
 int sm_count();
 void count_launch(int n = 1);
+bool pdl_enabled();
+
+// Launch with the programmatic-dependent-launch attribute (when enabled): the grid may become resident while its
+// predecessor on the stream is still draining; every kernel of this library therefore executes griddep_wait() before
+// it touches memory another kernel of the step may have written (and before it writes anything global).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                 Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+  if (e == cudaSuccess) count_launch(1);
+  return e;
+}
 
 // ---------------------------------------------------------------- device helpers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -46,6 +68,14 @@ __device__ __forceinline__ bool elect_one() {
       "{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}\n"
       : "=r"(pred));
   return pred != 0;
+}
+
+// ---- programmatic dependent launch (PDL)
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;\n" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory"); }
+// sub-CTA barrier (id 1..15) over `nthreads` threads
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 // ---- mbarrier
@@ -205,6 +235,18 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&t);
+}
+// one element of the dynamic per-token quantisation: q = rn(y / scale), e4m3 saturating or int8 round-half-even clamp 127
+template <int QD>
+__device__ __forceinline__ uint8_t quant_byte(float y, float scale) {
+  float q = __fdiv_rn(y, scale);
+  if constexpr (QD == B200_FP8_E4M3) {
+    return (uint8_t)__nv_cvt_float_to_fp8(q, __NV_SATFINITE, __NV_E4M3);
+  } else {
+    float r = rintf(q);
+    r = fminf(fmaxf(r, -127.f), 127.f);
+    return (uint8_t)(int8_t)(int)r;
+  }
 }
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll

@@ -2,21 +2,29 @@
 //
 //   out[m][n] = (sum_k a[m][k] w[n][k]) * a_scale[m] * w_scale[n] + bias[n] + residual[m][n]
 //
-// Decode has M = batch (<= 128) and is bound by streaming W from HBM, so the tile is "swap-AB": the 128 weight rows of
-// a tile fill the UMMA M slot, the (few) activation rows are the UMMA N.  Operands are staged by TMA
-// (cp.async.bulk.tensor, 128B swizzle) in a ring of stages; one thread issues tcgen05.mma (kind::f8f6f4 / kind::f16 /
-// kind::i8) into a TMEM accumulator; four epilogue warps read it back with tcgen05.ld, apply the per-token and
-// per-channel scales and write bf16/fp32.  When N/128 tiles cannot fill the SMs the K loop is split and fp32
-// partials are reduced by a second (deterministic, fixed-order) kernel.
+// Decode has M = batch (<= 128) and is bound by streaming W from HBM exactly once, so:
+//  * "swap-AB" tile: the 128 weight rows of a tile fill the UMMA M slot, the (few) activation rows are the UMMA N.
+//  * persistent stream-K schedule: one CTA per SM; the flattened (tile, k-block) space is cut into gridDim.x equal
+//    contiguous spans, so every SM streams the same number of weight bytes whatever N/128 is (32 .. 1002 tiles here).
+//    A tile cut by a span boundary is finished by whichever contributor arrives last: all contributors park their
+//    fp32 partial in the workspace, the last one sums them in FIXED contributor order (bit-reproducible) and runs
+//    the epilogue.  No second kernel, no spinning on other CTAs.
+//  * programmatic dependent launch: the grid becomes resident while the previous kernel drains and the TMA producer
+//    fills the whole smem ring with WEIGHT tiles (which no kernel of the step writes) before griddepcontrol.wait;
+//    activations are only touched after the wait.
+// Operands are staged by TMA (cp.async.bulk.tensor, 128B swizzle) in a ring of stages; one thread issues tcgen05.mma
+// (kind::f8f6f4 / kind::f16 / kind::i8) into a double-buffered TMEM accumulator; four epilogue warps read it back with
+// tcgen05.ld, apply the per-token and per-channel scales and write bf16/fp32.
 //
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2-5 = epilogue.
 #include "common.cuh"
 
 namespace b200 {
 
-constexpr int GEMM_BN = 128;      // weight rows per tile  (UMMA M)
+constexpr int GEMM_BN = 128;        // weight rows per tile  (UMMA M)
 constexpr int GEMM_BK_BYTES = 128;  // one 128B swizzle row of K per stage
 constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_CNT_INTS = 1024;  // fix-up counters at the head of the workspace (one per possible first contributor)
 
 template <int KIND>
 struct KindTraits;
@@ -33,6 +41,8 @@ struct KindTraits<KIND_I8> {
   static constexpr int ELEM = 1, CFMT = 2, ABFMT = 1;  // s8 in, s32 accumulate
 };
 
+enum { EPI_LINEAR = 0, EPI_SILU_MUL = 1 };
+
 struct GemmEpilogue {
   const float* a_scale;
   const float* w_scale;
@@ -40,44 +50,97 @@ struct GemmEpilogue {
   const __nv_bfloat16* residual;
   void* out;
   int out_f32;
+  float* tile_amax;  // EPI_SILU_MUL: [n_tiles][M] per-tile max |act| (for the per-token quantisation that follows)
 };
 
-__device__ __forceinline__ void store_out(const GemmEpilogue& ep, float acc, int m, int n, int N) {
+__device__ __forceinline__ float linear_value(const GemmEpilogue& ep, float acc, int m, int n, int N) {
   float y = acc;
   if (ep.a_scale) y *= ep.a_scale[m];
   if (ep.w_scale) y *= ep.w_scale[n];
   if (ep.bias) y += __bfloat162float(ep.bias[n]);
   if (ep.residual) y += __bfloat162float(ep.residual[(int64_t)m * N + n]);
+  return y;
+}
+__device__ __forceinline__ void store_out(const GemmEpilogue& ep, float acc, int m, int n, int N) {
+  float y = linear_value(ep, acc, m, n, N);
   if (ep.out_f32)
     reinterpret_cast<float*>(ep.out)[(int64_t)m * N + n] = y;
   else
     reinterpret_cast<__nv_bfloat16*>(ep.out)[(int64_t)m * N + n] = __float2bfloat16_rn(y);
 }
 
-template <int KIND, int BM, int NSTAGES>
-__global__ void __launch_bounds__(GEMM_THREADS)
-    gemm_tn_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap a_map, GemmEpilogue ep,
-                   float* __restrict__ partial, int M, int N, int num_kb, int kb_per_split) {
+// span of CTA c: units [U*c/P, U*(c+1)/P); owner(x) = the CTA whose span holds unit x
+__device__ __forceinline__ long long span_begin(long long U, int P, int c) { return U * c / P; }
+__device__ __forceinline__ int span_owner(long long U, int P, long long x) { return (int)(((x + 1) * P - 1) / U); }
+
+// Epilogue of one 16-token column chunk held in v[] by the lane that owns weight row n (EPI_LINEAR), or by the lane pair
+// (l, l^16) that owns the gate and the up row of one channel (EPI_SILU_MUL; W rows interleaved 16 gate / 16 up per warp).
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, const float (&v)[16], int m_base, int M, int n,
+                                               bool n_ok, int N, int lane, float (&amax)[8]) {
+  if constexpr (EPI == EPI_LINEAR) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int m = m_base + j;
+      if (m < M && n_ok) store_out(ep, v[j], m, n, N);
+    }
+  } else {
+    // this lane's row: gate (lane < 16) or up (lane >= 16) of channel ch; both rounded to bf16 like the unfused path
+    const int I = N >> 1;
+    const int ch = (n >> 5) * 16 + (lane & 15);
+    float mine[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int m = m_base + j;
+      float y = 0.f;
+      if (m < M && n_ok) y = __bfloat162float(__float2bfloat16_rn(linear_value(ep, v[j], m, n, N)));
+      mine[j] = y;
+    }
+    // lanes < 16 finish tokens 0..7 of the chunk, lanes >= 16 finish tokens 8..15
+    const bool hi = lane >= 16;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float send = hi ? mine[j] : mine[j + 8];        // what the partner needs from me
+      const float got = __shfl_xor_sync(0xffffffffu, send, 16);
+      const float g = hi ? got : mine[j];
+      const float u = hi ? mine[j + 8] : got;
+      const int m = m_base + (hi ? 8 : 0) + j;
+      const float sg = __fdiv_rn(1.f, 1.f + expf(-g));
+      const float a = __bfloat162float(__float2bfloat16_rn(g * sg * u));
+      if (m < M && n_ok) reinterpret_cast<__nv_bfloat16*>(ep.out)[(int64_t)m * I + ch] = __float2bfloat16_rn(a);
+      amax[j] = (m < M && n_ok) ? fabsf(a) : 0.f;  // token (hi ? 8 : 0) + j of the chunk
+    }
+  }
+}
+
+template <int KIND, int BM, int NSTAGES, int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+    gemm_streamk_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap a_map,
+                        GemmEpilogue ep, float* __restrict__ partials, int* __restrict__ counters, int M, int N, int m_tiles,
+                        int num_kb, int tiles, int w_stream_once) {
   using T = KindTraits<KIND>;
   constexpr int BK_ELEMS = GEMM_BK_BYTES / T::ELEM;
   constexpr int W_TILE = GEMM_BN * GEMM_BK_BYTES;
   constexpr int A_TILE = BM * GEMM_BK_BYTES;
   constexpr int STAGE = W_TILE + A_TILE;
-  constexpr uint32_t TMEM_COLS = BM < 32 ? 32 : BM;
+  constexpr uint32_t TMEM_COLS = 2 * BM < 32 ? 32 : 2 * BM;  // two accumulator stages
   constexpr uint32_t IDESC = umma_idesc(T::CFMT, T::ABFMT, GEMM_BN, BM);
+  static_assert(2 * BM <= 512 && (TMEM_COLS & (TMEM_COLS - 1)) == 0, "TMEM columns");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)NSTAGES * STAGE);
   uint64_t* empty = full + NSTAGES;
-  uint64_t* tmem_full = empty + NSTAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* tfull = empty + NSTAGES;   // [2] accumulator stage ready for the epilogue
+  uint64_t* tempty = tfull + 2;        // [2] accumulator stage drained
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  int* fix_flag = reinterpret_cast<int*>(tmem_slot + 1);
+  float* amax_sh = reinterpret_cast<float*>(fix_flag + 1);  // [4 warps][16] (EPI_SILU_MUL)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * GEMM_BN, m0 = blockIdx.y * BM;
-  const int kb0 = blockIdx.z * kb_per_split;
-  int nkb = num_kb - kb0;
-  if (nkb > kb_per_split) nkb = kb_per_split;
+  const int P = gridDim.x, c = blockIdx.x;
+  const long long U = (long long)tiles * num_kb;
+  const long long u0 = span_begin(U, P, c), u1 = span_begin(U, P, c + 1);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&w_map);
@@ -87,7 +150,10 @@ __global__ void __launch_bounds__(GEMM_THREADS)
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    mbar_init(tmem_full, 1);
+    mbar_init(&tfull[0], 1);
+    mbar_init(&tfull[1], 1);
+    mbar_init(&tempty[0], 4);
+    mbar_init(&tempty[1], 4);
     fence_mbar_init();
     fence_proxy_async();
   }
@@ -98,76 +164,177 @@ __global__ void __launch_bounds__(GEMM_THREADS)
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  griddep_launch();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      const uint64_t pol_w = policy_evict_first();  // weights are streamed once per step
-      const uint64_t pol_a = policy_evict_last();   // activations are re-read by every n-tile
-      for (int i = 0; i < nkb; ++i) {
+    if (lane == 0 && u1 > u0) {
+      const uint64_t pol_w = w_stream_once ? policy_evict_first() : policy_evict_last();
+      const uint64_t pol_a = policy_evict_last();  // activations are re-read by every CTA
+      const int total = (int)(u1 - u0);
+      const int npre = total < NSTAGES ? total : NSTAGES;
+      // weights do not depend on any kernel of the step: fill the ring with W tiles before the dependency resolves
+      for (int i = 0; i < npre; ++i) {
+        const long long u = u0 + i;
+        const int tile = (int)(u / num_kb), kb = (int)(u % num_kb);
+        mbar_expect_tx(&full[i], STAGE);
+        tma_load_2d_hint(smem + (size_t)i * STAGE, &w_map, &full[i], kb * BK_ELEMS, (tile / m_tiles) * GEMM_BN, pol_w);
+      }
+      griddep_wait();
+      for (int i = 0; i < npre; ++i) {
+        const long long u = u0 + i;
+        const int tile = (int)(u / num_kb), kb = (int)(u % num_kb);
+        tma_load_2d_hint(smem + (size_t)i * STAGE + W_TILE, &a_map, &full[i], kb * BK_ELEMS, (tile % m_tiles) * BM, pol_a);
+      }
+      for (int i = npre; i < total; ++i) {
         const int s = i % NSTAGES;
-        if (i >= NSTAGES) mbar_wait(&empty[s], ((i / NSTAGES) - 1) & 1);
+        const long long u = u0 + i;
+        const int tile = (int)(u / num_kb), kb = (int)(u % num_kb);
+        mbar_wait(&empty[s], ((i / NSTAGES) - 1) & 1);
         uint8_t* ws = smem + (size_t)s * STAGE;
         mbar_expect_tx(&full[s], STAGE);
-        tma_load_2d_hint(ws, &w_map, &full[s], (kb0 + i) * BK_ELEMS, n0, pol_w);
-        tma_load_2d_hint(ws + W_TILE, &a_map, &full[s], (kb0 + i) * BK_ELEMS, m0, pol_a);
+        tma_load_2d_hint(ws, &w_map, &full[s], kb * BK_ELEMS, (tile / m_tiles) * GEMM_BN, pol_w);
+        tma_load_2d_hint(ws + W_TILE, &a_map, &full[s], kb * BK_ELEMS, (tile % m_tiles) * BM, pol_a);
       }
     }
   } else if (warp == 1) {
-    for (int i = 0; i < nkb; ++i) {
-      const int s = i % NSTAGES;
-      mbar_wait(&full[s], (i / NSTAGES) & 1);
+    int i = 0, seg = 0;
+    for (long long u = u0; u < u1; ++seg) {
+      const int kb0 = (int)(u % num_kb);
+      const long long left = u1 - u;
+      const int nk = left < (long long)(num_kb - kb0) ? (int)left : num_kb - kb0;
+      const int as = seg & 1;
+      if (seg >= 2) mbar_wait(&tempty[as], ((seg >> 1) - 1) & 1);
       tc_fence_after();
-      if (lane == 0) {
-        const uint32_t wa = smem_u32(smem + (size_t)s * STAGE);
-        const uint32_t aa = wa + W_TILE;
+      const uint32_t acc = tmem_base + (uint32_t)(as * BM);
+      for (int k = 0; k < nk; ++k, ++i) {
+        const int s = i % NSTAGES;
+        mbar_wait(&full[s], (i / NSTAGES) & 1);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t wa = smem_u32(smem + (size_t)s * STAGE);
+          const uint32_t aa = wa + W_TILE;
 #pragma unroll
-        for (int k = 0; k < GEMM_BK_BYTES / 32; ++k)  // UMMA_K = 32 bytes of K
-          umma_ss<KIND>(tmem_base, umma_desc_sw128(wa + k * 32), umma_desc_sw128(aa + k * 32), IDESC, (uint32_t)((i | k) != 0));
-        tc_commit(&empty[s]);  // smem slot is free once these MMAs retire
+          for (int kk = 0; kk < GEMM_BK_BYTES / 32; ++kk)  // UMMA_K = 32 bytes of K
+            umma_ss<KIND>(acc, umma_desc_sw128(wa + kk * 32), umma_desc_sw128(aa + kk * 32), IDESC, (uint32_t)((k | kk) != 0));
+          tc_commit(&empty[s]);  // smem slot is free once these MMAs retire
+        }
+        __syncwarp();
       }
+      if (lane == 0) tc_commit(&tfull[as]);
       __syncwarp();
+      u += nk;
     }
-    if (lane == 0) tc_commit(tmem_full);
-    __syncwarp();
   } else {
     // epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31; lane = weight row of the tile
-    mbar_wait(tmem_full, 0);
-    tc_fence_after();
     const int lg = warp & 3;
-    const int n = n0 + lg * 32 + lane;
-    const bool n_ok = n < N;
+    const int et = threadIdx.x - 64;  // 0..127
+    griddep_wait();
+    int seg = 0;
+    for (long long u = u0; u < u1; ++seg) {
+      const int tile = (int)(u / num_kb), kb0 = (int)(u % num_kb);
+      const long long left = u1 - u;
+      const int nk = left < (long long)(num_kb - kb0) ? (int)left : num_kb - kb0;
+      const bool complete = kb0 == 0 && nk == num_kb;
+      const int as = seg & 1;
+      const int n_tile = tile / m_tiles, m0 = (tile % m_tiles) * BM;
+      const int nl = lg * 32 + lane;
+      const int n = n_tile * GEMM_BN + nl;
+      const bool n_ok = n < N;
+      mbar_wait(&tfull[as], (seg >> 1) & 1);
+      tc_fence_after();
+      const uint32_t acc = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(as * BM);
+      float* slot = partials + ((size_t)c * 2 + (seg == 0 ? 0 : 1)) * (size_t)(BM * GEMM_BN);
 #pragma unroll 1
-    for (int c = 0; c < BM / 16; ++c) {
-      uint32_t v[16];
-      tmem_ld_32x32b_x16(tmem_base + ((uint32_t)(lg * 32) << 16) + c * 16, v);
-      tmem_ld_wait();
+      for (int cc = 0; cc < BM / 16; ++cc) {
+        uint32_t v[16];
+        tmem_ld_32x32b_x16(acc + cc * 16, v);
+        tmem_ld_wait();
+        float f[16];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const int m = m0 + c * 16 + j;
-        if (m < M && n_ok) {
-          float acc = KIND == KIND_I8 ? (float)(int32_t)v[j] : __uint_as_float(v[j]);
-          if (partial)
-            partial[((int64_t)blockIdx.z * M + m) * N + n] = acc;
-          else
-            store_out(ep, acc, m, n, N);
+        for (int j = 0; j < 16; ++j) f[j] = KIND == KIND_I8 ? (float)(int32_t)v[j] : __uint_as_float(v[j]);
+        if (complete) {
+          float am[8];
+          epilogue_chunk<EPI>(ep, f, m0 + cc * 16, M, n, n_ok, N, lane, am);
+          if constexpr (EPI == EPI_SILU_MUL) {
+            // per-token max over the 64 channels of this tile: 16 lanes of a half-warp, then 4 warps via smem
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float x = am[j];
+#pragma unroll
+              for (int o = 1; o < 16; o <<= 1) x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, o));
+              if ((lane & 15) == 0) amax_sh[lg * 16 + (lane >= 16 ? 8 : 0) + j] = x;
+            }
+            named_bar_sync(1, 128);
+            if (et < 16) {
+              const int m = m0 + cc * 16 + et;
+              const float x = fmaxf(fmaxf(amax_sh[et], amax_sh[16 + et]), fmaxf(amax_sh[32 + et], amax_sh[48 + et]));
+              if (m < M) ep.tile_amax[(size_t)n_tile * M + m] = x;
+            }
+            named_bar_sync(1, 128);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) slot[(size_t)(cc * 16 + j) * GEMM_BN + nl] = f[j];
         }
       }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[as]);
+      if (!complete) {
+        // park-and-count: the contributor that arrives last reduces all partials of the tile in contributor order
+        const long long t0 = (long long)tile * num_kb;
+        const int c_first = span_owner(U, P, t0), c_last = span_owner(U, P, t0 + num_kb - 1);
+        __threadfence();
+        named_bar_sync(1, 128);
+        if (et == 0) {
+          const int old = atomicAdd(&counters[c_first], 1);
+          *fix_flag = old == c_last - c_first;
+        }
+        named_bar_sync(1, 128);
+        const bool last = *fix_flag != 0;
+        named_bar_sync(1, 128);  // everyone has read the flag before a later segment may rewrite it
+        if (last) {
+          __threadfence();
+          if (et == 0) counters[c_first] = 0;  // leave the workspace ready for the next launch
+#pragma unroll 1
+          for (int mb = 0; mb < BM; mb += 16) {
+            float f[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) f[j] = 0.f;
+            for (int cb = c_first; cb <= c_last; ++cb) {
+              const bool first_seg = (int)(span_begin(U, P, cb) / num_kb) == tile;
+              const float* ps = partials + ((size_t)cb * 2 + (first_seg ? 0 : 1)) * (size_t)(BM * GEMM_BN) + nl;
+#pragma unroll
+              for (int j = 0; j < 16; ++j) f[j] += __ldcg(ps + (size_t)(mb + j) * GEMM_BN);
+            }
+            float am[8];
+            epilogue_chunk<EPI>(ep, f, m0 + mb, M, n, n_ok, N, lane, am);
+            if constexpr (EPI == EPI_SILU_MUL) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                float x = am[j];
+#pragma unroll
+                for (int o = 1; o < 16; o <<= 1) x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, o));
+                if ((lane & 15) == 0) amax_sh[lg * 16 + (lane >= 16 ? 8 : 0) + j] = x;
+              }
+              named_bar_sync(1, 128);
+              if (et < 16) {
+                const int m = m0 + mb + et;
+                const float x = fmaxf(fmaxf(amax_sh[et], amax_sh[16 + et]), fmaxf(amax_sh[32 + et], amax_sh[48 + et]));
+                if (m < M) ep.tile_amax[(size_t)n_tile * M + m] = x;
+              }
+              named_bar_sync(1, 128);
+            }
+          }
+        }
+      }
+      u += nk;
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
-}
-
-// fixed-order reduction of split-K partials + epilogue
-__global__ void splitk_reduce_kernel(const float* __restrict__ partial, GemmEpilogue ep, int M, int N, int splits) {
-  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t total = (int64_t)M * N;
-  if (idx >= total) return;
-  float acc = 0.f;
-  for (int z = 0; z < splits; ++z) acc += partial[(int64_t)z * total + idx];
-  store_out(ep, acc, (int)(idx / N), (int)(idx % N), N);
 }
 
 }  // namespace b200
@@ -177,101 +344,72 @@ using namespace b200;
 namespace {
 
 struct GemmPlan {
-  int bm, stages, m_tiles, n_tiles, num_kb, splits, kb_per_split;
+  int bm, m_tiles, n_tiles, tiles, num_kb, ctas;
+  size_t smem, ws_bytes;
 };
 
 int elem_bytes(int dt) { return dt == B200_BF16 ? 2 : 1; }
+constexpr int stages_for(int bm) { return bm == 32 ? 10 : bm == 64 ? 8 : bm == 128 ? 6 : 4; }
+constexpr size_t smem_for(int bm) {
+  return (size_t)stages_for(bm) * (GEMM_BN * GEMM_BK_BYTES + bm * GEMM_BK_BYTES) + (2 * stages_for(bm) + 4) * 8 + 8 + 64 * 4 + 1024;
+}
 
-GemmPlan plan_gemm(int M, int N, int K, int ab_dtype, int split_k) {
+GemmPlan plan_gemm(int M, int N, int K, int ab_dtype, int max_ctas) {
   GemmPlan p;
   p.bm = M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256;
   p.m_tiles = (M + p.bm - 1) / p.bm;
   p.n_tiles = (N + GEMM_BN - 1) / GEMM_BN;
+  p.tiles = p.m_tiles * p.n_tiles;
   int bk = GEMM_BK_BYTES / elem_bytes(ab_dtype);
   p.num_kb = (K + bk - 1) / bk;
-  int tiles = p.m_tiles * p.n_tiles;
-  int sms = sm_count();
-  int s = split_k;
-  if (s <= 0) {
-    s = 1;
-    if (tiles * 4 <= sms * 3) {  // tiles cannot fill the SMs: split K so that ~one CTA lands on every SM
-      s = sms / tiles;
-      int max_s = p.num_kb / 4;  // keep >= 4 k-blocks per split
-      if (s > max_s) s = max_s;
-      if (s < 1) s = 1;
-    }
-  }
-  if (s > p.num_kb) s = p.num_kb;
-  p.kb_per_split = (p.num_kb + s - 1) / s;
-  p.splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;  // every split owns >= 1 k-block
-  // HBM-bound shapes want every CTA resident at once (they then share bandwidth evenly): if one CTA per SM cannot
-  // hold all tiles, halve the ring so two CTAs fit per SM.
-  int ctas = tiles * p.splits;
-  p.stages = (p.bm <= 64 && ctas <= sms) ? 8 : 4;
-  if (p.bm <= 64 && p.kb_per_split < 8) p.stages = 4;
+  long long units = (long long)p.tiles * p.num_kb;
+  int ctas = sm_count();
+  if (max_ctas > 0 && max_ctas < ctas) ctas = max_ctas;
+  if (ctas > GEMM_CNT_INTS) ctas = GEMM_CNT_INTS;
+  if ((long long)ctas > units) ctas = (int)units;
+  p.ctas = ctas;
+  p.smem = smem_for(p.bm);
+  p.ws_bytes = (size_t)GEMM_CNT_INTS * sizeof(int) + (size_t)ctas * 2 * p.bm * GEMM_BN * sizeof(float);
   return p;
 }
 
-template <int KIND, int BM, int NSTAGES>
-int launch_gemm(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilogue& ep, float* partial, int M, int N,
+template <int KIND, int BM, int EPI>
+int launch_gemm(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilogue& ep, void* workspace, int M, int N,
                 const GemmPlan& p, cudaStream_t stream) {
-  auto kern = gemm_tn_kernel<KIND, BM, NSTAGES>;
-  constexpr size_t smem = (size_t)NSTAGES * (GEMM_BN * GEMM_BK_BYTES + BM * GEMM_BK_BYTES) + (2 * NSTAGES + 1) * 8 + 16 + 1024;
+  auto kern = gemm_streamk_kernel<KIND, BM, stages_for(BM), EPI>;
+  constexpr size_t smem = smem_for(BM);
   static bool attr_done = false;
   if (!attr_done) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_done = true;
   }
-  dim3 grid(p.n_tiles, p.m_tiles, p.splits);
-  kern<<<grid, GEMM_THREADS, smem, stream>>>(wm, am, ep, partial, M, N, p.num_kb, p.kb_per_split);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
+  int* counters = (int*)workspace;
+  float* partials = (float*)((uint8_t*)workspace + GEMM_CNT_INTS * sizeof(int));
+  B200_CUDA_OK(launch_kernel(kern, dim3(p.ctas), dim3(GEMM_THREADS), smem, stream, wm, am, ep, partials, counters, M, N,
+                             p.m_tiles, p.num_kb, p.tiles, p.m_tiles == 1 ? 1 : 0));
   return B200_OK;
 }
 
-template <int KIND>
-int dispatch_gemm(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilogue& ep, float* partial, int M, int N,
+template <int KIND, int EPI>
+int dispatch_gemm(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilogue& ep, void* ws, int M, int N,
                   const GemmPlan& p, cudaStream_t stream) {
-  if (p.bm == 32) {
-    if (p.stages == 8) return launch_gemm<KIND, 32, 8>(wm, am, ep, partial, M, N, p, stream);
-    return launch_gemm<KIND, 32, 4>(wm, am, ep, partial, M, N, p, stream);
-  }
-  if (p.bm == 64) {
-    if (p.stages == 8) return launch_gemm<KIND, 64, 8>(wm, am, ep, partial, M, N, p, stream);
-    return launch_gemm<KIND, 64, 4>(wm, am, ep, partial, M, N, p, stream);
-  }
-  if (p.bm == 128) return launch_gemm<KIND, 128, 4>(wm, am, ep, partial, M, N, p, stream);
-  return launch_gemm<KIND, 256, 4>(wm, am, ep, partial, M, N, p, stream);
+  if (p.bm == 32) return launch_gemm<KIND, 32, EPI>(wm, am, ep, ws, M, N, p, stream);
+  if (p.bm == 64) return launch_gemm<KIND, 64, EPI>(wm, am, ep, ws, M, N, p, stream);
+  if (p.bm == 128) return launch_gemm<KIND, 128, EPI>(wm, am, ep, ws, M, N, p, stream);
+  return launch_gemm<KIND, 256, EPI>(wm, am, ep, ws, M, N, p, stream);
 }
 
-}  // namespace
-
-extern "C" {
-
-size_t b200_gemm_workspace_bytes(int M, int N, int K, int ab_dtype, int split_k) {
-  if (M <= 0 || N <= 0 || K <= 0) return 0;
-  GemmPlan p = plan_gemm(M, N, K, ab_dtype, split_k);
-  return p.splits > 1 ? (size_t)p.splits * M * N * sizeof(float) : 0;
-}
-
-int b200_gemm(const void* a, const void* w, void* out, const float* a_scale, const float* w_scale, const void* bias,
-              const void* residual, int M, int N, int K, int ab_dtype, int out_dtype, int split_k, void* workspace,
-              size_t workspace_bytes, void* stream) {
-  B200_REQUIRE(a && w && out, "gemm: null pointer");
+int gemm_common(const void* a, const void* w, const GemmEpilogue& ep, int epi, int M, int N, int K, int ab_dtype,
+                int max_ctas, void* workspace, size_t workspace_bytes, void* stream) {
+  B200_REQUIRE(a && w && ep.out, "gemm: null pointer");
   B200_REQUIRE(ab_dtype == B200_BF16 || ab_dtype == B200_FP8_E4M3 || ab_dtype == B200_INT8, "gemm: bad ab_dtype %d", ab_dtype);
-  B200_REQUIRE(out_dtype == B200_BF16 || out_dtype == B200_F32, "gemm: bad out_dtype %d", out_dtype);
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: bad shape M=%d N=%d K=%d", M, N, K);
   int eb = elem_bytes(ab_dtype);
   B200_REQUIRE(((int64_t)K * eb) % 16 == 0, "gemm: K*elem_bytes must be a multiple of 16 (TMA row pitch), K=%d", K);
-  GemmPlan p = plan_gemm(M, N, K, ab_dtype, split_k);
-  float* partial = nullptr;
-  if (p.splits > 1) {
-    size_t need = (size_t)p.splits * M * N * sizeof(float);
-    if (!workspace || workspace_bytes < need) {
-      set_last_error("gemm: workspace %zu < %zu bytes (splits=%d)", workspace_bytes, need, p.splits);
-      return B200_ERR_WORKSPACE;
-    }
-    partial = (float*)workspace;
+  GemmPlan p = plan_gemm(M, N, K, ab_dtype, max_ctas);
+  if (!workspace || workspace_bytes < p.ws_bytes) {
+    set_last_error("gemm: workspace %zu < %zu bytes", workspace_bytes, p.ws_bytes);
+    return B200_ERR_WORKSPACE;
   }
   CUtensorMapDataType dt = ab_dtype == B200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
   int bk = GEMM_BK_BYTES / eb;
@@ -280,22 +418,42 @@ int b200_gemm(const void* a, const void* w, void* out, const float* a_scale, con
   if (rc) return rc;
   rc = make_tmap_2d(&am, a, dt, eb, (uint64_t)K, (uint64_t)M, (uint64_t)K * eb, bk, p.bm);
   if (rc) return rc;
-  GemmEpilogue ep{a_scale, w_scale, (const __nv_bfloat16*)bias, (const __nv_bfloat16*)residual, out, out_dtype == B200_F32};
   cudaStream_t s = (cudaStream_t)stream;
-  if (ab_dtype == B200_BF16)
-    rc = dispatch_gemm<KIND_F16>(wm, am, ep, partial, M, N, p, s);
-  else if (ab_dtype == B200_FP8_E4M3)
-    rc = dispatch_gemm<KIND_F8F6F4>(wm, am, ep, partial, M, N, p, s);
-  else
-    rc = dispatch_gemm<KIND_I8>(wm, am, ep, partial, M, N, p, s);
-  if (rc) return rc;
-  if (partial) {
-    int64_t total = (int64_t)M * N;
-    splitk_reduce_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(partial, ep, M, N, p.splits);
-    B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
+  if (epi == EPI_LINEAR) {
+    if (ab_dtype == B200_BF16) return dispatch_gemm<KIND_F16, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, s);
+    if (ab_dtype == B200_FP8_E4M3) return dispatch_gemm<KIND_F8F6F4, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, s);
+    return dispatch_gemm<KIND_I8, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, s);
   }
-  return B200_OK;
+  if (ab_dtype == B200_BF16) return dispatch_gemm<KIND_F16, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, s);
+  if (ab_dtype == B200_FP8_E4M3) return dispatch_gemm<KIND_F8F6F4, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, s);
+  return dispatch_gemm<KIND_I8, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, s);
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t b200_gemm_workspace_bytes(int M, int N, int K, int ab_dtype, int max_ctas) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  return plan_gemm(M, N, K, ab_dtype, max_ctas).ws_bytes;
+}
+
+int b200_gemm(const void* a, const void* w, void* out, const float* a_scale, const float* w_scale, const void* bias,
+              const void* residual, int M, int N, int K, int ab_dtype, int out_dtype, int max_ctas, void* workspace,
+              size_t workspace_bytes, void* stream) {
+  B200_REQUIRE(out_dtype == B200_BF16 || out_dtype == B200_F32, "gemm: bad out_dtype %d", out_dtype);
+  GemmEpilogue ep{a_scale, w_scale, (const __nv_bfloat16*)bias, (const __nv_bfloat16*)residual, out, out_dtype == B200_F32,
+                  nullptr};
+  return gemm_common(a, w, ep, EPI_LINEAR, M, N, K, ab_dtype, max_ctas, workspace, workspace_bytes, stream);
+}
+
+int b200_gemm_silu_mul(const void* a, const void* w_gu, void* out_act, const float* a_scale, const float* w_scale,
+                       const void* bias, float* tile_amax, int M, int N2, int K, int ab_dtype, int max_ctas,
+                       void* workspace, size_t workspace_bytes, void* stream) {
+  B200_REQUIRE(tile_amax, "gemm_silu_mul: tile_amax required");
+  B200_REQUIRE(N2 % 32 == 0, "gemm_silu_mul: 2*I must be a multiple of 32 (16 gate + 16 up rows per group), got %d", N2);
+  GemmEpilogue ep{a_scale, w_scale, (const __nv_bfloat16*)bias, nullptr, out_act, 0, tile_amax};
+  return gemm_common(a, w_gu, ep, EPI_SILU_MUL, M, N2, K, ab_dtype, max_ctas, workspace, workspace_bytes, stream);
 }
 
 }  // extern "C"

@@ -12,6 +12,8 @@ namespace b200 {
 static thread_local char g_err[512] = "";
 static std::atomic<uint64_t> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+static std::atomic<int> g_pdl{1};
+bool pdl_enabled() { return g_pdl.load(std::memory_order_relaxed) != 0; }
 
 void set_last_error(const char* fmt, ...) {
   va_list ap;
@@ -92,6 +94,11 @@ int b200_abi_version(void) { return B200_ABI_VERSION; }
 const char* b200_last_error(void) { return b200::g_err; }
 
 uint64_t b200_launch_count(void) { return b200::g_launches.load(); }
+
+int b200_set_pdl(int enabled) {
+  int old = b200::g_pdl.exchange(enabled ? 1 : 0);
+  return old;
+}
 
 int b200_device_check(int device) {
   int n = 0;

@@ -10,6 +10,8 @@ __global__ void build_decode_meta_kernel(const int32_t* __restrict__ block_table
                                          const int32_t* __restrict__ row_ids, const int32_t* __restrict__ num_tokens,
                                          int64_t* __restrict__ slot_mapping, int64_t* __restrict__ positions,
                                          int32_t* __restrict__ ctx_lens, int B, int max_blocks, int bs) {
+  griddep_launch();
+  griddep_wait();
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   int r = row_ids ? row_ids[b] : b;
@@ -26,6 +28,8 @@ __global__ void build_decode_meta_kernel(const int32_t* __restrict__ block_table
 __global__ void build_prefill_meta_kernel(const int32_t* __restrict__ bt_row, int prompt_len, int num_computed,
                                           int64_t* __restrict__ slot_mapping, int64_t* __restrict__ positions,
                                           int max_model_len, int bs) {
+  griddep_launch();
+  griddep_wait();
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= max_model_len) return;
   int tok = num_computed + i;
@@ -36,6 +40,8 @@ __global__ void build_prefill_meta_kernel(const int32_t* __restrict__ bt_row, in
 
 __global__ void block_table_scatter_kernel(int32_t* __restrict__ block_table, int64_t bt_stride,
                                            const int32_t* __restrict__ updates, int n, int rows, int max_blocks) {
+  griddep_launch();
+  griddep_wait();
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   int r = updates[3 * i], c = updates[3 * i + 1], v = updates[3 * i + 2];
@@ -44,6 +50,8 @@ __global__ void block_table_scatter_kernel(int32_t* __restrict__ block_table, in
 
 __global__ void advance_decode_kernel(const int64_t* __restrict__ sampled, int64_t* __restrict__ tokens_io,
                                       int32_t* __restrict__ num_tokens, const int32_t* __restrict__ row_ids, int B) {
+  griddep_launch();
+  griddep_wait();
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   tokens_io[b] = sampled[b];
@@ -56,6 +64,8 @@ __global__ void advance_decode_kernel(const int64_t* __restrict__ sampled, int64
 __global__ void kv_write_kernel(const uint4* __restrict__ k, const uint4* __restrict__ v, int64_t k_stride_v,
                                 int64_t v_stride_v, uint4* __restrict__ k_pool, uint4* __restrict__ v_pool,
                                 const int64_t* __restrict__ slot_mapping, int Hkv, int dvec, int bs, int64_t num_slots) {
+  griddep_launch();
+  griddep_wait();
   int t = blockIdx.x;
   int64_t slot = slot_mapping[t];
   if (slot < 0 || slot >= num_slots) return;  // -1 = padding (model_runner.py:76-81)
@@ -94,6 +104,8 @@ __global__ void rope_kv_write_kernel(uint4* __restrict__ qkv, const int64_t* __r
                                      uint4* __restrict__ k_pool, uint4* __restrict__ v_pool,
                                      const int64_t* __restrict__ slot_mapping, int Hq, int Hkv, int D, int bs,
                                      int64_t num_slots) {
+  griddep_launch();
+  griddep_wait();
   int t = blockIdx.x;
   int dvec = D / 8, hvec = D / 16;
   int64_t row_v = (int64_t)(Hq + 2 * Hkv) * dvec;
@@ -165,26 +177,15 @@ __device__ __forceinline__ float block_max(float v, float* sh) {
   return warp_max(r);
 }
 
-template <int QD>
-__device__ __forceinline__ uint8_t quant1(float y, float scale) {
-  float q = __fdiv_rn(y, scale);
-  if constexpr (QD == B200_FP8_E4M3) {
-    return (uint8_t)__nv_cvt_float_to_fp8(q, __NV_SATFINITE, __NV_E4M3);
-  } else {
-    float r = rintf(q);
-    r = fminf(fmaxf(r, -127.f), 127.f);
-    return (uint8_t)(int8_t)(int)r;
-  }
-}
 __device__ __forceinline__ float bf16_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
 
 template <int QD>
 __device__ __forceinline__ uint2 quant8(const float (&y)[8], float scale) {
   uint32_t lo = 0, hi = 0;
 #pragma unroll
-  for (int e = 0; e < 4; ++e) lo |= (uint32_t)quant1<QD>(y[e], scale) << (8 * e);
+  for (int e = 0; e < 4; ++e) lo |= (uint32_t)quant_byte<QD>(y[e], scale) << (8 * e);
 #pragma unroll
-  for (int e = 0; e < 4; ++e) hi |= (uint32_t)quant1<QD>(y[4 + e], scale) << (8 * e);
+  for (int e = 0; e < 4; ++e) hi |= (uint32_t)quant_byte<QD>(y[4 + e], scale) << (8 * e);
   return make_uint2(lo, hi);
 }
 
@@ -196,6 +197,8 @@ template <int QD>
 __global__ void __launch_bounds__(NORM_THREADS)
     rmsnorm_kernel(const uint4* __restrict__ x, const uint4* __restrict__ w, uint4* __restrict__ out_bf16,
                    uint2* __restrict__ out_q, float* __restrict__ out_scale, int H, float eps) {
+  griddep_launch();
+  griddep_wait();
   __shared__ float sh[32];
   int t = blockIdx.x, nvec = H / 8;
   const uint4* xr = x + (int64_t)t * nvec;
@@ -256,6 +259,8 @@ template <int QD>
 __global__ void __launch_bounds__(NORM_THREADS)
     silu_mul_kernel(const uint4* __restrict__ gate_up, uint4* __restrict__ out_bf16, uint2* __restrict__ out_q,
                     float* __restrict__ out_scale, int I) {
+  griddep_launch();
+  griddep_wait();
   __shared__ float sh[32];
   int t = blockIdx.x, nvec = I / 8;
   const uint4* g = gate_up + (int64_t)t * 2 * nvec;
@@ -281,24 +286,38 @@ __global__ void __launch_bounds__(NORM_THREADS)
   }
 }
 
+// Dynamic per-token quantisation.  With tile_amax == nullptr the CTA of token t scans its row for max|x| first.
+// With tile_amax [n_tiles][T] (written by the fused gate/up GEMM epilogue) the row maximum is the max over the tiles,
+// so the row can be cut into gridDim.y column slices that quantise independently.
 template <int QD>
 __global__ void __launch_bounds__(NORM_THREADS)
-    quantize_kernel(const uint4* __restrict__ x, uint2* __restrict__ out_q, float* __restrict__ out_scale, int K) {
+    quantize_kernel(const uint4* __restrict__ x, uint2* __restrict__ out_q, float* __restrict__ out_scale, int K,
+                    const float* __restrict__ tile_amax, int n_tiles, int T) {
+  griddep_launch();
+  griddep_wait();
   __shared__ float sh[32];
   int t = blockIdx.x, nvec = K / 8;
   const uint4* xr = x + (int64_t)t * nvec;
   float amax = 0.f;
-  for (int vi = threadIdx.x; vi < nvec; vi += NORM_THREADS) {
-    float a[8];
-    unpack8(xr[vi], a);
+  int v0 = 0, v1 = nvec;
+  if (tile_amax) {
+    for (int i = threadIdx.x; i < n_tiles; i += NORM_THREADS) amax = fmaxf(amax, tile_amax[(int64_t)i * T + t]);
+    int per = (nvec + gridDim.y - 1) / gridDim.y;
+    v0 = blockIdx.y * per;
+    v1 = v0 + per < nvec ? v0 + per : nvec;
+  } else {
+    for (int vi = threadIdx.x; vi < nvec; vi += NORM_THREADS) {
+      float a[8];
+      unpack8(xr[vi], a);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(a[e]));
+      for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(a[e]));
+    }
   }
   amax = block_max(amax, sh);
   float qmax = QD == B200_FP8_E4M3 ? 448.f : 127.f;
   float scale = amax > 0.f ? __fdiv_rn(amax, qmax) : 1.f;
-  if (threadIdx.x == 0) out_scale[t] = scale;
-  for (int vi = threadIdx.x; vi < nvec; vi += NORM_THREADS) {
+  if (threadIdx.x == 0 && blockIdx.y == 0) out_scale[t] = scale;
+  for (int vi = v0 + threadIdx.x; vi < v1; vi += NORM_THREADS) {
     float a[8];
     unpack8(xr[vi], a);
     out_q[(int64_t)t * nvec + vi] = quant8<QD>(a, scale);
@@ -307,6 +326,8 @@ __global__ void __launch_bounds__(NORM_THREADS)
 
 __global__ void embedding_kernel(const int64_t* __restrict__ tokens, const uint4* __restrict__ table,
                                  uint4* __restrict__ out, int nvec, int V) {
+  griddep_launch();
+  griddep_wait();
   int t = blockIdx.x;
   int64_t tok = tokens[t];
   if (tok < 0) tok = 0;
@@ -318,6 +339,8 @@ __global__ void embedding_kernel(const int64_t* __restrict__ tokens, const uint4
 __global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ logits, int64_t row_stride,
                                                       float* __restrict__ out_val, int64_t* __restrict__ out_idx, int V,
                                                       int64_t idx_offset) {
+  griddep_launch();
+  griddep_wait();
   __shared__ float sv[32];
   __shared__ int si[32];
   int t = blockIdx.x;
@@ -380,10 +403,7 @@ int b200_build_decode_meta(const int32_t* block_table, int64_t bt_row_stride, co
   B200_REQUIRE(B >= 0 && max_blocks > 0 && block_size > 0, "build_decode_meta: bad sizes B=%d max_blocks=%d bs=%d", B,
                max_blocks, block_size);
   if (B == 0) return B200_OK;
-  build_decode_meta_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
-      block_table, bt_row_stride, row_ids, num_tokens, slot_mapping, positions, ctx_lens, B, max_blocks, block_size);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
+  B200_CUDA_OK(launch_kernel(build_decode_meta_kernel, dim3((B + 127) / 128), dim3(128), 0, (cudaStream_t)stream, block_table, bt_row_stride, row_ids, num_tokens, slot_mapping, positions, ctx_lens, B, max_blocks, block_size));
   return B200_OK;
 }
 
@@ -391,10 +411,7 @@ int b200_build_prefill_meta(const int32_t* block_table_row, int prompt_len, int 
                             int64_t* positions_out, int max_model_len, int block_size, void* stream) {
   B200_REQUIRE(block_table_row && slot_mapping_out && positions_out, "build_prefill_meta: null pointer");
   B200_REQUIRE(prompt_len >= 0 && num_computed >= 0 && max_model_len > 0 && block_size > 0, "build_prefill_meta: bad sizes");
-  build_prefill_meta_kernel<<<(max_model_len + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
-      block_table_row, prompt_len, num_computed, slot_mapping_out, positions_out, max_model_len, block_size);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
+  B200_CUDA_OK(launch_kernel(build_prefill_meta_kernel, dim3((max_model_len + 255) / 256), dim3(256), 0, (cudaStream_t)stream, block_table_row, prompt_len, num_computed, slot_mapping_out, positions_out, max_model_len, block_size));
   return B200_OK;
 }
 
@@ -402,10 +419,8 @@ int b200_block_table_scatter(int32_t* block_table, int64_t bt_row_stride, const 
                              int max_blocks, void* stream) {
   B200_REQUIRE(block_table && (updates || n == 0), "block_table_scatter: null pointer");
   if (n <= 0) return B200_OK;
-  block_table_scatter_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(block_table, bt_row_stride, updates, n,
-                                                                                 rows, max_blocks);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
+  B200_CUDA_OK(launch_kernel(block_table_scatter_kernel, dim3((n + 127) / 128), dim3(128), 0, (cudaStream_t)stream, block_table, bt_row_stride, updates, n,
+                                                                                 rows, max_blocks));
   return B200_OK;
 }
 
@@ -413,9 +428,7 @@ int b200_advance_decode(const int64_t* sampled, int64_t* tokens_io, int32_t* num
                         void* stream) {
   B200_REQUIRE(sampled && tokens_io && num_tokens, "advance_decode: null pointer");
   if (B <= 0) return B200_OK;
-  advance_decode_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(sampled, tokens_io, num_tokens, row_ids, B);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
+  B200_CUDA_OK(launch_kernel(advance_decode_kernel, dim3((B + 127) / 128), dim3(128), 0, (cudaStream_t)stream, sampled, tokens_io, num_tokens, row_ids, B));
   return B200_OK;
 }
 
@@ -425,11 +438,9 @@ int b200_kv_write(const void* k, const void* v, int64_t k_token_stride, int64_t 
   B200_REQUIRE(D % 8 == 0 && k_token_stride % 8 == 0 && v_token_stride % 8 == 0, "kv_write: D and strides must be multiples of 8");
   B200_REQUIRE((((uintptr_t)k | (uintptr_t)v | (uintptr_t)k_pool | (uintptr_t)v_pool) & 15) == 0, "kv_write: 16-byte alignment");
   if (T <= 0) return B200_OK;
-  kv_write_kernel<<<T, 128, 0, (cudaStream_t)stream>>>((const uint4*)k, (const uint4*)v, k_token_stride / 8,
+  B200_CUDA_OK(launch_kernel(kv_write_kernel, dim3(T), dim3(128), 0, (cudaStream_t)stream, (const uint4*)k, (const uint4*)v, k_token_stride / 8,
                                                        v_token_stride / 8, (uint4*)k_pool, (uint4*)v_pool, slot_mapping,
-                                                       Hkv, D / 8, block_size, (int64_t)num_blocks * block_size);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
+                                                       Hkv, D / 8, block_size, (int64_t)num_blocks * block_size));
   return B200_OK;
 }
 
@@ -439,11 +450,9 @@ int b200_rope_kv_write(void* qkv, const int64_t* positions, const float* cos_tab
   B200_REQUIRE(qkv && positions && cos_table && sin_table && k_pool && v_pool && slot_mapping, "rope_kv_write: null pointer");
   B200_REQUIRE(D % 16 == 0, "rope_kv_write: D must be a multiple of 16 (got %d)", D);
   if (T <= 0) return B200_OK;
-  rope_kv_write_kernel<<<T, 256, 0, (cudaStream_t)stream>>>((uint4*)qkv, positions, cos_table, sin_table, max_pos,
+  B200_CUDA_OK(launch_kernel(rope_kv_write_kernel, dim3(T), dim3(256), 0, (cudaStream_t)stream, (uint4*)qkv, positions, cos_table, sin_table, max_pos,
                                                             (uint4*)k_pool, (uint4*)v_pool, slot_mapping, Hq, Hkv, D,
-                                                            block_size, (int64_t)num_blocks * block_size);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
+                                                            block_size, (int64_t)num_blocks * block_size));
   return B200_OK;
 }
 
@@ -456,18 +465,16 @@ int b200_rmsnorm(const void* x, const void* w, void* out_bf16, void* out_q, floa
   cudaStream_t s = (cudaStream_t)stream;
   if (q_dtype == B200_BF16) {
     B200_REQUIRE(out_bf16, "rmsnorm: out_bf16 required");
-    rmsnorm_kernel<B200_BF16><<<T, NORM_THREADS, 0, s>>>((const uint4*)x, (const uint4*)w, (uint4*)out_bf16, nullptr, nullptr, H, eps);
+    B200_CUDA_OK(launch_kernel(rmsnorm_kernel<B200_BF16>, dim3(T), dim3(NORM_THREADS), 0, s, (const uint4*)x, (const uint4*)w, (uint4*)out_bf16, nullptr, nullptr, H, eps));
   } else if (q_dtype == B200_FP8_E4M3) {
     B200_REQUIRE(out_q && out_scale, "rmsnorm: out_q/out_scale required");
-    rmsnorm_kernel<B200_FP8_E4M3><<<T, NORM_THREADS, 0, s>>>((const uint4*)x, (const uint4*)w, (uint4*)out_bf16, (uint2*)out_q, out_scale, H, eps);
+    B200_CUDA_OK(launch_kernel(rmsnorm_kernel<B200_FP8_E4M3>, dim3(T), dim3(NORM_THREADS), 0, s, (const uint4*)x, (const uint4*)w, (uint4*)out_bf16, (uint2*)out_q, out_scale, H, eps));
   } else if (q_dtype == B200_INT8) {
     B200_REQUIRE(out_q && out_scale, "rmsnorm: out_q/out_scale required");
-    rmsnorm_kernel<B200_INT8><<<T, NORM_THREADS, 0, s>>>((const uint4*)x, (const uint4*)w, (uint4*)out_bf16, (uint2*)out_q, out_scale, H, eps);
+    B200_CUDA_OK(launch_kernel(rmsnorm_kernel<B200_INT8>, dim3(T), dim3(NORM_THREADS), 0, s, (const uint4*)x, (const uint4*)w, (uint4*)out_bf16, (uint2*)out_q, out_scale, H, eps));
   } else {
     B200_REQUIRE(false, "rmsnorm: bad q_dtype %d", q_dtype);
   }
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -479,34 +486,41 @@ int b200_silu_mul(const void* gate_up, void* out_bf16, void* out_q, float* out_s
   cudaStream_t s = (cudaStream_t)stream;
   if (q_dtype == B200_BF16) {
     B200_REQUIRE(out_bf16, "silu_mul: out_bf16 required");
-    silu_mul_kernel<B200_BF16><<<T, NORM_THREADS, 0, s>>>((const uint4*)gate_up, (uint4*)out_bf16, nullptr, nullptr, I);
+    B200_CUDA_OK(launch_kernel(silu_mul_kernel<B200_BF16>, dim3(T), dim3(NORM_THREADS), 0, s, (const uint4*)gate_up, (uint4*)out_bf16, nullptr, nullptr, I));
   } else if (q_dtype == B200_FP8_E4M3) {
     B200_REQUIRE(out_q && out_scale, "silu_mul: out_q/out_scale required");
-    silu_mul_kernel<B200_FP8_E4M3><<<T, NORM_THREADS, 0, s>>>((const uint4*)gate_up, (uint4*)out_bf16, (uint2*)out_q, out_scale, I);
+    B200_CUDA_OK(launch_kernel(silu_mul_kernel<B200_FP8_E4M3>, dim3(T), dim3(NORM_THREADS), 0, s, (const uint4*)gate_up, (uint4*)out_bf16, (uint2*)out_q, out_scale, I));
   } else if (q_dtype == B200_INT8) {
     B200_REQUIRE(out_q && out_scale, "silu_mul: out_q/out_scale required");
-    silu_mul_kernel<B200_INT8><<<T, NORM_THREADS, 0, s>>>((const uint4*)gate_up, (uint4*)out_bf16, (uint2*)out_q, out_scale, I);
+    B200_CUDA_OK(launch_kernel(silu_mul_kernel<B200_INT8>, dim3(T), dim3(NORM_THREADS), 0, s, (const uint4*)gate_up, (uint4*)out_bf16, (uint2*)out_q, out_scale, I));
   } else {
     B200_REQUIRE(false, "silu_mul: bad q_dtype %d", q_dtype);
   }
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
   return B200_OK;
 }
 
-int b200_quantize_per_token(const void* x, void* out_q, float* out_scale, int T, int K, int q_dtype, void* stream) {
+int b200_quantize_per_token(const void* x, void* out_q, float* out_scale, const float* tile_amax, int n_tiles, int T, int K,
+                            int q_dtype, void* stream) {
   B200_REQUIRE(x && out_q && out_scale, "quantize_per_token: null pointer");
   B200_REQUIRE(K % 8 == 0, "quantize_per_token: K must be a multiple of 8");
+  B200_REQUIRE(!tile_amax || n_tiles > 0, "quantize_per_token: n_tiles must be positive with tile_amax");
   if (T <= 0) return B200_OK;
   cudaStream_t s = (cudaStream_t)stream;
+  int slices = 1;
+  if (tile_amax) {  // no row scan needed: cut rows so that ~2 CTAs land on every SM
+    slices = (2 * sm_count() + T - 1) / T;
+    int max_slices = (K / 8 + NORM_THREADS - 1) / NORM_THREADS;
+    if (slices > max_slices) slices = max_slices;
+    if (slices < 1) slices = 1;
+  }
   if (q_dtype == B200_FP8_E4M3)
-    quantize_kernel<B200_FP8_E4M3><<<T, NORM_THREADS, 0, s>>>((const uint4*)x, (uint2*)out_q, out_scale, K);
+    B200_CUDA_OK(launch_kernel(quantize_kernel<B200_FP8_E4M3>, dim3(T, slices), dim3(NORM_THREADS), 0, s, (const uint4*)x,
+                               (uint2*)out_q, out_scale, K, tile_amax, n_tiles, T));
   else if (q_dtype == B200_INT8)
-    quantize_kernel<B200_INT8><<<T, NORM_THREADS, 0, s>>>((const uint4*)x, (uint2*)out_q, out_scale, K);
+    B200_CUDA_OK(launch_kernel(quantize_kernel<B200_INT8>, dim3(T, slices), dim3(NORM_THREADS), 0, s, (const uint4*)x,
+                               (uint2*)out_q, out_scale, K, tile_amax, n_tiles, T));
   else
     B200_REQUIRE(false, "quantize_per_token: bad q_dtype %d", q_dtype);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
   return B200_OK;
 }
 
@@ -514,9 +528,7 @@ int b200_embedding(const int64_t* tokens, const void* table, void* out, int T, i
   B200_REQUIRE(tokens && table && out, "embedding: null pointer");
   B200_REQUIRE(H % 8 == 0, "embedding: H must be a multiple of 8");
   if (T <= 0) return B200_OK;
-  embedding_kernel<<<T, 256, 0, (cudaStream_t)stream>>>(tokens, (const uint4*)table, (uint4*)out, H / 8, V);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
+  B200_CUDA_OK(launch_kernel(embedding_kernel, dim3(T), dim3(256), 0, (cudaStream_t)stream, tokens, (const uint4*)table, (uint4*)out, H / 8, V));
   return B200_OK;
 }
 
@@ -525,9 +537,7 @@ int b200_argmax(const float* logits, int64_t row_stride, float* out_val, int64_t
   B200_REQUIRE(logits && out_idx, "argmax: null pointer");
   B200_REQUIRE(V > 0, "argmax: V must be positive");
   if (T <= 0) return B200_OK;
-  argmax_kernel<<<T, 1024, 0, (cudaStream_t)stream>>>(logits, row_stride, out_val, out_idx, V, idx_offset);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
+  B200_CUDA_OK(launch_kernel(argmax_kernel, dim3(T), dim3(1024), 0, (cudaStream_t)stream, logits, row_stride, out_val, out_idx, V, idx_offset));
   return B200_OK;
 }
 

@@ -37,6 +37,62 @@ __device__ __forceinline__ void issue_tile_pair(const CUtensorMap* kmap, const C
   for (int bx = 0; bx < NBOX; ++bx) tma_load_2d(vdst + bx * 4096, vmap, bar, bx * 64, tile_row);
 }
 
+// ---- balanced flash-decoding partition
+// All (sequence, kv head) pairs are laid end to end as one list of 32-token blocks:
+//   pair (b, kvh) owns global blocks [Hkv*pre[b] + kvh*nblk(b), +nblk(b)),  pre[b] = sum_{b' < b} nblk(b').
+// Worker w (one warp) takes the contiguous range [w*R, (w+1)*R) of that list, R = max(ceil(total / workers), min_quota),
+// so every warp streams the same number of KV bytes whatever the context lengths are (ragged batches, ctx % chunk != 0).
+// A pair cut by a range boundary gets one partial (m, l, O) per worker that touched it: worker w writes part index
+// w - first_worker(pair); the combine kernel recomputes the same arithmetic to know how many parts a pair has.
+constexpr int DEC_MAX_B = 2048;  // sequences per launch (prefix table lives in shared memory)
+
+struct PairPos {
+  int b, kvh, blk, nblk;
+};
+// largest b with Hkv*pre[b] <= g (skips empty sequences), then the position inside the pair
+__device__ __forceinline__ PairPos locate_block(const int* pre, int B, int Hkv, int g) {
+  int lo = 0, hi = B - 1;
+  while (lo < hi) {
+    int mid = (lo + hi + 1) >> 1;
+    if (Hkv * pre[mid] <= g)
+      lo = mid;
+    else
+      hi = mid - 1;
+  }
+  PairPos p;
+  p.b = lo;
+  p.nblk = pre[lo + 1] - pre[lo];
+  int rem = g - Hkv * pre[lo];
+  p.kvh = rem / p.nblk;
+  p.blk = rem - p.kvh * p.nblk;
+  return p;
+}
+
+// exclusive prefix of blocks-per-sequence into shared memory (pre[0..B]); all threads of the CTA call this
+__device__ __forceinline__ int blocks_of(int ctx, int max_blocks) {
+  int n = ctx > 0 ? (ctx + BS - 1) / BS : 0;
+  return n < max_blocks ? n : max_blocks;
+}
+__device__ __forceinline__ void build_block_prefix(int* pre, const int32_t* __restrict__ ctx_lens, int B, int max_blocks) {
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    int carry = 0;
+    for (int base = 0; base < B; base += 32) {
+      int b = base + lane;
+      int x = b < B ? blocks_of(ctx_lens[b], max_blocks) : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
+      }
+      if (b < B) pre[b + 1] = carry + x;
+      carry += __shfl_sync(0xffffffffu, x, 31);
+    }
+    if (lane == 0) pre[0] = 0;
+  }
+  __syncthreads();
+}
+
 template <int D, int NSTAGES, int NWARPS>
 __global__ void __launch_bounds__(NWARPS * 32, 1)
     paged_attn_decode_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
@@ -44,7 +100,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
                              const int32_t* __restrict__ block_table, int64_t bt_stride,
                              const int32_t* __restrict__ row_ids, const int32_t* __restrict__ ctx_lens,
                              float* __restrict__ part_o, float* __restrict__ part_ml, int B, int Hq, int Hkv,
-                             int max_chunks, int chunk_blocks, float scale_log2) {
+                             int max_parts, int min_quota, int max_blocks, float scale_log2) {
   constexpr int TILE = BS * D * 2;  // bytes of one K (or V) tile
   constexpr int KSTEPS = D / 16;
   extern __shared__ uint8_t smem_raw[];
@@ -52,6 +108,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint8_t* my_tiles = smem + (size_t)warp * NSTAGES * 2 * TILE;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)NWARPS * NSTAGES * 2 * TILE) + warp * NSTAGES;
+  int* pre = reinterpret_cast<int*>(smem + (size_t)NWARPS * NSTAGES * 2 * TILE + NWARPS * NSTAGES * 8);
 
   if (lane == 0) {
 #pragma unroll
@@ -59,42 +116,60 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
     fence_mbar_init();
     fence_proxy_async();
   }
-  __syncwarp();
+  griddep_launch();
+  griddep_wait();  // ctx_lens, q and the newest KV slot come from kernels earlier in the step
+  build_block_prefix(pre, ctx_lens, B, max_blocks);
 
   const int G = Hq / Hkv;
-  const int worker = blockIdx.x * NWARPS + warp, nworkers = gridDim.x * NWARPS;
-  const int total_items = B * Hkv * max_chunks;
+  const int total = Hkv * pre[B];
+  const int nworkers = gridDim.x * NWARPS;
+  int R = (total + nworkers - 1) / nworkers;
+  if (R < min_quota) R = min_quota;
+  const int w = blockIdx.x * NWARPS + warp;
+  const int g0 = w * R;
+  if (g0 >= total) return;
+  const int g1 = g0 + R < total ? g0 + R : total;
+
   uint32_t parity = 0;  // bit s = parity to wait for on stage s
   const int h0 = (lane & 3) * 2;
   const int qn = lane >> 2;  // head slot this lane feeds into the B operand
 
-  for (int item = worker; item < total_items; item += nworkers) {
-    const int chunk = item % max_chunks;
-    const int kvh = (item / max_chunks) % Hkv;
-    const int b = item / (max_chunks * Hkv);
-    const int ctx = ctx_lens[b];
-    const int nblk_total = (ctx + BS - 1) / BS;
-    const int blk0 = chunk * chunk_blocks;
-    int nblk = nblk_total - blk0;
-    if (nblk > chunk_blocks) nblk = chunk_blocks;
-    if (nblk <= 0) continue;
-    const int row = row_ids ? row_ids[b] : b;
-    const int bt_reg = lane < nblk ? block_table[(int64_t)row * bt_stride + blk0 + lane] : 0;
-
-    auto issue = [&](int s, int jj) {
-      int blkid = __shfl_sync(0xffffffffu, bt_reg, jj);
-      if (lane == 0)
-        issue_tile_pair<D>(&k_map, &v_map, 0, my_tiles + (size_t)s * 2 * TILE, my_tiles + (size_t)s * 2 * TILE + TILE,
-                           &bars[s], (blkid * Hkv + kvh) * BS);
-    };
+  // TMA row coordinate of global block g: ((block id) * Hkv + kvh) * 32, resolved through the block table
+  auto tile_row_of = [&](int g) -> int {
+    if (g >= g1) return 0;
+    PairPos p = locate_block(pre, B, Hkv, g);
+    const int row = row_ids ? row_ids[p.b] : p.b;
+    const int blkid = block_table[(int64_t)row * bt_stride + p.blk];
+    return (blkid * Hkv + p.kvh) * BS;
+  };
+  // lane l of tr_cur holds the coordinate of block (batch base + l); tr_next the following 32
+  int tr_cur = tile_row_of(g0 + lane);
+  int tr_next = tile_row_of(g0 + 32 + lane);
+  auto issue = [&](int s, int rel) {  // rel = g - g0
+    if ((rel & 31) == 0 && rel > 0) {
+      tr_cur = tr_next;
+      tr_next = tile_row_of(g0 + rel + 32 + lane);
+    }
+    const int tr = __shfl_sync(0xffffffffu, tr_cur, rel & 31);
+    if (lane == 0)
+      issue_tile_pair<D>(&k_map, &v_map, 0, my_tiles + (size_t)s * 2 * TILE, my_tiles + (size_t)s * 2 * TILE + TILE,
+                         &bars[s], tr);
+  };
 #pragma unroll
-    for (int s = 0; s < NSTAGES; ++s)
-      if (s < nblk) issue(s, s);
+  for (int s = 0; s < NSTAGES; ++s)
+    if (g0 + s < g1) issue(s, s);
 
-    // Q^T as the B operand: lane holds head (lane/4), dims (lane%4)*2+{0,1} (+8) of every 16-dim step
-    uint32_t qb[KSTEPS][2];
-    {
-      const __nv_bfloat16* qp = q + (int64_t)b * q_stride + (int64_t)(kvh * G + (qn < G ? qn : 0)) * D + h0;
+  PairPos cur = locate_block(pre, B, Hkv, g0);
+  int ctx = ctx_lens[cur.b];
+  bool fresh = true;
+  uint32_t qb[KSTEPS][2];
+  float oacc[KSTEPS][4];
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+
+  for (int g = g0; g < g1; ++g) {
+    if (fresh) {
+      // Q^T as the B operand: lane holds head (lane/4), dims (lane%4)*2+{0,1} (+8) of every 16-dim step
+      const __nv_bfloat16* qp = q + (int64_t)cur.b * q_stride + (int64_t)(cur.kvh * G + (qn < G ? qn : 0)) * D + h0;
 #pragma unroll
       for (int ks = 0; ks < KSTEPS; ++ks) {
         uint32_t v0 = *reinterpret_cast<const uint32_t*>(qp + ks * 16);
@@ -102,145 +177,251 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
         qb[ks][0] = qn < G ? v0 : 0u;
         qb[ks][1] = qn < G ? v1 : 0u;
       }
+#pragma unroll
+      for (int i = 0; i < KSTEPS; ++i) oacc[i][0] = oacc[i][1] = oacc[i][2] = oacc[i][3] = 0.f;
+      m0 = m1 = -INFINITY;
+      l0 = l1 = 0.f;
+      fresh = false;
     }
+    const int rel = g - g0;
+    const int s = rel % NSTAGES;
+    mbar_wait(&bars[s], (parity >> s) & 1u);
+    parity ^= 1u << s;
+    const uint32_t kbase = smem_u32(my_tiles + (size_t)s * 2 * TILE);
+    const uint32_t vbase = kbase + TILE;
+    const int nvalid = ctx - cur.blk * BS;  // >= 1; >= 32 for all but the last block
 
-    float oacc[KSTEPS][4];
+    // ---- S^T[32 tokens][8 heads] = K Q^T
+    float sacc[2][4];
 #pragma unroll
-    for (int i = 0; i < KSTEPS; ++i) oacc[i][0] = oacc[i][1] = oacc[i][2] = oacc[i][3] = 0.f;
-    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-
-    for (int j = 0; j < nblk; ++j) {
-      const int s = j % NSTAGES;
-      mbar_wait(&bars[s], (parity >> s) & 1u);
-      parity ^= 1u << s;
-      const uint32_t kbase = smem_u32(my_tiles + (size_t)s * 2 * TILE);
-      const uint32_t vbase = kbase + TILE;
-      const int nvalid = ctx - (blk0 + j) * BS;  // >= 1; >= 32 for all but the last block
-
-      // ---- S^T[32 tokens][8 heads] = K Q^T
-      float sacc[2][4];
+    for (int mt = 0; mt < 2; ++mt) {
+      sacc[mt][0] = sacc[mt][1] = sacc[mt][2] = sacc[mt][3] = 0.f;
 #pragma unroll
-      for (int mt = 0; mt < 2; ++mt) {
-        sacc[mt][0] = sacc[mt][1] = sacc[mt][2] = sacc[mt][3] = 0.f;
-#pragma unroll
-        for (int ks = 0; ks < KSTEPS; ++ks) {
-          uint32_t a[4];
-          ldmatrix_x4(a, tile_addr(kbase, mt * 16 + (lane & 15), ks * 2 + (lane >> 4)));
-          mma_bf16_16816(sacc[mt], a, qb[ks][0], qb[ks][1]);
-        }
+      for (int ks = 0; ks < KSTEPS; ++ks) {
+        uint32_t a[4];
+        ldmatrix_x4(a, tile_addr(kbase, mt * 16 + (lane & 15), ks * 2 + (lane >> 4)));
+        mma_bf16_16816(sacc[mt], a, qb[ks][0], qb[ks][1]);
       }
-      // ---- online softmax, per head (2 heads per lane: h0, h0+1), log2 domain
-      float bm0 = -INFINITY, bm1 = -INFINITY;
-#pragma unroll
-      for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-        for (int hf = 0; hf < 2; ++hf) {
-          const bool ok = mt * 16 + hf * 8 + (lane >> 2) < nvalid;
-          float x0 = ok ? sacc[mt][hf * 2] * scale_log2 : -INFINITY;
-          float x1 = ok ? sacc[mt][hf * 2 + 1] * scale_log2 : -INFINITY;
-          sacc[mt][hf * 2] = x0;
-          sacc[mt][hf * 2 + 1] = x1;
-          bm0 = fmaxf(bm0, x0);
-          bm1 = fmaxf(bm1, x1);
-        }
-#pragma unroll
-      for (int o = 4; o <= 16; o <<= 1) {
-        bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, o));
-        bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, o));
-      }
-      const float mn0 = fmaxf(m0, bm0), mn1 = fmaxf(m1, bm1);
-      const float r0 = mn0 == -INFINITY ? 0.f : mn0, r1 = mn1 == -INFINITY ? 0.f : mn1;
-      const float al0 = exp2f(m0 - r0), al1 = exp2f(m1 - r1);
-      m0 = mn0;
-      m1 = mn1;
-      float ps0 = 0.f, ps1 = 0.f;
-      uint32_t pb[2][2];
-#pragma unroll
-      for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-        for (int hf = 0; hf < 2; ++hf) {
-          float p0 = exp2f(sacc[mt][hf * 2] - r0);
-          float p1 = exp2f(sacc[mt][hf * 2 + 1] - r1);
-          ps0 += p0;
-          ps1 += p1;
-          pb[mt][hf] = movmatrix_trans(pack_bf16(p0, p1));  // -> (head = lane/4, tokens (lane%4)*2+{0,1})
-        }
-      l0 = l0 * al0 + ps0;
-      l1 = l1 * al1 + ps1;
-      // ---- O^T[D][8 heads] = alpha * O^T + V^T P^T
-#pragma unroll
-      for (int dm = 0; dm < KSTEPS; ++dm) {
-        oacc[dm][0] *= al0;
-        oacc[dm][1] *= al1;
-        oacc[dm][2] *= al0;
-        oacc[dm][3] *= al1;
-#pragma unroll
-        for (int ks = 0; ks < 2; ++ks) {
-          uint32_t a[4];
-          ldmatrix_x4_trans(a, tile_addr(vbase, ks * 16 + (lane & 7) + ((lane >> 4) & 1) * 8, dm * 2 + ((lane >> 3) & 1)));
-          mma_bf16_16816(oacc[dm], a, pb[ks][0], pb[ks][1]);
-        }
-      }
-      __syncwarp();
-      if (j + NSTAGES < nblk) issue(s, j + NSTAGES);
     }
-
-    // ---- partial (unnormalised O, running max m in log2 units, sum l) for this chunk
+    // ---- online softmax, per head (2 heads per lane: h0, h0+1), log2 domain
+    float bm0 = -INFINITY, bm1 = -INFINITY;
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+        const bool ok = mt * 16 + hf * 8 + (lane >> 2) < nvalid;
+        float x0 = ok ? sacc[mt][hf * 2] * scale_log2 : -INFINITY;
+        float x1 = ok ? sacc[mt][hf * 2 + 1] * scale_log2 : -INFINITY;
+        sacc[mt][hf * 2] = x0;
+        sacc[mt][hf * 2 + 1] = x1;
+        bm0 = fmaxf(bm0, x0);
+        bm1 = fmaxf(bm1, x1);
+      }
 #pragma unroll
     for (int o = 4; o <= 16; o <<= 1) {
-      l0 += __shfl_xor_sync(0xffffffffu, l0, o);
-      l1 += __shfl_xor_sync(0xffffffffu, l1, o);
+      bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, o));
+      bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, o));
     }
-    const int d0 = lane >> 2;
-    if (h0 < G) {
-      int64_t base = ((int64_t)(b * Hq + kvh * G + h0) * max_chunks + chunk);
+    const float mn0 = fmaxf(m0, bm0), mn1 = fmaxf(m1, bm1);
+    const float r0 = mn0 == -INFINITY ? 0.f : mn0, r1 = mn1 == -INFINITY ? 0.f : mn1;
+    const float al0 = exp2f(m0 - r0), al1 = exp2f(m1 - r1);
+    m0 = mn0;
+    m1 = mn1;
+    float ps0 = 0.f, ps1 = 0.f;
+    uint32_t pb[2][2];
 #pragma unroll
-      for (int dm = 0; dm < KSTEPS; ++dm) {
-        part_o[base * D + dm * 16 + d0] = oacc[dm][0];
-        part_o[base * D + dm * 16 + d0 + 8] = oacc[dm][2];
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+        float p0 = exp2f(sacc[mt][hf * 2] - r0);
+        float p1 = exp2f(sacc[mt][hf * 2 + 1] - r1);
+        ps0 += p0;
+        ps1 += p1;
+        pb[mt][hf] = movmatrix_trans(pack_bf16(p0, p1));  // -> (head = lane/4, tokens (lane%4)*2+{0,1})
       }
-      if (d0 == 0) {
-        part_ml[base * 2] = m0;
-        part_ml[base * 2 + 1] = l0;
+    l0 = l0 * al0 + ps0;
+    l1 = l1 * al1 + ps1;
+    // ---- O^T[D][8 heads] = alpha * O^T + V^T P^T
+#pragma unroll
+    for (int dm = 0; dm < KSTEPS; ++dm) {
+      oacc[dm][0] *= al0;
+      oacc[dm][1] *= al1;
+      oacc[dm][2] *= al0;
+      oacc[dm][3] *= al1;
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks) {
+        uint32_t a[4];
+        ldmatrix_x4_trans(a, tile_addr(vbase, ks * 16 + (lane & 7) + ((lane >> 4) & 1) * 8, dm * 2 + ((lane >> 3) & 1)));
+        mma_bf16_16816(oacc[dm], a, pb[ks][0], pb[ks][1]);
       }
     }
-    if (h0 + 1 < G) {
-      int64_t base = ((int64_t)(b * Hq + kvh * G + h0 + 1) * max_chunks + chunk);
+    __syncwarp();
+    if (g + NSTAGES < g1) issue(s, rel + NSTAGES);
+
+    // ---- end of this worker's part of the pair: park the partial (unnormalised O, running max in log2 units, sum)
+    const bool pair_done = cur.blk + 1 == cur.nblk;
+    if (pair_done || g + 1 == g1) {
+      float t0 = l0, t1 = l1;
 #pragma unroll
-      for (int dm = 0; dm < KSTEPS; ++dm) {
-        part_o[base * D + dm * 16 + d0] = oacc[dm][1];
-        part_o[base * D + dm * 16 + d0 + 8] = oacc[dm][3];
+      for (int o = 4; o <= 16; o <<= 1) {
+        t0 += __shfl_xor_sync(0xffffffffu, t0, o);
+        t1 += __shfl_xor_sync(0xffffffffu, t1, o);
       }
-      if (d0 == 0) {
-        part_ml[base * 2] = m1;
-        part_ml[base * 2 + 1] = l1;
+      const int pair_start = Hkv * pre[cur.b] + cur.kvh * cur.nblk;
+      const int part = w - pair_start / R;
+      const int d0 = lane >> 2;
+      if (h0 < G) {
+        int64_t base = ((int64_t)(cur.b * Hq + cur.kvh * G + h0) * max_parts + part);
+#pragma unroll
+        for (int dm = 0; dm < KSTEPS; ++dm) {
+          part_o[base * D + dm * 16 + d0] = oacc[dm][0];
+          part_o[base * D + dm * 16 + d0 + 8] = oacc[dm][2];
+        }
+        if (d0 == 0) {
+          part_ml[base * 2] = m0;
+          part_ml[base * 2 + 1] = t0;
+        }
       }
+      if (h0 + 1 < G) {
+        int64_t base = ((int64_t)(cur.b * Hq + cur.kvh * G + h0 + 1) * max_parts + part);
+#pragma unroll
+        for (int dm = 0; dm < KSTEPS; ++dm) {
+          part_o[base * D + dm * 16 + d0] = oacc[dm][1];
+          part_o[base * D + dm * 16 + d0 + 8] = oacc[dm][3];
+        }
+        if (d0 == 0) {
+          part_ml[base * 2] = m1;
+          part_ml[base * 2 + 1] = t1;
+        }
+      }
+      fresh = true;
+    }
+    // ---- advance the cursor
+    if (pair_done) {
+      cur.blk = 0;
+      if (++cur.kvh == Hkv) {
+        cur.kvh = 0;
+        do {
+          ++cur.b;
+        } while (cur.b < B && pre[cur.b + 1] == pre[cur.b]);
+        if (cur.b < B) {
+          cur.nblk = pre[cur.b + 1] - pre[cur.b];
+          ctx = ctx_lens[cur.b];
+        }
+      }
+    } else {
+      ++cur.blk;
     }
   }
 }
 
-// merge the per-chunk partials: out = sum_i 2^(m_i - M) O_i / sum_i 2^(m_i - M) l_i
-template <int D>
-__global__ void __launch_bounds__(D) paged_attn_combine_kernel(const float* __restrict__ part_o,
-                                                               const float* __restrict__ part_ml,
-                                                               const int32_t* __restrict__ ctx_lens,
-                                                               __nv_bfloat16* __restrict__ out, int Hq, int max_chunks,
-                                                               int chunk_blocks) {
-  const int bh = blockIdx.x, b = bh / Hq, d = threadIdx.x;
-  const int ctx = ctx_lens[b];
-  const int nblk = (ctx + BS - 1) / BS;
-  const int nch = (nblk + chunk_blocks - 1) / chunk_blocks;
-  const float* po = part_o + (int64_t)bh * max_chunks * D;
-  const float* pml = part_ml + (int64_t)bh * max_chunks * 2;
-  float M = -INFINITY;
-  for (int c = 0; c < nch; ++c) M = fmaxf(M, pml[2 * c]);
-  float acc = 0.f, L = 0.f;
-  for (int c = 0; c < nch; ++c) {
-    float w = exp2f(pml[2 * c] - M);
-    acc += w * po[(int64_t)c * D + d];
-    L += w * pml[2 * c + 1];
+// Merge the per-worker partials of one token and (optionally) quantise the token's attention output for the o_proj
+// GEMM in the same pass:  out = sum_i 2^(m_i - M) O_i / sum_i 2^(m_i - M) l_i, rounded to bf16; then per-token
+// scale = max|out| / qmax, q = rn(out / scale) exactly as quantize_per_token does on the bf16 tensor.
+constexpr int COMB_THREADS = 256;
+constexpr int COMB_MAXV = 4;  // 8-element vectors per thread -> Hq*D <= 8192
+
+template <int QD>
+__global__ void __launch_bounds__(COMB_THREADS)
+    paged_attn_combine_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
+                              const int32_t* __restrict__ ctx_lens, __nv_bfloat16* __restrict__ out,
+                              uint2* __restrict__ out_q, float* __restrict__ out_scale, int B, int Hq, int Hkv, int D,
+                              int max_parts, int min_quota, int max_blocks, int nworkers) {
+  griddep_launch();
+  griddep_wait();
+  __shared__ int sh_i[2][32];
+  __shared__ float sh_f[32];
+  const int b = blockIdx.x;
+  // blocks before this sequence and in total (same arithmetic as the main kernel's prefix table)
+  int before = 0, all = 0;
+  for (int i = threadIdx.x; i < B; i += COMB_THREADS) {
+    int n = blocks_of(ctx_lens[i], max_blocks);
+    all += n;
+    if (i < b) before += n;
   }
-  out[(int64_t)bh * D + d] = __float2bfloat16_rn(nch > 0 && L > 0.f ? acc / L : 0.f);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    before += __shfl_xor_sync(0xffffffffu, before, o);
+    all += __shfl_xor_sync(0xffffffffu, all, o);
+  }
+  const int wid = threadIdx.x >> 5, ln = threadIdx.x & 31;
+  if (ln == 0) {
+    sh_i[0][wid] = before;
+    sh_i[1][wid] = all;
+  }
+  __syncthreads();
+  before = all = 0;
+  for (int i = 0; i < COMB_THREADS / 32; ++i) {
+    before += sh_i[0][i];
+    all += sh_i[1][i];
+  }
+  const int nblk = blocks_of(ctx_lens[b], max_blocks);
+  const int total = Hkv * all;
+  int R = (total + nworkers - 1) / nworkers;
+  if (R < min_quota) R = min_quota;
+  const int G = Hq / Hkv;
+  const int dvec = D / 8, nvec = Hq * dvec;
+
+  float y[COMB_MAXV][8];
+  float amax = 0.f;
+#pragma unroll
+  for (int i = 0; i < COMB_MAXV; ++i) {
+    const int vi = threadIdx.x + i * COMB_THREADS;
+    if (vi < nvec) {
+      const int h = vi / dvec, dv = vi % dvec;
+      const int pair_start = Hkv * before + (h / G) * nblk;
+      const int nparts = nblk > 0 ? (pair_start + nblk - 1) / R - pair_start / R + 1 : 0;
+      const float* pml = part_ml + (int64_t)(b * Hq + h) * max_parts * 2;
+      const float* po = part_o + (int64_t)(b * Hq + h) * max_parts * D + dv * 8;
+      float Mx = -INFINITY;
+      for (int c = 0; c < nparts; ++c) Mx = fmaxf(Mx, pml[2 * c]);
+      float acc[8], L = 0.f;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+      for (int c = 0; c < nparts; ++c) {
+        const float wgt = exp2f(pml[2 * c] - Mx);
+        const float4 a0 = *reinterpret_cast<const float4*>(po + (int64_t)c * D);
+        const float4 a1 = *reinterpret_cast<const float4*>(po + (int64_t)c * D + 4);
+        acc[0] += wgt * a0.x; acc[1] += wgt * a0.y; acc[2] += wgt * a0.z; acc[3] += wgt * a0.w;
+        acc[4] += wgt * a1.x; acc[5] += wgt * a1.y; acc[6] += wgt * a1.z; acc[7] += wgt * a1.w;
+        L += wgt * pml[2 * c + 1];
+      }
+      const bool ok = nparts > 0 && L > 0.f;
+      uint32_t packed[4];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float v = ok ? acc[e] / L : 0.f;
+        y[i][e] = __bfloat162float(__float2bfloat16_rn(v));
+        amax = fmaxf(amax, fabsf(y[i][e]));
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) packed[e] = pack_bf16(y[i][2 * e], y[i][2 * e + 1]);
+      if (out) *reinterpret_cast<uint4*>(out + ((int64_t)b * Hq + h) * D + dv * 8) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+    }
+  }
+  if constexpr (QD != B200_BF16) {
+    amax = warp_max(amax);
+    __syncthreads();
+    if (ln == 0) sh_f[wid] = amax;
+    __syncthreads();
+    amax = 0.f;
+    for (int i = 0; i < COMB_THREADS / 32; ++i) amax = fmaxf(amax, sh_f[i]);
+    const float qmax = QD == B200_FP8_E4M3 ? 448.f : 127.f;
+    const float scale = amax > 0.f ? __fdiv_rn(amax, qmax) : 1.f;
+    if (threadIdx.x == 0) out_scale[b] = scale;
+#pragma unroll
+    for (int i = 0; i < COMB_MAXV; ++i) {
+      const int vi = threadIdx.x + i * COMB_THREADS;
+      if (vi < nvec) {
+        uint32_t lo = 0, hi = 0;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) lo |= (uint32_t)quant_byte<QD>(y[i][e], scale) << (8 * e);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) hi |= (uint32_t)quant_byte<QD>(y[i][4 + e], scale) << (8 * e);
+        out_q[(int64_t)b * nvec + vi] = make_uint2(lo, hi);
+      }
+    }
+  }
 }
 
 // ============================================================ prefix-cached prefill (one sequence)
@@ -261,6 +442,8 @@ __global__ void __launch_bounds__(128)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int head = blockIdx.y, kvh = head / (Hq / Hkv);
   const int q0 = blockIdx.x * 64;
+  griddep_launch();
+  griddep_wait();
   if (threadIdx.x == 0) {
     for (int s = 0; s < NST; ++s) {
       mbar_init(&full[s], 1);
@@ -440,49 +623,53 @@ int pool_tmap(const void* pool, int num_blocks, int Hkv, int D, CUtensorMap* out
 
 constexpr int DEC_WARPS = 4;
 constexpr int DEC_STAGES = 3;
+constexpr int DEC_MIN_QUOTA = 4;  // blocks per worker below which spreading further only adds partials
 
-int pick_chunk_blocks(int B, int Hkv, int max_blocks) {
-  int workers = sm_count() * DEC_WARPS;
-  int best = 32;
-  double best_cost = 1e30;
-  for (int cb = 32; cb >= 2; cb >>= 1) {
-    int c = cb < max_blocks ? cb : max_blocks;
-    long items = (long)B * Hkv * ((max_blocks + c - 1) / c);
-    long rounds = (items + workers - 1) / workers;
-    double cost = (double)rounds * (c + 1.5);
-    if (cost < best_cost - 1e-9) {
-      best_cost = cost;
-      best = c;
-    }
-  }
-  return best;
+struct DecodePlan {
+  int min_quota, max_parts, grid;
+  size_t ws_bytes;
+};
+DecodePlan plan_decode(int B, int Hq, int Hkv, int D, int max_blocks, int min_quota) {
+  DecodePlan p;
+  p.min_quota = min_quota > 0 ? min_quota : DEC_MIN_QUOTA;
+  p.max_parts = (max_blocks + p.min_quota - 1) / p.min_quota + 1;
+  long max_total = (long)B * Hkv * max_blocks;
+  long want = (max_total + (long)p.min_quota * DEC_WARPS - 1) / ((long)p.min_quota * DEC_WARPS);
+  p.grid = (int)(want < sm_count() ? want : sm_count());
+  if (p.grid < 1) p.grid = 1;
+  p.ws_bytes = (size_t)B * Hq * p.max_parts * (D + 2) * sizeof(float);
+  return p;
 }
 
 template <int D>
 int launch_decode(const CUtensorMap& km, const CUtensorMap& vm, const void* q, int64_t q_stride, const int32_t* bt,
-                  int64_t bt_stride, const int32_t* row_ids, const int32_t* ctx_lens, void* out, float* part_o,
-                  float* part_ml, int B, int Hq, int Hkv, int max_chunks, int chunk_blocks, float scale,
-                  cudaStream_t stream) {
+                  int64_t bt_stride, const int32_t* row_ids, const int32_t* ctx_lens, void* out, void* out_q,
+                  float* out_scale, int q_dtype, float* part_o, float* part_ml, int B, int Hq, int Hkv, int max_blocks,
+                  const DecodePlan& p, float scale, cudaStream_t stream) {
   auto kern = paged_attn_decode_kernel<D, DEC_STAGES, DEC_WARPS>;
-  constexpr size_t smem = (size_t)DEC_WARPS * DEC_STAGES * 2 * BS * D * 2 + DEC_WARPS * DEC_STAGES * 8 + 1024;
+  const size_t smem = (size_t)DEC_WARPS * DEC_STAGES * 2 * BS * D * 2 + DEC_WARPS * DEC_STAGES * 8 + (size_t)(B + 1) * 4 + 1024;
+  constexpr size_t smem_max = (size_t)DEC_WARPS * DEC_STAGES * 2 * BS * D * 2 + DEC_WARPS * DEC_STAGES * 8 + (size_t)(DEC_MAX_B + 1) * 4 + 1024;
   static bool attr_done = false;
   if (!attr_done) {
-    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
     attr_done = true;
   }
-  long items = (long)B * Hkv * max_chunks;
-  int grid = (int)((items + DEC_WARPS - 1) / DEC_WARPS);
-  if (grid > sm_count()) grid = sm_count();
-  if (grid < 1) grid = 1;
-  kern<<<grid, DEC_WARPS * 32, smem, stream>>>(km, vm, (const __nv_bfloat16*)q, q_stride, bt, bt_stride, row_ids, ctx_lens,
-                                               part_o, part_ml, B, Hq, Hkv, max_chunks, chunk_blocks,
-                                               scale * 1.4426950408889634f);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
-  paged_attn_combine_kernel<D><<<B * Hq, D, 0, stream>>>(part_o, part_ml, ctx_lens, (__nv_bfloat16*)out, Hq, max_chunks,
-                                                        chunk_blocks);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
+  B200_CUDA_OK(launch_kernel(kern, dim3(p.grid), dim3(DEC_WARPS * 32), smem, stream, km, vm, (const __nv_bfloat16*)q,
+                             q_stride, bt, bt_stride, row_ids, ctx_lens, part_o, part_ml, B, Hq, Hkv, p.max_parts,
+                             p.min_quota, max_blocks, scale * 1.4426950408889634f));
+  const int nworkers = p.grid * DEC_WARPS;
+  if (q_dtype == B200_FP8_E4M3)
+    B200_CUDA_OK(launch_kernel(paged_attn_combine_kernel<B200_FP8_E4M3>, dim3(B), dim3(COMB_THREADS), 0, stream, part_o,
+                               part_ml, ctx_lens, (__nv_bfloat16*)out, (uint2*)out_q, out_scale, B, Hq, Hkv, D, p.max_parts,
+                               p.min_quota, max_blocks, nworkers));
+  else if (q_dtype == B200_INT8)
+    B200_CUDA_OK(launch_kernel(paged_attn_combine_kernel<B200_INT8>, dim3(B), dim3(COMB_THREADS), 0, stream, part_o,
+                               part_ml, ctx_lens, (__nv_bfloat16*)out, (uint2*)out_q, out_scale, B, Hq, Hkv, D, p.max_parts,
+                               p.min_quota, max_blocks, nworkers));
+  else
+    B200_CUDA_OK(launch_kernel(paged_attn_combine_kernel<B200_BF16>, dim3(B), dim3(COMB_THREADS), 0, stream, part_o,
+                               part_ml, ctx_lens, (__nv_bfloat16*)out, (uint2*)nullptr, (float*)nullptr, B, Hq, Hkv, D,
+                               p.max_parts, p.min_quota, max_blocks, nworkers));
   return B200_OK;
 }
 
@@ -497,10 +684,8 @@ int launch_prefill(const CUtensorMap& km, const CUtensorMap& vm, const void* q, 
     attr_done = true;
   }
   dim3 grid((S_new + 63) / 64, Hq);
-  kern<<<grid, 128, smem, stream>>>(km, vm, (const __nv_bfloat16*)q, q_stride, bt_row, (__nv_bfloat16*)out, S_new,
-                                    computed_len, Hq, Hkv, scale * 1.4426950408889634f);
-  B200_CUDA_OK(cudaGetLastError());
-  B200_LAUNCHED(1);
+  B200_CUDA_OK(launch_kernel(kern, grid, dim3(128), smem, stream, km, vm, (const __nv_bfloat16*)q, q_stride, bt_row,
+                             (__nv_bfloat16*)out, S_new, computed_len, Hq, Hkv, scale * 1.4426950408889634f));
   return B200_OK;
 }
 
@@ -508,35 +693,36 @@ int launch_prefill(const CUtensorMap& km, const CUtensorMap& vm, const void* q, 
 
 extern "C" {
 
-size_t b200_paged_attn_decode_workspace_bytes(int B, int Hq, int Hkv, int D, int max_blocks, int chunk_blocks) {
+size_t b200_paged_attn_decode_workspace_bytes(int B, int Hq, int Hkv, int D, int max_blocks, int min_quota) {
   if (B <= 0 || Hq <= 0 || Hkv <= 0 || D <= 0 || max_blocks <= 0) return 0;
-  // sized for the smallest chunk the heuristic may pick (2 blocks) unless the caller pins chunk_blocks
-  int cb = chunk_blocks > 0 ? chunk_blocks : 2;
-  size_t max_chunks = (size_t)(max_blocks + cb - 1) / cb;
-  return (size_t)B * Hq * max_chunks * (D + 2) * sizeof(float);
+  return plan_decode(B, Hq, Hkv, D, max_blocks, min_quota).ws_bytes;
 }
 
 int b200_paged_attn_decode(const void* q, int64_t q_token_stride, const void* k_pool, const void* v_pool, int num_blocks,
                            const int32_t* block_table, int64_t bt_row_stride, const int32_t* row_ids,
-                           const int32_t* ctx_lens, void* out, void* workspace, size_t workspace_bytes, int B, int Hq,
-                           int Hkv, int D, int block_size, int max_blocks, int chunk_blocks, float scale, void* stream) {
-  B200_REQUIRE(q && k_pool && v_pool && block_table && ctx_lens && out && workspace, "paged_attn_decode: null pointer");
+                           const int32_t* ctx_lens, void* out, void* out_q, float* out_scale, int q_dtype, void* workspace,
+                           size_t workspace_bytes, int B, int Hq, int Hkv, int D, int block_size, int max_blocks,
+                           int min_quota, float scale, void* stream) {
+  B200_REQUIRE(q && k_pool && v_pool && block_table && ctx_lens && workspace, "paged_attn_decode: null pointer");
+  B200_REQUIRE(q_dtype == B200_BF16 || q_dtype == B200_FP8_E4M3 || q_dtype == B200_INT8, "paged_attn_decode: bad q_dtype %d", q_dtype);
+  B200_REQUIRE(q_dtype == B200_BF16 ? out != nullptr : (out_q && out_scale), "paged_attn_decode: output pointer(s) missing");
   B200_REQUIRE(block_size == BS, "paged_attn_decode: block_size must be 32 (pa_block_size), got %d", block_size);
   B200_REQUIRE(Hkv > 0 && Hq % Hkv == 0 && Hq / Hkv <= 8, "paged_attn_decode: need Hq %% Hkv == 0 and group <= 8 (Hq=%d Hkv=%d)", Hq, Hkv);
   B200_REQUIRE(q_token_stride % 2 == 0 && ((uintptr_t)q & 3) == 0, "paged_attn_decode: q must be 4-byte aligned");
+  B200_REQUIRE(B <= DEC_MAX_B, "paged_attn_decode: at most %d sequences per call (got %d)", DEC_MAX_B, B);
   if (D != 64 && D != 128) {
     set_last_error("paged_attn_decode: head_dim %d unsupported (64 or 128)", D);
     return B200_ERR_UNSUPPORTED;
   }
+  if (Hq * D > 8 * COMB_THREADS * COMB_MAXV) {
+    set_last_error("paged_attn_decode: Hq*D = %d exceeds %d", Hq * D, 8 * COMB_THREADS * COMB_MAXV);
+    return B200_ERR_UNSUPPORTED;
+  }
   if (B <= 0) return B200_OK;
   B200_REQUIRE(max_blocks > 0, "paged_attn_decode: max_blocks must be positive");
-  int cb = chunk_blocks > 0 ? chunk_blocks : pick_chunk_blocks(B, Hkv, max_blocks);
-  if (cb > 32) cb = 32;
-  if (cb > max_blocks) cb = max_blocks;
-  int max_chunks = (max_blocks + cb - 1) / cb;
-  size_t need = (size_t)B * Hq * max_chunks * (D + 2) * sizeof(float);
-  if (workspace_bytes < need) {
-    set_last_error("paged_attn_decode: workspace %zu < %zu bytes", workspace_bytes, need);
+  DecodePlan p = plan_decode(B, Hq, Hkv, D, max_blocks, min_quota);
+  if (workspace_bytes < p.ws_bytes) {
+    set_last_error("paged_attn_decode: workspace %zu < %zu bytes", workspace_bytes, p.ws_bytes);
     return B200_ERR_WORKSPACE;
   }
   CUtensorMap km, vm;
@@ -545,13 +731,13 @@ int b200_paged_attn_decode(const void* q, int64_t q_token_stride, const void* k_
   rc = pool_tmap(v_pool, num_blocks, Hkv, D, &vm);
   if (rc) return rc;
   float* part_o = (float*)workspace;
-  float* part_ml = part_o + (size_t)B * Hq * max_chunks * D;
+  float* part_ml = part_o + (size_t)B * Hq * p.max_parts * D;
   cudaStream_t s = (cudaStream_t)stream;
   if (D == 128)
-    return launch_decode<128>(km, vm, q, q_token_stride, block_table, bt_row_stride, row_ids, ctx_lens, out, part_o,
-                              part_ml, B, Hq, Hkv, max_chunks, cb, scale, s);
-  return launch_decode<64>(km, vm, q, q_token_stride, block_table, bt_row_stride, row_ids, ctx_lens, out, part_o, part_ml,
-                           B, Hq, Hkv, max_chunks, cb, scale, s);
+    return launch_decode<128>(km, vm, q, q_token_stride, block_table, bt_row_stride, row_ids, ctx_lens, out, out_q,
+                              out_scale, q_dtype, part_o, part_ml, B, Hq, Hkv, max_blocks, p, scale, s);
+  return launch_decode<64>(km, vm, q, q_token_stride, block_table, bt_row_stride, row_ids, ctx_lens, out, out_q, out_scale,
+                           q_dtype, part_o, part_ml, B, Hq, Hkv, max_blocks, p, scale, s);
 }
 
 int b200_paged_attn_prefill(const void* q, int64_t q_token_stride, const void* k_pool, const void* v_pool, int num_blocks,

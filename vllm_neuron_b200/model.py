@@ -126,6 +126,13 @@ class _Linear:
         self.bias = None if bias is None else bias.to(device).contiguous()
         self.quant = quant
         self.n, self.k = self.w.shape
+        self.interleaved = False
+
+    def interleave_gate_up(self):
+        """Store [gate; up] rows as 16 gate / 16 up groups (what the fused SiLU*mul GEMM epilogue reads)."""
+        self.w, self.scale, self.bias = ops.interleave_gate_up(self.w, self.scale, self.bias)
+        self.interleaved = True
+        return self
 
 
 @dataclass
@@ -176,7 +183,7 @@ class B200CausalLM:
                     "post_norm": lw["post_norm"].to(dev).contiguous(),
                     "qkv": _Linear(lw["wqkv"], quant, dev, row_slices=qkv_rows, bias=lw.get("bqkv")),
                     "o": _Linear(lw["wo"], quant, dev, col_slice=plan["o_cols"]),
-                    "gu": _Linear(lw["wgu"], quant, dev, row_slices=gu_rows),
+                    "gu": _Linear(lw["wgu"], quant, dev, row_slices=gu_rows).interleave_gate_up(),
                     "down": _Linear(lw["wdown"], quant, dev, col_slice=plan["down_cols"]),
                 }
             )
@@ -206,7 +213,8 @@ class B200CausalLM:
             for lin in self._linears():
                 dt = {"bf16": 0, "fp8": 1, "int8": 2}[lin.quant]
                 nbytes = max(nbytes, ops.gemm_workspace_bytes(m, lin.n, lin.k, dt, 0))
-        self.gemm_ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        # zero-filled once: the stream-K fix-up counters at its head are left at zero by every GEMM
+        self.gemm_ws = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
         self.attn_ws = torch.empty(
             max(16, ops.paged_attn_decode_workspace_bytes(self.max_num_seqs, self.hq, self.hkv, self.d, self.max_blocks, 0)),
             dtype=torch.uint8, device=dev)
@@ -236,19 +244,22 @@ class B200CausalLM:
             qkv = self._linear(L["qkv"], h, hs)
             kp, vp = self.kv[li][0], self.kv[li][1]
             ops.rope_kv_write(qkv, positions, self.cos, self.sin, kp, vp, slot_mapping, self.hq)
-            a = attn_fn(qkv[:, :qd].unflatten(1, (self.hq, self.d)), kp, vp).reshape(t, qd)
+            a = attn_fn(qkv[:, :qd].unflatten(1, (self.hq, self.d)), kp, vp, q)
             if q is None:
-                x = self._all_reduce(self._linear(L["o"], a, None, x if first else None))
+                x = self._all_reduce(self._linear(L["o"], a.reshape(t, qd), None, x if first else None))
             else:
-                aq, a_s = ops.quantize_per_token(a, q)
-                x = self._all_reduce(self._linear(L["o"], aq, a_s, x if first else None))
+                if not isinstance(a, tuple):  # prefill attention returns bf16; decode quantises in its merge kernel
+                    a = ops.quantize_per_token(a.reshape(t, qd), q)
+                x = self._all_reduce(self._linear(L["o"], a[0], a[1], x if first else None))
             h2, h2s = self._norm(x, L["post_norm"])
-            gu = self._linear(L["gu"], h2, h2s)
+            gu = L["gu"]
+            # gate/up GEMM with SiLU(gate)*up in the epilogue; the per-tile maxima feed the per-token quantisation
+            act, tile_amax = ops.gemm_silu_mul(h2, gu.w, h2s, gu.scale, gu.bias, workspace=self.gemm_ws)
             if q is None:
-                x = self._all_reduce(self._linear(L["down"], ops.silu_mul(gu), None, x if first else None))
+                x = self._all_reduce(self._linear(L["down"], act, None, x if first else None))
             else:
-                act, act_s = ops.silu_mul(gu, quant=q)
-                x = self._all_reduce(self._linear(L["down"], act, act_s, x if first else None))
+                aq, a_s = ops.quantize_per_token(act, q, tile_amax=tile_amax)
+                x = self._all_reduce(self._linear(L["down"], aq, a_s, x if first else None))
         return x
 
     def _sample(self, x_rows):
@@ -290,9 +301,9 @@ class B200CausalLM:
                               bufs.ctx_lens, self.block_size)
         x = ops.embedding(bufs.tokens, self.embed)
 
-        def attn(qv, kp, vp):
+        def attn(qv, kp, vp, quant):
             return ops.paged_attn_decode(qv, kp, vp, self.block_table, bufs.ctx_lens, self.scale, workspace=self.attn_ws,
-                                         row_ids=bufs.row_ids, max_blocks=max_ctx_blocks)
+                                         row_ids=bufs.row_ids, max_blocks=max_ctx_blocks, quant=quant)
 
         x = self._layers(x, bufs.positions, bufs.slot_mapping, attn)
         ids, _ = self._sample(x)
@@ -344,7 +355,7 @@ class B200CausalLM:
         slots, positions = slot_full[:s_new], pos_full[:s_new]
         x = ops.embedding(new_tokens, self.embed)
 
-        def attn(qv, kp, vp):
+        def attn(qv, kp, vp, quant):
             return ops.paged_attn_prefill(qv, kp, vp, bt_row, computed_len, self.scale)
 
         x = self._layers(x, positions, slots, attn)

@@ -79,6 +79,11 @@ def device_check(device: int = 0):
     check(_cabi.load().b200_device_check(device), "b200_device_check")
 
 
+def set_pdl(enabled: bool) -> bool:
+    """Programmatic dependent launch on/off for every kernel of the library; returns the previous setting."""
+    return bool(_cabi.load().b200_set_pdl(1 if enabled else 0))
+
+
 def launch_count() -> int:
     """Kernel launches issued through libb200_paged.so by this process so far."""
     return int(_cabi.load().b200_launch_count())
@@ -173,34 +178,41 @@ def rope_kv_write(qkv, positions, cos, sin, k_pool, v_pool, slot_mapping, num_q_
 
 
 # ------------------------------------------------------------------ paged attention
-def paged_attn_decode_workspace_bytes(b, hq, hkv, d, max_blocks, chunk_blocks=0) -> int:
-    return int(_cabi.load().b200_paged_attn_decode_workspace_bytes(b, hq, hkv, d, max_blocks, chunk_blocks))
+def paged_attn_decode_workspace_bytes(b, hq, hkv, d, max_blocks, min_quota=0) -> int:
+    return int(_cabi.load().b200_paged_attn_decode_workspace_bytes(b, hq, hkv, d, max_blocks, min_quota))
 
 
 def paged_attn_decode(q, k_pool, v_pool, block_table, ctx_lens, scale, out=None, workspace=None, row_ids=None,
-                      max_blocks=None, chunk_blocks=0):
-    """q [B, Hq, D] bf16 (token stride arbitrary); block_table int32 [rows, max_blocks]; ctx_lens int32 [B]."""
+                      max_blocks=None, min_quota=0, quant=None):
+    """q [B, Hq, D] bf16 (token stride arbitrary); block_table int32 [rows, max_blocks]; ctx_lens int32 [B].
+    quant None -> bf16 out [B, Hq, D]; "fp8"/"int8" -> (q [B, Hq*D], scale [B]) quantised per token in the merge kernel."""
     _cuda(q, k_pool, v_pool, block_table, ctx_lens)
     b, hq, d = q.shape
     nb, hkv, bs, d2 = k_pool.shape
     assert d == d2 and q.stride(2) == 1 and q.stride(1) == d and q.dtype == torch.bfloat16
     assert block_table.dtype == torch.int32 and ctx_lens.dtype == torch.int32
     mb = block_table.shape[1] if max_blocks is None else min(max_blocks, block_table.shape[1])
-    if out is None:
-        out = torch.empty((b, hq, d), dtype=q.dtype, device=q.device)
-    assert out.is_contiguous()
+    qd = _QDT[quant]
+    oq = osc = None
+    if qd == BF16:
+        if out is None:
+            out = torch.empty((b, hq, d), dtype=q.dtype, device=q.device)
+        assert out.is_contiguous()
+    else:
+        oq = torch.empty((b, hq * d), dtype=_TORCH_Q[qd], device=q.device)
+        osc = torch.empty((b,), dtype=torch.float32, device=q.device)
     if workspace is None:
-        workspace = torch.empty(paged_attn_decode_workspace_bytes(b, hq, hkv, d, mb, chunk_blocks), dtype=torch.uint8, device=q.device)
+        workspace = torch.empty(paged_attn_decode_workspace_bytes(b, hq, hkv, d, mb, min_quota), dtype=torch.uint8, device=q.device)
     with _k("paged_attn_decode"):
         check(
             _cabi.load().b200_paged_attn_decode(
                 _ptr(q), q.stride(0), _ptr(k_pool), _ptr(v_pool), nb, _ptr(block_table), block_table.stride(0),
-                _ptr(row_ids), _ptr(ctx_lens), _ptr(out), _ptr(workspace), workspace.numel() * workspace.element_size(),
-                b, hq, hkv, d, bs, mb, chunk_blocks, float(scale), _stream(),
+                _ptr(row_ids), _ptr(ctx_lens), _ptr(out), _ptr(oq), _ptr(osc), qd, _ptr(workspace),
+                workspace.numel() * workspace.element_size(), b, hq, hkv, d, bs, mb, min_quota, float(scale), _stream(),
             ),
             "b200_paged_attn_decode",
         )
-    return out
+    return out if qd == BF16 else (oq, osc)
 
 
 def paged_attn_prefill(q, k_pool, v_pool, block_table_row, computed_len: int, scale, out=None):
@@ -233,11 +245,16 @@ def _ab_dtype(t):
     raise _cabi.B200Error(f"unsupported GEMM operand dtype {t.dtype}")
 
 
-def gemm_workspace_bytes(m, n, k, ab_dtype, split_k=0) -> int:
-    return int(_cabi.load().b200_gemm_workspace_bytes(m, n, k, ab_dtype, split_k))
+def gemm_workspace_bytes(m, n, k, ab_dtype, max_ctas=0) -> int:
+    return int(_cabi.load().b200_gemm_workspace_bytes(m, n, k, ab_dtype, max_ctas))
 
 
-def gemm(a, w, a_scale=None, w_scale=None, bias=None, residual=None, out=None, out_dtype=torch.bfloat16, split_k=0,
+def gemm_workspace(m, n, k, ab_dtype, device, max_ctas=0):
+    """Zero-filled workspace (the fix-up counters at its head must start at zero; every call leaves them zeroed)."""
+    return torch.zeros(gemm_workspace_bytes(m, n, k, ab_dtype, max_ctas), dtype=torch.uint8, device=device)
+
+
+def gemm(a, w, a_scale=None, w_scale=None, bias=None, residual=None, out=None, out_dtype=torch.bfloat16, max_ctas=0,
          workspace=None):
     """out[M,N] = (a[M,K] @ w[N,K]^T) * a_scale[m] * w_scale[n] + bias[n] + residual[m,n]."""
     _cuda(a, w, a_scale, w_scale, bias, residual)
@@ -252,17 +269,51 @@ def gemm(a, w, a_scale=None, w_scale=None, bias=None, residual=None, out=None, o
     if residual is not None:
         assert residual.dtype == torch.bfloat16 and residual.is_contiguous() and residual.shape == (m, n)
     if workspace is None:
-        nbytes = gemm_workspace_bytes(m, n, k, dt, split_k)
-        workspace = torch.empty(nbytes, dtype=torch.uint8, device=a.device) if nbytes else None
+        workspace = gemm_workspace(m, n, k, dt, a.device, max_ctas)
     with _k(f"gemm_{_DTN[dt]}[{m}x{n}x{k}]"):
         check(
             _cabi.load().b200_gemm(
                 _ptr(a), _ptr(w), _ptr(out), _ptr(a_scale), _ptr(w_scale), _ptr(bias), _ptr(residual), m, n, k, dt, odt,
-                split_k, _ptr(workspace), 0 if workspace is None else workspace.numel() * workspace.element_size(), _stream(),
+                max_ctas, _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(),
             ),
             "b200_gemm",
         )
     return out
+
+
+def interleave_gate_up(w_gu, *others):
+    """Row permutation expected by gemm_silu_mul: [gate(I); up(I)] -> groups of 32 rows = 16 gate rows followed by the
+    16 up rows of the same channels.  Applied (load time) to the weight and to every per-row companion (scale, bias)."""
+    i = w_gu.shape[0] // 2
+    assert i % 16 == 0, "intermediate size must be a multiple of 16"
+    idx = torch.arange(i, device=w_gu.device).view(-1, 16)
+    perm = torch.cat([idx, idx + i], dim=1).reshape(-1)
+    res = [w_gu[perm].contiguous()] + [None if o is None else o[perm].contiguous() for o in others]
+    return res[0] if not others else tuple(res)
+
+
+def gemm_silu_mul(a, w_gu_interleaved, a_scale=None, w_scale=None, bias=None, max_ctas=0, workspace=None):
+    """act[M, I] = bf16(silu(bf16(gate)) * bf16(up)) with gate/up = the two halves of a @ w_gu^T (rows interleaved by
+    interleave_gate_up); also returns tile_amax [ceil(2I/128), M] for quantize_per_token."""
+    _cuda(a, w_gu_interleaved, a_scale, w_scale, bias)
+    m, k = a.shape
+    n2, k2 = w_gu_interleaved.shape
+    assert k == k2 and a.is_contiguous() and w_gu_interleaved.is_contiguous() and a.dtype == w_gu_interleaved.dtype
+    dt = _ab_dtype(a)
+    act = torch.empty((m, n2 // 2), dtype=torch.bfloat16, device=a.device)
+    n_tiles = (n2 + 127) // 128
+    tile_amax = torch.empty((n_tiles, m), dtype=torch.float32, device=a.device)
+    if workspace is None:
+        workspace = gemm_workspace(m, n2, k, dt, a.device, max_ctas)
+    with _k(f"gemm_silu_mul_{_DTN[dt]}[{m}x{n2}x{k}]"):
+        check(
+            _cabi.load().b200_gemm_silu_mul(
+                _ptr(a), _ptr(w_gu_interleaved), _ptr(act), _ptr(a_scale), _ptr(w_scale), _ptr(bias), _ptr(tile_amax),
+                m, n2, k, dt, max_ctas, _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(),
+            ),
+            "b200_gemm_silu_mul",
+        )
+    return act, tile_amax
 
 
 # ------------------------------------------------------------------ glue
@@ -303,15 +354,21 @@ def silu_mul(gate_up, quant=None):
     return q, s
 
 
-def quantize_per_token(x, quant: str):
-    _cuda(x)
+def quantize_per_token(x, quant: str, tile_amax=None):
+    """x [T, K] bf16 -> (q [T, K], scale [T]).  tile_amax [n_tiles, T] (from gemm_silu_mul) skips the row scan."""
+    _cuda(x, tile_amax)
     t, k = x.shape
     assert x.is_contiguous() and x.dtype == torch.bfloat16
     qd = _QDT[quant]
     q = torch.empty((t, k), dtype=_TORCH_Q[qd], device=x.device)
     s = torch.empty((t,), dtype=torch.float32, device=x.device)
+    nt = 0
+    if tile_amax is not None:
+        assert tile_amax.dtype == torch.float32 and tile_amax.is_contiguous() and tile_amax.shape[1] == t
+        nt = tile_amax.shape[0]
     with _k("quantize_per_token"):
-        check(_cabi.load().b200_quantize_per_token(_ptr(x), _ptr(q), _ptr(s), t, k, qd, _stream()), "b200_quantize_per_token")
+        check(_cabi.load().b200_quantize_per_token(_ptr(x), _ptr(q), _ptr(s), _ptr(tile_amax), nt, t, k, qd, _stream()),
+              "b200_quantize_per_token")
     return q, s
 
 
