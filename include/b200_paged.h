@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 2
+#define B200_ABI_VERSION 3
 
 enum {
   B200_OK = 0,
@@ -113,20 +113,23 @@ int b200_paged_attn_prefill(const void* q, int64_t q_token_stride, const void* k
  * out[M][N] = (sum_k a[m][k] * w[n][k]) * a_scale[m] * w_scale[n] + bias[n] + residual[m][n]
  * a: [M][K], w: [N][K], both `ab_dtype` (BF16 | FP8_E4M3 | INT8); scales fp32 (NULL = 1), bias bf16 [N] or NULL,
  * residual bf16 [M][N] or NULL; out_dtype BF16 | F32.
- * Persistent stream-K: max_ctas CTAs (0 = one per SM) each take an equal share of the (tile, k-block) space; tiles cut
- * by a share boundary are summed in fixed order by the last contributor.  `workspace` (b200_gemm_workspace_bytes) holds
- * the fix-up counters in its first 4 KiB: it must be ZERO-FILLED before its first use and is left zeroed by every call;
- * one workspace may serve all GEMMs issued on one stream. */
-size_t b200_gemm_workspace_bytes(int M, int N, int K, int ab_dtype, int max_ctas);
+ * M <= 128 (decode): one CTA per (128-row weight tile, K split); the `split_k` CTAs (0 = auto; 1, 2, 4 or 8) of a tile
+ *   form a thread-block cluster and are summed through distributed shared memory in fixed rank order; needs no workspace.
+ * M > 128 (prefill): persistent stream-K over min(split_k, #SM) CTAs (0 = one per SM), each an equal share of the
+ *   (tile, k-block) space; tiles cut by a share boundary are summed in fixed order by the last contributor.
+ *   `workspace` (b200_gemm_workspace_bytes) holds the fix-up counters in its first 4 KiB: it must be ZERO-FILLED before
+ *   its first use and is left zeroed by every call; one workspace may serve all GEMMs issued on one stream. */
+size_t b200_gemm_workspace_bytes(int M, int N, int K, int ab_dtype, int split_k);
 int b200_gemm(const void* a, const void* w, void* out, const float* a_scale, const float* w_scale, const void* bias,
-              const void* residual, int M, int N, int K, int ab_dtype, int out_dtype, int max_ctas, void* workspace,
+              const void* residual, int M, int N, int K, int ab_dtype, int out_dtype, int split_k, void* workspace,
               size_t workspace_bytes, void* stream);
 /* gate/up projection with SiLU(gate)*up fused into the epilogue.  w_gu [2I][K] holds, per group of 32 rows, 16 gate rows
  * followed by the 16 up rows of the same channels (w_scale / bias permuted alike); out_act [M][I] bf16 =
- * bf16(silu(bf16(gate)) * bf16(up)) exactly as b200_gemm + b200_silu_mul produce; tile_amax [ceil(2I/128)][M] fp32
- * receives max|act| per 64-channel tile for the per-token quantisation that follows (b200_quantize_per_token). */
+ * bf16(silu(bf16(gate)) * bf16(up)) exactly as b200_gemm + b200_silu_mul produce; group_amax [M][2I/32] fp32 receives
+ * max|act| over the 16 channels of every row group, for the per-token quantisation that follows
+ * (b200_quantize_per_token).  split_k as b200_gemm, at most 4 in the decode schedule. */
 int b200_gemm_silu_mul(const void* a, const void* w_gu, void* out_act, const float* a_scale, const float* w_scale,
-                       const void* bias, float* tile_amax, int M, int N2, int K, int ab_dtype, int max_ctas,
+                       const void* bias, float* group_amax, int M, int N2, int K, int ab_dtype, int split_k,
                        void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------- glue kernels of the decoder step */
@@ -137,9 +140,9 @@ int b200_rmsnorm(const void* x, const void* w, void* out_bf16, void* out_q, floa
 /* act = silu(gate) * up from gate_up [T][2I] (gate columns first); same output options as rmsnorm. */
 int b200_silu_mul(const void* gate_up, void* out_bf16, void* out_q, float* out_scale, int T, int I, int q_dtype,
                   void* stream);
-/* Dynamic per-token quantisation of x [T][K] bf16.  tile_amax [n_tiles][T] (optional, from b200_gemm_silu_mul) supplies
- * the row maxima so rows can be cut across CTAs; NULL = scan the row. */
-int b200_quantize_per_token(const void* x, void* out_q, float* out_scale, const float* tile_amax, int n_tiles, int T, int K,
+/* Dynamic per-token quantisation of x [T][K] bf16.  group_amax [T][n_groups] (optional, from b200_gemm_silu_mul)
+ * supplies partial row maxima so rows can be cut across CTAs without a scan; NULL = scan the row. */
+int b200_quantize_per_token(const void* x, void* out_q, float* out_scale, const float* group_amax, int n_groups, int T, int K,
                             int q_dtype, void* stream);
 int b200_embedding(const int64_t* tokens, const void* table, void* out, int T, int H, int V, void* stream);
 /* Greedy sampling (reference: top_k=1, temperature=1.0 for temperature 0, model_runner.py:1126-1128).

@@ -33,7 +33,7 @@ def test_header_and_binding_agree(lib):
 
 
 def test_abi_version(lib):
-    assert lib.b200_abi_version() == 2
+    assert lib.b200_abi_version() == 3
 
 
 def test_no_device_is_an_error_not_a_fallback(lib):

@@ -31,19 +31,23 @@ def _assert_close(got, want, exact_int=False):
     assert not bad.any(), f"{bad.sum().item()} / {bad.numel()} outside tolerance; max err {(got - want).abs().max().item()} rms {rms}"
 
 
-# last column = max_ctas of the persistent stream-K schedule (0 = one CTA per SM)
+# last column = split_k: cluster size along K for the decode schedule (M <= 128; 0 = auto), CTA cap for stream-K (M > 128)
 SHAPES = [
-    (64, 6144, 4096, 0),     # cfg3 qkv
-    (64, 4096, 4096, 0),     # o_proj (32 tiles cut over 148 CTAs)
+    (64, 6144, 4096, 0),     # cfg3 qkv (auto: clusters of 4)
+    (64, 4096, 4096, 0),     # o_proj (auto: clusters of 8)
     (64, 4096, 14336, 0),    # down_proj (long K)
-    (64, 1024, 512, 1),      # one CTA walks every tile: no fix-up
-    (64, 1024, 512, 5),      # 8 tiles x 4 k-blocks over 5 CTAs: spans start and end mid-tile
-    (64, 1024, 512, 32),     # one k-block per CTA: every tile has 4 contributors
+    (64, 1024, 512, 1),      # no split: epilogue straight from TMEM
+    (64, 1024, 512, 2),      # clusters of 2: 64-row slices
+    (64, 1024, 512, 4),      # clusters of 4, one k-block per CTA (fp8)
+    (33, 896, 2048, 8),      # clusters of 8: 16-row slices; N, M ragged
     (4, 2048, 2048, 0),      # TinyLlama decode batch
     (1, 256, 128, 0),        # single row, single k-block
     (128, 640, 1152, 0),     # Qwen TP=8 o-proj-like, M=128
+    (128, 640, 1152, 4),     # M=128 tile through the cluster reduction
     (100, 16032, 256, 0),    # N not a multiple of 128 (vocab shard), ragged M
-    (300, 384, 640, 0),      # M > 256: two m-tiles
+    (300, 384, 640, 0),      # M > 128: persistent stream-K, two m-tiles
+    (300, 384, 640, 5),      # stream-K over 5 CTAs: spans start and end mid-tile
+    (200, 1024, 512, 32),    # stream-K, every tile has several contributors
 ]
 
 
@@ -59,18 +63,18 @@ def test_w8a8_gemm(ops, m, n, k, ctas, kind):
     res = torch.randn(m, n, generator=g).bfloat16() if k % 1024 == 0 else None
     want = quant_ref.qgemm_ref(xq, xs, wq, ws, bias, res)
     got = ops.gemm(xq.cuda(), wq.cuda(), xs.cuda(), ws.cuda(), None if bias is None else bias.cuda(),
-                   None if res is None else res.cuda(), max_ctas=ctas)
+                   None if res is None else res.cuda(), split_k=ctas)
     torch.cuda.synchronize()
     _assert_close(got, want, exact_int=(kind == "int8"))
 
 
-@pytest.mark.parametrize("m,n,k,ctas", SHAPES[:5] + SHAPES[6:9])
+@pytest.mark.parametrize("m,n,k,ctas", SHAPES[:5] + SHAPES[6:10] + SHAPES[12:14])
 def test_bf16_gemm(ops, m, n, k, ctas):
     g = torch.Generator().manual_seed(m + n + k)
     x = torch.randn(m, k, generator=g).bfloat16()
     w = (torch.randn(n, k, generator=g) * 0.02).bfloat16()
     want = quant_ref.gemm_ref(x, w)
-    got = ops.gemm(x.cuda(), w.cuda(), max_ctas=ctas)
+    got = ops.gemm(x.cuda(), w.cuda(), split_k=ctas)
     torch.cuda.synchronize()
     _assert_close(got, want)
 
@@ -91,31 +95,45 @@ def test_fp32_out_and_linearity(ops):
     assert torch.equal(o1[:8].cpu(), want)
 
 
-def test_gemm_stream_k_is_deterministic_and_leaves_workspace_clean(ops):
-    """Fix-up sums run in fixed contributor order -> same bits every launch, with PDL on or off; the counters at the head
-    of a shared workspace are zero again after every call (that is what lets one workspace serve a whole step)."""
+def test_gemm_is_deterministic_and_stream_k_leaves_workspace_clean(ops):
+    """Partial sums are added in fixed order (cluster rank / stream-K contributor) -> same bits every launch, with PDL on
+    or off; the stream-K counters at the head of a shared workspace are zero again after every call (that is what lets
+    one workspace serve a whole step)."""
     g = torch.Generator().manual_seed(2)
-    x = torch.randn(64, 4096, generator=g).bfloat16().cuda()
     w = torch.randn(4096, 4096, generator=g).bfloat16().cuda()
-    ws = ops.gemm_workspace(64, 4096, 4096, 0, x.device)
-    a = ops.gemm(x, w, workspace=ws)
-    assert int(ws[:4096].view(torch.int32).abs().sum()) == 0
-    b = ops.gemm(x, w, workspace=ws)
-    old = ops.set_pdl(False)
-    try:
-        c = ops.gemm(x, w, workspace=ws)
-    finally:
-        ops.set_pdl(old)
-    assert torch.equal(a, b) and torch.equal(a, c)
-    assert int(ws[:4096].view(torch.int32).abs().sum()) == 0
+    for m in (64, 200):
+        x = torch.randn(m, 4096, generator=g).bfloat16().cuda()
+        ws = ops.gemm_workspace(m, 4096, 4096, 0, x.device)
+        assert (ws is None) == (m <= 128)
+        a = ops.gemm(x, w, workspace=ws)
+        b = ops.gemm(x, w, workspace=ws)
+        old = ops.set_pdl(False)
+        try:
+            c = ops.gemm(x, w, workspace=ws)
+        finally:
+            ops.set_pdl(old)
+        assert torch.equal(a, b) and torch.equal(a, c)
+        if ws is not None:
+            assert int(ws[:4096].view(torch.int32).abs().sum()) == 0
+
+
+def test_gemm_rejects_bad_split(ops):
+    from vllm_neuron_b200._cabi import B200Error
+
+    x = torch.zeros(64, 256, dtype=torch.bfloat16, device="cuda")
+    w = torch.zeros(256, 256, dtype=torch.bfloat16, device="cuda")
+    for bad in (3, 16, 8):  # not a power of two / above 8 / more CTAs than k-blocks (256 bf16 = 4 k-blocks)
+        with pytest.raises(B200Error):
+            ops.gemm(x, w, split_k=bad)
 
 
 @pytest.mark.parametrize("kind", ["bf16", "fp8", "int8"])
-@pytest.mark.parametrize("m,i,k,ctas", [(64, 14336, 4096, 0), (4, 5632, 2048, 0), (100, 96, 256, 3), (300, 1792, 512, 0)])
+@pytest.mark.parametrize("m,i,k,ctas", [(64, 14336, 4096, 0), (4, 5632, 2048, 0), (64, 5632, 2048, 2), (100, 96, 512, 4),
+                                         (128, 3584, 1024, 1), (300, 1792, 512, 0), (300, 1792, 512, 3)])
 def test_gemm_silu_mul_matches_unfused(ops, kind, m, i, k, ctas):
     """gate/up GEMM with SiLU*mul in the epilogue == b200_gemm (on the same interleaved rows) followed by b200_silu_mul,
-    bit for bit (same tiles, same stream-K cuts, fixed fix-up order), and within the GEMM tolerance of the oracle.  The per-tile
-    maxima it emits give exactly the per-token scale of the oracle's quantiser."""
+    bit for bit (same tiles, same stream-K cuts, fixed fix-up order), and within the GEMM tolerance of the oracle.  The per-group
+    maxima it emits are exact and give the per-token scale of the oracle's quantiser."""
     from oracle import kv_ref
 
     g = torch.Generator().manual_seed(m + i + k)
@@ -132,21 +150,22 @@ def test_gemm_silu_mul_matches_unfused(ops, kind, m, i, k, ctas):
     dev = lambda t: None if t is None else t.cuda()  # noqa: E731
     wi, si = ops.interleave_gate_up(dev(wq), dev(ws))
     # unfused twin on the SAME row order (same tiles, same stream-K cuts), de-interleaved before SiLU*mul
-    gu_i = ops.gemm(dev(xq), wi, dev(xs), si, max_ctas=ctas)
+    gu_i = ops.gemm(dev(xq), wi, dev(xs), si, split_k=ctas)
     idx = torch.arange(i).view(-1, 16)
     perm = torch.cat([idx, idx + i], dim=1).reshape(-1).cuda()
     gu = torch.empty_like(gu_i)
     gu[:, perm] = gu_i
     unfused = ops.silu_mul(gu)
-    act, tile_amax = ops.gemm_silu_mul(dev(xq), wi, dev(xs), si, max_ctas=ctas)
+    act, group_amax = ops.gemm_silu_mul(dev(xq), wi, dev(xs), si, split_k=ctas)
     torch.cuda.synchronize()
     assert torch.equal(act, unfused)
     got, wantf = act.float().cpu(), want.float()
     rms = wantf.pow(2).mean().sqrt().item()
     assert ((got - wantf).abs() <= 2e-2 * rms + wantf.abs() * 2.0**-6 + 1e-6).all()
-    assert torch.equal(tile_amax.max(dim=0).values.cpu(), act.float().abs().max(dim=1).values.cpu())
+    assert group_amax.shape == (m, 2 * i // 32)
+    assert torch.equal(group_amax.cpu(), act.float().abs().view(m, -1, 16).max(dim=2).values.cpu())
     for qk in ("fp8", "int8"):
-        q1, s1 = ops.quantize_per_token(act, qk, tile_amax=tile_amax)
+        q1, s1 = ops.quantize_per_token(act, qk, group_amax=group_amax)
         qw, sw = quant_ref.quantize_act_per_token(act.cpu(), qk)
         assert torch.equal(s1.cpu(), sw)
         assert torch.equal(q1.cpu().view(torch.uint8), qw.view(torch.uint8))

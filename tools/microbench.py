@@ -23,17 +23,29 @@ except Exception:
 HBM = PEAKS.get("hbm_gbs", 6650.0)
 
 
-def time_calls(fns, iters=3, warmup=1):
-    """fns: list of closures run back to back (one 'round'); returns avg ms per closure."""
+def time_calls(fns, iters=3, warmup=1, graph=True):
+    """fns: list of closures run back to back (one 'round'); returns avg ms per closure.  With graph=True the round is
+    captured into a CUDA graph and replayed, so the number is device time, not Python/ctypes launch rate."""
     for _ in range(warmup):
         for f in fns:
             f()
     torch.cuda.synchronize()
+    if graph:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for f in fns:
+                f()
+        run = g.replay
+        run()
+        torch.cuda.synchronize()
+    else:
+        def run():
+            for f in fns:
+                f()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(iters):
-        for f in fns:
-            f()
+        run()
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / (iters * len(fns))

@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200_paged.so")
 
 OK = 0
-ABI_VERSION = 2
+ABI_VERSION = 3
 BF16, FP8_E4M3, INT8, F32 = 0, 1, 2, 3
 
 _p = C.c_void_p

@@ -286,13 +286,13 @@ __global__ void __launch_bounds__(NORM_THREADS)
   }
 }
 
-// Dynamic per-token quantisation.  With tile_amax == nullptr the CTA of token t scans its row for max|x| first.
-// With tile_amax [n_tiles][T] (written by the fused gate/up GEMM epilogue) the row maximum is the max over the tiles,
+// Dynamic per-token quantisation.  With group_amax == nullptr the CTA of token t scans its row for max|x| first.
+// With group_amax [T][n_groups] (written by the fused gate/up GEMM epilogue) the row maximum is the max over the groups,
 // so the row can be cut into gridDim.y column slices that quantise independently.
 template <int QD>
 __global__ void __launch_bounds__(NORM_THREADS)
     quantize_kernel(const uint4* __restrict__ x, uint2* __restrict__ out_q, float* __restrict__ out_scale, int K,
-                    const float* __restrict__ tile_amax, int n_tiles, int T) {
+                    const float* __restrict__ group_amax, int n_groups) {
   griddep_launch();
   griddep_wait();
   __shared__ float sh[32];
@@ -300,8 +300,8 @@ __global__ void __launch_bounds__(NORM_THREADS)
   const uint4* xr = x + (int64_t)t * nvec;
   float amax = 0.f;
   int v0 = 0, v1 = nvec;
-  if (tile_amax) {
-    for (int i = threadIdx.x; i < n_tiles; i += NORM_THREADS) amax = fmaxf(amax, tile_amax[(int64_t)i * T + t]);
+  if (group_amax) {
+    for (int i = threadIdx.x; i < n_groups; i += NORM_THREADS) amax = fmaxf(amax, group_amax[(int64_t)t * n_groups + i]);
     int per = (nvec + gridDim.y - 1) / gridDim.y;
     v0 = blockIdx.y * per;
     v1 = v0 + per < nvec ? v0 + per : nvec;
@@ -499,15 +499,15 @@ int b200_silu_mul(const void* gate_up, void* out_bf16, void* out_q, float* out_s
   return B200_OK;
 }
 
-int b200_quantize_per_token(const void* x, void* out_q, float* out_scale, const float* tile_amax, int n_tiles, int T, int K,
-                            int q_dtype, void* stream) {
+int b200_quantize_per_token(const void* x, void* out_q, float* out_scale, const float* group_amax, int n_groups, int T,
+                            int K, int q_dtype, void* stream) {
   B200_REQUIRE(x && out_q && out_scale, "quantize_per_token: null pointer");
   B200_REQUIRE(K % 8 == 0, "quantize_per_token: K must be a multiple of 8");
-  B200_REQUIRE(!tile_amax || n_tiles > 0, "quantize_per_token: n_tiles must be positive with tile_amax");
+  B200_REQUIRE(!group_amax || n_groups > 0, "quantize_per_token: n_groups must be positive with group_amax");
   if (T <= 0) return B200_OK;
   cudaStream_t s = (cudaStream_t)stream;
   int slices = 1;
-  if (tile_amax) {  // no row scan needed: cut rows so that ~2 CTAs land on every SM
+  if (group_amax) {  // no row scan needed: cut rows so that ~2 CTAs land on every SM
     slices = (2 * sm_count() + T - 1) / T;
     int max_slices = (K / 8 + NORM_THREADS - 1) / NORM_THREADS;
     if (slices > max_slices) slices = max_slices;
@@ -515,10 +515,10 @@ int b200_quantize_per_token(const void* x, void* out_q, float* out_scale, const 
   }
   if (q_dtype == B200_FP8_E4M3)
     B200_CUDA_OK(launch_kernel(quantize_kernel<B200_FP8_E4M3>, dim3(T, slices), dim3(NORM_THREADS), 0, s, (const uint4*)x,
-                               (uint2*)out_q, out_scale, K, tile_amax, n_tiles, T));
+                               (uint2*)out_q, out_scale, K, group_amax, n_groups));
   else if (q_dtype == B200_INT8)
     B200_CUDA_OK(launch_kernel(quantize_kernel<B200_INT8>, dim3(T, slices), dim3(NORM_THREADS), 0, s, (const uint4*)x,
-                               (uint2*)out_q, out_scale, K, tile_amax, n_tiles, T));
+                               (uint2*)out_q, out_scale, K, group_amax, n_groups));
   else
     B200_REQUIRE(false, "quantize_per_token: bad q_dtype %d", q_dtype);
   return B200_OK;

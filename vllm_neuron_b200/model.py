@@ -253,12 +253,12 @@ class B200CausalLM:
                 x = self._all_reduce(self._linear(L["o"], a[0], a[1], x if first else None))
             h2, h2s = self._norm(x, L["post_norm"])
             gu = L["gu"]
-            # gate/up GEMM with SiLU(gate)*up in the epilogue; the per-tile maxima feed the per-token quantisation
-            act, tile_amax = ops.gemm_silu_mul(h2, gu.w, h2s, gu.scale, gu.bias, workspace=self.gemm_ws)
+            # gate/up GEMM with SiLU(gate)*up in the epilogue; the per-group maxima feed the per-token quantisation
+            act, group_amax = ops.gemm_silu_mul(h2, gu.w, h2s, gu.scale, gu.bias, workspace=self.gemm_ws)
             if q is None:
                 x = self._all_reduce(self._linear(L["down"], act, None, x if first else None))
             else:
-                aq, a_s = ops.quantize_per_token(act, q, tile_amax=tile_amax)
+                aq, a_s = ops.quantize_per_token(act, q, group_amax=group_amax)
                 x = self._all_reduce(self._linear(L["down"], aq, a_s, x if first else None))
         return x
 

@@ -245,16 +245,18 @@ def _ab_dtype(t):
     raise _cabi.B200Error(f"unsupported GEMM operand dtype {t.dtype}")
 
 
-def gemm_workspace_bytes(m, n, k, ab_dtype, max_ctas=0) -> int:
-    return int(_cabi.load().b200_gemm_workspace_bytes(m, n, k, ab_dtype, max_ctas))
+def gemm_workspace_bytes(m, n, k, ab_dtype, split_k=0) -> int:
+    return int(_cabi.load().b200_gemm_workspace_bytes(m, n, k, ab_dtype, split_k))
 
 
-def gemm_workspace(m, n, k, ab_dtype, device, max_ctas=0):
-    """Zero-filled workspace (the fix-up counters at its head must start at zero; every call leaves them zeroed)."""
-    return torch.zeros(gemm_workspace_bytes(m, n, k, ab_dtype, max_ctas), dtype=torch.uint8, device=device)
+def gemm_workspace(m, n, k, ab_dtype, device, split_k=0):
+    """Zero-filled workspace (stream-K fix-up counters at its head must start at zero; every call leaves them zeroed).
+    The decode schedule (M <= 128) needs none: returns None."""
+    nbytes = gemm_workspace_bytes(m, n, k, ab_dtype, split_k)
+    return torch.zeros(nbytes, dtype=torch.uint8, device=device) if nbytes else None
 
 
-def gemm(a, w, a_scale=None, w_scale=None, bias=None, residual=None, out=None, out_dtype=torch.bfloat16, max_ctas=0,
+def gemm(a, w, a_scale=None, w_scale=None, bias=None, residual=None, out=None, out_dtype=torch.bfloat16, split_k=0,
          workspace=None):
     """out[M,N] = (a[M,K] @ w[N,K]^T) * a_scale[m] * w_scale[n] + bias[n] + residual[m,n]."""
     _cuda(a, w, a_scale, w_scale, bias, residual)
@@ -269,12 +271,12 @@ def gemm(a, w, a_scale=None, w_scale=None, bias=None, residual=None, out=None, o
     if residual is not None:
         assert residual.dtype == torch.bfloat16 and residual.is_contiguous() and residual.shape == (m, n)
     if workspace is None:
-        workspace = gemm_workspace(m, n, k, dt, a.device, max_ctas)
+        workspace = gemm_workspace(m, n, k, dt, a.device, split_k)
     with _k(f"gemm_{_DTN[dt]}[{m}x{n}x{k}]"):
         check(
             _cabi.load().b200_gemm(
                 _ptr(a), _ptr(w), _ptr(out), _ptr(a_scale), _ptr(w_scale), _ptr(bias), _ptr(residual), m, n, k, dt, odt,
-                max_ctas, _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(),
+                split_k, _ptr(workspace), 0 if workspace is None else workspace.numel() * workspace.element_size(), _stream(),
             ),
             "b200_gemm",
         )
@@ -292,28 +294,29 @@ def interleave_gate_up(w_gu, *others):
     return res[0] if not others else tuple(res)
 
 
-def gemm_silu_mul(a, w_gu_interleaved, a_scale=None, w_scale=None, bias=None, max_ctas=0, workspace=None):
+def gemm_silu_mul(a, w_gu_interleaved, a_scale=None, w_scale=None, bias=None, split_k=0, workspace=None):
     """act[M, I] = bf16(silu(bf16(gate)) * bf16(up)) with gate/up = the two halves of a @ w_gu^T (rows interleaved by
-    interleave_gate_up); also returns tile_amax [ceil(2I/128), M] for quantize_per_token."""
+    interleave_gate_up); also returns group_amax [M, 2I/32] for quantize_per_token."""
     _cuda(a, w_gu_interleaved, a_scale, w_scale, bias)
     m, k = a.shape
     n2, k2 = w_gu_interleaved.shape
     assert k == k2 and a.is_contiguous() and w_gu_interleaved.is_contiguous() and a.dtype == w_gu_interleaved.dtype
     dt = _ab_dtype(a)
     act = torch.empty((m, n2 // 2), dtype=torch.bfloat16, device=a.device)
-    n_tiles = (n2 + 127) // 128
-    tile_amax = torch.empty((n_tiles, m), dtype=torch.float32, device=a.device)
+    assert n2 % 32 == 0
+    group_amax = torch.empty((m, n2 // 32), dtype=torch.float32, device=a.device)
     if workspace is None:
-        workspace = gemm_workspace(m, n2, k, dt, a.device, max_ctas)
+        workspace = gemm_workspace(m, n2, k, dt, a.device, split_k)
     with _k(f"gemm_silu_mul_{_DTN[dt]}[{m}x{n2}x{k}]"):
         check(
             _cabi.load().b200_gemm_silu_mul(
-                _ptr(a), _ptr(w_gu_interleaved), _ptr(act), _ptr(a_scale), _ptr(w_scale), _ptr(bias), _ptr(tile_amax),
-                m, n2, k, dt, max_ctas, _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(),
+                _ptr(a), _ptr(w_gu_interleaved), _ptr(act), _ptr(a_scale), _ptr(w_scale), _ptr(bias), _ptr(group_amax),
+                m, n2, k, dt, split_k, _ptr(workspace), 0 if workspace is None else workspace.numel() * workspace.element_size(),
+                _stream(),
             ),
             "b200_gemm_silu_mul",
         )
-    return act, tile_amax
+    return act, group_amax
 
 
 # ------------------------------------------------------------------ glue
@@ -354,20 +357,20 @@ def silu_mul(gate_up, quant=None):
     return q, s
 
 
-def quantize_per_token(x, quant: str, tile_amax=None):
-    """x [T, K] bf16 -> (q [T, K], scale [T]).  tile_amax [n_tiles, T] (from gemm_silu_mul) skips the row scan."""
-    _cuda(x, tile_amax)
+def quantize_per_token(x, quant: str, group_amax=None):
+    """x [T, K] bf16 -> (q [T, K], scale [T]).  group_amax [T, n_groups] (from gemm_silu_mul) skips the row scan."""
+    _cuda(x, group_amax)
     t, k = x.shape
     assert x.is_contiguous() and x.dtype == torch.bfloat16
     qd = _QDT[quant]
     q = torch.empty((t, k), dtype=_TORCH_Q[qd], device=x.device)
     s = torch.empty((t,), dtype=torch.float32, device=x.device)
     nt = 0
-    if tile_amax is not None:
-        assert tile_amax.dtype == torch.float32 and tile_amax.is_contiguous() and tile_amax.shape[1] == t
-        nt = tile_amax.shape[0]
+    if group_amax is not None:
+        assert group_amax.dtype == torch.float32 and group_amax.is_contiguous() and group_amax.shape[0] == t
+        nt = group_amax.shape[1]
     with _k("quantize_per_token"):
-        check(_cabi.load().b200_quantize_per_token(_ptr(x), _ptr(q), _ptr(s), _ptr(tile_amax), nt, t, k, qd, _stream()),
+        check(_cabi.load().b200_quantize_per_token(_ptr(x), _ptr(q), _ptr(s), _ptr(group_amax), nt, t, k, qd, _stream()),
               "b200_quantize_per_token")
     return q, s
 
