@@ -346,8 +346,13 @@ def run_b200(args, shape):
         }
         print(json.dumps(line), flush=True)
     if world > 1:
+        # Leave without tearing NCCL down: destroy_process_group() with captured graphs that hold NCCL kernels alive
+        # hung the 2-GPU run (all ranks had finished and printed).  Everything measured is already out.
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def run_e2e(args, shape, model, bt_host, dev, rank, world, group, barrier, n_start):

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 3
+#define B200_ABI_VERSION 4
 
 enum {
   B200_OK = 0,
@@ -115,11 +115,17 @@ int b200_paged_attn_prefill(const void* q, int64_t q_token_stride, const void* k
  * residual bf16 [M][N] or NULL; out_dtype BF16 | F32.
  * M <= 128 (decode): one CTA per (128-row weight tile, K split); the `split_k` CTAs (0 = auto; 1, 2, 4 or 8) of a tile
  *   form a thread-block cluster and are summed through distributed shared memory in fixed rank order; needs no workspace.
+ *   Weights stream through a deep TMA ring (up to 176 KB per SM in flight, issued before the previous kernel of the
+ *   stream has finished), activations through a shallow one; the schedule (S, CTAs per SM, ring depths) is picked per
+ *   shape from occupancy queries and a latency/bandwidth model (b200_gemm_decode_plan reports it).
  * M > 128 (prefill): persistent stream-K over min(split_k, #SM) CTAs (0 = one per SM), each an equal share of the
  *   (tile, k-block) space; tiles cut by a share boundary are summed in fixed order by the last contributor.
  *   `workspace` (b200_gemm_workspace_bytes) holds the fix-up counters in its first 4 KiB: it must be ZERO-FILLED before
  *   its first use and is left zeroed by every call; one workspace may serve all GEMMs issued on one stream. */
 size_t b200_gemm_workspace_bytes(int M, int N, int K, int ab_dtype, int split_k);
+/* The decode schedule (M <= 128) chosen on the current device for a shape: out6 = {cluster size S, CTAs per SM, weight
+ * ring depth, activation ring depth, CTAs the chip holds at once, dynamic shared memory bytes}.  Needs a device. */
+int b200_gemm_decode_plan(int M, int N, int K, int ab_dtype, int split_k, int silu_mul, int has_residual, int* out6);
 int b200_gemm(const void* a, const void* w, void* out, const float* a_scale, const float* w_scale, const void* bias,
               const void* residual, int M, int N, int K, int ab_dtype, int out_dtype, int split_k, void* workspace,
               size_t workspace_bytes, void* stream);

@@ -39,7 +39,9 @@ SHAPES = [
     (64, 1024, 512, 1),      # no split: epilogue straight from TMEM
     (64, 1024, 512, 2),      # clusters of 2: 64-row slices
     (64, 1024, 512, 4),      # clusters of 4, one k-block per CTA (fp8)
-    (33, 896, 2048, 8),      # clusters of 8: 16-row slices; N, M ragged
+    (33, 896, 2048, 8),      # clusters of 8; N, M ragged (tokens 33 / 8 per owner)
+    (64, 896, 2048, 3),      # clusters of 3: 21/21/22 tokens per owner
+    (5, 512, 2048, 7),       # fewer tokens than ranks: some owners finish nothing
     (4, 2048, 2048, 0),      # TinyLlama decode batch
     (1, 256, 128, 0),        # single row, single k-block
     (128, 640, 1152, 0),     # Qwen TP=8 o-proj-like, M=128
@@ -122,13 +124,13 @@ def test_gemm_rejects_bad_split(ops):
 
     x = torch.zeros(64, 256, dtype=torch.bfloat16, device="cuda")
     w = torch.zeros(256, 256, dtype=torch.bfloat16, device="cuda")
-    for bad in (3, 16, 8):  # not a power of two / above 8 / more CTAs than k-blocks (256 bf16 = 4 k-blocks)
+    for bad in (9, 16, 8, -1):  # above 8 / more CTAs than k-blocks (256 bf16 = 4 k-blocks) / negative
         with pytest.raises(B200Error):
             ops.gemm(x, w, split_k=bad)
 
 
 @pytest.mark.parametrize("kind", ["bf16", "fp8", "int8"])
-@pytest.mark.parametrize("m,i,k,ctas", [(64, 14336, 4096, 0), (4, 5632, 2048, 0), (64, 5632, 2048, 2), (100, 96, 512, 4),
+@pytest.mark.parametrize("m,i,k,ctas", [(64, 14336, 4096, 0), (4, 5632, 2048, 0), (64, 5632, 2048, 2), (100, 96, 512, 4), (64, 5632, 2048, 6),
                                          (128, 3584, 1024, 1), (300, 1792, 512, 0), (300, 1792, 512, 3)])
 def test_gemm_silu_mul_matches_unfused(ops, kind, m, i, k, ctas):
     """gate/up GEMM with SiLU*mul in the epilogue == b200_gemm (on the same interleaved rows) followed by b200_silu_mul,

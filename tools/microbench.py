@@ -82,7 +82,7 @@ def bench_attn(b=64, hq=32, hkv=8, d=128, ctx=2048, layers=8, quotas=(0, 8, 16))
     return res
 
 
-def bench_gemm(shapes=None, kinds=("fp8", "bf16"), pdl=True):
+def bench_gemm(shapes=None, kinds=("fp8", "bf16"), pdl=True, splits=(0,)):
     shapes = shapes or [(64, 6144, 4096), (64, 4096, 4096), (64, 28672, 4096), (64, 4096, 14336), (64, 128256, 4096)]
     ops.set_pdl(pdl)
     res = []
@@ -102,13 +102,19 @@ def bench_gemm(shapes=None, kinds=("fp8", "bf16"), pdl=True):
             out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
             nbytes = ops.gemm_workspace_bytes(m, n, k, 0 if kind == "bf16" else 1, 0)
             wsp = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device="cuda")  # stream-K counters start at zero
-            fns = [(lambda w=w: ops.gemm(a, w, sa, sw, out=out, workspace=wsp)) for w in ws_]
-            ms = time_calls(fns, iters=5)
-            alg = n * k * eb + n * 4 + m * k * eb + m * 4 + 2 * m * n
-            gbs = alg / ms / 1e6
-            res.append({"kernel": f"gemm_{kind}", "pdl": pdl, "M": m, "N": n, "K": k, "ms": ms, "GBps": gbs, "frac_hbm": gbs / HBM,
-                        "TFLOPs": 2 * m * n * k / ms / 1e9})
-            print(res[-1], flush=True)
+            for sk in splits:
+                try:
+                    plan = ops.gemm_decode_plan(m, n, k, 0 if kind == "bf16" else 1, split_k=sk)
+                except Exception:
+                    continue
+                fns = [(lambda w=w: ops.gemm(a, w, sa, sw, out=out, workspace=wsp, split_k=sk)) for w in ws_]
+                ms = time_calls(fns, iters=5)
+                alg = n * k * eb + n * 4 + m * k * eb + m * 4 + 2 * m * n
+                gbs = alg / ms / 1e6
+                res.append({"kernel": f"gemm_{kind}", "pdl": pdl, "M": m, "N": n, "K": k, "split_k": sk, "us": round(ms * 1e3, 2),
+                            "GBps": round(gbs, 1), "frac_hbm": round(gbs / HBM, 4),
+                            "TFLOPs": round(2 * m * n * k / ms / 1e9, 1), "plan": plan})
+                print(res[-1], flush=True)
             del ws_
     return res
 
@@ -126,5 +132,7 @@ if __name__ == "__main__":
         out += bench_gemm()
         out += bench_gemm(kinds=("fp8",), pdl=False)
         ops.set_pdl(True)
+    if a.what == "gemmsweep":
+        out += bench_gemm(kinds=("fp8",), splits=(0, 1, 2, 3, 4, 5, 6, 7, 8))
     if a.json:
         json.dump(out, open(a.json, "w"), indent=1)

@@ -22,6 +22,12 @@
 // Both use programmatic dependent launch: the grid becomes resident while the previous kernel drains and the TMA
 // producer fills the smem ring with WEIGHT tiles (which no kernel of the step writes) before griddepcontrol.wait;
 // activations are only touched after the wait.
+#include <stdlib.h>
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -58,13 +64,18 @@ struct GemmEpilogue {
   float* group_amax;  // EPI_SILU_MUL: [M][N/32] max |act| over the 16 channels of each interleaved row group
 };
 
-__device__ __forceinline__ float linear_value(const GemmEpilogue& ep, float acc, int m, int n, int N) {
-  float y = acc;
-  if (ep.a_scale) y *= ep.a_scale[m];
-  if (ep.w_scale) y *= ep.w_scale[n];
-  if (ep.bias) y += __bfloat162float(ep.bias[n]);
-  if (ep.residual) y += __bfloat162float(ep.residual[(int64_t)m * N + n]);
+// out = ((acc * a_scale) * w_scale + bias) + residual, every step rounded on its own (no FMA contraction), so that the
+// decode, prefill and fused-epilogue paths produce identical bits for the same accumulator
+__device__ __forceinline__ float scaled_value(float acc, float a, float w, bool has_bias, float b, bool has_res, float r) {
+  float y = __fmul_rn(__fmul_rn(acc, a), w);
+  if (has_bias) y = __fadd_rn(y, b);
+  if (has_res) y = __fadd_rn(y, r);
   return y;
+}
+__device__ __forceinline__ float linear_value(const GemmEpilogue& ep, float acc, int m, int n, int N) {
+  return scaled_value(acc, ep.a_scale ? ep.a_scale[m] : 1.f, ep.w_scale ? ep.w_scale[n] : 1.f, ep.bias != nullptr,
+                      ep.bias ? __bfloat162float(ep.bias[n]) : 0.f, ep.residual != nullptr,
+                      ep.residual ? __bfloat162float(ep.residual[(int64_t)m * N + n]) : 0.f);
 }
 __device__ __forceinline__ void store_out(const GemmEpilogue& ep, float acc, int m, int n, int N) {
   float y = linear_value(ep, acc, m, n, N);
@@ -120,6 +131,55 @@ __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, const flo
       const float a = silu_mul_bf16(g, u);
       if (ok) reinterpret_cast<__nv_bfloat16*>(ep.out)[(int64_t)m * I + ch] = __float2bfloat16_rn(a);
       float x = ok ? fabsf(a) : 0.f;  // max over the 16 channels of the group (one half-warp)
+#pragma unroll
+      for (int o = 1; o < 16; o <<= 1) x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, o));
+      if ((lane & 15) == 0 && ok) ep.group_amax[(int64_t)m * n_groups + (n >> 5)] = x;
+    }
+  }
+}
+
+// Same, with every epilogue operand already staged: a_s[] per-token scales in shared memory, this lane's channel scale /
+// bias in registers, the residual column of this lane in shared memory (resid[m * resid_stride]).
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk_staged(const GemmEpilogue& ep, const float (&v)[16], int m_base, int M, int n,
+                                                      bool n_ok, int N, int lane, const float* a_s, float w_sc, float bias_v,
+                                                      const __nv_bfloat16* resid, int resid_stride) {
+  const bool hb = ep.bias != nullptr, hr = ep.residual != nullptr;
+  if constexpr (EPI == EPI_LINEAR) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int m = m_base + j;
+      const float y = scaled_value(v[j], a_s[m], w_sc, hb, bias_v, hr, hr ? __bfloat162float(resid[m * resid_stride]) : 0.f);
+      if (m < M && n_ok) {
+        if (ep.out_f32)
+          reinterpret_cast<float*>(ep.out)[(int64_t)m * N + n] = y;
+        else
+          reinterpret_cast<__nv_bfloat16*>(ep.out)[(int64_t)m * N + n] = __float2bfloat16_rn(y);
+      }
+    }
+  } else {
+    const int I = N >> 1, n_groups = N >> 5;
+    const int ch = (n >> 5) * 16 + (lane & 15);
+    float mine[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int m = m_base + j;
+      float y = 0.f;
+      if (m < M && n_ok) y = __bfloat162float(__float2bfloat16_rn(scaled_value(v[j], a_s[m], w_sc, hb, bias_v, false, 0.f)));
+      mine[j] = y;
+    }
+    const bool hi = lane >= 16;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float send = hi ? mine[j] : mine[j + 8];
+      const float got = __shfl_xor_sync(0xffffffffu, send, 16);
+      const float g = hi ? got : mine[j];
+      const float u = hi ? mine[j + 8] : got;
+      const int m = m_base + (hi ? 8 : 0) + j;
+      const bool ok = m < M && n_ok;
+      const float a = silu_mul_bf16(g, u);
+      if (ok) reinterpret_cast<__nv_bfloat16*>(ep.out)[(int64_t)m * I + ch] = __float2bfloat16_rn(a);
+      float x = ok ? fabsf(a) : 0.f;
 #pragma unroll
       for (int o = 1; o < 16; o <<= 1) x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, o));
       if ((lane & 15) == 0 && ok) ep.group_amax[(int64_t)m * n_groups + (n >> 5)] = x;
@@ -317,31 +377,55 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 
 
 // ============================================================ decode schedule (M <= 128): cluster split-K
-// grid = n_tiles * S CTAs, cluster = the S CTAs (S = 1, 2, 4, 8) that share weight tile blockIdx.x / S; cluster rank r
-// accumulates k-blocks [num_kb*r/S, num_kb*(r+1)/S).  Reduction buffer `red` (S > 1) in every CTA:
-//   red[src rank][token m][row] fp32, row = weight row inside this CTA's slice of 128/S rows,
-// written by the peers with st.shared::cluster (32 lanes -> 32 consecutive floats), read locally after one cluster
-// barrier.  EPI_SILU_MUL needs whole 32-row groups per slice: S <= 4.
+// grid = n_tiles * S CTAs, cluster = the S CTAs (S = 1 .. 8) that share weight tile blockIdx.x / S; cluster rank r
+// accumulates k-blocks [num_kb*r/S, num_kb*(r+1)/S).
+//
+// Measured on B200 (profiles/r01_gemm_sweep_*.json): one SM ingests ~55 GB/s through TMA however deep its ring is, and the
+// activation tiles (L2 hits) count against that like the weight tiles do.  So the time of a decode GEMM is a fixed ~6 us
+// of dependent latencies plus (bytes received by the busiest SM) / 55 GB/s: the schedule's job is to spread the
+// (tile, k-block) units evenly over all 148 SMs -- hence the free choice of S -- and to keep the fixed part short.
+//
+// Shared memory: a ring of `nst` stages, weight tile (16 KB) and activation tile in separate arrays with separate
+// barriers; all weight stages are issued before griddepcontrol.wait (weights are constants of the step), the activation
+// tiles after it.  While the ring streams, the four epilogue warps stage everything the epilogue needs from global
+// memory (per-token scales, per-channel scale / bias, the residual tile, the DSMEM address of every token's owner),
+// so nothing between the last MMA and the output stores waits on a global load.
+//
+// Split-K reduction (S > 1): the M tokens are divided among the cluster, rank q owns tokens [M*q/S, M*(q+1)/S).
+// Every CTA pushes its fp32 partial of token m (128 weight rows = 32 lanes x 4 warps, 128 B per warp store) into
+//   red[src rank][owned token][128 rows]   of the owner (st.shared::cluster),
+// one cluster barrier, then the owner adds the S partials in rank order (bit-reproducible), applies the epilogue on
+// float4 row groups and stores whole 256 B output rows.
+constexpr int DEC_MAX_ST = 12;
+
 template <int KIND, int BM, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
     gemm_decode_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap a_map,
-                       GemmEpilogue ep, int M, int N, int num_kb, int nstages) {
+                       GemmEpilogue ep, int M, int N, int num_kb, int nst) {
   using T = KindTraits<KIND>;
   constexpr int BK_ELEMS = GEMM_BK_BYTES / T::ELEM;
   constexpr int W_TILE = GEMM_BN * GEMM_BK_BYTES;
   constexpr int A_TILE = BM * GEMM_BK_BYTES;
-  constexpr int STAGE = W_TILE + A_TILE;
   constexpr uint32_t TMEM_COLS = BM < 32 ? 32 : BM;
   constexpr uint32_t IDESC = umma_idesc(T::CFMT, T::ABFMT, GEMM_BN, BM);
-  constexpr int MAX_STAGES = 8;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int S = (int)cluster_nctarank(), r = (int)cluster_ctarank();
-  float* red = reinterpret_cast<float*>(smem + (size_t)nstages * STAGE);
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)nstages * STAGE + (S > 1 ? (size_t)GEMM_BN * BM * 4 : 0));
-  uint64_t* empty = full + MAX_STAGES;
-  uint64_t* tfull = empty + MAX_STAGES;
+  const int tp_max = (M + S - 1) / S;                                   // most tokens one rank owns
+  const int m_lo = (int)((long long)M * r / S), m_hi = (int)((long long)M * (r + 1) / S);  // tokens this rank finishes
+  uint8_t* w_ring = smem;
+  uint8_t* a_ring = smem + (size_t)nst * W_TILE;
+  float* red = reinterpret_cast<float*>(a_ring + (size_t)nst * A_TILE);  // [S][tp_max][128] (S > 1)
+  float* a_s = red + (S > 1 ? (size_t)S * tp_max * GEMM_BN : 0);         // [BM] per-token scales
+  uint32_t* push_addr = reinterpret_cast<uint32_t*>(a_s + BM);           // [BM] DSMEM address of token m's slot (S > 1)
+  __nv_bfloat16* resid_s = reinterpret_cast<__nv_bfloat16*>(push_addr + BM);  // [owned tokens][128] (iff residual)
+  uint64_t* full_w = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(resid_s) +
+                                                 (ep.residual ? (size_t)(S > 1 ? tp_max : BM) * GEMM_BN * 2 : 0));
+  uint64_t* empty_w = full_w + DEC_MAX_ST;
+  uint64_t* full_a = empty_w + DEC_MAX_ST;
+  uint64_t* empty_a = full_a + DEC_MAX_ST;
+  uint64_t* tfull = empty_a + DEC_MAX_ST;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -352,9 +436,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&w_map);
     tma_prefetch_desc(&a_map);
-    for (int s = 0; s < nstages; ++s) {
-      mbar_init(&full[s], 1);
-      mbar_init(&empty[s], 1);
+    for (int s = 0; s < nst; ++s) {
+      mbar_init(&full_w[s], 1);
+      mbar_init(&empty_w[s], 1);
+      mbar_init(&full_a[s], 1);
+      mbar_init(&empty_a[s], 1);
     }
     mbar_init(tfull, 1);
     fence_mbar_init();
@@ -372,48 +458,62 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
   if (S > 1) cluster_arrive_relaxed();
   const uint32_t tmem_base = *tmem_slot;
 
+  // per-thread epilogue constants (epilogue warps only; filled while the ring streams)
+  const int lg = warp & 3;
+  const int nl = lg * 32 + lane;  // weight row of the tile this lane reads from TMEM
+  const int et = threadIdx.x - 64;
+  const int t4 = et & 31, tq = et >> 5;  // reduction phase: rows 4*t4 .. 4*t4+3, owned tokens tq, tq+4, ...
+  float w_sc = 1.f, bias_v = 0.f;        // S == 1: row nl
+  float w4[4] = {1.f, 1.f, 1.f, 1.f}, b4[4] = {0.f, 0.f, 0.f, 0.f};  // S > 1: rows 4*t4 + e
+
   if (warp == 0) {
     if (lane == 0 && nk > 0) {
       const uint64_t pol_w = policy_evict_first();  // every weight byte is read once per step
       const uint64_t pol_a = policy_evict_last();   // activations are re-read by every tile
-      const int npre = nk < nstages ? nk : nstages;
+      const int npre = nk < nst ? nk : nst;
       // weights do not depend on any kernel of the step: fill the ring with W tiles before the dependency resolves
       for (int i = 0; i < npre; ++i) {
-        mbar_expect_tx(&full[i], STAGE);
-        tma_load_2d_hint(smem + (size_t)i * STAGE, &w_map, &full[i], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
+        mbar_expect_tx(&full_w[i], W_TILE);
+        tma_load_2d_hint(w_ring + (size_t)i * W_TILE, &w_map, &full_w[i], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
       }
       griddep_wait();
-      for (int i = 0; i < npre; ++i)
-        tma_load_2d_hint(smem + (size_t)i * STAGE + W_TILE, &a_map, &full[i], (kb0 + i) * BK_ELEMS, 0, pol_a);
-      int s = 0, ph = 0;  // stage / parity of the empty barrier for refills
+      for (int i = 0; i < npre; ++i) {
+        mbar_expect_tx(&full_a[i], A_TILE);
+        tma_load_2d_hint(a_ring + (size_t)i * A_TILE, &a_map, &full_a[i], (kb0 + i) * BK_ELEMS, 0, pol_a);
+      }
+      int s = 0, ph = 0;  // stage / parity of the empty barriers for refills
       for (int i = npre; i < nk; ++i) {
-        mbar_wait(&empty[s], ph);
-        uint8_t* ws = smem + (size_t)s * STAGE;
-        mbar_expect_tx(&full[s], STAGE);
-        tma_load_2d_hint(ws, &w_map, &full[s], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
-        tma_load_2d_hint(ws + W_TILE, &a_map, &full[s], (kb0 + i) * BK_ELEMS, 0, pol_a);
-        if (++s == nstages) {
+        mbar_wait(&empty_a[s], ph);
+        mbar_expect_tx(&full_a[s], A_TILE);
+        tma_load_2d_hint(a_ring + (size_t)s * A_TILE, &a_map, &full_a[s], (kb0 + i) * BK_ELEMS, 0, pol_a);
+        mbar_wait(&empty_w[s], ph);
+        mbar_expect_tx(&full_w[s], W_TILE);
+        tma_load_2d_hint(w_ring + (size_t)s * W_TILE, &w_map, &full_w[s], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
+        if (++s == nst) {
           s = 0;
           ph ^= 1;
         }
       }
     }
+    __syncwarp();  // lanes 1..31 park here
   } else if (warp == 1) {
     int s = 0, ph = 0;
     for (int i = 0; i < nk; ++i) {
-      mbar_wait(&full[s], ph);
+      mbar_wait(&full_w[s], ph);
+      mbar_wait(&full_a[s], ph);
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t wa = smem_u32(smem + (size_t)s * STAGE);
-        const uint32_t aa = wa + W_TILE;
+        const uint32_t wa = smem_u32(w_ring + (size_t)s * W_TILE);
+        const uint32_t aa = smem_u32(a_ring + (size_t)s * A_TILE);
 #pragma unroll
         for (int kk = 0; kk < GEMM_BK_BYTES / 32; ++kk)  // UMMA_K = 32 bytes of K
           umma_ss<KIND>(tmem_base, umma_desc_sw128(wa + kk * 32), umma_desc_sw128(aa + kk * 32), IDESC,
                         (uint32_t)((i | kk) != 0));
-        tc_commit(&empty[s]);
+        tc_commit(&empty_a[s]);
+        tc_commit(&empty_w[s]);
       }
       __syncwarp();
-      if (++s == nstages) {
+      if (++s == nst) {
         s = 0;
         ph ^= 1;
       }
@@ -421,15 +521,64 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
     if (lane == 0) tc_commit(tfull);
     __syncwarp();
   } else {
-    // epilogue warps: warp w may touch TMEM lanes 32*(w%4) .. +31; lane = weight row of the tile
-    const int lg = warp & 3;
-    const int nl = lg * 32 + lane;
+    // ---- epilogue warps, part 1: stage the epilogue operands while the ring streams
     griddep_wait();
+    for (int m = et; m < BM; m += 128) {
+      a_s[m] = (ep.a_scale && m < M) ? ep.a_scale[m] : 1.f;
+      if (S > 1) {
+        uint32_t addr = 0;
+        if (m < M) {
+          const int q = (int)((((long long)m + 1) * S - 1) / M);  // owner: largest q with M*q/S <= m
+          const int lo = (int)((long long)M * q / S);
+          addr = mapa_shared(smem_u32(red), (uint32_t)q) + (uint32_t)((((size_t)r * tp_max + (m - lo)) * GEMM_BN) * 4);
+        }
+        push_addr[m] = addr;
+      }
+    }
+    const int n0 = n_tile * GEMM_BN;
+    if (S == 1) {
+      if (n0 + nl < N) {
+        if (ep.w_scale) w_sc = ep.w_scale[n0 + nl];
+        if (ep.bias) bias_v = __bfloat162float(ep.bias[n0 + nl]);
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int n = n0 + 4 * t4 + e;
+        if (n < N) {
+          if (ep.w_scale) w4[e] = ep.w_scale[n];
+          if (ep.bias) b4[e] = __bfloat162float(ep.bias[n]);
+        }
+      }
+    }
+    if (ep.residual) {
+      // rows [n0, n0+128) of the tokens this CTA finishes: S == 1 all of them, else [m_lo, m_hi)
+      const int t_lo = S == 1 ? 0 : m_lo, t_cnt = S == 1 ? (M < BM ? M : BM) : m_hi - m_lo;
+      const bool vec = (N & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.residual) & 15) == 0;
+#pragma unroll 4
+      for (int idx = et; idx < t_cnt * 16; idx += 128) {  // 16 vectors of 8 bf16 per token row
+        const int ml = idx >> 4, c8 = (idx & 15) * 8;
+        const __nv_bfloat16* src = ep.residual + (int64_t)(t_lo + ml) * N + n0 + c8;
+        uint4 val = make_uint4(0u, 0u, 0u, 0u);
+        if (vec) {
+          if (n0 + c8 < N) val = *reinterpret_cast<const uint4*>(src);
+        } else {
+          __nv_bfloat16 tmp[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) tmp[e] = n0 + c8 + e < N ? src[e] : __float2bfloat16_rn(0.f);
+          val = *reinterpret_cast<uint4*>(tmp);
+        }
+        *reinterpret_cast<uint4*>(resid_s + ml * GEMM_BN + c8) = val;
+      }
+    }
+    named_bar_sync(1, 128);
+
+    // ---- part 2: the accumulator is final
     mbar_wait(tfull, 0);
     tc_fence_after();
     const uint32_t acc = tmem_base + ((uint32_t)(lg * 32) << 16);
     if (S == 1) {
-      const int n = n_tile * GEMM_BN + nl;
+      const int n = n0 + nl;
 #pragma unroll 1
       for (int cc = 0; cc < BM / 16; ++cc) {
         uint32_t v[16];
@@ -438,23 +587,21 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
         float f[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) f[j] = KIND == KIND_I8 ? (float)(int32_t)v[j] : __uint_as_float(v[j]);
-        epilogue_chunk<EPI>(ep, f, cc * 16, M, n, n < N, N, lane);
+        epilogue_chunk_staged<EPI>(ep, f, cc * 16, M, n, n < N, N, lane, a_s, w_sc, bias_v, resid_s + nl, GEMM_BN);
       }
     } else {
-      // push this CTA's partial of weight row nl to the CTA that owns the row (once every peer is known to run)
-      cluster_wait();
-      const int rows_per = GEMM_BN / S;
-      const uint32_t dst = mapa_shared(smem_u32(red), (uint32_t)(nl / rows_per)) +
-                           (uint32_t)(((size_t)r * BM * rows_per + (nl % rows_per)) * 4);
+      cluster_wait();  // every peer is known to run: its `red` may be written
 #pragma unroll 1
       for (int cc = 0; cc < BM / 16; ++cc) {
+        if (cc * 16 >= M) break;
         uint32_t v[16];
         tmem_ld_32x32b_x16(acc + cc * 16, v);
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
+          const uint32_t dst = push_addr[cc * 16 + j];
           const float f = KIND == KIND_I8 ? (float)(int32_t)v[j] : __uint_as_float(v[j]);
-          st_cluster_f32(dst + (uint32_t)((cc * 16 + j) * rows_per * 4), f);
+          if (dst) st_cluster_f32(dst + (uint32_t)(nl * 4), f);
         }
       }
     }
@@ -465,31 +612,83 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
     if (warp < 2) cluster_wait();  // phase 1 for the warps that do not push
     cluster_sync_all();            // phase 2: all partials have landed
     if (warp >= 2) {
-      const int rows_per = GEMM_BN / S;
-      const int et = threadIdx.x - 64;
-      const int n_base = n_tile * GEMM_BN + r * rows_per;
-      // element (m, row) of this CTA's slice: consecutive threads take consecutive rows (conflict-free smem reads,
-      // contiguous global stores); S partials added in rank order
-#pragma unroll 1
-      for (int idx = et; idx < BM * rows_per; idx += 128) {
-        const int row = idx % rows_per, m = idx / rows_per;
-        float acc = 0.f;
-        for (int q = 0; q < S; ++q) acc += red[((size_t)q * BM + m) * rows_per + row];
-        const int n = n_base + row;
-        const bool ok = m < M && n < N;
+      const int n0 = n_tile * GEMM_BN + 4 * t4;
+      const bool hb = ep.bias != nullptr, hr = EPI == EPI_LINEAR && ep.residual != nullptr;
+#pragma unroll 2
+      for (int ml = tq; ml < m_hi - m_lo; ml += 4) {
+        const int m = m_lo + ml;
+        float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (q < S) {
+            const float4 p = *reinterpret_cast<const float4*>(red + ((size_t)q * tp_max + ml) * GEMM_BN + 4 * t4);
+            sum.x += p.x;
+            sum.y += p.y;
+            sum.z += p.z;
+            sum.w += p.w;
+          }
+        }
+        const float as = a_s[m];
+        float rs[4] = {0.f, 0.f, 0.f, 0.f};
+        if (hr) {
+          const uint2 rv = *reinterpret_cast<const uint2*>(resid_s + ml * GEMM_BN + 4 * t4);
+          const __nv_bfloat162 r01 = *reinterpret_cast<const __nv_bfloat162*>(&rv.x);
+          const __nv_bfloat162 r23 = *reinterpret_cast<const __nv_bfloat162*>(&rv.y);
+          rs[0] = __low2float(r01);
+          rs[1] = __high2float(r01);
+          rs[2] = __low2float(r23);
+          rs[3] = __high2float(r23);
+        }
+        float y[4];
+        y[0] = scaled_value(sum.x, as, w4[0], hb, b4[0], hr, rs[0]);
+        y[1] = scaled_value(sum.y, as, w4[1], hb, b4[1], hr, rs[1]);
+        y[2] = scaled_value(sum.z, as, w4[2], hb, b4[2], hr, rs[2]);
+        y[3] = scaled_value(sum.w, as, w4[3], hb, b4[3], hr, rs[3]);
         if constexpr (EPI == EPI_LINEAR) {
-          if (ok) store_out(ep, acc, m, n, N);
+          if ((N & 3) == 0 && n0 + 3 < N) {
+            if (ep.out_f32)
+              *reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.out) + (int64_t)m * N + n0) =
+                  make_float4(y[0], y[1], y[2], y[3]);
+            else
+              *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + (int64_t)m * N + n0) =
+                  make_uint2(pack_bf16(y[0], y[1]), pack_bf16(y[2], y[3]));
+          } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              if (n0 + e < N) {
+                if (ep.out_f32)
+                  reinterpret_cast<float*>(ep.out)[(int64_t)m * N + n0 + e] = y[e];
+                else
+                  reinterpret_cast<__nv_bfloat16*>(ep.out)[(int64_t)m * N + n0 + e] = __float2bfloat16_rn(y[e]);
+              }
+            }
+          }
         } else {
-          // rows_per is 32, 64 or 128 here: this warp holds one whole 32-row group of token m (lane = row & 31)
+          // rows of one 32-row group: 16 gate rows (lanes 8g .. 8g+3) then the 16 up rows of the same channels
+          // (lanes 8g+4 .. 8g+7); N2 % 32 == 0, so a group is inside N or outside as a whole
           const int I = N >> 1, n_groups = N >> 5;
-          const float mine = ok ? __bfloat162float(__float2bfloat16_rn(linear_value(ep, acc, m, n, N))) : 0.f;
-          const float other = __shfl_xor_sync(0xffffffffu, mine, 16);
-          const bool is_gate = lane < 16;
-          const float a = silu_mul_bf16(is_gate ? mine : other, is_gate ? other : mine);
-          if (ok && is_gate)
-            reinterpret_cast<__nv_bfloat16*>(ep.out)[(int64_t)m * I + (n >> 5) * 16 + lane] = __float2bfloat16_rn(a);
-          const float x = warp_max(ok ? fabsf(a) : 0.f);
-          if (lane == 0 && ok) ep.group_amax[(int64_t)m * n_groups + (n >> 5)] = x;
+          const bool ok = n0 < N;
+          float mine[4], other[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            mine[e] = ok ? __bfloat162float(__float2bfloat16_rn(y[e])) : 0.f;
+            other[e] = __shfl_xor_sync(0xffffffffu, mine[e], 4);
+          }
+          const bool is_gate = (lane & 4) == 0;
+          float a[4], x = 0.f;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            a[e] = silu_mul_bf16(is_gate ? mine[e] : other[e], is_gate ? other[e] : mine[e]);
+            x = fmaxf(x, ok ? fabsf(a[e]) : 0.f);
+          }
+          x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, 1));
+          x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, 2));
+          if (ok && is_gate) {
+            const int ch = (n0 >> 5) * 16 + (lane & 3) * 4;
+            *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + (int64_t)m * I + ch) =
+                make_uint2(pack_bf16(a[0], a[1]), pack_bf16(a[2], a[3]));
+            if ((lane & 7) == 0) ep.group_amax[(int64_t)m * n_groups + (n0 >> 5)] = x;
+          }
         }
       }
     }
@@ -507,8 +706,7 @@ namespace {
 struct GemmPlan {
   bool decode;  // M <= 128: cluster split-K kernel; else persistent stream-K
   int bm, m_tiles, n_tiles, tiles, num_kb;
-  int split, nstages;  // decode
-  int ctas;            // stream-K
+  int ctas;  // stream-K
   size_t smem, ws_bytes;
 };
 
@@ -517,19 +715,9 @@ constexpr int stages_for(int bm) { return bm == 32 ? 10 : bm == 64 ? 8 : bm == 1
 constexpr size_t smem_for(int bm) {
   return (size_t)stages_for(bm) * (GEMM_BN * GEMM_BK_BYTES + bm * GEMM_BK_BYTES) + (2 * stages_for(bm) + 4) * 8 + 8 + 1024;
 }
-// decode kernel: ring depth chosen so that two CTAs fit on an SM (BM <= 64); the reduction buffer takes one stage's room
-int decode_stages(int bm, int split) {
-  if (bm == 32) return split > 1 ? 4 : 5;
-  if (bm == 64) return split > 1 ? 3 : 4;
-  return split > 1 ? 4 : 6;
-}
-size_t decode_smem(int bm, int split) {
-  return 1024 + (size_t)decode_stages(bm, split) * (GEMM_BN + bm) * GEMM_BK_BYTES +
-         (split > 1 ? (size_t)GEMM_BN * bm * 4 : 0) + 256;
-}
 
 // split_k: decode = cluster size along K (0 = auto; 1, 2, 4, 8); stream-K = cap on the persistent CTAs (0 = one per SM)
-int plan_gemm(GemmPlan& p, int M, int N, int K, int ab_dtype, int split_k, int epi) {
+int plan_gemm(GemmPlan& p, int M, int N, int K, int ab_dtype, int split_k) {
   p.decode = M <= 128;
   p.bm = M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256;
   p.m_tiles = (M + p.bm - 1) / p.bm;
@@ -537,29 +725,10 @@ int plan_gemm(GemmPlan& p, int M, int N, int K, int ab_dtype, int split_k, int e
   p.tiles = p.m_tiles * p.n_tiles;
   int bk = GEMM_BK_BYTES / elem_bytes(ab_dtype);
   p.num_kb = (K + bk - 1) / bk;
-  p.split = 1;
-  p.nstages = 0;
   p.ctas = 0;
-  if (p.decode) {
-    const int max_split = epi == EPI_SILU_MUL ? 4 : 8;
-    int s = split_k;
-    if (s == 0) {
-      // fill the CTA slots of the chip (two per SM for BM <= 64) without dropping below 2 k-blocks per CTA
-      const long slots = (long)sm_count() * (p.bm <= 64 ? 2 : 1);
-      s = 1;
-      while (s * 2 <= max_split && (long)p.n_tiles * s * 2 <= slots && p.num_kb >= s * 4) s *= 2;
-    }
-    if (!(s == 1 || s == 2 || s == 4 || s == 8) || s > max_split || s > p.num_kb) {
-      set_last_error("gemm: split_k %d invalid here (1, 2, 4%s; at most %d k-blocks)", split_k,
-                     epi == EPI_SILU_MUL ? "" : ", 8", p.num_kb);
-      return B200_ERR_INVALID_ARG;
-    }
-    p.split = s;
-    p.nstages = decode_stages(p.bm, s);
-    p.smem = decode_smem(p.bm, s);
-    p.ws_bytes = 0;
-    return B200_OK;
-  }
+  p.smem = 0;
+  p.ws_bytes = 0;
+  if (p.decode) return B200_OK;  // the decode schedule is planned per kernel instantiation (occupancy queries)
   long long units = (long long)p.tiles * p.num_kb;
   int ctas = sm_count();
   if (split_k > 0 && split_k < ctas) ctas = split_k;
@@ -589,28 +758,140 @@ int launch_streamk(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilo
   return B200_OK;
 }
 
+// ---- decode schedule: (cluster size S, CTAs per SM, ring depths) per problem shape
+constexpr size_t SMEM_ONE_PER_SM = 232448;  // 227 KB: the per-CTA maximum
+constexpr size_t SMEM_TWO_PER_SM = 115712;  // (228 KB - 2 x 1 KB reserved) / 2
+constexpr int W_TILE_BYTES = GEMM_BN * GEMM_BK_BYTES;
+
+struct DecodeCfg {
+  int S, nst;
+  size_t smem;
+  int cap_ctas;  // CTAs the chip holds at once in this configuration
+  double cost_us;
+};
+
+// ring depth that fits `budget` bytes
+bool decode_rings(int bm, int M, int S, int nk, bool resid, size_t budget, DecodeCfg& c) {
+  const int a_tile = bm * GEMM_BK_BYTES;
+  const int tp_max = (M + S - 1) / S;
+  const size_t red = S > 1 ? (size_t)S * tp_max * GEMM_BN * 4 : 0;
+  const size_t fixed = 1024 + red + (size_t)bm * 8 + (resid ? (size_t)(S > 1 ? tp_max : bm) * GEMM_BN * 2 : 0) + 512;
+  if (budget < fixed + (size_t)(a_tile + W_TILE_BYTES)) return false;
+  int n = (int)((budget - fixed) / (size_t)(a_tile + W_TILE_BYTES));
+  if (n > DEC_MAX_ST) n = DEC_MAX_ST;
+  if (n > nk) n = nk;
+  if (n < 1) return false;
+  c.nst = n;
+  c.smem = fixed + (size_t)n * (a_tile + W_TILE_BYTES);
+  return true;
+}
+
 template <int KIND, int BM, int EPI>
-int launch_decode(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilogue& ep, int M, int N, const GemmPlan& p,
-                  cudaStream_t stream) {
+int plan_decode(DecodeCfg& best, int M, int n_tiles, int num_kb, int split_k, bool resid) {
   auto kern = gemm_decode_kernel<KIND, BM, EPI>;
+  static std::mutex mu;
+  static std::map<std::tuple<int, int, int, int, bool>, DecodeCfg> cache;
+  const auto key = std::make_tuple(M, n_tiles, num_kb, split_k, resid);
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) {
+      best = it->second;
+      return B200_OK;
+    }
+  }
   static bool attr_done = false;
   if (!attr_done) {
-    const size_t mx = decode_smem(BM, 1) > decode_smem(BM, 2) ? decode_smem(BM, 1) : decode_smem(BM, 2);
-    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mx));
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_ONE_PER_SM));
     attr_done = true;
   }
-  B200_CUDA_OK(launch_kernel_cluster(kern, dim3(p.n_tiles * p.split), dim3(GEMM_THREADS), p.smem, p.split, stream, wm, am,
-                                     ep, M, N, p.num_kb, p.nstages));
+  if (split_k < 0 || split_k > 8 || split_k > num_kb) {
+    set_last_error("gemm: split_k %d invalid here (0 = auto, or 1 .. 8 and at most %d k-blocks)", split_k, num_kb);
+    return B200_ERR_INVALID_ARG;
+  }
+  static const int force_occ = getenv("B200_GEMM_FORCE_OCC") ? atoi(getenv("B200_GEMM_FORCE_OCC")) : 0;  // tuning aid
+  const int sms = sm_count();
+  const size_t budget = (BM <= 64 && force_occ != 1) ? SMEM_TWO_PER_SM : SMEM_ONE_PER_SM;
+  const int per_sm = budget == SMEM_TWO_PER_SM ? 2 : 1;
+  bool found = false;
+  for (int S = 1; S <= 8; ++S) {
+    if (split_k != 0 && S != split_k) continue;
+    if (S > num_kb) break;
+    const int nk = (num_kb + S - 1) / S;
+    DecodeCfg c{};
+    c.S = S;
+    if (!decode_rings(BM, M, S, nk, resid, budget, c)) continue;
+    // clusters of 4 and 8 strand SMs (GPC packing): ask the runtime how many clusters one wave holds
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(n_tiles * S);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = c.smem;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)S;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    int clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg) != cudaSuccess || clusters <= 0) {
+      cudaGetLastError();
+      continue;
+    }
+    c.cap_ctas = clusters * S;
+    // cost model (us), fitted to the sweeps in profiles/r01_gemm_sweep_v3.json:
+    //   fixed latency chain  +  max(busiest SM's stages at its latency-bound rate, chip ingest, HBM)  +  reduction.
+    // An SM's ingest rate grows with the stages it has in flight (one ring round trip ~1.55 us); CTAs spread
+    // round-robin, so with more CTAs than SMs the busiest SM runs two rings side by side.
+    const int ctas = n_tiles * S;
+    const double stage_bytes = (double)(W_TILE_BYTES + BM * GEMM_BK_BYTES);
+    const int sm_used = ctas < sms ? ctas : sms;
+    int on_busiest = (ctas + sm_used - 1) / sm_used;
+    const int resident = on_busiest < per_sm ? on_busiest : per_sm;
+    const double rate_sm = resident * c.nst * stage_bytes / 1.55;  // bytes per us
+    const double t_sm = on_busiest * nk * stage_bytes / rate_sm;
+    const double t_chip = (double)n_tiles * num_kb * stage_bytes / 9.5e6;
+    const double t_hbm = (double)n_tiles * num_kb * W_TILE_BYTES / 6.2e6;
+    double t = t_sm > t_chip ? t_sm : t_chip;
+    if (t_hbm > t) t = t_hbm;
+    t += 6.0;
+    if (S > 1) t += 0.8 + 0.05 * ((M + S - 1) / S);
+    const int capacity = c.cap_ctas * per_sm;  // the occupancy query counts one CTA per SM
+    if (ctas > capacity) t += ((ctas - 1) / capacity) * (3.0 + nk * stage_bytes / (c.nst * stage_bytes / 1.55));
+    c.cost_us = t;
+    if (!found || c.cost_us < best.cost_us - 1e-9) {
+      best = c;
+      found = true;
+    }
+  }
+  if (!found) {
+    set_last_error("gemm: no decode configuration fits (n_tiles %d, k-blocks %d, split_k %d)", n_tiles, num_kb, split_k);
+    return B200_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> g(mu);
+  cache[key] = best;
+  return B200_OK;
+}
+
+template <int KIND, int BM, int EPI>
+int launch_decode(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilogue& ep, int M, int N, const GemmPlan& p,
+                  int split_k, cudaStream_t stream) {
+  DecodeCfg c;
+  int rc = plan_decode<KIND, BM, EPI>(c, M, p.n_tiles, p.num_kb, split_k, ep.residual != nullptr);
+  if (rc) return rc;
+  auto kern = gemm_decode_kernel<KIND, BM, EPI>;
+  B200_CUDA_OK(launch_kernel_cluster(kern, dim3(p.n_tiles * c.S), dim3(GEMM_THREADS), c.smem, c.S, stream, wm, am, ep, M, N,
+                                     p.num_kb, c.nst));
   return B200_OK;
 }
 
 template <int KIND, int EPI>
 int dispatch_gemm(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilogue& ep, void* ws, int M, int N,
-                  const GemmPlan& p, cudaStream_t stream) {
+                  const GemmPlan& p, int split_k, cudaStream_t stream) {
   if (!p.decode) return launch_streamk<KIND, EPI>(wm, am, ep, ws, M, N, p, stream);
-  if (p.bm == 32) return launch_decode<KIND, 32, EPI>(wm, am, ep, M, N, p, stream);
-  if (p.bm == 64) return launch_decode<KIND, 64, EPI>(wm, am, ep, M, N, p, stream);
-  return launch_decode<KIND, 128, EPI>(wm, am, ep, M, N, p, stream);
+  if (p.bm == 32) return launch_decode<KIND, 32, EPI>(wm, am, ep, M, N, p, split_k, stream);
+  if (p.bm == 64) return launch_decode<KIND, 64, EPI>(wm, am, ep, M, N, p, split_k, stream);
+  return launch_decode<KIND, 128, EPI>(wm, am, ep, M, N, p, split_k, stream);
 }
 
 int gemm_common(const void* a, const void* w, const GemmEpilogue& ep, int epi, int M, int N, int K, int ab_dtype,
@@ -622,7 +903,7 @@ int gemm_common(const void* a, const void* w, const GemmEpilogue& ep, int epi, i
   int eb = elem_bytes(ab_dtype);
   B200_REQUIRE(((int64_t)K * eb) % 16 == 0, "gemm: K*elem_bytes must be a multiple of 16 (TMA row pitch), K=%d", K);
   GemmPlan p;
-  int rc = plan_gemm(p, M, N, K, ab_dtype, split_k, epi);
+  int rc = plan_gemm(p, M, N, K, ab_dtype, split_k);
   if (rc) return rc;
   if (p.ws_bytes && (!workspace || workspace_bytes < p.ws_bytes)) {
     set_last_error("gemm: workspace %zu < %zu bytes", workspace_bytes, p.ws_bytes);
@@ -637,23 +918,59 @@ int gemm_common(const void* a, const void* w, const GemmEpilogue& ep, int epi, i
   if (rc) return rc;
   cudaStream_t s = (cudaStream_t)stream;
   if (epi == EPI_LINEAR) {
-    if (ab_dtype == B200_BF16) return dispatch_gemm<KIND_F16, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, s);
-    if (ab_dtype == B200_FP8_E4M3) return dispatch_gemm<KIND_F8F6F4, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, s);
-    return dispatch_gemm<KIND_I8, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, s);
+    if (ab_dtype == B200_BF16) return dispatch_gemm<KIND_F16, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, split_k, s);
+    if (ab_dtype == B200_FP8_E4M3) return dispatch_gemm<KIND_F8F6F4, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, split_k, s);
+    return dispatch_gemm<KIND_I8, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, split_k, s);
   }
-  if (ab_dtype == B200_BF16) return dispatch_gemm<KIND_F16, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, s);
-  if (ab_dtype == B200_FP8_E4M3) return dispatch_gemm<KIND_F8F6F4, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, s);
-  return dispatch_gemm<KIND_I8, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, s);
+  if (ab_dtype == B200_BF16) return dispatch_gemm<KIND_F16, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, split_k, s);
+  if (ab_dtype == B200_FP8_E4M3) return dispatch_gemm<KIND_F8F6F4, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, split_k, s);
+  return dispatch_gemm<KIND_I8, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, split_k, s);
 }
 
 }  // namespace
 
+namespace {
+template <int KIND, int EPI>
+int query_plan(DecodeCfg& c, int bm, int M, int n_tiles, int num_kb, int split_k, bool resid) {
+  if (bm == 32) return plan_decode<KIND, 32, EPI>(c, M, n_tiles, num_kb, split_k, resid);
+  if (bm == 64) return plan_decode<KIND, 64, EPI>(c, M, n_tiles, num_kb, split_k, resid);
+  return plan_decode<KIND, 128, EPI>(c, M, n_tiles, num_kb, split_k, resid);
+}
+}  // namespace
+
 extern "C" {
+
+int b200_gemm_decode_plan(int M, int N, int K, int ab_dtype, int split_k, int silu_mul, int has_residual, int* out6) {
+  B200_REQUIRE(out6 && M > 0 && M <= 128 && N > 0 && K > 0, "gemm_decode_plan: bad arguments");
+  B200_REQUIRE(ab_dtype == B200_BF16 || ab_dtype == B200_FP8_E4M3 || ab_dtype == B200_INT8, "gemm_decode_plan: bad dtype");
+  GemmPlan p;
+  int rc = plan_gemm(p, M, N, K, ab_dtype, split_k);
+  if (rc) return rc;
+  DecodeCfg c{};
+  const bool r = has_residual != 0;
+  if (silu_mul) {
+    rc = ab_dtype == B200_BF16 ? query_plan<KIND_F16, EPI_SILU_MUL>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
+         : ab_dtype == B200_FP8_E4M3 ? query_plan<KIND_F8F6F4, EPI_SILU_MUL>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
+                                     : query_plan<KIND_I8, EPI_SILU_MUL>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r);
+  } else {
+    rc = ab_dtype == B200_BF16 ? query_plan<KIND_F16, EPI_LINEAR>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
+         : ab_dtype == B200_FP8_E4M3 ? query_plan<KIND_F8F6F4, EPI_LINEAR>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
+                                     : query_plan<KIND_I8, EPI_LINEAR>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r);
+  }
+  if (rc) return rc;
+  out6[0] = c.S;
+  out6[1] = c.smem > SMEM_TWO_PER_SM ? 1 : 2;
+  out6[2] = c.nst;
+  out6[3] = c.nst;
+  out6[4] = c.cap_ctas;
+  out6[5] = (int)c.smem;
+  return B200_OK;
+}
 
 size_t b200_gemm_workspace_bytes(int M, int N, int K, int ab_dtype, int split_k) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   GemmPlan p;
-  if (plan_gemm(p, M, N, K, ab_dtype, split_k, EPI_LINEAR)) return 0;
+  if (plan_gemm(p, M, N, K, ab_dtype, split_k)) return 0;
   return p.ws_bytes;
 }
 

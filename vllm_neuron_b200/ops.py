@@ -245,6 +245,16 @@ def _ab_dtype(t):
     raise _cabi.B200Error(f"unsupported GEMM operand dtype {t.dtype}")
 
 
+def gemm_decode_plan(m, n, k, ab_dtype, split_k=0, silu_mul=False, has_residual=False) -> dict:
+    """The decode schedule the library picks for this shape on the current device (for benches / DESIGN notes)."""
+    import ctypes
+
+    out = (ctypes.c_int * 6)()
+    check(_cabi.load().b200_gemm_decode_plan(m, n, k, ab_dtype, split_k, int(silu_mul), int(has_residual), out),
+          "b200_gemm_decode_plan")
+    return dict(zip(("split", "ctas_per_sm", "w_stages", "a_stages", "cap_ctas", "smem"), list(out)))
+
+
 def gemm_workspace_bytes(m, n, k, ab_dtype, split_k=0) -> int:
     return int(_cabi.load().b200_gemm_workspace_bytes(m, n, k, ab_dtype, split_k))
 
