@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 4
+#define B200_ABI_VERSION 5
 
 enum {
   B200_OK = 0,
@@ -155,6 +155,19 @@ int b200_embedding(const int64_t* tokens, const void* table, void* out, int T, i
  * out_idx[t] = idx_offset + first index of the row maximum; out_val[t] = that maximum (for TP merges). */
 int b200_argmax(const float* logits, int64_t row_stride, float* out_val, int64_t* out_idx, int T, int V,
                 int64_t idx_offset, void* stream);
+
+/* ---------------------------------------------------------------- tensor-parallel exchange (NVLink peer memory)
+ * All-reduce (sum over `world` ranks, bf16) of the row-parallel GEMM outputs fused with the RMSNorm (+ dynamic per-token
+ * quantisation) that consumes it; replaces the Neuron-runtime collectives NxDI issues after o_proj / down_proj
+ * (tp_degree, model_loader.py:752-753).  host_peer_bufs[p] / host_peer_flags[p] are HOST arrays of `world` DEVICE
+ * pointers: rank p's partial [T][H] bf16 and rank p's flag area ([>= T][8] uint32, zero-initialised once), both inside
+ * peer-mapped (symmetric) memory.  epoch [>= T] uint32 is local, zero-initialised once.  Every rank must issue the same
+ * sequence of calls; consecutive calls must alternate between two partial buffers (see csrc/tp_allreduce.cu).
+ * Outputs (local): x_out [T][H] bf16 = the sum (ranks added in rank order, identical bits on every rank); with norm_w:
+ * out_bf16 and/or out_q + out_scale as b200_rmsnorm.  norm_w == NULL: plain all-reduce. */
+int b200_allreduce_rmsnorm(const void* const* host_peer_bufs, void* const* host_peer_flags, uint32_t* epoch, int rank,
+                           int world, void* x_out, const void* norm_w, void* out_bf16, void* out_q, float* out_scale, int T,
+                           int H, float eps, int q_dtype, void* stream);
 
 #ifdef __cplusplus
 }

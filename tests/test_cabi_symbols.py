@@ -34,7 +34,7 @@ def test_header_and_binding_agree(lib):
 
 def test_abi_version(lib):
     from vllm_neuron_b200 import _cabi
-    assert lib.b200_abi_version() == _cabi.ABI_VERSION == 4
+    assert lib.b200_abi_version() == _cabi.ABI_VERSION == 5
 
 
 def test_no_device_is_an_error_not_a_fallback(lib):
@@ -52,7 +52,7 @@ def test_argument_validation_without_gpu(lib):
     assert lib.b200_gemm(None, None, None, None, None, None, None, 1, 1, 16, 0, 0, 0, None, 0, None) == -1
     assert lib.b200_paged_attn_decode(None, 0, None, None, 0, None, 0, None, None, None, None, None, 0, None, 0, 1, 8, 8, 128, 32, 4, 0, 1.0, None) == -1
     # balanced split: at most ceil(max_blocks / min_quota) + 1 partials per (sequence, head)
-    assert lib.b200_paged_attn_decode_workspace_bytes(64, 32, 8, 128, 64, 8) == 64 * 32 * 9 * 130 * 4
+    assert lib.b200_paged_attn_decode_workspace_bytes(64, 32, 8, 128, 64, 8) == 64 * 32 * 9 * 130 * 4 + 64 * 8 * 4  # + part counts per (sequence, kv head)
 
 
 def test_ops_refuse_cpu_tensors():

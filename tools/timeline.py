@@ -32,13 +32,22 @@ def main():
     ap.add_argument("--ctx", type=int, default=2048)
     ap.add_argument("--json", default=None)
     a = ap.parse_args()
-    ops.device_check(0)
+    rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    group = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        group = dist.group.WORLD
+    ops.device_check(local)
     shape = replace(PRESETS[a.model], layers=a.layers)
     bs = 32
     mml = -(-(a.ctx + 64) // bs) * bs
     mb = mml // bs
     nb = a.batch * mb + 1
-    model = B200CausalLM(shape, None, quant=a.quant, num_blocks=nb, max_num_seqs=a.batch, max_model_len=mml, device="cuda:0")
+    model = B200CausalLM(shape, None, quant=a.quant, num_blocks=nb, max_num_seqs=a.batch, max_model_len=mml, device=f"cuda:{local}",
+                         tp_rank=rank, tp_size=world, tp_group=group)
     perm = torch.randperm(nb - 1, generator=torch.Generator().manual_seed(7)) + 1
     model.block_table.copy_(perm.reshape(a.batch, mb).to(torch.int32))
     for kv in model.kv:
@@ -55,6 +64,9 @@ def main():
         for _ in range(3):
             model.decode_step(a.batch, advance=True, use_graph=True)
         torch.cuda.synchronize()
+    if rank != 0:
+        torch.distributed.barrier()
+        os._exit(0)
     evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA and "memcpy" not in e.name.lower()
            and "memset" not in e.name.lower()]
     evs.sort(key=lambda e: e.time_range.start)
@@ -88,6 +100,12 @@ def main():
         base = 3 + per_layer
         for st, dur, pitch, name in rows[base: base + per_layer]:
             print(f"  {st:9.1f} {dur:7.2f} {pitch:7.2f}  {name[:80]}")
+    if world > 1:
+        sys.stdout.flush()
+        torch.distributed.barrier()
+        if a.json:
+            json.dump({"step_us": step, "layers": a.layers, "kernels": out}, open(a.json, "w"), indent=1)
+        os._exit(0)
     if a.json:
         json.dump({"step_us": step, "layers": a.layers, "kernels": out,
                    "layer_trace": [{"start_us": r[0], "dur_us": r[1], "pitch_us": r[2], "kernel": r[3]}

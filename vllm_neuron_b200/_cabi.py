@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200_paged.so")
 
 OK = 0
-ABI_VERSION = 4
+ABI_VERSION = 5
 BF16, FP8_E4M3, INT8, F32 = 0, 1, 2, 3
 
 _p = C.c_void_p
@@ -49,6 +49,7 @@ SIGNATURES = {
     "b200_quantize_per_token": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _p]),
     "b200_embedding": (_i, [_p, _p, _p, _i, _i, _i, _p]),
     "b200_argmax": (_i, [_p, _i64, _p, _p, _i, _i, _i64, _p]),
+    "b200_allreduce_rmsnorm": (_i, [_p, _p, _p, _i, _i, _p, _p, _p, _p, _p, _i, _i, _f, _i, _p]),
 }
 
 _lib = None

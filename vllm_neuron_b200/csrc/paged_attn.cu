@@ -99,8 +99,8 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
                              const __nv_bfloat16* __restrict__ q, int64_t q_stride,
                              const int32_t* __restrict__ block_table, int64_t bt_stride,
                              const int32_t* __restrict__ row_ids, const int32_t* __restrict__ ctx_lens,
-                             float* __restrict__ part_o, float* __restrict__ part_ml, int B, int Hq, int Hkv,
-                             int max_parts, int min_quota, int max_blocks, float scale_log2) {
+                             float* __restrict__ part_o, float* __restrict__ part_ml, int32_t* __restrict__ part_cnt,
+                             int B, int Hq, int Hkv, int max_parts, int min_quota, int max_blocks, float scale_log2) {
   constexpr int TILE = BS * D * 2;  // bytes of one K (or V) tile
   constexpr int KSTEPS = D / 16;
   extern __shared__ uint8_t smem_raw[];
@@ -270,6 +270,8 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
       const int pair_start = Hkv * pre[cur.b] + cur.kvh * cur.nblk;
       const int part = w - pair_start / R;
       const int d0 = lane >> 2;
+      // the worker that finishes the pair holds its last part: tell the merge kernel how many there are
+      if (pair_done && lane == 0) part_cnt[cur.b * Hkv + cur.kvh] = part + 1;
       if (h0 < G) {
         int64_t base = ((int64_t)(cur.b * Hq + cur.kvh * G + h0) * max_parts + part);
 #pragma unroll
@@ -318,49 +320,27 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 // Merge the per-worker partials of one token and (optionally) quantise the token's attention output for the o_proj
 // GEMM in the same pass:  out = sum_i 2^(m_i - M) O_i / sum_i 2^(m_i - M) l_i, rounded to bf16; then per-token
 // scale = max|out| / qmax, q = rn(out / scale) exactly as quantize_per_token does on the bf16 tensor.
-constexpr int COMB_THREADS = 256;
-constexpr int COMB_MAXV = 4;  // 8-element vectors per thread -> Hq*D <= 8192
+// Latency is all that matters here (a few MB out of L2): one thread per 8 output elements, and every load of the first
+// COMB_CHUNK parts -- the part count, the (m, l) pairs and the partial rows -- is issued before any of them is used, so
+// the common case (<= 4 parts per pair) costs one memory round trip.  Parts are always added in index order.
+constexpr int COMB_THREADS = 512;
+constexpr int COMB_MAXV = 4;   // 8-element vectors per thread -> Hq*D <= 16384
+constexpr int COMB_CHUNK = 4;  // parts merged per round trip
 
 template <int QD>
 __global__ void __launch_bounds__(COMB_THREADS)
     paged_attn_combine_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
-                              const int32_t* __restrict__ ctx_lens, __nv_bfloat16* __restrict__ out,
-                              uint2* __restrict__ out_q, float* __restrict__ out_scale, int B, int Hq, int Hkv, int D,
-                              int max_parts, int min_quota, int max_blocks, int nworkers) {
+                              const int32_t* __restrict__ part_cnt, const int32_t* __restrict__ ctx_lens,
+                              __nv_bfloat16* __restrict__ out, uint2* __restrict__ out_q, float* __restrict__ out_scale,
+                              int B, int Hq, int Hkv, int D, int max_parts) {
   griddep_launch();
   griddep_wait();
-  __shared__ int sh_i[2][32];
-  __shared__ float sh_f[32];
+  __shared__ float sh_f[COMB_THREADS / 32];
   const int b = blockIdx.x;
-  // blocks before this sequence and in total (same arithmetic as the main kernel's prefix table)
-  int before = 0, all = 0;
-  for (int i = threadIdx.x; i < B; i += COMB_THREADS) {
-    int n = blocks_of(ctx_lens[i], max_blocks);
-    all += n;
-    if (i < b) before += n;
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    before += __shfl_xor_sync(0xffffffffu, before, o);
-    all += __shfl_xor_sync(0xffffffffu, all, o);
-  }
   const int wid = threadIdx.x >> 5, ln = threadIdx.x & 31;
-  if (ln == 0) {
-    sh_i[0][wid] = before;
-    sh_i[1][wid] = all;
-  }
-  __syncthreads();
-  before = all = 0;
-  for (int i = 0; i < COMB_THREADS / 32; ++i) {
-    before += sh_i[0][i];
-    all += sh_i[1][i];
-  }
-  const int nblk = blocks_of(ctx_lens[b], max_blocks);
-  const int total = Hkv * all;
-  int R = (total + nworkers - 1) / nworkers;
-  if (R < min_quota) R = min_quota;
   const int G = Hq / Hkv;
   const int dvec = D / 8, nvec = Hq * dvec;
+  const bool empty = ctx_lens[b] <= 0;
 
   float y[COMB_MAXV][8];
   float amax = 0.f;
@@ -369,22 +349,62 @@ __global__ void __launch_bounds__(COMB_THREADS)
     const int vi = threadIdx.x + i * COMB_THREADS;
     if (vi < nvec) {
       const int h = vi / dvec, dv = vi % dvec;
-      const int pair_start = Hkv * before + (h / G) * nblk;
-      const int nparts = nblk > 0 ? (pair_start + nblk - 1) / R - pair_start / R + 1 : 0;
-      const float* pml = part_ml + (int64_t)(b * Hq + h) * max_parts * 2;
+      const float2* pml = reinterpret_cast<const float2*>(part_ml) + (int64_t)(b * Hq + h) * max_parts;
       const float* po = part_o + (int64_t)(b * Hq + h) * max_parts * D + dv * 8;
+      // ---- first chunk: everything in flight at once (slots >= nparts hold stale data and are masked below)
+      const int cnt_raw = part_cnt[b * Hkv + h / G];
+      float2 ml0[COMB_CHUNK];
+      float4 a0[COMB_CHUNK], a1[COMB_CHUNK];
+#pragma unroll
+      for (int c = 0; c < COMB_CHUNK; ++c) {
+        const int cc = c < max_parts ? c : 0;
+        ml0[c] = pml[cc];
+        a0[c] = *reinterpret_cast<const float4*>(po + (int64_t)cc * D);
+        a1[c] = *reinterpret_cast<const float4*>(po + (int64_t)cc * D + 4);
+      }
+      const int nparts = empty ? 0 : (cnt_raw < max_parts ? cnt_raw : max_parts);
       float Mx = -INFINITY;
-      for (int c = 0; c < nparts; ++c) Mx = fmaxf(Mx, pml[2 * c]);
+#pragma unroll
+      for (int c = 0; c < COMB_CHUNK; ++c)
+        if (c < nparts) Mx = fmaxf(Mx, ml0[c].x);
+      for (int c0 = COMB_CHUNK; c0 < nparts; c0 += COMB_CHUNK) {
+        float mm[COMB_CHUNK];
+#pragma unroll
+        for (int c = 0; c < COMB_CHUNK; ++c) mm[c] = c0 + c < nparts ? pml[c0 + c].x : -INFINITY;
+#pragma unroll
+        for (int c = 0; c < COMB_CHUNK; ++c) Mx = fmaxf(Mx, mm[c]);
+      }
       float acc[8], L = 0.f;
 #pragma unroll
       for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-      for (int c = 0; c < nparts; ++c) {
-        const float wgt = exp2f(pml[2 * c] - Mx);
-        const float4 a0 = *reinterpret_cast<const float4*>(po + (int64_t)c * D);
-        const float4 a1 = *reinterpret_cast<const float4*>(po + (int64_t)c * D + 4);
-        acc[0] += wgt * a0.x; acc[1] += wgt * a0.y; acc[2] += wgt * a0.z; acc[3] += wgt * a0.w;
-        acc[4] += wgt * a1.x; acc[5] += wgt * a1.y; acc[6] += wgt * a1.z; acc[7] += wgt * a1.w;
-        L += wgt * pml[2 * c + 1];
+#pragma unroll
+      for (int c = 0; c < COMB_CHUNK; ++c) {
+        if (c < nparts) {
+          const float wgt = exp2f(ml0[c].x - Mx);
+          acc[0] += wgt * a0[c].x; acc[1] += wgt * a0[c].y; acc[2] += wgt * a0[c].z; acc[3] += wgt * a0[c].w;
+          acc[4] += wgt * a1[c].x; acc[5] += wgt * a1[c].y; acc[6] += wgt * a1[c].z; acc[7] += wgt * a1[c].w;
+          L += wgt * ml0[c].y;
+        }
+      }
+      for (int c0 = COMB_CHUNK; c0 < nparts; c0 += COMB_CHUNK) {
+        float2 ml[COMB_CHUNK];
+        float4 b0[COMB_CHUNK], b1[COMB_CHUNK];
+#pragma unroll
+        for (int c = 0; c < COMB_CHUNK; ++c) {
+          const int cc = c0 + c < nparts ? c0 + c : c0;
+          ml[c] = pml[cc];
+          b0[c] = *reinterpret_cast<const float4*>(po + (int64_t)cc * D);
+          b1[c] = *reinterpret_cast<const float4*>(po + (int64_t)cc * D + 4);
+        }
+#pragma unroll
+        for (int c = 0; c < COMB_CHUNK; ++c) {
+          if (c0 + c < nparts) {
+            const float wgt = exp2f(ml[c].x - Mx);
+            acc[0] += wgt * b0[c].x; acc[1] += wgt * b0[c].y; acc[2] += wgt * b0[c].z; acc[3] += wgt * b0[c].w;
+            acc[4] += wgt * b1[c].x; acc[5] += wgt * b1[c].y; acc[6] += wgt * b1[c].z; acc[7] += wgt * b1[c].w;
+            L += wgt * ml[c].y;
+          }
+        }
       }
       const bool ok = nparts > 0 && L > 0.f;
       uint32_t packed[4];
@@ -401,10 +421,10 @@ __global__ void __launch_bounds__(COMB_THREADS)
   }
   if constexpr (QD != B200_BF16) {
     amax = warp_max(amax);
-    __syncthreads();
     if (ln == 0) sh_f[wid] = amax;
     __syncthreads();
     amax = 0.f;
+#pragma unroll
     for (int i = 0; i < COMB_THREADS / 32; ++i) amax = fmaxf(amax, sh_f[i]);
     const float qmax = QD == B200_FP8_E4M3 ? 448.f : 127.f;
     const float scale = amax > 0.f ? __fdiv_rn(amax, qmax) : 1.f;
@@ -637,15 +657,15 @@ DecodePlan plan_decode(int B, int Hq, int Hkv, int D, int max_blocks, int min_qu
   long want = (max_total + (long)p.min_quota * DEC_WARPS - 1) / ((long)p.min_quota * DEC_WARPS);
   p.grid = (int)(want < sm_count() ? want : sm_count());
   if (p.grid < 1) p.grid = 1;
-  p.ws_bytes = (size_t)B * Hq * p.max_parts * (D + 2) * sizeof(float);
+  p.ws_bytes = (size_t)B * Hq * p.max_parts * (D + 2) * sizeof(float) + (size_t)B * Hkv * sizeof(int32_t);
   return p;
 }
 
 template <int D>
 int launch_decode(const CUtensorMap& km, const CUtensorMap& vm, const void* q, int64_t q_stride, const int32_t* bt,
                   int64_t bt_stride, const int32_t* row_ids, const int32_t* ctx_lens, void* out, void* out_q,
-                  float* out_scale, int q_dtype, float* part_o, float* part_ml, int B, int Hq, int Hkv, int max_blocks,
-                  const DecodePlan& p, float scale, cudaStream_t stream) {
+                  float* out_scale, int q_dtype, float* part_o, float* part_ml, int32_t* part_cnt, int B, int Hq, int Hkv,
+                  int max_blocks, const DecodePlan& p, float scale, cudaStream_t stream) {
   auto kern = paged_attn_decode_kernel<D, DEC_STAGES, DEC_WARPS>;
   const size_t smem = (size_t)DEC_WARPS * DEC_STAGES * 2 * BS * D * 2 + DEC_WARPS * DEC_STAGES * 8 + (size_t)(B + 1) * 4 + 1024;
   constexpr size_t smem_max = (size_t)DEC_WARPS * DEC_STAGES * 2 * BS * D * 2 + DEC_WARPS * DEC_STAGES * 8 + (size_t)(DEC_MAX_B + 1) * 4 + 1024;
@@ -655,21 +675,20 @@ int launch_decode(const CUtensorMap& km, const CUtensorMap& vm, const void* q, i
     attr_done = true;
   }
   B200_CUDA_OK(launch_kernel(kern, dim3(p.grid), dim3(DEC_WARPS * 32), smem, stream, km, vm, (const __nv_bfloat16*)q,
-                             q_stride, bt, bt_stride, row_ids, ctx_lens, part_o, part_ml, B, Hq, Hkv, p.max_parts,
+                             q_stride, bt, bt_stride, row_ids, ctx_lens, part_o, part_ml, part_cnt, B, Hq, Hkv, p.max_parts,
                              p.min_quota, max_blocks, scale * 1.4426950408889634f));
-  const int nworkers = p.grid * DEC_WARPS;
   if (q_dtype == B200_FP8_E4M3)
     B200_CUDA_OK(launch_kernel(paged_attn_combine_kernel<B200_FP8_E4M3>, dim3(B), dim3(COMB_THREADS), 0, stream, part_o,
-                               part_ml, ctx_lens, (__nv_bfloat16*)out, (uint2*)out_q, out_scale, B, Hq, Hkv, D, p.max_parts,
-                               p.min_quota, max_blocks, nworkers));
+                               part_ml, part_cnt, ctx_lens, (__nv_bfloat16*)out, (uint2*)out_q, out_scale, B, Hq, Hkv, D,
+                               p.max_parts));
   else if (q_dtype == B200_INT8)
     B200_CUDA_OK(launch_kernel(paged_attn_combine_kernel<B200_INT8>, dim3(B), dim3(COMB_THREADS), 0, stream, part_o,
-                               part_ml, ctx_lens, (__nv_bfloat16*)out, (uint2*)out_q, out_scale, B, Hq, Hkv, D, p.max_parts,
-                               p.min_quota, max_blocks, nworkers));
+                               part_ml, part_cnt, ctx_lens, (__nv_bfloat16*)out, (uint2*)out_q, out_scale, B, Hq, Hkv, D,
+                               p.max_parts));
   else
     B200_CUDA_OK(launch_kernel(paged_attn_combine_kernel<B200_BF16>, dim3(B), dim3(COMB_THREADS), 0, stream, part_o,
-                               part_ml, ctx_lens, (__nv_bfloat16*)out, (uint2*)nullptr, (float*)nullptr, B, Hq, Hkv, D,
-                               p.max_parts, p.min_quota, max_blocks, nworkers));
+                               part_ml, part_cnt, ctx_lens, (__nv_bfloat16*)out, (uint2*)nullptr, (float*)nullptr, B, Hq, Hkv,
+                               D, p.max_parts));
   return B200_OK;
 }
 
@@ -732,12 +751,13 @@ int b200_paged_attn_decode(const void* q, int64_t q_token_stride, const void* k_
   if (rc) return rc;
   float* part_o = (float*)workspace;
   float* part_ml = part_o + (size_t)B * Hq * p.max_parts * D;
+  int32_t* part_cnt = reinterpret_cast<int32_t*>(part_ml + (size_t)B * Hq * p.max_parts * 2);
   cudaStream_t s = (cudaStream_t)stream;
   if (D == 128)
     return launch_decode<128>(km, vm, q, q_token_stride, block_table, bt_row_stride, row_ids, ctx_lens, out, out_q,
-                              out_scale, q_dtype, part_o, part_ml, B, Hq, Hkv, max_blocks, p, scale, s);
+                              out_scale, q_dtype, part_o, part_ml, part_cnt, B, Hq, Hkv, max_blocks, p, scale, s);
   return launch_decode<64>(km, vm, q, q_token_stride, block_table, bt_row_stride, row_ids, ctx_lens, out, out_q, out_scale,
-                           q_dtype, part_o, part_ml, B, Hq, Hkv, max_blocks, p, scale, s);
+                           q_dtype, part_o, part_ml, part_cnt, B, Hq, Hkv, max_blocks, p, scale, s);
 }
 
 int b200_paged_attn_prefill(const void* q, int64_t q_token_stride, const void* k_pool, const void* v_pool, int num_blocks,

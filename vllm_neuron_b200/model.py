@@ -148,7 +148,8 @@ class StepBuffers:
 class B200CausalLM:
     def __init__(self, shape: ModelShape, full_weights: dict | None, *, quant: str = "bf16", num_blocks: int,
                  max_num_seqs: int, max_model_len: int, block_size: int = 32, device="cuda", tp_rank: int = 0,
-                 tp_size: int = 1, tp_group=None, quant_lm_head: bool = True, seed: int = 0):
+                 tp_size: int = 1, tp_group=None, quant_lm_head: bool = True, seed: int = 0,
+                 use_peer_exchange: bool = True):
         assert quant in ("bf16", "fp8", "int8"), f"quant mode {quant!r} not built yet"
         assert shape.num_q_heads % tp_size == 0 and shape.num_kv_heads % tp_size == 0, "heads must divide TP"
         assert shape.intermediate % tp_size == 0 and shape.vocab % tp_size == 0
@@ -199,6 +200,12 @@ class B200CausalLM:
         self._decode_bufs: dict[int, StepBuffers] = {}
         self._graphs: dict[tuple, tuple] = {}
         self._alloc_workspaces()
+        # TP exchange over NVLink peer memory (our kernel); NCCL stays for prefill-sized batches and the greedy merge
+        self.tp_comm = None
+        if tp_size > 1 and use_peer_exchange:
+            from .tp_comm import TpComm
+
+            self.tp_comm = TpComm(tp_group, tp_rank, tp_size, max_num_seqs, shape.hidden, dev)
 
     # ------------------------------------------------------------------ workspaces
     def _linears(self):
@@ -220,8 +227,8 @@ class B200CausalLM:
             dtype=torch.uint8, device=dev)
 
     # ------------------------------------------------------------------ building blocks
-    def _linear(self, lin: _Linear, x, xs=None, residual=None, out_dtype=torch.bfloat16):
-        return ops.gemm(x, lin.w, xs, lin.scale, lin.bias, residual, out_dtype=out_dtype, workspace=self.gemm_ws)
+    def _linear(self, lin: _Linear, x, xs=None, residual=None, out_dtype=torch.bfloat16, out=None):
+        return ops.gemm(x, lin.w, xs, lin.scale, lin.bias, residual, out=out, out_dtype=out_dtype, workspace=self.gemm_ws)
 
     def _norm(self, x, w):
         q = _QKIND[self.quant]
@@ -229,37 +236,54 @@ class B200CausalLM:
             return ops.rmsnorm(x, w, self.shape.rms_eps), None
         return ops.rmsnorm(x, w, self.shape.rms_eps, quant=q)
 
-    def _all_reduce(self, x):
-        if self.tp_size > 1:
+    def _row_parallel(self, lin: _Linear, a, a_s, x, next_norm_w):
+        """Row-parallel linear (o_proj / down_proj) + residual, the TP exchange, and the RMSNorm that consumes the sum.
+        Returns (x_new, h, h_scale); h is None when next_norm_w is None.
+        TP=1: GEMM then rmsnorm.  TP>1, decode-sized batches: the GEMM writes its partial into peer-mapped memory and ONE
+        kernel (b200_allreduce_rmsnorm) sums the ranks over NVLink and normalises/quantises.  Larger batches (prefill):
+        NCCL all-reduce + rmsnorm."""
+        t = a.shape[0]
+        first = self.tp_rank == 0  # the residual is folded into rank 0's GEMM epilogue; the exchange sums it in once
+        res = x if first else None
+        if self.tp_size == 1:
+            x = self._linear(lin, a, a_s, res)
+        elif self.tp_comm is not None and t <= self.tp_comm.rows:
+            i, part = self.tp_comm.next_partial(t)
+            self._linear(lin, a, a_s, res, out=part)
+            return self.tp_comm.exchange(i, t, next_norm_w, self.shape.rms_eps, _QKIND[self.quant])
+        else:
+            x = self._linear(lin, a, a_s, res)
             torch.distributed.all_reduce(x, group=self.tp_group)
-        return x
+        if next_norm_w is None:
+            return x, None, None
+        h, hs = self._norm(x, next_norm_w)
+        return x, h, hs
 
     def _layers(self, x, positions, slot_mapping, attn_fn):
         t = x.shape[0]
         q = _QKIND[self.quant]
         qd = self.hq * self.d
-        first = self.tp_rank == 0  # the residual is folded into rank 0's GEMM epilogue; the all-reduce sums it in once
+        n_layers = len(self.layers)
+        h, hs = self._norm(x, self.layers[0]["input_norm"])
         for li, L in enumerate(self.layers):
-            h, hs = self._norm(x, L["input_norm"])
             qkv = self._linear(L["qkv"], h, hs)
             kp, vp = self.kv[li][0], self.kv[li][1]
             ops.rope_kv_write(qkv, positions, self.cos, self.sin, kp, vp, slot_mapping, self.hq)
             a = attn_fn(qkv[:, :qd].unflatten(1, (self.hq, self.d)), kp, vp, q)
             if q is None:
-                x = self._all_reduce(self._linear(L["o"], a.reshape(t, qd), None, x if first else None))
-            else:
-                if not isinstance(a, tuple):  # prefill attention returns bf16; decode quantises in its merge kernel
-                    a = ops.quantize_per_token(a.reshape(t, qd), q)
-                x = self._all_reduce(self._linear(L["o"], a[0], a[1], x if first else None))
-            h2, h2s = self._norm(x, L["post_norm"])
+                a = (a.reshape(t, qd), None)
+            elif not isinstance(a, tuple):  # prefill attention returns bf16; decode quantises in its merge kernel
+                a = ops.quantize_per_token(a.reshape(t, qd), q)
+            x, h2, h2s = self._row_parallel(L["o"], a[0], a[1], x, L["post_norm"])
             gu = L["gu"]
             # gate/up GEMM with SiLU(gate)*up in the epilogue; the per-group maxima feed the per-token quantisation
             act, group_amax = ops.gemm_silu_mul(h2, gu.w, h2s, gu.scale, gu.bias, workspace=self.gemm_ws)
             if q is None:
-                x = self._all_reduce(self._linear(L["down"], act, None, x if first else None))
+                aq, a_s = act, None
             else:
                 aq, a_s = ops.quantize_per_token(act, q, group_amax=group_amax)
-                x = self._all_reduce(self._linear(L["down"], aq, a_s, x if first else None))
+            nxt = self.layers[li + 1]["input_norm"] if li + 1 < n_layers else None
+            x, h, hs = self._row_parallel(L["down"], aq, a_s, x, nxt)
         return x
 
     def _sample(self, x_rows):

@@ -406,3 +406,31 @@ def argmax(logits, idx_offset: int = 0, want_val: bool = False):
     with _k("argmax"):
         check(_cabi.load().b200_argmax(_ptr(logits), logits.stride(0), _ptr(val), _ptr(idx), t, v, idx_offset, _stream()), "b200_argmax")
     return (val, idx) if want_val else idx
+
+
+def allreduce_rmsnorm(peer_bufs, peer_flags, epoch, rank, world, t, h, norm_w, eps, quant=None, want_bf16=False):
+    """One-shot all-reduce over NVLink peer memory fused with RMSNorm (+ per-token quantisation).
+    peer_bufs / peer_flags: ctypes arrays of `world` device pointers (tp_comm.TpComm).  Returns (x, h_out, h_scale):
+    x = the reduced bf16 residual stream; h_out = normed bf16 (quant None) or quantised tensor; h_scale = scales or None."""
+    dev = epoch.device
+    x = torch.empty((t, h), dtype=torch.bfloat16, device=dev)
+    qd = _QDT[quant]
+    if norm_w is None:
+        with _k("allreduce"):
+            check(_cabi.load().b200_allreduce_rmsnorm(peer_bufs, peer_flags, _ptr(epoch), rank, world, _ptr(x), 0, 0, 0, 0,
+                                                      t, h, float(eps), BF16, _stream()), "b200_allreduce_rmsnorm")
+        return x, None, None
+    if qd == BF16:
+        y = torch.empty_like(x)
+        with _k("allreduce_rmsnorm"):
+            check(_cabi.load().b200_allreduce_rmsnorm(peer_bufs, peer_flags, _ptr(epoch), rank, world, _ptr(x), _ptr(norm_w),
+                                                      _ptr(y), 0, 0, t, h, float(eps), qd, _stream()), "b200_allreduce_rmsnorm")
+        return x, y, None
+    q = torch.empty((t, h), dtype=_TORCH_Q[qd], device=dev)
+    s = torch.empty((t,), dtype=torch.float32, device=dev)
+    y = torch.empty_like(x) if want_bf16 else None
+    with _k("allreduce_rmsnorm_quant"):
+        check(_cabi.load().b200_allreduce_rmsnorm(peer_bufs, peer_flags, _ptr(epoch), rank, world, _ptr(x), _ptr(norm_w),
+                                                  _ptr(y), _ptr(q), _ptr(s), t, h, float(eps), qd, _stream()),
+              "b200_allreduce_rmsnorm")
+    return x, q, s

@@ -1,0 +1,51 @@
+"""Peer-memory plumbing for the tensor-parallel exchange step (b200_allreduce_rmsnorm).
+
+torch.distributed's symmetric memory is used ONLY to obtain peer-mapped device memory (one region per rank with the same
+layout, every region mapped into every process); the exchange itself is our kernel (csrc/tp_allreduce.cu), not NCCL.
+Region layout (bytes):  [ partial A : rows*hidden bf16 | partial B : rows*hidden bf16 | flags : rows*8 uint32 ].
+The row-parallel GEMMs (o_proj, down_proj) write their outputs straight into partial A / B of the local region.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+
+class TpComm:
+    FLAG_SLOTS = 8  # = AR_MAX_TP in csrc/tp_allreduce.cu
+
+    def __init__(self, group, rank: int, world: int, rows: int, hidden: int, device):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.rank, self.world, self.rows, self.hidden = rank, world, rows, hidden
+        part_bytes = rows * hidden * 2
+        part_bytes = (part_bytes + 255) // 256 * 256
+        flag_bytes = rows * self.FLAG_SLOTS * 4
+        self._region = symm_mem.empty((2 * part_bytes + flag_bytes,), dtype=torch.uint8, device=device)
+        self._region.zero_()
+        self._hdl = symm_mem.rendezvous(self._region, group)
+        base = [int(p) for p in self._hdl.buffer_ptrs]
+        assert len(base) == world and base[rank] == self._region.data_ptr()
+        self.partials = [self._region[i * part_bytes: i * part_bytes + rows * hidden * 2].view(torch.bfloat16).view(rows, hidden)
+                         for i in range(2)]
+        arr = C.c_void_p * world
+        self._peer_bufs = [arr(*[b + i * part_bytes for b in base]) for i in range(2)]
+        self._peer_flags = arr(*[b + 2 * part_bytes for b in base])
+        self.epoch = torch.zeros((rows,), dtype=torch.int32, device=device)
+        self._next = 0
+        torch.cuda.synchronize(device)
+        self._hdl.barrier()  # every rank has zeroed its flags before anyone signals
+
+    def next_partial(self, t: int):
+        """The buffer the next row-parallel GEMM must write ([t, hidden] view); alternates A / B."""
+        i = self._next
+        return i, self.partials[i][:t]
+
+    def exchange(self, i: int, t: int, norm_w, eps: float, quant):
+        from . import ops
+
+        assert i == self._next, "exchange sites must alternate between the two partial buffers"
+        self._next ^= 1
+        return ops.allreduce_rmsnorm(self._peer_bufs[i], self._peer_flags, self.epoch, self.rank, self.world, t, self.hidden,
+                                     norm_w, eps, quant)
