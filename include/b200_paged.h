@@ -126,6 +126,9 @@ size_t b200_gemm_workspace_bytes(int M, int N, int K, int ab_dtype, int split_k)
 /* The decode schedule (M <= 128) chosen on the current device for a shape: out6 = {cluster size S, CTAs per SM, weight
  * ring depth, activation ring depth, CTAs the chip holds at once, dynamic shared memory bytes}.  Needs a device. */
 int b200_gemm_decode_plan(int M, int N, int K, int ab_dtype, int split_k, int silu_mul, int has_residual, int* out6);
+/* Profiling aid: with a non-NULL device buffer ([#CTAs][8] uint64) every decode-schedule GEMM CTA records %globaltimer
+ * at its phase boundaries (tools/gemm_trace.py); NULL (default) switches it off. */
+void b200_gemm_set_trace(void* device_buf);
 int b200_gemm(const void* a, const void* w, void* out, const float* a_scale, const float* w_scale, const void* bias,
               const void* residual, int M, int N, int K, int ab_dtype, int out_dtype, int split_k, void* workspace,
               size_t workspace_bytes, void* stream);

@@ -102,7 +102,10 @@ def bench_exchange(group, rank, world, dev, rows=64, hidden=4096, reps=64):
 
 
 def check_model(group, rank, world, dev):
-    shape = PRESETS["tiny-test"]
+    from vllm_neuron_b200.config import ModelShape
+
+    # 8 kv heads so the same weights shard at TP = 2, 4 and 8 (one kv head per rank at 8)
+    shape = ModelShape("tp-test", 512, 2, 16, 8, 64, 1024, 2048, 10000.0, None, 1e-5)
     bs, mml, nb, b = 32, 256, 33, 4
     w = random_init_full_weights(shape, seed=3, std=0.05)
     for quant in ("bf16", "fp8"):

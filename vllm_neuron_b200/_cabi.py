@@ -42,6 +42,7 @@ SIGNATURES = {
     "b200_paged_attn_prefill": (_i, [_p, _i64, _p, _p, _i, _p, _p, _i, _i, _i, _i, _i, _i, _f, _p]),
     "b200_gemm_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "b200_gemm_decode_plan": (_i, [_i, _i, _i, _i, _i, _i, _i, _p]),
+    "b200_gemm_set_trace": (None, [_p]),
     "b200_gemm": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _sz, _p]),
     "b200_gemm_silu_mul": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _sz, _p]),
     "b200_rmsnorm": (_i, [_p, _p, _p, _p, _p, _i, _i, _f, _i, _p]),

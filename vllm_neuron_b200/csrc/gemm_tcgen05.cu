@@ -401,12 +401,16 @@ constexpr int DEC_MAX_ST = 12;
 template <int KIND, int BM, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
     gemm_decode_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap a_map,
-                       GemmEpilogue ep, int M, int N, int num_kb, int nst) {
+                       GemmEpilogue ep, int M, int N, int num_kb, int nst, unsigned long long* __restrict__ trace) {
   using T = KindTraits<KIND>;
   constexpr int BK_ELEMS = GEMM_BK_BYTES / T::ELEM;
   constexpr int W_TILE = GEMM_BN * GEMM_BK_BYTES;
   constexpr int A_TILE = BM * GEMM_BK_BYTES;
   constexpr uint32_t TMEM_COLS = BM < 32 ? 32 : BM;
+  // optional per-CTA time stamps (b200_gemm_set_trace; tools/gemm_trace.py): 0 start, 1 producer past the dependency,
+  // 2 first stage landed, 3 last MMA retired, 4 partials pushed, 5 cluster barrier passed, 6 outputs stored
+#define B200_STAMP(k) do { if (trace) trace[(size_t)blockIdx.x * 8 + (k)] = globaltimer_ns(); } while (0)
+  if (threadIdx.x == 0) B200_STAMP(0);
   constexpr uint32_t IDESC = umma_idesc(T::CFMT, T::ABFMT, GEMM_BN, BM);
 
   extern __shared__ uint8_t smem_raw[];
@@ -477,6 +481,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
         tma_load_2d_hint(w_ring + (size_t)i * W_TILE, &w_map, &full_w[i], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
       }
       griddep_wait();
+      B200_STAMP(1);
       for (int i = 0; i < npre; ++i) {
         mbar_expect_tx(&full_a[i], A_TILE);
         tma_load_2d_hint(a_ring + (size_t)i * A_TILE, &a_map, &full_a[i], (kb0 + i) * BK_ELEMS, 0, pol_a);
@@ -503,6 +508,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
       mbar_wait(&full_a[s], ph);
       tc_fence_after();
       if (lane == 0) {
+        if (i == 0) B200_STAMP(2);
         const uint32_t wa = smem_u32(w_ring + (size_t)s * W_TILE);
         const uint32_t aa = smem_u32(a_ring + (size_t)s * A_TILE);
 #pragma unroll
@@ -576,6 +582,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
     // ---- part 2: the accumulator is final
     mbar_wait(tfull, 0);
     tc_fence_after();
+    if (et == 0) B200_STAMP(3);
     const uint32_t acc = tmem_base + ((uint32_t)(lg * 32) << 16);
     if (S == 1) {
       const int n = n0 + nl;
@@ -608,9 +615,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
   }
   tc_fence_before();
   __syncwarp();
+  if (threadIdx.x == 64) B200_STAMP(4);
   if (S > 1) {
     if (warp < 2) cluster_wait();  // phase 1 for the warps that do not push
     cluster_sync_all();            // phase 2: all partials have landed
+    if (threadIdx.x == 64) B200_STAMP(5);
     if (warp >= 2) {
       const int n0 = n_tile * GEMM_BN + 4 * t4;
       const bool hb = ep.bias != nullptr, hr = EPI == EPI_LINEAR && ep.residual != nullptr;
@@ -694,6 +703,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
     }
   }
   __syncthreads();
+  if (threadIdx.x == 0) B200_STAMP(6);
+#undef B200_STAMP
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
@@ -702,6 +713,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
 using namespace b200;
 
 namespace {
+
+unsigned long long* g_trace = nullptr;  // b200_gemm_set_trace
 
 struct GemmPlan {
   bool decode;  // M <= 128: cluster split-K kernel; else persistent stream-K
@@ -881,7 +894,7 @@ int launch_decode(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilog
   if (rc) return rc;
   auto kern = gemm_decode_kernel<KIND, BM, EPI>;
   B200_CUDA_OK(launch_kernel_cluster(kern, dim3(p.n_tiles * c.S), dim3(GEMM_THREADS), c.smem, c.S, stream, wm, am, ep, M, N,
-                                     p.num_kb, c.nst));
+                                     p.num_kb, c.nst, g_trace));
   return B200_OK;
 }
 
@@ -939,6 +952,8 @@ int query_plan(DecodeCfg& c, int bm, int M, int n_tiles, int num_kb, int split_k
 }  // namespace
 
 extern "C" {
+
+void b200_gemm_set_trace(void* buf) { g_trace = (unsigned long long*)buf; }
 
 int b200_gemm_decode_plan(int M, int N, int K, int ab_dtype, int split_k, int silu_mul, int has_residual, int* out6) {
   B200_REQUIRE(out6 && M > 0 && M <= 128 && N > 0 && K > 0, "gemm_decode_plan: bad arguments");

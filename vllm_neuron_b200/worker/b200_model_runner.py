@@ -163,6 +163,10 @@ class B200ModelRunner:
         self._pin_upd = torch.zeros((max(64, 4 * n), 3), dtype=torch.int32).pin_memory()
         self._dev_upd = torch.zeros_like(self._pin_upd, device=self.device)
         self._pin_out = torch.zeros(n, dtype=torch.int64).pin_memory()
+        # numpy views of the pinned staging buffers: one vectorised store per field instead of per-request tensor
+        # __setitem__ calls (the reference builds Python lists and calls torch.tensor() on them, RUNNER:887-917)
+        self._np_tokens, self._np_rows = self._pin_tokens.numpy(), self._pin_rows.numpy()
+        self._np_ntok, self._np_out = self._pin_ntok.numpy(), self._pin_out.numpy()
 
     # ------------------------------------------------------------------ state tracking (RUNNER:381-510)
     def _update_states(self, so) -> list[tuple[int, int, int]]:
@@ -245,13 +249,14 @@ class B200ModelRunner:
         dec_ids = list(scheduler_output.scheduled_cached_reqs.req_ids)
         if dec_ids:
             b = len(dec_ids)
-            max_ctx = 0
-            for i, rid in enumerate(dec_ids):
-                st = self.requests[rid]
-                self._pin_tokens[i] = st.output_token_ids[-1] if st.output_token_ids else st.prompt_token_ids[-1]
-                self._pin_rows[i] = st.row
-                self._pin_ntok[st.row] = st.num_tokens
-                max_ctx = max(max_ctx, st.num_tokens)
+            reqs = self.requests
+            sts = [reqs[rid] for rid in dec_ids]
+            rows = [st.row for st in sts]
+            ntok = [len(st.prompt_token_ids) + len(st.output_token_ids) for st in sts]
+            self._np_tokens[:b] = [st.output_token_ids[-1] if st.output_token_ids else st.prompt_token_ids[-1] for st in sts]
+            self._np_rows[:b] = rows
+            self._np_ntok[rows] = ntok
+            max_ctx = max(ntok)
             bufs = self.model.decode_buffers(b)
             bufs.tokens.copy_(self._pin_tokens[:b], non_blocking=True)
             bufs.row_ids.copy_(self._pin_rows[:b], non_blocking=True)
@@ -267,8 +272,7 @@ class B200ModelRunner:
         self._pin_out[:n].copy_(ids, non_blocking=True)
         torch.cuda.current_stream().synchronize()
         self.d2h_bytes_last += n * 8
-        sampled = [[int(x)] for x in self._pin_out[:n].tolist()]
-        sampled = [[x for x in row if x != -1] for row in sampled]  # RUNNER:304-306
+        sampled = [[x] if x != -1 else [] for x in self._np_out[:n].tolist()]  # RUNNER:304-306: -1 is padding
         for rid, row in zip(req_ids, sampled):
             self.requests[rid].output_token_ids.extend(row)  # RUNNER:325-339
         if self.tp_rank != 0 and self.tp_size > 1:
