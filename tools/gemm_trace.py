@@ -30,7 +30,7 @@ def main():
     x = torch.randn(m, k, device="cuda", dtype=torch.bfloat16)
     out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
     sw = torch.ones(n, device="cuda")
-    trace = torch.zeros(ctas * 8, dtype=torch.int64, device="cuda")
+    trace = torch.zeros(ctas * 24, dtype=torch.int64, device="cuda")
 
     def chain():
         for w in ws:
@@ -47,7 +47,8 @@ def main():
     for _ in range(3):
         g.replay()
     torch.cuda.synchronize()
-    t = trace.view(ctas, 8).cpu().double()
+    kb = trace[ctas * 8:].view(ctas, 16).cpu().double()
+    t = trace[: ctas * 8].view(ctas, 8).cpu().double()
     t0 = t[:, 1].median()  # dependency resolved
     print(f"M={m} N={n} K={k} plan={plan} ctas={ctas}")
     for i, name in enumerate(NAMES):
@@ -57,6 +58,10 @@ def main():
             continue
         r = (col - t0) / 1e3
         print(f"  {name:26s} median {r.median():7.2f} us   min {r.min():7.2f}   max {r.max():7.2f}")
+    for i in range(8):
+        w_, a_ = kb[:, i], kb[:, 8 + i]
+        if (w_ > 0).any():
+            print(f"  k-block {i}: W seen {((w_[w_ > 0] - t0) / 1e3).median():6.2f} us, A seen {((a_[a_ > 0] - t0) / 1e3).median():6.2f} us (medians)")
 
 
 if __name__ == "__main__":

@@ -134,6 +134,16 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
 __device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
   asm volatile("st.shared::cluster.f32 [%0], %1;\n" ::"r"(addr), "f"(v) : "memory");
 }
+__device__ __forceinline__ void cluster_arrive_release() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+}
+// bulk copy own shared memory -> shared memory of a cluster peer; `dst` and `mbar` are shared::cluster addresses (mapa),
+// completion (bytes) is signalled on the peer's mbarrier
+__device__ __forceinline__ void bulk_copy_to_cluster(uint32_t dst, uint32_t src_cta, uint32_t bytes, uint32_t mbar) {
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst),
+               "r"(src_cta), "r"(bytes), "r"(mbar)
+               : "memory");
+}
 // split arrive / wait: every thread of every CTA executes each exactly once per phase
 __device__ __forceinline__ void cluster_arrive_relaxed() {
   asm volatile("barrier.cluster.arrive.relaxed.aligned;\n" ::: "memory");

@@ -392,16 +392,18 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 // so nothing between the last MMA and the output stores waits on a global load.
 //
 // Split-K reduction (S > 1): the M tokens are divided among the cluster, rank q owns tokens [M*q/S, M*(q+1)/S).
-// Every CTA pushes its fp32 partial of token m (128 weight rows = 32 lanes x 4 warps, 128 B per warp store) into
-//   red[src rank][owned token][128 rows]   of the owner (st.shared::cluster),
-// one cluster barrier, then the owner adds the S partials in rank order (bit-reproducible), applies the epilogue on
+// Every CTA stages its fp32 partial tile [token][128 rows] in its own (dead) ring memory and sends each owner its slab
+// with ONE bulk DSMEM copy (cp.async.bulk.shared::cluster) into
+//   red[src rank][owned token][128 rows]   of the owner, completing on the owner's mbarrier (measured: 64 scalar
+// st.shared::cluster per thread took 2.8 us per GEMM); then the owner adds the S partials in rank order (bit-reproducible), applies the epilogue on
 // float4 row groups and stores whole 256 B output rows.
 constexpr int DEC_MAX_ST = 12;
 
 template <int KIND, int BM, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
     gemm_decode_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap a_map,
-                       GemmEpilogue ep, int M, int N, int num_kb, int nst, unsigned long long* __restrict__ trace) {
+                       GemmEpilogue ep, int M, int N, int num_kb, int nst, int ring_bytes,
+                       unsigned long long* __restrict__ trace) {
   using T = KindTraits<KIND>;
   constexpr int BK_ELEMS = GEMM_BK_BYTES / T::ELEM;
   constexpr int W_TILE = GEMM_BN * GEMM_BK_BYTES;
@@ -419,18 +421,19 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
   const int tp_max = (M + S - 1) / S;                                   // most tokens one rank owns
   const int m_lo = (int)((long long)M * r / S), m_hi = (int)((long long)M * (r + 1) / S);  // tokens this rank finishes
   uint8_t* w_ring = smem;
-  uint8_t* a_ring = smem + (size_t)nst * W_TILE;
+  uint8_t* a_ring = smem + ring_bytes;  // ring_bytes = max(nst weight stages, the staging tile)
   float* red = reinterpret_cast<float*>(a_ring + (size_t)nst * A_TILE);  // [S][tp_max][128] (S > 1)
   float* a_s = red + (S > 1 ? (size_t)S * tp_max * GEMM_BN : 0);         // [BM] per-token scales
-  uint32_t* push_addr = reinterpret_cast<uint32_t*>(a_s + BM);           // [BM] DSMEM address of token m's slot (S > 1)
-  __nv_bfloat16* resid_s = reinterpret_cast<__nv_bfloat16*>(push_addr + BM);  // [owned tokens][128] (iff residual)
+  __nv_bfloat16* resid_s = reinterpret_cast<__nv_bfloat16*>(a_s + BM);  // [owned tokens][128] (iff residual)
   uint64_t* full_w = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(resid_s) +
                                                  (ep.residual ? (size_t)(S > 1 ? tp_max : BM) * GEMM_BN * 2 : 0));
   uint64_t* empty_w = full_w + DEC_MAX_ST;
   uint64_t* full_a = empty_w + DEC_MAX_ST;
   uint64_t* empty_a = full_a + DEC_MAX_ST;
   uint64_t* tfull = empty_a + DEC_MAX_ST;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull + 1);
+  uint64_t* red_full = tfull + 1;  // all S partials of this CTA's tokens have landed in `red`
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(red_full + 1);
+  float* stage = reinterpret_cast<float*>(smem);  // [BM][128] fp32 partial, aliases the (dead) ring after the last MMA
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_tile = blockIdx.x / S;
@@ -447,8 +450,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
       mbar_init(&empty_a[s], 1);
     }
     mbar_init(tfull, 1);
+    mbar_init(red_full, 1);
     fence_mbar_init();
     fence_proxy_async();
+    // the S incoming bulk copies (one per rank, this CTA's own included) complete on red_full
+    if (S > 1 && m_hi > m_lo) mbar_expect_tx(red_full, (uint32_t)(S * (m_hi - m_lo) * GEMM_BN * 4));
   }
   if (warp == 1) {
     tmem_alloc(tmem_slot, TMEM_COLS);
@@ -458,8 +464,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
   __syncthreads();
   tc_fence_after();
   griddep_launch();
-  // phase 1 of the cluster barrier: "this CTA runs" -- peers wait for it before their first DSMEM store
-  if (S > 1) cluster_arrive_relaxed();
+  // phase 1 of the cluster barrier: "this CTA runs, its red_full barrier is armed" -- peers wait for it before their
+  // first copy into this CTA's shared memory
+  if (S > 1) cluster_arrive_release();
   const uint32_t tmem_base = *tmem_slot;
 
   // per-thread epilogue constants (epilogue warps only; filled while the ring streams)
@@ -505,7 +512,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
     int s = 0, ph = 0;
     for (int i = 0; i < nk; ++i) {
       mbar_wait(&full_w[s], ph);
+      if (trace && lane == 0 && i < 8) trace[(size_t)gridDim.x * 8 + (size_t)blockIdx.x * 16 + i] = globaltimer_ns();
       mbar_wait(&full_a[s], ph);
+      if (trace && lane == 0 && i < 8) trace[(size_t)gridDim.x * 8 + (size_t)blockIdx.x * 16 + 8 + i] = globaltimer_ns();
       tc_fence_after();
       if (lane == 0) {
         if (i == 0) B200_STAMP(2);
@@ -529,18 +538,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
   } else {
     // ---- epilogue warps, part 1: stage the epilogue operands while the ring streams
     griddep_wait();
-    for (int m = et; m < BM; m += 128) {
-      a_s[m] = (ep.a_scale && m < M) ? ep.a_scale[m] : 1.f;
-      if (S > 1) {
-        uint32_t addr = 0;
-        if (m < M) {
-          const int q = (int)((((long long)m + 1) * S - 1) / M);  // owner: largest q with M*q/S <= m
-          const int lo = (int)((long long)M * q / S);
-          addr = mapa_shared(smem_u32(red), (uint32_t)q) + (uint32_t)((((size_t)r * tp_max + (m - lo)) * GEMM_BN) * 4);
-        }
-        push_addr[m] = addr;
-      }
-    }
+    for (int m = et; m < BM; m += 128) a_s[m] = (ep.a_scale && m < M) ? ep.a_scale[m] : 1.f;
     const int n0 = n_tile * GEMM_BN;
     if (S == 1) {
       if (n0 + nl < N) {
@@ -597,7 +595,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
         epilogue_chunk_staged<EPI>(ep, f, cc * 16, M, n, n < N, N, lane, a_s, w_sc, bias_v, resid_s + nl, GEMM_BN);
       }
     } else {
-      cluster_wait();  // every peer is known to run: its `red` may be written
+      // TMEM -> local staging tile [token][128 rows] (the ring is dead: every MMA of this CTA has retired) ...
 #pragma unroll 1
       for (int cc = 0; cc < BM / 16; ++cc) {
         if (cc * 16 >= M) break;
@@ -605,11 +603,21 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
         tmem_ld_32x32b_x16(acc + cc * 16, v);
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const uint32_t dst = push_addr[cc * 16 + j];
-          const float f = KIND == KIND_I8 ? (float)(int32_t)v[j] : __uint_as_float(v[j]);
-          if (dst) st_cluster_f32(dst + (uint32_t)(nl * 4), f);
-        }
+        for (int j = 0; j < 16; ++j)
+          stage[(cc * 16 + j) * GEMM_BN + nl] = KIND == KIND_I8 ? (float)(int32_t)v[j] : __uint_as_float(v[j]);
+      }
+      fence_proxy_async();  // generic-proxy writes -> visible to the bulk-copy (async proxy) reads below
+      named_bar_sync(1, 128);
+      // ... then ONE bulk DSMEM copy per owner: tokens [M*q/S, M*(q+1)/S) are a contiguous slab of the staging tile and
+      // land in slot `r` of owner q's `red`, completing on the owner's red_full barrier
+      cluster_wait();  // phase 1: every peer runs and has armed its red_full barrier
+      if (et < S) {
+        const int q = et;
+        const int lo = (int)((long long)M * q / S), hi = (int)((long long)M * (q + 1) / S);
+        if (hi > lo)
+          bulk_copy_to_cluster(mapa_shared(smem_u32(red + (size_t)r * tp_max * GEMM_BN), (uint32_t)q),
+                               smem_u32(stage + (size_t)lo * GEMM_BN), (uint32_t)((hi - lo) * GEMM_BN * 4),
+                               mapa_shared(smem_u32(red_full), (uint32_t)q));
       }
     }
   }
@@ -618,8 +626,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
   if (threadIdx.x == 64) B200_STAMP(4);
   if (S > 1) {
     if (warp < 2) cluster_wait();  // phase 1 for the warps that do not push
-    cluster_sync_all();            // phase 2: all partials have landed
+    if (warp >= 2 && m_hi > m_lo) mbar_wait(red_full, 0);  // the S partials of this CTA's tokens have landed
     if (threadIdx.x == 64) B200_STAMP(5);
+    // phase 2: nobody may exit while a peer's copy still reads its staging tile; arriving here means "all copies INTO
+    // me are complete", so once every CTA has arrived every copy OUT of everyone is complete too
+    cluster_arrive_relaxed();
     if (warp >= 2) {
       const int n0 = n_tile * GEMM_BN + 4 * t4;
       const bool hb = ep.bias != nullptr, hr = EPI == EPI_LINEAR && ep.residual != nullptr;
@@ -702,6 +713,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
       }
     }
   }
+  if (S > 1) cluster_wait();  // phase 2
   __syncthreads();
   if (threadIdx.x == 0) B200_STAMP(6);
 #undef B200_STAMP
@@ -777,7 +789,7 @@ constexpr size_t SMEM_TWO_PER_SM = 115712;  // (228 KB - 2 x 1 KB reserved) / 2
 constexpr int W_TILE_BYTES = GEMM_BN * GEMM_BK_BYTES;
 
 struct DecodeCfg {
-  int S, nst;
+  int S, nst, ring_bytes;
   size_t smem;
   int cap_ctas;  // CTAs the chip holds at once in this configuration
   double cost_us;
@@ -795,8 +807,12 @@ bool decode_rings(int bm, int M, int S, int nk, bool resid, size_t budget, Decod
   if (n > nk) n = nk;
   if (n < 1) return false;
   c.nst = n;
-  c.smem = fixed + (size_t)n * (a_tile + W_TILE_BYTES);
-  return true;
+  size_t ring = (size_t)n * W_TILE_BYTES;
+  const size_t stage = S > 1 ? (size_t)bm * GEMM_BN * 4 : 0;  // the partial tile is staged over the dead ring
+  if (ring < stage) ring = stage;
+  c.ring_bytes = (int)ring;
+  c.smem = fixed + ring + (size_t)n * a_tile;
+  return c.smem <= budget;
 }
 
 template <int KIND, int BM, int EPI>
@@ -894,7 +910,7 @@ int launch_decode(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilog
   if (rc) return rc;
   auto kern = gemm_decode_kernel<KIND, BM, EPI>;
   B200_CUDA_OK(launch_kernel_cluster(kern, dim3(p.n_tiles * c.S), dim3(GEMM_THREADS), c.smem, c.S, stream, wm, am, ep, M, N,
-                                     p.num_kb, c.nst, g_trace));
+                                     p.num_kb, c.nst, c.ring_bytes, g_trace));
   return B200_OK;
 }
 
