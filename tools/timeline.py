@@ -81,25 +81,29 @@ def main():
         name = e.name.split("(")[0].replace("b200::", "")
         dur = e.time_range.end - e.time_range.start
         pitch = nxt - e.time_range.start  # start-to-start: what the kernel costs the step
-        rows.append((e.time_range.start - t0, dur, pitch, name))
-        s = agg.setdefault(name, [0, 0.0, 0.0])
+        prev_end = max((x.time_range.end for x in evs[:i]), default=e.time_range.start)
+        tail = max(0.0, e.time_range.end - prev_end)  # end-to-end: what the kernel adds after everything before it ended
+        rows.append((e.time_range.start - t0, dur, pitch, name, tail))
+        s = agg.setdefault(name, [0, 0.0, 0.0, 0.0])
         s[0] += 1
         s[1] += dur
         s[2] += pitch
+        s[3] += tail
     step = t_end - t0
     print(f"step {step:.1f} us, {len(evs)} kernels, layers={a.layers}")
-    print(f"{'kernel':70s} {'n':>4s} {'dur us':>8s} {'pitch us':>9s} {'share':>6s}")
+    print(f"{'kernel':70s} {'n':>4s} {'dur us':>8s} {'pitch us':>9s} {'tail us':>8s} {'share':>6s}")
     out = []
-    for name, (cnt, dur, pitch) in sorted(agg.items(), key=lambda kv: -kv[1][2]):
-        print(f"{name[:70]:70s} {cnt:4d} {dur / cnt:8.2f} {pitch / cnt:9.2f} {pitch / step:6.1%}")
-        out.append({"kernel": name, "n": cnt, "mean_dur_us": dur / cnt, "mean_pitch_us": pitch / cnt, "share": pitch / step})
+    for name, (cnt, dur, pitch, tail) in sorted(agg.items(), key=lambda kv: -kv[1][3]):
+        print(f"{name[:70]:70s} {cnt:4d} {dur / cnt:8.2f} {pitch / cnt:9.2f} {tail / cnt:8.2f} {tail / step:6.1%}")
+        out.append({"kernel": name, "n": cnt, "mean_dur_us": dur / cnt, "mean_pitch_us": pitch / cnt,
+                    "mean_tail_us": tail / cnt, "share": tail / step})
     # one layer in order (the second layer of the step)
     per_layer = (len(evs) - 6) // a.layers if a.layers else 0
     if per_layer > 0:
-        print("\none layer, in launch order (start us, dur us, pitch us):")
+        print("\none layer, in launch order (start us, dur us, start-to-start us, end-to-end us):")
         base = 3 + per_layer
-        for st, dur, pitch, name in rows[base: base + per_layer]:
-            print(f"  {st:9.1f} {dur:7.2f} {pitch:7.2f}  {name[:80]}")
+        for st, dur, pitch, name, tail in rows[base: base + per_layer]:
+            print(f"  {st:9.1f} {dur:7.2f} {pitch:7.2f} {tail:7.2f}  {name[:80]}")
     if world > 1:
         sys.stdout.flush()
         torch.distributed.barrier()
@@ -108,7 +112,7 @@ def main():
         os._exit(0)
     if a.json:
         json.dump({"step_us": step, "layers": a.layers, "kernels": out,
-                   "layer_trace": [{"start_us": r[0], "dur_us": r[1], "pitch_us": r[2], "kernel": r[3]}
+                   "layer_trace": [{"start_us": r[0], "dur_us": r[1], "pitch_us": r[2], "tail_us": r[4], "kernel": r[3]}
                                    for r in rows[3 + per_layer: 3 + 2 * per_layer]] if per_layer > 0 else []},
                   open(a.json, "w"), indent=1)
 
