@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 5
+#define B200_ABI_VERSION 6
 
 enum {
   B200_OK = 0,
@@ -44,7 +44,8 @@ enum {
   B200_ERR_DRIVER = -5          /* cuTensorMapEncodeTiled / driver entry point failure */
 };
 
-enum { B200_BF16 = 0, B200_FP8_E4M3 = 1, B200_INT8 = 2, B200_F32 = 3 };
+/* B200_INT8_WO is only valid as a GEMM `ab_dtype`: bf16 activations x int8 weights (weight-only quantisation) */
+enum { B200_BF16 = 0, B200_FP8_E4M3 = 1, B200_INT8 = 2, B200_F32 = 3, B200_INT8_WO = 4 };
 
 int b200_abi_version(void);
 const char* b200_last_error(void);
@@ -132,6 +133,13 @@ void b200_gemm_set_trace(void* device_buf);
 int b200_gemm(const void* a, const void* w, void* out, const float* a_scale, const float* w_scale, const void* bias,
               const void* residual, int M, int N, int K, int ab_dtype, int out_dtype, int split_k, void* workspace,
               size_t workspace_bytes, void* stream);
+/* INT8 weight-only linear (SURVEY 8(b) `b200_gemm_int8_wo`; reference config keys quantized / quantization_dtype=int8 with
+ * bf16 activations, model_loader.py:885-898): out = (a_bf16 . w_int8^T) * w_scale[n] + bias + residual.  The int8 rows are
+ * streamed from HBM as int8 (half the bytes of bf16) and widened to bf16 operand tiles in shared memory by the CTA's
+ * epilogue warps (exact), then multiplied with kind::f16.  Same as b200_gemm with ab_dtype = B200_INT8_WO. */
+int b200_gemm_int8_wo(const void* a_bf16, const void* w_int8, void* out, const float* w_scale, const void* bias,
+                      const void* residual, int M, int N, int K, int out_dtype, int split_k, void* workspace,
+                      size_t workspace_bytes, void* stream);
 /* gate/up projection with SiLU(gate)*up fused into the epilogue.  w_gu [2I][K] holds, per group of 32 rows, 16 gate rows
  * followed by the 16 up rows of the same channels (w_scale / bias permuted alike); out_act [M][I] bf16 =
  * bf16(silu(bf16(gate)) * bf16(up)) exactly as b200_gemm + b200_silu_mul produce; group_amax [M][2I/32] fp32 receives

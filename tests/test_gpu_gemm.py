@@ -81,6 +81,36 @@ def test_bf16_gemm(ops, m, n, k, ctas):
     _assert_close(got, want)
 
 
+@pytest.mark.parametrize("m,n,k,ctas", SHAPES[:10] + SHAPES[11:])
+def test_int8_weight_only_gemm(ops, m, n, k, ctas):
+    """bf16 activations x int8 per-channel weights (cfg4, Qwen2.5-32B INT8 weight-only): the int8 rows are widened to
+    bf16 inside the kernel (exact), so the result is the bf16 GEMM on the dequantised codes -> same bar as bf16."""
+    g = torch.Generator().manual_seed(m * 3 + n + k)
+    x = torch.randn(m, k, generator=g).bfloat16()
+    w = (torch.randn(n, k, generator=g) * 0.02).bfloat16()
+    wq, ws = quant_ref.quantize_weight_per_channel(w, "int8")
+    bias = torch.randn(n, generator=g).bfloat16() if n % 256 == 0 else None
+    res = torch.randn(m, n, generator=g).bfloat16() if k % 1024 == 0 else None
+    want = quant_ref.wo_gemm_ref(x, wq, ws, bias, res)
+    got = ops.gemm(x.cuda(), wq.cuda(), None, ws.cuda(), None if bias is None else bias.cuda(),
+                   None if res is None else res.cuda(), split_k=ctas)
+    torch.cuda.synchronize()
+    _assert_close(got, want)
+
+
+def test_int8_weight_only_exact_on_integer_activations(ops):
+    """Size-independent property: with small-integer bf16 activations every product and partial sum is an exact integer
+    below 2^24, so the weight-only GEMM must reproduce the integer GEMM bit for bit (decode and stream-K schedules)."""
+    g = torch.Generator().manual_seed(5)
+    n, k = 1280, 1152
+    w = torch.randint(-127, 128, (n, k), generator=g, dtype=torch.int8)
+    for m in (64, 128, 300):
+        a = torch.randint(-8, 9, (m, k), generator=g).to(torch.bfloat16)
+        got = ops.gemm(a.cuda(), w.cuda(), out_dtype=torch.float32)
+        want = (a.double() @ w.double().t()).float()
+        assert torch.equal(got.cpu(), want), m
+
+
 def test_fp32_out_and_linearity(ops):
     """Size-independent property at a BASELINE-size shape (lm_head shard): GEMM(a1+a2) == GEMM(a1)+GEMM(a2) in fp32 out
     for int8 codes (exact integer arithmetic), and fp32 output equals the oracle."""
@@ -129,7 +159,7 @@ def test_gemm_rejects_bad_split(ops):
             ops.gemm(x, w, split_k=bad)
 
 
-@pytest.mark.parametrize("kind", ["bf16", "fp8", "int8"])
+@pytest.mark.parametrize("kind", ["bf16", "fp8", "int8", "int8_wo"])
 @pytest.mark.parametrize("m,i,k,ctas", [(64, 14336, 4096, 0), (4, 5632, 2048, 0), (64, 5632, 2048, 2), (100, 96, 512, 4), (64, 5632, 2048, 6),
                                          (128, 3584, 1024, 1), (300, 1792, 512, 0), (300, 1792, 512, 3)])
 def test_gemm_silu_mul_matches_unfused(ops, kind, m, i, k, ctas):
@@ -144,6 +174,10 @@ def test_gemm_silu_mul_matches_unfused(ops, kind, m, i, k, ctas):
     if kind == "bf16":
         xq, xs, wq, ws = x, None, w, None
         want_gu = quant_ref.gemm_ref(x, w)
+    elif kind == "int8_wo":
+        wq, ws = quant_ref.quantize_weight_per_channel(w, "int8")
+        xq, xs = x, None
+        want_gu = quant_ref.wo_gemm_ref(x, wq, ws)
     else:
         xq, xs = quant_ref.quantize_act_per_token(x, kind)
         wq, ws = quant_ref.quantize_weight_per_channel(w, kind)

@@ -23,6 +23,8 @@ def _run(quant, steps=12, use_graph=True):
     weights = random_init_full_weights(shape, seed=3, std=0.05)
     override = {} if quant == "bf16" else {"quantized": True, "quantization_dtype": "f8e4m3" if quant == "fp8" else "int8",
                                             "quantization_type": "per_channel_symmetric"}
+    if quant == "int8_wo":
+        override["weight_only"] = True
     cfg = make_vllm_config(shape, max_num_seqs=mns, max_model_len=mml, num_gpu_blocks_override=nb + 1, override=override,
                            enforce_eager=not use_graph)
     model = B200CausalLM(shape, weights, quant=quant, num_blocks=nb + 1, max_num_seqs=mns, max_model_len=mml)
@@ -121,7 +123,7 @@ def _rms(x):
     return x.float().pow(2).mean().sqrt().item()
 
 
-@pytest.mark.parametrize("quant", ["bf16", "fp8", "int8"])
+@pytest.mark.parametrize("quant", ["bf16", "fp8", "int8", "int8_wo"])
 def test_greedy_tokens_match_oracle(quant):
     runner, model, ref, outs, ref_outs, margins, live, blocks = _run(quant)
     keys = sorted(outs)
@@ -152,6 +154,10 @@ def test_greedy_tokens_match_oracle(quant):
         assert e_gh < 1.15 * e_q, msg
         assert e_g < 1.5 * e_q, msg
         assert e_q < (0.15 if quant == "fp8" else 0.05) * std, msg
+        if quant == "int8_wo":
+            # weight-only: both sides multiply the SAME int8 codes with bf16 activations (no activation codes to flip),
+            # so the CUDA path tracks the quantised oracle as closely as the bf16 model tracks its oracle
+            assert e_g < 1e-2 * std, msg
     # greedy tokens: identical except where the oracle's own top-2 margin is inside the logit error band
     bad = [i for i in mism if flat_margin[i] > 6 * e_g]
     assert not bad, msg + f"; mismatches outside the error band at {bad}: margins {[flat_margin[i] for i in bad]}"

@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200_paged.so")
 
 OK = 0
-ABI_VERSION = 5
+ABI_VERSION = 6
 BF16, FP8_E4M3, INT8, F32 = 0, 1, 2, 3
 
 _p = C.c_void_p
@@ -44,6 +44,7 @@ SIGNATURES = {
     "b200_gemm_decode_plan": (_i, [_i, _i, _i, _i, _i, _i, _i, _p]),
     "b200_gemm_set_trace": (None, [_p]),
     "b200_gemm": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _sz, _p]),
+    "b200_gemm_int8_wo": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _sz, _p]),
     "b200_gemm_silu_mul": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _sz, _p]),
     "b200_rmsnorm": (_i, [_p, _p, _p, _p, _p, _i, _i, _f, _i, _p]),
     "b200_silu_mul": (_i, [_p, _p, _p, _p, _i, _i, _i, _p]),

@@ -33,6 +33,9 @@ int check_cuda(cudaError_t e, const char* what);
 // box = box_cols x box_rows, 128B swizzle (box_cols * elem_bytes must be 128).
 int make_tmap_2d(CUtensorMap* out, const void* base, CUtensorMapDataType dt, uint32_t elem_bytes, uint64_t cols,
                  uint64_t rows, uint64_t row_pitch_bytes, uint32_t box_cols, uint32_t box_rows);
+// same without swizzle (box_cols * elem_bytes a multiple of 16): tiles read back with plain shared-memory loads
+int make_tmap_2d_plain(CUtensorMap* out, const void* base, CUtensorMapDataType dt, uint32_t elem_bytes, uint64_t cols,
+                       uint64_t rows, uint64_t row_pitch_bytes, uint32_t box_cols, uint32_t box_rows);
 int sm_count();
 void count_launch(int n = 1);
 bool pdl_enabled();

@@ -52,6 +52,40 @@ struct KindTraits<KIND_I8> {
   static constexpr int ELEM = 1, CFMT = 2, ABFMT = 1;  // s8 in, s32 accumulate
 };
 
+// INT8 weight-only (W8A16): bf16 activations, int8 weights streamed from HBM as int8 and widened to bf16 inside the
+// kernel (exact: |w| <= 127), then kind::f16.  The per-channel scale is applied in the epilogue like the other kinds.
+constexpr int KIND_WO8 = 3;
+template <>
+struct KindTraits<KIND_WO8> {
+  static constexpr int ELEM = 2, CFMT = 1, ABFMT = 1;
+};
+constexpr int RAW_TILE = GEMM_BN * (GEMM_BK_BYTES / 2);  // 128 rows x 64 int8 of one k-block (un-swizzled)
+
+// Widen one raw int8 weight tile [128 rows][64 B] into the K-major 128B-swizzled bf16 tile the UMMA descriptor expects
+// (row pitch 128 B, 8-row groups 1024 B apart, 16-byte chunk c of row r stored at chunk c ^ (r & 7)).
+// 128 threads; each handles 4 (row, 16-byte) pieces: consecutive threads read consecutive 16 B and the two output
+// chunks of neighbouring rows fall into disjoint bank groups.
+__device__ __forceinline__ void widen_w_tile(const uint8_t* __restrict__ raw, uint8_t* __restrict__ dst, int t) {
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    const int id = t + it * 128;
+    const int row = id >> 2, c4 = id & 3;
+    const uint4 v = *reinterpret_cast<const uint4*>(raw + row * 64 + c4 * 16);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t o[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int b0 = (int)(int8_t)(w[j] & 0xff), b1 = (int)(int8_t)((w[j] >> 8) & 0xff);
+      const int b2 = (int)(int8_t)((w[j] >> 16) & 0xff), b3 = (int)(int8_t)(w[j] >> 24);
+      o[2 * j] = pack_bf16((float)b0, (float)b1);
+      o[2 * j + 1] = pack_bf16((float)b2, (float)b3);
+    }
+    uint8_t* rowp = dst + (row >> 3) * 1024 + (row & 7) * 128;
+    *reinterpret_cast<uint4*>(rowp + (((2 * c4) ^ (row & 7)) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
+    *reinterpret_cast<uint4*>(rowp + (((2 * c4 + 1) ^ (row & 7)) << 4)) = make_uint4(o[4], o[5], o[6], o[7]);
+  }
+}
+
 enum { EPI_LINEAR = 0, EPI_SILU_MUL = 1 };
 
 struct GemmEpilogue {
@@ -188,7 +222,7 @@ __device__ __forceinline__ void epilogue_chunk_staged(const GemmEpilogue& ep, co
 }
 
 template <int KIND, int BM, int NSTAGES, int EPI>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(KIND == KIND_WO8 ? GEMM_THREADS + 128 : GEMM_THREADS, 1)
     gemm_streamk_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap a_map,
                         GemmEpilogue ep, float* __restrict__ partials, int* __restrict__ counters, int M, int N, int m_tiles,
                         int num_kb, int tiles, int w_stream_once) {
@@ -199,13 +233,19 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   constexpr int STAGE = W_TILE + A_TILE;
   constexpr uint32_t TMEM_COLS = 2 * BM < 32 ? 32 : 2 * BM;  // two accumulator stages
   constexpr uint32_t IDESC = umma_idesc(T::CFMT, T::ABFMT, GEMM_BN, BM);
+  constexpr bool WO = KIND == KIND_WO8;
+  constexpr int MK = KIND == KIND_WO8 ? (int)KIND_F16 : KIND;
   static_assert(2 * BM <= 512 && (TMEM_COLS & (TMEM_COLS - 1)) == 0, "TMEM columns");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)NSTAGES * STAGE);
+  uint8_t* raw_ring = smem + (size_t)NSTAGES * STAGE;  // weight-only: NSTAGES raw int8 weight tiles
+  uint64_t* full = reinterpret_cast<uint64_t*>(raw_ring + (WO ? (size_t)NSTAGES * RAW_TILE : 0));
   uint64_t* empty = full + NSTAGES;
-  uint64_t* tfull = empty + NSTAGES;   // [2] accumulator stage ready for the epilogue
+  uint64_t* full_raw = empty + NSTAGES;   // weight-only: raw tile landed
+  uint64_t* empty_raw = full_raw + NSTAGES;  // weight-only: raw tile widened (128 arrivals)
+  uint64_t* full_cvt = empty_raw + NSTAGES;  // weight-only: bf16 operand tile written (128 arrivals)
+  uint64_t* tfull = full_cvt + NSTAGES;   // [2] accumulator stage ready for the epilogue
   uint64_t* tempty = tfull + 2;        // [2] accumulator stage drained
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
   int* fix_flag = reinterpret_cast<int*>(tmem_slot + 1);
@@ -222,6 +262,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     for (int s = 0; s < NSTAGES; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
+      if (WO) {
+        mbar_init(&full_raw[s], 1);
+        mbar_init(&empty_raw[s], 128);
+        mbar_init(&full_cvt[s], 128);
+      }
     }
     mbar_init(&tfull[0], 1);
     mbar_init(&tfull[1], 1);
@@ -250,8 +295,15 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       for (int i = 0; i < npre; ++i) {
         const long long u = u0 + i;
         const int tile = (int)(u / num_kb), kb = (int)(u % num_kb);
-        mbar_expect_tx(&full[i], STAGE);
-        tma_load_2d_hint(smem + (size_t)i * STAGE, &w_map, &full[i], kb * BK_ELEMS, (tile / m_tiles) * GEMM_BN, pol_w);
+        if constexpr (WO) {
+          mbar_expect_tx(&full[i], A_TILE);
+          mbar_expect_tx(&full_raw[i], RAW_TILE);
+          tma_load_2d_hint(raw_ring + (size_t)i * RAW_TILE, &w_map, &full_raw[i], kb * BK_ELEMS, (tile / m_tiles) * GEMM_BN,
+                           pol_w);
+        } else {
+          mbar_expect_tx(&full[i], STAGE);
+          tma_load_2d_hint(smem + (size_t)i * STAGE, &w_map, &full[i], kb * BK_ELEMS, (tile / m_tiles) * GEMM_BN, pol_w);
+        }
       }
       griddep_wait();
       for (int i = 0; i < npre; ++i) {
@@ -265,8 +317,16 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         const int tile = (int)(u / num_kb), kb = (int)(u % num_kb);
         mbar_wait(&empty[s], ((i / NSTAGES) - 1) & 1);
         uint8_t* ws = smem + (size_t)s * STAGE;
-        mbar_expect_tx(&full[s], STAGE);
-        tma_load_2d_hint(ws, &w_map, &full[s], kb * BK_ELEMS, (tile / m_tiles) * GEMM_BN, pol_w);
+        if constexpr (WO) {
+          mbar_wait(&empty_raw[s], ((i / NSTAGES) - 1) & 1);
+          mbar_expect_tx(&full_raw[s], RAW_TILE);
+          tma_load_2d_hint(raw_ring + (size_t)s * RAW_TILE, &w_map, &full_raw[s], kb * BK_ELEMS, (tile / m_tiles) * GEMM_BN,
+                           pol_w);
+          mbar_expect_tx(&full[s], A_TILE);
+        } else {
+          mbar_expect_tx(&full[s], STAGE);
+          tma_load_2d_hint(ws, &w_map, &full[s], kb * BK_ELEMS, (tile / m_tiles) * GEMM_BN, pol_w);
+        }
         tma_load_2d_hint(ws + W_TILE, &a_map, &full[s], kb * BK_ELEMS, (tile % m_tiles) * BM, pol_a);
       }
     }
@@ -283,13 +343,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       for (int k = 0; k < nk; ++k, ++i) {
         const int s = i % NSTAGES;
         mbar_wait(&full[s], (i / NSTAGES) & 1);
+        if constexpr (WO) mbar_wait(&full_cvt[s], (i / NSTAGES) & 1);
         tc_fence_after();
         if (lane == 0) {
           const uint32_t wa = smem_u32(smem + (size_t)s * STAGE);
           const uint32_t aa = wa + W_TILE;
 #pragma unroll
           for (int kk = 0; kk < GEMM_BK_BYTES / 32; ++kk)  // UMMA_K = 32 bytes of K
-            umma_ss<KIND>(acc, umma_desc_sw128(wa + kk * 32), umma_desc_sw128(aa + kk * 32), IDESC, (uint32_t)((k | kk) != 0));
+            umma_ss<MK>(acc, umma_desc_sw128(wa + kk * 32), umma_desc_sw128(aa + kk * 32), IDESC, (uint32_t)((k | kk) != 0));
           tc_commit(&empty[s]);  // smem slot is free once these MMAs retire
         }
         __syncwarp();
@@ -297,6 +358,19 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       if (lane == 0) tc_commit(&tfull[as]);
       __syncwarp();
       u += nk;
+    }
+  } else if (WO && warp >= 6) {
+    // weight-only: warps 6..9 widen raw int8 weight tiles into the bf16 operand half of each stage
+    const int ct = threadIdx.x - 192;  // 0..127
+    const int total = (int)(u1 - u0);
+    for (int i = 0; i < total; ++i) {
+      const int s = i % NSTAGES;
+      mbar_wait(&full_raw[s], (i / NSTAGES) & 1);
+      if (i >= NSTAGES) mbar_wait(&empty[s], ((i / NSTAGES) - 1) & 1);
+      widen_w_tile(raw_ring + (size_t)s * RAW_TILE, smem + (size_t)s * STAGE, ct);
+      fence_proxy_async();
+      mbar_arrive(&full_cvt[s]);
+      mbar_arrive(&empty_raw[s]);
     }
   } else {
     // epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31; lane = weight row of the tile
@@ -414,6 +488,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
 #define B200_STAMP(k) do { if (trace) trace[(size_t)blockIdx.x * 8 + (k)] = globaltimer_ns(); } while (0)
   if (threadIdx.x == 0) B200_STAMP(0);
   constexpr uint32_t IDESC = umma_idesc(T::CFMT, T::ABFMT, GEMM_BN, BM);
+  constexpr bool WO = KIND == KIND_WO8;
+  constexpr int MK = KIND == KIND_WO8 ? (int)KIND_F16 : KIND;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -422,7 +498,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
   const int m_lo = (int)((long long)M * r / S), m_hi = (int)((long long)M * (r + 1) / S);  // tokens this rank finishes
   uint8_t* w_ring = smem;
   uint8_t* a_ring = smem + ring_bytes;  // ring_bytes = max(nst weight stages, the staging tile)
-  float* red = reinterpret_cast<float*>(a_ring + (size_t)nst * A_TILE);  // [S][tp_max][128] (S > 1)
+  uint8_t* raw_ring = a_ring + (size_t)nst * A_TILE;  // weight-only: nst raw int8 tiles
+  float* red = reinterpret_cast<float*>(raw_ring + (WO ? (size_t)nst * RAW_TILE : 0));  // [S][tp_max][128] (S > 1)
   float* a_s = red + (S > 1 ? (size_t)S * tp_max * GEMM_BN : 0);         // [BM] per-token scales
   __nv_bfloat16* resid_s = reinterpret_cast<__nv_bfloat16*>(a_s + BM);  // [owned tokens][128] (iff residual)
   uint64_t* full_w = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(resid_s) +
@@ -430,7 +507,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
   uint64_t* empty_w = full_w + DEC_MAX_ST;
   uint64_t* full_a = empty_w + DEC_MAX_ST;
   uint64_t* empty_a = full_a + DEC_MAX_ST;
-  uint64_t* tfull = empty_a + DEC_MAX_ST;
+  uint64_t* full_raw = empty_a + DEC_MAX_ST;   // weight-only: raw int8 tile landed / consumed by the widening warps
+  uint64_t* empty_raw = full_raw + DEC_MAX_ST;
+  uint64_t* tfull = empty_raw + DEC_MAX_ST;
   uint64_t* red_full = tfull + 1;  // all S partials of this CTA's tokens have landed in `red`
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(red_full + 1);
   float* stage = reinterpret_cast<float*>(smem);  // [BM][128] fp32 partial, aliases the (dead) ring after the last MMA
@@ -444,10 +523,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
     tma_prefetch_desc(&w_map);
     tma_prefetch_desc(&a_map);
     for (int s = 0; s < nst; ++s) {
-      mbar_init(&full_w[s], 1);
+      mbar_init(&full_w[s], WO ? 128 : 1);  // weight-only: every widening thread arrives after its writes
       mbar_init(&empty_w[s], 1);
       mbar_init(&full_a[s], 1);
       mbar_init(&empty_a[s], 1);
+      if (WO) {
+        mbar_init(&full_raw[s], 1);
+        mbar_init(&empty_raw[s], 128);
+      }
     }
     mbar_init(tfull, 1);
     mbar_init(red_full, 1);
@@ -484,8 +567,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
       const int npre = nk < nst ? nk : nst;
       // weights do not depend on any kernel of the step: fill the ring with W tiles before the dependency resolves
       for (int i = 0; i < npre; ++i) {
-        mbar_expect_tx(&full_w[i], W_TILE);
-        tma_load_2d_hint(w_ring + (size_t)i * W_TILE, &w_map, &full_w[i], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
+        if constexpr (WO) {
+          mbar_expect_tx(&full_raw[i], RAW_TILE);
+          tma_load_2d_hint(raw_ring + (size_t)i * RAW_TILE, &w_map, &full_raw[i], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
+        } else {
+          mbar_expect_tx(&full_w[i], W_TILE);
+          tma_load_2d_hint(w_ring + (size_t)i * W_TILE, &w_map, &full_w[i], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
+        }
       }
       griddep_wait();
       B200_STAMP(1);
@@ -498,9 +586,15 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
         mbar_wait(&empty_a[s], ph);
         mbar_expect_tx(&full_a[s], A_TILE);
         tma_load_2d_hint(a_ring + (size_t)s * A_TILE, &a_map, &full_a[s], (kb0 + i) * BK_ELEMS, 0, pol_a);
-        mbar_wait(&empty_w[s], ph);
-        mbar_expect_tx(&full_w[s], W_TILE);
-        tma_load_2d_hint(w_ring + (size_t)s * W_TILE, &w_map, &full_w[s], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
+        if constexpr (WO) {
+          mbar_wait(&empty_raw[s], ph);
+          mbar_expect_tx(&full_raw[s], RAW_TILE);
+          tma_load_2d_hint(raw_ring + (size_t)s * RAW_TILE, &w_map, &full_raw[s], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
+        } else {
+          mbar_wait(&empty_w[s], ph);
+          mbar_expect_tx(&full_w[s], W_TILE);
+          tma_load_2d_hint(w_ring + (size_t)s * W_TILE, &w_map, &full_w[s], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
+        }
         if (++s == nst) {
           s = 0;
           ph ^= 1;
@@ -522,8 +616,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
         const uint32_t aa = smem_u32(a_ring + (size_t)s * A_TILE);
 #pragma unroll
         for (int kk = 0; kk < GEMM_BK_BYTES / 32; ++kk)  // UMMA_K = 32 bytes of K
-          umma_ss<KIND>(tmem_base, umma_desc_sw128(wa + kk * 32), umma_desc_sw128(aa + kk * 32), IDESC,
-                        (uint32_t)((i | kk) != 0));
+          umma_ss<MK>(tmem_base, umma_desc_sw128(wa + kk * 32), umma_desc_sw128(aa + kk * 32), IDESC,
+                      (uint32_t)((i | kk) != 0));
         tc_commit(&empty_a[s]);
         tc_commit(&empty_w[s]);
       }
@@ -576,6 +670,24 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
       }
     }
     named_bar_sync(1, 128);
+
+    if constexpr (WO) {
+      // ---- weight-only: these 128 threads widen every raw int8 tile into the bf16 operand tile the MMA reads.
+      // The raw tiles were requested before the dependency resolved, so the first ones are usually waiting here.
+      int s = 0, ph = 0;
+      for (int i = 0; i < nk; ++i) {
+        mbar_wait(&full_raw[s], ph);
+        if (i >= nst) mbar_wait(&empty_w[s], ph ^ 1);  // the MMAs that read the previous contents have retired
+        widen_w_tile(raw_ring + (size_t)s * RAW_TILE, w_ring + (size_t)s * W_TILE, et);
+        fence_proxy_async();  // generic-proxy writes -> visible to the tensor core (async proxy)
+        mbar_arrive(&full_w[s]);
+        mbar_arrive(&empty_raw[s]);
+        if (++s == nst) {
+          s = 0;
+          ph ^= 1;
+        }
+      }
+    }
 
     // ---- part 2: the accumulator is final
     mbar_wait(tfull, 0);
@@ -735,10 +847,13 @@ struct GemmPlan {
   size_t smem, ws_bytes;
 };
 
-int elem_bytes(int dt) { return dt == B200_BF16 ? 2 : 1; }
-constexpr int stages_for(int bm) { return bm == 32 ? 10 : bm == 64 ? 8 : bm == 128 ? 6 : 4; }
-constexpr size_t smem_for(int bm) {
-  return (size_t)stages_for(bm) * (GEMM_BN * GEMM_BK_BYTES + bm * GEMM_BK_BYTES) + (2 * stages_for(bm) + 4) * 8 + 8 + 1024;
+// bytes of one ACTIVATION element (weight-only: bf16 activations, int8 weights)
+int elem_bytes(int dt) { return (dt == B200_BF16 || dt == B200_INT8_WO) ? 2 : 1; }
+int w_elem_bytes(int dt) { return dt == B200_BF16 ? 2 : 1; }
+constexpr int stages_for(int bm, bool wo = false) { return bm == 32 ? 10 : bm == 64 ? 8 : bm == 128 ? 6 : wo ? 3 : 4; }
+constexpr size_t smem_for(int bm, bool wo = false) {
+  return (size_t)stages_for(bm, wo) * (GEMM_BN * GEMM_BK_BYTES + bm * GEMM_BK_BYTES + (wo ? RAW_TILE : 0)) +
+         (5 * stages_for(bm, wo) + 4) * 8 + 8 + 1024;
 }
 
 // split_k: decode = cluster size along K (0 = auto; 1, 2, 4, 8); stream-K = cap on the persistent CTAs (0 = one per SM)
@@ -760,7 +875,7 @@ int plan_gemm(GemmPlan& p, int M, int N, int K, int ab_dtype, int split_k) {
   if (ctas > GEMM_CNT_INTS) ctas = GEMM_CNT_INTS;
   if ((long long)ctas > units) ctas = (int)units;
   p.ctas = ctas;
-  p.smem = smem_for(p.bm);
+  p.smem = smem_for(p.bm, ab_dtype == B200_INT8_WO);
   p.ws_bytes = (size_t)GEMM_CNT_INTS * sizeof(int) + (size_t)ctas * 2 * p.bm * GEMM_BN * sizeof(float);
   return B200_OK;
 }
@@ -769,8 +884,9 @@ template <int KIND, int EPI>
 int launch_streamk(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilogue& ep, void* workspace, int M, int N,
                    const GemmPlan& p, cudaStream_t stream) {
   constexpr int BM = 256;
-  auto kern = gemm_streamk_kernel<KIND, BM, stages_for(BM), EPI>;
-  constexpr size_t smem = smem_for(BM);
+  constexpr bool WO = KIND == KIND_WO8;
+  auto kern = gemm_streamk_kernel<KIND, BM, stages_for(BM, WO), EPI>;
+  constexpr size_t smem = smem_for(BM, WO);
   static bool attr_done = false;
   if (!attr_done) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -778,7 +894,8 @@ int launch_streamk(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilo
   }
   int* counters = (int*)workspace;
   float* partials = (float*)((uint8_t*)workspace + GEMM_CNT_INTS * sizeof(int));
-  B200_CUDA_OK(launch_kernel(kern, dim3(p.ctas), dim3(GEMM_THREADS), smem, stream, wm, am, ep, partials, counters, M, N,
+  B200_CUDA_OK(launch_kernel(kern, dim3(p.ctas), dim3(WO ? GEMM_THREADS + 128 : GEMM_THREADS), smem, stream, wm, am, ep,
+                             partials, counters, M, N,
                              p.m_tiles, p.num_kb, p.tiles, p.m_tiles == 1 ? 1 : 0));
   return B200_OK;
 }
@@ -796,11 +913,11 @@ struct DecodeCfg {
 };
 
 // ring depth that fits `budget` bytes
-bool decode_rings(int bm, int M, int S, int nk, bool resid, size_t budget, DecodeCfg& c) {
-  const int a_tile = bm * GEMM_BK_BYTES;
+bool decode_rings(int bm, int M, int S, int nk, bool resid, size_t budget, DecodeCfg& c, bool wo = false) {
+  const int a_tile = bm * GEMM_BK_BYTES + (wo ? RAW_TILE : 0);  // weight-only: one raw int8 tile rides with every stage
   const int tp_max = (M + S - 1) / S;
   const size_t red = S > 1 ? (size_t)S * tp_max * GEMM_BN * 4 : 0;
-  const size_t fixed = 1024 + red + (size_t)bm * 8 + (resid ? (size_t)(S > 1 ? tp_max : bm) * GEMM_BN * 2 : 0) + 512;
+  const size_t fixed = 1024 + red + (size_t)bm * 8 + (resid ? (size_t)(S > 1 ? tp_max : bm) * GEMM_BN * 2 : 0) + 768;
   if (budget < fixed + (size_t)(a_tile + W_TILE_BYTES)) return false;
   int n = (int)((budget - fixed) / (size_t)(a_tile + W_TILE_BYTES));
   if (n > DEC_MAX_ST) n = DEC_MAX_ST;
@@ -849,7 +966,7 @@ int plan_decode(DecodeCfg& best, int M, int n_tiles, int num_kb, int split_k, bo
     const int nk = (num_kb + S - 1) / S;
     DecodeCfg c{};
     c.S = S;
-    if (!decode_rings(BM, M, S, nk, resid, budget, c)) continue;
+    if (!decode_rings(BM, M, S, nk, resid, budget, c, KIND == KIND_WO8)) continue;
     // clusters of 4 and 8 strand SMs (GPC packing): ask the runtime how many clusters one wave holds
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(n_tiles * S);
@@ -873,14 +990,14 @@ int plan_decode(DecodeCfg& best, int M, int n_tiles, int num_kb, int split_k, bo
     // An SM's ingest rate grows with the stages it has in flight (one ring round trip ~1.55 us); CTAs spread
     // round-robin, so with more CTAs than SMs the busiest SM runs two rings side by side.
     const int ctas = n_tiles * S;
-    const double stage_bytes = (double)(W_TILE_BYTES + BM * GEMM_BK_BYTES);
+    const double stage_bytes = (double)((KIND == KIND_WO8 ? RAW_TILE : W_TILE_BYTES) + BM * GEMM_BK_BYTES);
     const int sm_used = ctas < sms ? ctas : sms;
     int on_busiest = (ctas + sm_used - 1) / sm_used;
     const int resident = on_busiest < per_sm ? on_busiest : per_sm;
     const double rate_sm = resident * c.nst * stage_bytes / 1.55;  // bytes per us
     const double t_sm = on_busiest * nk * stage_bytes / rate_sm;
     const double t_chip = (double)n_tiles * num_kb * stage_bytes / 9.5e6;
-    const double t_hbm = (double)n_tiles * num_kb * W_TILE_BYTES / 6.2e6;
+    const double t_hbm = (double)n_tiles * num_kb * (KIND == KIND_WO8 ? RAW_TILE : W_TILE_BYTES) / 6.2e6;
     double t = t_sm > t_chip ? t_sm : t_chip;
     if (t_hbm > t) t = t_hbm;
     t += 6.0;
@@ -926,11 +1043,15 @@ int dispatch_gemm(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilog
 int gemm_common(const void* a, const void* w, const GemmEpilogue& ep, int epi, int M, int N, int K, int ab_dtype,
                 int split_k, void* workspace, size_t workspace_bytes, void* stream) {
   B200_REQUIRE(a && w && ep.out, "gemm: null pointer");
-  B200_REQUIRE(ab_dtype == B200_BF16 || ab_dtype == B200_FP8_E4M3 || ab_dtype == B200_INT8, "gemm: bad ab_dtype %d", ab_dtype);
+  B200_REQUIRE(ab_dtype == B200_BF16 || ab_dtype == B200_FP8_E4M3 || ab_dtype == B200_INT8 || ab_dtype == B200_INT8_WO,
+               "gemm: bad ab_dtype %d", ab_dtype);
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: bad shape M=%d N=%d K=%d", M, N, K);
   B200_REQUIRE(split_k >= 0, "gemm: bad split_k %d", split_k);
+  const bool wo = ab_dtype == B200_INT8_WO;
   int eb = elem_bytes(ab_dtype);
-  B200_REQUIRE(((int64_t)K * eb) % 16 == 0, "gemm: K*elem_bytes must be a multiple of 16 (TMA row pitch), K=%d", K);
+  B200_REQUIRE(((int64_t)K * w_elem_bytes(ab_dtype)) % 16 == 0,
+               "gemm: K*elem_bytes must be a multiple of 16 (TMA row pitch), K=%d", K);
+  B200_REQUIRE(!wo || ep.a_scale == nullptr, "gemm: weight-only takes bf16 activations (a_scale must be NULL)");
   GemmPlan p;
   int rc = plan_gemm(p, M, N, K, ab_dtype, split_k);
   if (rc) return rc;
@@ -938,10 +1059,13 @@ int gemm_common(const void* a, const void* w, const GemmEpilogue& ep, int epi, i
     set_last_error("gemm: workspace %zu < %zu bytes", workspace_bytes, p.ws_bytes);
     return B200_ERR_WORKSPACE;
   }
-  CUtensorMapDataType dt = ab_dtype == B200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
+  CUtensorMapDataType dt = eb == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
   int bk = GEMM_BK_BYTES / eb;
   CUtensorMap wm, am;
-  rc = make_tmap_2d(&wm, w, dt, eb, (uint64_t)K, (uint64_t)N, (uint64_t)K * eb, bk, GEMM_BN);
+  if (wo)  // raw int8 rows, 64 B of K per row and stage, no swizzle: the widening warps read them with plain loads
+    rc = make_tmap_2d_plain(&wm, w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)K, (uint64_t)N, (uint64_t)K, bk, GEMM_BN);
+  else
+    rc = make_tmap_2d(&wm, w, dt, eb, (uint64_t)K, (uint64_t)N, (uint64_t)K * eb, bk, GEMM_BN);
   if (rc) return rc;
   rc = make_tmap_2d(&am, a, dt, eb, (uint64_t)K, (uint64_t)M, (uint64_t)K * eb, bk, p.bm);
   if (rc) return rc;
@@ -949,10 +1073,12 @@ int gemm_common(const void* a, const void* w, const GemmEpilogue& ep, int epi, i
   if (epi == EPI_LINEAR) {
     if (ab_dtype == B200_BF16) return dispatch_gemm<KIND_F16, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, split_k, s);
     if (ab_dtype == B200_FP8_E4M3) return dispatch_gemm<KIND_F8F6F4, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, split_k, s);
+    if (wo) return dispatch_gemm<KIND_WO8, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, split_k, s);
     return dispatch_gemm<KIND_I8, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, split_k, s);
   }
   if (ab_dtype == B200_BF16) return dispatch_gemm<KIND_F16, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, split_k, s);
   if (ab_dtype == B200_FP8_E4M3) return dispatch_gemm<KIND_F8F6F4, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, split_k, s);
+  if (wo) return dispatch_gemm<KIND_WO8, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, split_k, s);
   return dispatch_gemm<KIND_I8, EPI_SILU_MUL>(wm, am, ep, workspace, M, N, p, split_k, s);
 }
 
@@ -973,7 +1099,8 @@ void b200_gemm_set_trace(void* buf) { g_trace = (unsigned long long*)buf; }
 
 int b200_gemm_decode_plan(int M, int N, int K, int ab_dtype, int split_k, int silu_mul, int has_residual, int* out6) {
   B200_REQUIRE(out6 && M > 0 && M <= 128 && N > 0 && K > 0, "gemm_decode_plan: bad arguments");
-  B200_REQUIRE(ab_dtype == B200_BF16 || ab_dtype == B200_FP8_E4M3 || ab_dtype == B200_INT8, "gemm_decode_plan: bad dtype");
+  B200_REQUIRE(ab_dtype == B200_BF16 || ab_dtype == B200_FP8_E4M3 || ab_dtype == B200_INT8 || ab_dtype == B200_INT8_WO,
+               "gemm_decode_plan: bad dtype");
   GemmPlan p;
   int rc = plan_gemm(p, M, N, K, ab_dtype, split_k);
   if (rc) return rc;
@@ -982,10 +1109,12 @@ int b200_gemm_decode_plan(int M, int N, int K, int ab_dtype, int split_k, int si
   if (silu_mul) {
     rc = ab_dtype == B200_BF16 ? query_plan<KIND_F16, EPI_SILU_MUL>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
          : ab_dtype == B200_FP8_E4M3 ? query_plan<KIND_F8F6F4, EPI_SILU_MUL>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
+         : ab_dtype == B200_INT8_WO  ? query_plan<KIND_WO8, EPI_SILU_MUL>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
                                      : query_plan<KIND_I8, EPI_SILU_MUL>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r);
   } else {
     rc = ab_dtype == B200_BF16 ? query_plan<KIND_F16, EPI_LINEAR>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
          : ab_dtype == B200_FP8_E4M3 ? query_plan<KIND_F8F6F4, EPI_LINEAR>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
+         : ab_dtype == B200_INT8_WO  ? query_plan<KIND_WO8, EPI_LINEAR>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
                                      : query_plan<KIND_I8, EPI_LINEAR>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r);
   }
   if (rc) return rc;
@@ -1012,6 +1141,13 @@ int b200_gemm(const void* a, const void* w, void* out, const float* a_scale, con
   GemmEpilogue ep{a_scale, w_scale, (const __nv_bfloat16*)bias, (const __nv_bfloat16*)residual, out, out_dtype == B200_F32,
                   nullptr};
   return gemm_common(a, w, ep, EPI_LINEAR, M, N, K, ab_dtype, split_k, workspace, workspace_bytes, stream);
+}
+
+int b200_gemm_int8_wo(const void* a_bf16, const void* w_int8, void* out, const float* w_scale, const void* bias,
+                      const void* residual, int M, int N, int K, int out_dtype, int split_k, void* workspace,
+                      size_t workspace_bytes, void* stream) {
+  return b200_gemm(a_bf16, w_int8, out, nullptr, w_scale, bias, residual, M, N, K, B200_INT8_WO, out_dtype, split_k, workspace,
+                   workspace_bytes, stream);
 }
 
 int b200_gemm_silu_mul(const void* a, const void* w_gu, void* out_act, const float* a_scale, const float* w_scale,

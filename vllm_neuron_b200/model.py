@@ -19,7 +19,8 @@ import torch
 from . import ops
 from .config import ModelShape
 
-_QKIND = {"bf16": None, "fp8": "fp8", "int8": "int8"}
+# activation quantisation per mode: W8A8 modes quantise activations per token; weight-only keeps them bf16
+_QKIND = {"bf16": None, "fp8": "fp8", "int8": "int8", "int8_wo": None}
 
 
 def rope_tables(head_dim: int, max_pos: int, theta: float, scaling: dict | None, device):
@@ -108,8 +109,8 @@ class _Linear:
 
     def __init__(self, w_full: torch.Tensor, quant: str, device, row_slices=None, col_slice=None, bias=None):
         # quantise the FULL weight first (per-channel scales are properties of the un-sharded matrix), then shard
-        if quant in ("fp8", "int8"):
-            wq, ws = quantize_weight(w_full, quant)  # on whatever device the master weight lives
+        if quant in ("fp8", "int8", "int8_wo"):
+            wq, ws = quantize_weight(w_full, "fp8" if quant == "fp8" else "int8")  # on the master weight's device
             wq, ws = wq.to(device), ws.to(device)
         else:
             wq, ws = w_full.to(device), None
@@ -150,7 +151,7 @@ class B200CausalLM:
                  max_num_seqs: int, max_model_len: int, block_size: int = 32, device="cuda", tp_rank: int = 0,
                  tp_size: int = 1, tp_group=None, quant_lm_head: bool = True, seed: int = 0,
                  use_peer_exchange: bool = True):
-        assert quant in ("bf16", "fp8", "int8"), f"quant mode {quant!r} not built yet"
+        assert quant in ("bf16", "fp8", "int8", "int8_wo"), f"unknown quant mode {quant!r}"
         assert shape.num_q_heads % tp_size == 0 and shape.num_kv_heads % tp_size == 0, "heads must divide TP"
         assert shape.intermediate % tp_size == 0 and shape.vocab % tp_size == 0
         ops.device_check(torch.device(device).index or 0)
@@ -218,7 +219,7 @@ class B200CausalLM:
         nbytes = 16
         for m in {self.max_num_seqs, min(self.max_model_len, 4096)}:
             for lin in self._linears():
-                dt = {"bf16": 0, "fp8": 1, "int8": 2}[lin.quant]
+                dt = {"bf16": 0, "fp8": 1, "int8": 2, "int8_wo": 4}[lin.quant]
                 nbytes = max(nbytes, ops.gemm_workspace_bytes(m, lin.n, lin.k, dt, 0))
         # zero-filled once: the stream-K fix-up counters at its head are left at zero by every GEMM
         self.gemm_ws = torch.zeros(nbytes, dtype=torch.uint8, device=dev)

@@ -12,7 +12,8 @@ from ._cabi import BF16, F32, FP8_E4M3, INT8, check
 
 _QDT = {None: BF16, "bf16": BF16, "fp8": FP8_E4M3, "int8": INT8}
 _TORCH_Q = {FP8_E4M3: torch.float8_e4m3fn, INT8: torch.int8}
-_DTN = {BF16: "bf16", FP8_E4M3: "fp8", INT8: "int8"}
+INT8_WO = 4  # GEMM ab_dtype only: bf16 activations x int8 weights
+_DTN = {BF16: "bf16", FP8_E4M3: "fp8", INT8: "int8", INT8_WO: "int8wo"}
 
 
 def _stream():
@@ -245,6 +246,15 @@ def _ab_dtype(t):
     raise _cabi.B200Error(f"unsupported GEMM operand dtype {t.dtype}")
 
 
+def _gemm_dtype(a, w):
+    """ab_dtype code of a GEMM: both operands alike, or bf16 activations x int8 weights (weight-only)."""
+    if a.dtype == torch.bfloat16 and w.dtype == torch.int8:
+        return INT8_WO
+    if a.dtype != w.dtype:
+        raise _cabi.B200Error(f"GEMM operand dtypes {a.dtype} x {w.dtype} not supported")
+    return _ab_dtype(a)
+
+
 def gemm_decode_plan(m, n, k, ab_dtype, split_k=0, silu_mul=False, has_residual=False) -> dict:
     """The decode schedule the library picks for this shape on the current device (for benches / DESIGN notes)."""
     import ctypes
@@ -272,8 +282,8 @@ def gemm(a, w, a_scale=None, w_scale=None, bias=None, residual=None, out=None, o
     _cuda(a, w, a_scale, w_scale, bias, residual)
     m, k = a.shape
     n, k2 = w.shape
-    assert k == k2 and a.is_contiguous() and w.is_contiguous() and a.dtype == w.dtype
-    dt = _ab_dtype(a)
+    assert k == k2 and a.is_contiguous() and w.is_contiguous()
+    dt = _gemm_dtype(a, w)
     if out is None:
         out = torch.empty((m, n), dtype=out_dtype, device=a.device)
     assert out.is_contiguous() and out.shape == (m, n)
@@ -310,8 +320,8 @@ def gemm_silu_mul(a, w_gu_interleaved, a_scale=None, w_scale=None, bias=None, sp
     _cuda(a, w_gu_interleaved, a_scale, w_scale, bias)
     m, k = a.shape
     n2, k2 = w_gu_interleaved.shape
-    assert k == k2 and a.is_contiguous() and w_gu_interleaved.is_contiguous() and a.dtype == w_gu_interleaved.dtype
-    dt = _ab_dtype(a)
+    assert k == k2 and a.is_contiguous() and w_gu_interleaved.is_contiguous()
+    dt = _gemm_dtype(a, w_gu_interleaved)
     act = torch.empty((m, n2 // 2), dtype=torch.bfloat16, device=a.device)
     assert n2 % 32 == 0
     group_amax = torch.empty((m, n2 // 32), dtype=torch.float32, device=a.device)
