@@ -162,6 +162,20 @@ int b200_silu_mul(const void* gate_up, void* out_bf16, void* out_q, float* out_s
 int b200_quantize_per_token(const void* x, void* out_q, float* out_scale, const float* group_amax, int n_groups, int T, int K,
                             int q_dtype, void* stream);
 int b200_embedding(const int64_t* tokens, const void* table, void* out, int T, int H, int V, void* stream);
+/* ---------------------------------------------------------------- on-device sampling (top-k / top-p / temperature)
+ * Replaces NxDI's on-device sampler behind `self.model.sample(...)` (model_runner.py:1084-1098, model_loader.py:367-382)
+ * fed by the [B][3] (top_k, top_p, temperature) tensor of get_nxd_sampling_params (model_runner.py:1106-1140).
+ * b200_topk_candidates: per row the 256 (= _MAX_NEURON_SAMPLING_TOP_K, model_runner.py:74) largest fp32 logits of the
+ *   local vocab shard, sorted by (value desc, index asc): cand_val [B][256] fp32, cand_idx [B][256] int64 (global token id
+ *   = idx_offset + column; -inf / -1 padding when V < 256).  Exact (radix select), ties towards the lower index.
+ * b200_sample_candidates: cand_* laid out [groups][B][256] (groups = TP shards, all-gathered by the caller); merges the
+ *   groups, keeps top_k (1..256), w_j = exp((v_j - v_0)/temperature), keeps the shortest prefix with cumulative weight
+ *   >= top_p * Z, and draws by inverse CDF with the caller's uniform u[b] in [0,1).  top_k == 1 is greedy (== b200_argmax).
+ *   fp32, sequential, fixed order: the result is a pure function of (logits, params, u). */
+int b200_topk_candidates(const float* logits, int64_t row_stride, float* cand_val, int64_t* cand_idx, int B, int V,
+                         int64_t idx_offset, void* stream);
+int b200_sample_candidates(const float* cand_val, const int64_t* cand_idx, int groups, int B, const float* params,
+                           const float* u, int64_t* out_ids, void* stream);
 /* Greedy sampling (reference: top_k=1, temperature=1.0 for temperature 0, model_runner.py:1126-1128).
  * out_idx[t] = idx_offset + first index of the row maximum; out_val[t] = that maximum (for TP merges). */
 int b200_argmax(const float* logits, int64_t row_stride, float* out_val, int64_t* out_idx, int T, int V,

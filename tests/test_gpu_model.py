@@ -177,3 +177,65 @@ def test_kv_cache_contents_bit_exact_bf16():
     assert (kd[0] == 0).all() and (vd[0] == 0).all()  # null block never written
     unused = [b for b in range(1, model.num_blocks) if b not in used]
     assert (kd[unused] == 0).all()  # nothing leaked outside the allocated blocks
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_execute_model_with_on_device_sampling(use_graph):
+    """Stochastic requests through execute_model: per-request (top_k, top_p, temperature) rows (RUNNER:1106-1140) and
+    seeded uniforms go to the device sampler; every sampled id must equal the oracle sampler applied to the device's own
+    logits with the same uniform, and a greedy request in the same batch must still get the argmax."""
+    from types import SimpleNamespace
+
+    import numpy as np
+
+    from oracle import sampling_ref
+    from vllm_neuron_b200.config import PRESETS
+    from vllm_neuron_b200.model import B200CausalLM, random_init_full_weights
+    from vllm_neuron_b200.worker.b200_model_runner import B200ModelRunner
+
+    shape = PRESETS["tiny-test"]
+    weights = random_init_full_weights(shape, seed=3, std=0.05)
+    cfg = make_vllm_config(shape, max_num_seqs=4, max_model_len=256, num_gpu_blocks_override=41, enforce_eager=not use_graph)
+    model = B200CausalLM(shape, weights, quant="bf16", num_blocks=41, max_num_seqs=4, max_model_len=256)
+    runner = B200ModelRunner(cfg, torch.device("cuda"), model=model)
+    runner.load_model(load_dummy_weights=True)
+    runner.initialize_kv_cache(num_blocks=41)
+    sps = {"a": SimpleNamespace(top_k=20, top_p=0.9, temperature=0.8, seed=7),
+           "b": SimpleNamespace(top_k=0, top_p=1.0, temperature=0.0, seed=None),      # greedy
+           "c": SimpleNamespace(top_k=-1, top_p=0.5, temperature=1.3, seed=9)}        # top_k disabled -> 256
+    rngs = {"a": np.random.Generator(np.random.PCG64(7)), "c": np.random.Generator(np.random.PCG64(9))}
+    g = torch.Generator().manual_seed(5)
+    blocks = {"a": [3, 9], "b": [4], "c": [11, 12]}
+    prompts = {"a": torch.randint(0, shape.vocab, (40,), generator=g).tolist(),
+               "b": torch.randint(0, shape.vocab, (20,), generator=g).tolist(),
+               "c": torch.randint(0, shape.vocab, (33,), generator=g).tolist()}
+
+    def expect(rids, logits):
+        """oracle sampler on the device logits of this step, rows in `rids` order"""
+        rows = np.array([runner.sampling_row(runner.requests[r]) for r in rids], dtype=np.float32)
+        u = np.array([np.float32(rngs[r].random(dtype=np.float32)) if rows[i, 0] != 1 else 0.0 for i, r in enumerate(rids)],
+                     dtype=np.float32)
+        cv, ci = sampling_ref.topk_candidates_ref(logits.float().cpu().numpy())
+        ids, margin = sampling_ref.sample_candidates_ref(cv, ci, rows, u)
+        return ids, margin
+
+    checked = 0
+    for rid in ["a", "b", "c"]:
+        so = sched_output(new_reqs=[(rid, prompts[rid], blocks[rid], 0)])
+        so.scheduled_new_reqs[0].sampling_params = sps[rid]
+        out = runner.execute_model(so)
+        want, margin = expect([rid], model.last_logits)
+        if margin[0] > 1e-5:
+            assert out.sampled_token_ids[0] == [int(want[0])], rid
+            checked += 1
+    live = ["a", "b", "c"]
+    for step in range(6):
+        out = runner.execute_model(sched_output(cached=[(r, None) for r in live]))
+        want, margin = expect(live, model.last_logits)
+        for i, r in enumerate(live):
+            if margin[i] > 1e-5:
+                assert out.sampled_token_ids[out.req_id_to_index[r]] == [int(want[i])], (step, r)
+                checked += 1
+    assert checked >= 18
+    # the greedy request got the argmax every step
+    assert runner.sampling_row(runner.requests["b"]) == (1.0, 1.0, 1.0)

@@ -1,0 +1,62 @@
+"""CPU tests of the sampler oracle (oracle/sampling_ref.py): the restated top-k / temperature / top-p / inverse-CDF rule
+against first-principles properties (no GPU)."""
+import numpy as np
+
+from oracle import sampling_ref as S
+
+
+def _logits(b, v, seed):
+    return np.random.default_rng(seed).standard_normal((b, v)).astype(np.float32) * 3
+
+
+def test_candidates_are_the_sorted_top_256_with_low_index_ties():
+    x = _logits(3, 5000, 0)
+    x[1, 10] = x[1, 4000] = x[1].max() + 1  # tie at the top: index 10 first
+    val, idx = S.topk_candidates_ref(x, idx_offset=7)
+    assert idx[1, 0] == 17 and idx[1, 1] == 4007
+    for r in range(3):
+        assert np.array_equal(val[r], np.sort(x[r])[::-1][:256])
+        assert np.array_equal(x[r, idx[r] - 7], val[r])
+    v2, i2 = S.topk_candidates_ref(x[:, :100])
+    assert np.isinf(v2[:, 100:]).all() and (i2[:, 100:] == -1).all()
+
+
+def test_greedy_and_degenerate_rows():
+    x = _logits(4, 1000, 1)
+    val, idx = S.topk_candidates_ref(x)
+    params = np.array([[1, 1.0, 1.0], [50, 1e-6, 1.0], [50, 1.0, 1e-3], [256, 1.0, 1.0]], dtype=np.float32)
+    u = np.array([0.99, 0.99, 0.5, 0.0], dtype=np.float32)
+    ids, _ = S.sample_candidates_ref(val, idx, params, u)
+    am = x.argmax(axis=1)
+    assert ids[0] == am[0]  # top_k 1
+    assert ids[1] == am[1]  # top_p -> 0 keeps one token
+    assert ids[2] == am[2]  # temperature -> 0 concentrates on the max
+    assert ids[3] == am[3]  # u = 0 picks the most likely token
+
+
+def test_empirical_distribution_matches_truncated_softmax():
+    x = _logits(1, 300, 2)
+    val, idx = S.topk_candidates_ref(x)
+    k, top_p, temp = 8, 0.8, 0.7
+    n = 4000
+    u = ((np.arange(n) + 0.5) / n).astype(np.float32)  # stratified uniforms
+    params = np.tile(np.array([[k, top_p, temp]], dtype=np.float32), (n, 1))
+    ids, _ = S.sample_candidates_ref(np.repeat(val, n, 0), np.repeat(idx, n, 0), params, u)
+    w = np.exp((val[0, :k] - val[0, 0]) / temp).astype(np.float64)
+    p = w / w.sum()
+    kept = int(np.searchsorted(np.cumsum(p), top_p - 1e-9) + 1)
+    q = p[:kept] / p[:kept].sum()
+    counts = np.array([(ids == idx[0, j]).sum() for j in range(kept)]) / n
+    assert counts.sum() == 1.0 and np.abs(counts - q).max() < 2e-3
+
+
+def test_merging_shards_equals_unsharded():
+    x = _logits(5, 4096, 3)
+    val, idx = S.topk_candidates_ref(x)
+    parts = [S.topk_candidates_ref(x[:, s * 1024:(s + 1) * 1024], idx_offset=s * 1024) for s in range(4)]
+    gv, gi = np.stack([p[0] for p in parts]), np.stack([p[1] for p in parts])
+    params = np.tile(np.array([[40, 0.9, 1.1]], dtype=np.float32), (5, 1))
+    u = np.random.default_rng(4).random(5).astype(np.float32)
+    a, _ = S.sample_candidates_ref(val, idx, params, u)
+    b, _ = S.sample_candidates_ref(gv, gi, params, u)
+    assert np.array_equal(a, b)

@@ -68,3 +68,36 @@ def test_config_and_kv_spec_follow_the_reference_keys():
     assert len(spec) == PRESETS["tiny-test"].layers
     s0 = next(iter(spec.values()))
     assert s0.block_size == 32 and s0.num_kv_heads == 2 and s0.head_size == 64 and s0.dtype == torch.bfloat16
+
+
+def test_sampling_rows_follow_the_reference_rule(golden_index):
+    """RUNNER:1106-1140, pinned by the golden vectors generated from the reference's own get_nxd_sampling_params:
+    top_k outside (0, max_topk) -> max_topk = min(global_topk | vocab, 256); temperature 0 -> (1, top_p, 1.0)."""
+    from types import SimpleNamespace
+
+    from vllm_neuron_b200.worker.b200_model_runner import CachedRequest
+
+    for c in golden_index["sampling"]:
+        r = _runner()
+        r.global_topk = c["global_topk"] or 0
+        r.model_config.get_vocab_size = lambda v=c["vocab"]: v
+        for i, (k, p, t) in enumerate(c["params"]):
+            st = CachedRequest(f"s{i}", [1], sampling_params=SimpleNamespace(top_k=k, top_p=p, temperature=t, seed=None))
+            got = r.sampling_row(st)
+            assert got == (float(c["top_k"][i]), pytest.approx(c["top_p"][i]), pytest.approx(c["temperature"][i])), (c, i, got)
+
+
+def test_all_greedy_batch_takes_the_argmax_path_and_seeded_draws_repeat():
+    from types import SimpleNamespace
+
+    from vllm_neuron_b200.worker.b200_model_runner import CachedRequest
+
+    r = _runner()
+    greedy = CachedRequest("g", [1], sampling_params=SimpleNamespace(top_k=0, top_p=1.0, temperature=0.0, seed=None))
+    assert r._sampling_inputs([greedy, greedy]) is None
+    a = CachedRequest("a", [1], sampling_params=SimpleNamespace(top_k=50, top_p=0.9, temperature=0.8, seed=123))
+    b = CachedRequest("b", [1], sampling_params=SimpleNamespace(top_k=50, top_p=0.9, temperature=0.8, seed=123))
+    rows, u = r._sampling_inputs([greedy, a])
+    assert rows[0] == (1.0, 1.0, 1.0) and rows[1] == (50.0, 0.9, 0.8) and u[0] == 0.0 and 0.0 <= u[1] < 1.0
+    _, u2 = r._sampling_inputs([b])
+    assert u2[0] == u[1]  # same SamplingParams.seed -> same stream of uniforms

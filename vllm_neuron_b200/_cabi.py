@@ -51,6 +51,8 @@ SIGNATURES = {
     "b200_quantize_per_token": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _p]),
     "b200_embedding": (_i, [_p, _p, _p, _i, _i, _i, _p]),
     "b200_argmax": (_i, [_p, _i64, _p, _p, _i, _i, _i64, _p]),
+    "b200_topk_candidates": (_i, [_p, _i64, _p, _p, _i, _i, _i64, _p]),
+    "b200_sample_candidates": (_i, [_p, _p, _i, _i, _p, _p, _p, _p]),
     "b200_allreduce_rmsnorm": (_i, [_p, _p, _p, _i, _i, _p, _p, _p, _p, _p, _i, _i, _f, _i, _p]),
 }
 

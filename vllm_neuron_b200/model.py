@@ -144,6 +144,8 @@ class StepBuffers:
     positions: torch.Tensor
     ctx_lens: torch.Tensor
     sampled: torch.Tensor
+    samp_params: torch.Tensor  # [b, 3] fp32 (top_k, top_p, temperature) -- RUNNER:1106-1140
+    samp_u: torch.Tensor       # [b] fp32 uniforms in [0, 1) for the inverse-CDF draw
 
 
 class B200CausalLM:
@@ -287,8 +289,9 @@ class B200CausalLM:
             x, h, hs = self._row_parallel(L["down"], aq, a_s, x, nxt)
         return x
 
-    def _sample(self, x_rows):
-        """final norm -> lm_head (fp32 logits of the local vocab shard) -> greedy argmax (TP: merge (val, idx))."""
+    def _sample(self, x_rows, samp=None):
+        """final norm -> lm_head (fp32 logits of the local vocab shard) -> greedy argmax (TP: merge (val, idx)), or with
+        samp = (params [T,3], u [T]) the on-device top-k / top-p / temperature sampler (TP: candidates all-gathered)."""
         lm_q = _QKIND[self.lm_head.quant]
         if lm_q is None:
             h, hs = ops.rmsnorm(x_rows, self.final_norm, self.shape.rms_eps), None
@@ -296,6 +299,15 @@ class B200CausalLM:
             h, hs = ops.rmsnorm(x_rows, self.final_norm, self.shape.rms_eps, quant=lm_q)
         logits = self._linear(self.lm_head, h, hs, out_dtype=torch.float32)
         self.last_logits = logits  # kept for parity tests (a reference, no copy)
+        if samp is not None:
+            cv, ci = ops.topk_candidates(logits, idx_offset=self.vocab_offset)
+            if self.tp_size > 1:
+                gv = torch.empty((self.tp_size, *cv.shape), dtype=cv.dtype, device=cv.device)
+                gi = torch.empty((self.tp_size, *ci.shape), dtype=ci.dtype, device=ci.device)
+                torch.distributed.all_gather_into_tensor(gv, cv, group=self.tp_group)
+                torch.distributed.all_gather_into_tensor(gi, ci, group=self.tp_group)
+                cv, ci = gv, gi
+            return ops.sample_candidates(cv, ci, samp[0], samp[1]), logits
         if self.tp_size == 1:
             return ops.argmax(logits), logits
         val, idx = ops.argmax(logits, idx_offset=self.vocab_offset, want_val=True)
@@ -316,10 +328,12 @@ class B200CausalLM:
                 positions=torch.zeros(b, dtype=torch.int64, device=dev),
                 ctx_lens=torch.zeros(b, dtype=torch.int32, device=dev),
                 sampled=torch.zeros(b, dtype=torch.int64, device=dev),
+                samp_params=torch.tensor([[1.0, 1.0, 1.0]], dtype=torch.float32, device=dev).repeat(b, 1),
+                samp_u=torch.zeros(b, dtype=torch.float32, device=dev),
             )
         return self._decode_bufs[b]
 
-    def _decode_body(self, bufs: StepBuffers, max_ctx_blocks: int, advance: bool):
+    def _decode_body(self, bufs: StepBuffers, max_ctx_blocks: int, advance: bool, sampled: bool = False):
         b = bufs.tokens.numel()
         # index construction on device (RUNNER:765-832): positions, slot_mapping, context lengths
         ops.build_decode_meta(self.block_table, bufs.row_ids, self.num_tokens, bufs.slot_mapping, bufs.positions,
@@ -331,34 +345,36 @@ class B200CausalLM:
                                          row_ids=bufs.row_ids, max_blocks=max_ctx_blocks, quant=quant)
 
         x = self._layers(x, bufs.positions, bufs.slot_mapping, attn)
-        ids, _ = self._sample(x)
+        ids, _ = self._sample(x, (bufs.samp_params, bufs.samp_u) if sampled else None)
         bufs.sampled.copy_(ids)
         if advance:  # device-side twin of RUNNER:325-339 so the captured step can be replayed back to back
             ops.advance_decode(bufs.sampled, bufs.tokens, self.num_tokens, bufs.row_ids)
         return bufs.sampled
 
-    def decode_step(self, b: int, *, max_ctx_blocks: int | None = None, advance: bool = False, use_graph: bool = False):
+    def decode_step(self, b: int, *, max_ctx_blocks: int | None = None, advance: bool = False, use_graph: bool = False,
+                    sampled: bool = False):
         """One decode step for the `b` rows in decode_buffers(b).row_ids; inputs already on the device:
-        bufs.tokens (last sampled token per row), self.num_tokens[row] (= prompt + outputs incl. that token)."""
+        bufs.tokens (last sampled token per row), self.num_tokens[row] (= prompt + outputs incl. that token).
+        sampled=True draws with bufs.samp_params / bufs.samp_u instead of the greedy argmax."""
         bufs = self.decode_buffers(b)
         mcb = self.max_blocks if max_ctx_blocks is None else max_ctx_blocks
         if not use_graph:
-            return self._decode_body(bufs, mcb, advance)
-        key = (b, mcb, advance)
+            return self._decode_body(bufs, mcb, advance, sampled)
+        key = (b, mcb, advance, sampled)
         if key not in self._graphs:
             nt = self.num_tokens.clone()
             tk = bufs.tokens.clone()
             s = torch.cuda.Stream()
             s.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(s):  # warm-up outside capture (function attributes, NCCL channels)
-                self._decode_body(bufs, mcb, advance)
+                self._decode_body(bufs, mcb, advance, sampled)
             torch.cuda.current_stream().wait_stream(s)
             torch.cuda.synchronize()
             self.num_tokens.copy_(nt)
             bufs.tokens.copy_(tk)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                self._decode_body(bufs, mcb, advance)
+                self._decode_body(bufs, mcb, advance, sampled)
             self.num_tokens.copy_(nt)
             bufs.tokens.copy_(tk)
             self._graphs[key] = (g, self.last_logits)
@@ -367,9 +383,10 @@ class B200CausalLM:
         return bufs.sampled
 
     # ------------------------------------------------------------------ prefill (batch 1, prefix-cached)
-    def prefill(self, row: int, new_tokens: torch.Tensor, prompt_len: int, computed_len: int):
+    def prefill(self, row: int, new_tokens: torch.Tensor, prompt_len: int, computed_len: int, samp=None):
         """Compute the uncached suffix `new_tokens` (device int64 [prompt_len - computed_len]) of one request whose
-        block ids are already in block_table[row]; returns the sampled next token (device int64 [1])."""
+        block ids are already in block_table[row]; returns the sampled next token (device int64 [1]).
+        samp = (params [1,3], u [1]) selects the on-device sampler instead of greedy."""
         s_new = prompt_len - computed_len
         assert new_tokens.numel() == s_new and s_new > 0
         dev = self.device
@@ -384,7 +401,7 @@ class B200CausalLM:
             return ops.paged_attn_prefill(qv, kp, vp, bt_row, computed_len, self.scale)
 
         x = self._layers(x, positions, slots, attn)
-        ids, _ = self._sample(x[-1:].contiguous())
+        ids, _ = self._sample(x[-1:].contiguous(), samp)
         self.num_tokens[row] = prompt_len
         return ids
 

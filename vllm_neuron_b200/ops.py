@@ -418,6 +418,39 @@ def argmax(logits, idx_offset: int = 0, want_val: bool = False):
     return (val, idx) if want_val else idx
 
 
+SAMPLE_K = 256  # candidates per (row, vocab shard); the reference's _MAX_NEURON_SAMPLING_TOP_K (RUNNER:74)
+
+
+def topk_candidates(logits, idx_offset: int = 0):
+    """logits fp32 [B, V] -> (cand_val [B,256] fp32, cand_idx [B,256] int64) sorted by (value desc, index asc)."""
+    _cuda(logits)
+    b, v = logits.shape
+    assert logits.dtype == torch.float32 and logits.stride(1) == 1
+    val = torch.empty((b, SAMPLE_K), dtype=torch.float32, device=logits.device)
+    idx = torch.empty((b, SAMPLE_K), dtype=torch.int64, device=logits.device)
+    with _k("topk_candidates"):
+        check(_cabi.load().b200_topk_candidates(_ptr(logits), logits.stride(0), _ptr(val), _ptr(idx), b, v, idx_offset,
+                                                _stream()), "b200_topk_candidates")
+    return val, idx
+
+
+def sample_candidates(cand_val, cand_idx, params, u, out=None):
+    """cand_* [B,256] or [groups,B,256]; params fp32 [B,3] = (top_k, top_p, temperature); u fp32 [B] in [0,1)."""
+    _cuda(cand_val, cand_idx, params, u)
+    if cand_val.dim() == 2:
+        cand_val, cand_idx = cand_val.unsqueeze(0), cand_idx.unsqueeze(0)
+    g, b, k = cand_val.shape
+    assert k == SAMPLE_K and cand_val.is_contiguous() and cand_idx.is_contiguous() and cand_idx.dtype == torch.int64
+    assert params.shape == (b, 3) and params.dtype == torch.float32 and params.is_contiguous()
+    assert u.shape == (b,) and u.dtype == torch.float32
+    if out is None:
+        out = torch.empty((b,), dtype=torch.int64, device=cand_val.device)
+    with _k("sample_candidates"):
+        check(_cabi.load().b200_sample_candidates(_ptr(cand_val), _ptr(cand_idx), g, b, _ptr(params), _ptr(u), _ptr(out),
+                                                  _stream()), "b200_sample_candidates")
+    return out
+
+
 def allreduce_rmsnorm(peer_bufs, peer_flags, epoch, rank, world, t, h, norm_w, eps, quant=None, want_bf16=False):
     """One-shot all-reduce over NVLink peer memory fused with RMSNorm (+ per-token quantisation).
     peer_bufs / peer_flags: ctypes arrays of `world` device pointers (tp_comm.TpComm).  Returns (x, h_out, h_scale):

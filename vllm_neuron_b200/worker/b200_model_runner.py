@@ -27,6 +27,7 @@ from ..model import B200CausalLM
 
 logger = logging.getLogger(__name__)
 
+_MAX_SAMPLING_TOP_K = 256  # RUNNER:74 (_MAX_NEURON_SAMPLING_TOP_K)
 _SLOT_MAPPING_PAD = -1  # RUNNER:80
 _BLOCK_TABLE_PAD = 0  # RUNNER:81
 
@@ -40,6 +41,7 @@ class CachedRequest:
     num_computed_tokens: int = 0
     row: int = -1  # persistent block-table row (the reference's "neuron seq id")
     sampling_params: object = None
+    rng: object = None  # per-request numpy Generator (SamplingParams.seed), created on first stochastic draw
 
     @property
     def num_tokens(self) -> int:
@@ -80,6 +82,12 @@ class B200ModelRunner:
         self._stage = None
         self.h2d_bytes_last = 0
         self.d2h_bytes_last = 0
+        import numpy as np
+
+        add = getattr(vllm_config, "additional_config", None) or {}
+        ods = (add.get("override_neuron_config") or {}).get("on_device_sampling_config") or {}
+        self.global_topk = int(ods.get("global_topk", 0)) if isinstance(ods, dict) else int(getattr(ods, "global_topk", 0))
+        self._rng = np.random.Generator(np.random.PCG64(getattr(self.model_config, "seed", 0) or 0))
 
     # ------------------------------------------------------------------ config / load / KV allocation
     def build_b200_config(self) -> B200Config:
@@ -163,6 +171,9 @@ class B200ModelRunner:
         self._pin_upd = torch.zeros((max(64, 4 * n), 3), dtype=torch.int32).pin_memory()
         self._dev_upd = torch.zeros_like(self._pin_upd, device=self.device)
         self._pin_out = torch.zeros(n, dtype=torch.int64).pin_memory()
+        self._pin_samp = torch.ones((n, 3), dtype=torch.float32).pin_memory()
+        self._pin_u = torch.zeros(n, dtype=torch.float32).pin_memory()
+        self._np_samp, self._np_u = self._pin_samp.numpy(), self._pin_u.numpy()
         # numpy views of the pinned staging buffers: one vectorised store per field instead of per-request tensor
         # __setitem__ calls (the reference builds Python lists and calls torch.tensor() on them, RUNNER:887-917)
         self._np_tokens, self._np_rows = self._pin_tokens.numpy(), self._pin_rows.numpy()
@@ -219,6 +230,45 @@ class B200ModelRunner:
         ops.block_table_scatter(self.model.block_table, self._dev_upd[:n])
         self.h2d_bytes_last += n * 12
 
+    # ------------------------------------------------------------------ sampling parameters (RUNNER:1106-1140)
+    def sampling_row(self, st: CachedRequest) -> tuple[float, float, float]:
+        """(top_k, top_p, temperature) of one request by the reference's rule: top_k outside (0, max_topk) -> max_topk
+        (= min(global_topk or vocab, 256)); temperature 0 -> top_k 1, temperature 1.0 (greedy)."""
+        sp = st.sampling_params
+        gv = getattr(self.model_config, "get_vocab_size", None)
+        vocab = gv() if callable(gv) else self.model_shape().vocab
+        max_topk = min(self.global_topk or vocab, _MAX_SAMPLING_TOP_K)
+        if sp is None:
+            return (1.0, 1.0, 1.0)
+        k = getattr(sp, "top_k", 0) or 0
+        top_k = k if 0 < k < max_topk else max_topk
+        top_p = float(getattr(sp, "top_p", 1.0))
+        temp = float(getattr(sp, "temperature", 1.0))
+        if temp == 0.0:
+            top_k, temp = 1, 1.0
+        return (float(top_k), top_p, temp)
+
+    def _draw_uniform(self, st: CachedRequest) -> float:
+        """One uniform in [0,1) for the request's next draw: its own generator when SamplingParams.seed is set, else the
+        runner's (seeded from model_config.seed).  The device kernel is a pure function of (logits, params, u)."""
+        import numpy as np
+
+        seed = getattr(st.sampling_params, "seed", None)
+        if seed is not None:
+            if st.rng is None:
+                st.rng = np.random.Generator(np.random.PCG64(seed))
+            g = st.rng
+        else:
+            g = self._rng
+        return float(np.float32(g.random(dtype=np.float32)))
+
+    def _sampling_inputs(self, sts: list[CachedRequest]):
+        """None when every request of the batch is greedy (argmax path); else host lists (params rows, uniforms)."""
+        rows = [self.sampling_row(st) for st in sts]
+        if all(r[0] == 1.0 for r in rows):
+            return None
+        return rows, [self._draw_uniform(st) if r[0] != 1.0 else 0.0 for st, r in zip(sts, rows)]
+
     # ------------------------------------------------------------------ the step
     @torch.inference_mode()
     def execute_model(self, scheduler_output, intermediate_tensors=None):
@@ -243,7 +293,13 @@ class B200ModelRunner:
             new = torch.tensor(st.prompt_token_ids[st.num_computed_tokens:], dtype=torch.int64).pin_memory()
             new_d = new.to(self.device, non_blocking=True)
             self.h2d_bytes_last += new.numel() * 8
-            pending.append(self.model.prefill(st.row, new_d, plen, st.num_computed_tokens))
+            samp = self._sampling_inputs([st])
+            if samp is not None:
+                sp_d = torch.tensor(samp[0], dtype=torch.float32).pin_memory().to(self.device, non_blocking=True)
+                u_d = torch.tensor(samp[1], dtype=torch.float32).pin_memory().to(self.device, non_blocking=True)
+                self.h2d_bytes_last += 16
+                samp = (sp_d, u_d)
+            pending.append(self.model.prefill(st.row, new_d, plen, st.num_computed_tokens, samp))
             req_ids.append(nr.req_id)
         # ---- decode batch (RUNNER:765-832)
         dec_ids = list(scheduler_output.scheduled_cached_reqs.req_ids)
@@ -262,9 +318,17 @@ class B200ModelRunner:
             bufs.row_ids.copy_(self._pin_rows[:b], non_blocking=True)
             self.model.num_tokens.copy_(self._pin_ntok, non_blocking=True)
             self.h2d_bytes_last += b * 12 + self._pin_ntok.numel() * 4
+            samp = self._sampling_inputs(sts)
+            if samp is not None:
+                self._np_samp[:b] = samp[0]
+                self._np_u[:b] = samp[1]
+                bufs.samp_params.copy_(self._pin_samp[:b], non_blocking=True)
+                bufs.samp_u.copy_(self._pin_u[:b], non_blocking=True)
+                self.h2d_bytes_last += b * 16
             # bound the context split by the longest live context, rounded to 8 blocks so few graphs are captured
             mcb = min(self.model.max_blocks, -(-(-(-max_ctx // self.block_size)) // 8) * 8)
-            pending.append(self.model.decode_step(b, max_ctx_blocks=mcb, use_graph=self.use_cuda_graph))
+            pending.append(self.model.decode_step(b, max_ctx_blocks=mcb, use_graph=self.use_cuda_graph,
+                                                  sampled=samp is not None))
             req_ids += dec_ids
         # ---- one D2H read of all sampled ids (the step's only sync point; RUNNER:304-306 `.tolist()`)
         ids = torch.cat(pending) if len(pending) > 1 else pending[0]
