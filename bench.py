@@ -425,7 +425,7 @@ def run_e2e(args, shape, model, bt_host, dev, rank, world, group, barrier, n_sta
     for i in range(b):
         rid = f"req-{i}"
         prompt = torch.randint(0, shape.vocab, (n_start,), generator=gen).tolist()
-        runner.requests[rid] = CachedRequest(rid, prompt, [], bt_host[i].tolist(), n_start - 1, i, None)
+        runner.requests[rid] = CachedRequest(rid, prompt, [], bt_host[i].tolist(), n_start - 1, i, None, prefilled=n_start)
         runner.req_to_row[rid] = i
     runner.free_rows.clear()
     so = sched_output(cached=[(f"req-{i}", None) for i in range(b)])

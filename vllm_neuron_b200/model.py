@@ -383,10 +383,13 @@ class B200CausalLM:
         return bufs.sampled
 
     # ------------------------------------------------------------------ prefill (batch 1, prefix-cached)
-    def prefill(self, row: int, new_tokens: torch.Tensor, prompt_len: int, computed_len: int, samp=None):
+    def prefill(self, row: int, new_tokens: torch.Tensor, prompt_len: int, computed_len: int, samp=None,
+                sample: bool = True):
         """Compute the uncached suffix `new_tokens` (device int64 [prompt_len - computed_len]) of one request whose
         block ids are already in block_table[row]; returns the sampled next token (device int64 [1]).
-        samp = (params [1,3], u [1]) selects the on-device sampler instead of greedy."""
+        samp = (params [1,3], u [1]) selects the on-device sampler instead of greedy.
+        Chunked prefill: `prompt_len` is the END of this chunk (tokens [computed_len, prompt_len) are computed against the
+        cached prefix); sample=False for a chunk that does not finish the prompt (no lm_head, returns None)."""
         s_new = prompt_len - computed_len
         assert new_tokens.numel() == s_new and s_new > 0
         dev = self.device
@@ -401,8 +404,10 @@ class B200CausalLM:
             return ops.paged_attn_prefill(qv, kp, vp, bt_row, computed_len, self.scale)
 
         x = self._layers(x, positions, slots, attn)
-        ids, _ = self._sample(x[-1:].contiguous(), samp)
         self.num_tokens[row] = prompt_len
+        if not sample:
+            return None
+        ids, _ = self._sample(x[-1:].contiguous(), samp)
         return ids
 
     def kv_bytes_per_block(self) -> int:

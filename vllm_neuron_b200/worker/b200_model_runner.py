@@ -42,6 +42,7 @@ class CachedRequest:
     row: int = -1  # persistent block-table row (the reference's "neuron seq id")
     sampling_params: object = None
     rng: object = None  # per-request numpy Generator (SamplingParams.seed), created on first stochastic draw
+    prefilled: int = 0  # prompt tokens whose K/V are in the cache (prefix-cache hits + chunks computed so far)
 
     @property
     def num_tokens(self) -> int:
@@ -215,7 +216,8 @@ class B200ModelRunner:
                 assert new_blocks is not None
                 st.block_ids = list(new_blocks)  # RUNNER:467-471: replace after preemption
                 updates += [(st.row, c, b) for c, b in enumerate(st.block_ids)]
-            st.num_computed_tokens = st.num_tokens - 1
+            if st.prefilled >= len(st.prompt_token_ids):
+                st.num_computed_tokens = st.num_tokens - 1
         return updates
 
     def _push_block_updates(self, updates):
@@ -282,27 +284,41 @@ class B200ModelRunner:
 
         req_ids: list[str] = []
         pending: list[torch.Tensor] = []
-        # ---- prefill: one request at a time (SCHED:116 guarantees batch 1; several are processed in turn)
-        for nr in scheduler_output.scheduled_new_reqs:
-            st = self.requests[nr.req_id]
-            n_sched = scheduler_output.num_scheduled_tokens[nr.req_id]
+        no_sample: list[str] = []  # requests whose chunk did not finish the prompt (reference: -1 rows, RUNNER:1060-1064)
+        # ---- prefill: one request at a time (SCHED:116 guarantees batch 1; several are processed in turn).  A chunk
+        # (vLLM's native scheduler, RUNNER:654-679) is a prefill of tokens [prefilled, prefilled + n) against the cached
+        # prefix; only the chunk that completes the prompt samples (prefill_completion_state, RUNNER:938-1051).
+        cached_ids = list(scheduler_output.scheduled_cached_reqs.req_ids)
+        chunk_reqs = [self.requests[nr.req_id] for nr in scheduler_output.scheduled_new_reqs]
+        for st in chunk_reqs:
+            st.prefilled = st.num_computed_tokens
+        chunk_reqs += [self.requests[r] for r in cached_ids if self.requests[r].prefilled < len(self.requests[r].prompt_token_ids)]
+        for st in chunk_reqs:
+            n_sched = scheduler_output.num_scheduled_tokens[st.req_id]
             plen = len(st.prompt_token_ids)
-            if st.num_computed_tokens + n_sched != plen:
-                raise NotImplementedError("chunked prefill is not on the B200 hot path yet (SURVEY 8(f)-3)")
-            assert plen <= self.max_model_len
-            new = torch.tensor(st.prompt_token_ids[st.num_computed_tokens:], dtype=torch.int64).pin_memory()
+            end = st.prefilled + n_sched
+            assert 0 < n_sched and end <= plen <= self.max_model_len, (st.req_id, st.prefilled, n_sched, plen)
+            new = torch.tensor(st.prompt_token_ids[st.prefilled:end], dtype=torch.int64).pin_memory()
             new_d = new.to(self.device, non_blocking=True)
             self.h2d_bytes_last += new.numel() * 8
-            samp = self._sampling_inputs([st])
+            last = end == plen
+            samp = self._sampling_inputs([st]) if last else None
             if samp is not None:
                 sp_d = torch.tensor(samp[0], dtype=torch.float32).pin_memory().to(self.device, non_blocking=True)
                 u_d = torch.tensor(samp[1], dtype=torch.float32).pin_memory().to(self.device, non_blocking=True)
                 self.h2d_bytes_last += 16
                 samp = (sp_d, u_d)
-            pending.append(self.model.prefill(st.row, new_d, plen, st.num_computed_tokens, samp))
-            req_ids.append(nr.req_id)
+            tok = self.model.prefill(st.row, new_d, end, st.prefilled, samp, sample=last)
+            st.prefilled = end
+            st.num_computed_tokens = end
+            if last:
+                pending.append(tok)
+                req_ids.append(st.req_id)
+            else:
+                no_sample.append(st.req_id)
         # ---- decode batch (RUNNER:765-832)
-        dec_ids = list(scheduler_output.scheduled_cached_reqs.req_ids)
+        chunk_set = {st.req_id for st in chunk_reqs}
+        dec_ids = [r for r in cached_ids if r not in chunk_set]
         if dec_ids:
             b = len(dec_ids)
             reqs = self.requests
@@ -331,16 +347,18 @@ class B200ModelRunner:
                                                   sampled=samp is not None))
             req_ids += dec_ids
         # ---- one D2H read of all sampled ids (the step's only sync point; RUNNER:304-306 `.tolist()`)
-        ids = torch.cat(pending) if len(pending) > 1 else pending[0]
-        n = ids.numel()
-        self._pin_out[:n].copy_(ids, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        self.d2h_bytes_last += n * 8
-        sampled = [[x] if x != -1 else [] for x in self._np_out[:n].tolist()]  # RUNNER:304-306: -1 is padding
+        sampled: list[list[int]] = []
+        if pending:
+            ids = torch.cat(pending) if len(pending) > 1 else pending[0]
+            n = ids.numel()
+            self._pin_out[:n].copy_(ids, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            self.d2h_bytes_last += n * 8
+            sampled = [[x] if x != -1 else [] for x in self._np_out[:n].tolist()]  # RUNNER:304-306: -1 is padding
         for rid, row in zip(req_ids, sampled):
             self.requests[rid].output_token_ids.extend(row)  # RUNNER:325-339
-        if self.tp_rank != 0 and self.tp_size > 1:
-            pass  # every rank tracks state; only the driver's output is used (WORKER:65-69)
+        req_ids += no_sample  # partial chunks report no token this step
+        sampled += [[] for _ in no_sample]
         return ModelRunnerOutput(
             req_ids=req_ids,
             req_id_to_index={r: i for i, r in enumerate(req_ids)},
