@@ -476,7 +476,7 @@ constexpr int DEC_MAX_ST = 12;
 template <int KIND, int BM, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
     gemm_decode_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap a_map,
-                       GemmEpilogue ep, int M, int N, int num_kb, int nst, int ring_bytes,
+                       GemmEpilogue ep, int M, int N, int num_kb, int nst, int ring_bytes, int l2_ahead,
                        unsigned long long* __restrict__ trace) {
   using T = KindTraits<KIND>;
   constexpr int BK_ELEMS = GEMM_BK_BYTES / T::ELEM;
@@ -574,6 +574,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
           mbar_expect_tx(&full_w[i], W_TILE);
           tma_load_2d_hint(w_ring + (size_t)i * W_TILE, &w_map, &full_w[i], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
         }
+      }
+      // ... and pull the next `l2_ahead` weight tiles of this CTA's stream into L2: HBM is idle while the predecessor
+      // (a small glue kernel, or the tail of a GEMM) drains, so by the time the ring recycles these loads are L2 hits
+      {
+        const int pf_end = nk < npre + l2_ahead ? nk : npre + l2_ahead;
+        for (int i = npre; i < pf_end; ++i) tma_prefetch_l2_2d(&w_map, (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN);
       }
       griddep_wait();
       B200_STAMP(1);
@@ -1026,8 +1032,9 @@ int launch_decode(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilog
   int rc = plan_decode<KIND, BM, EPI>(c, M, p.n_tiles, p.num_kb, split_k, ep.residual != nullptr);
   if (rc) return rc;
   auto kern = gemm_decode_kernel<KIND, BM, EPI>;
+  static const int l2_ahead = getenv("B200_GEMM_L2_AHEAD") ? atoi(getenv("B200_GEMM_L2_AHEAD")) : 0;  // tuning aid
   B200_CUDA_OK(launch_kernel_cluster(kern, dim3(p.n_tiles * c.S), dim3(GEMM_THREADS), c.smem, c.S, stream, wm, am, ep, M, N,
-                                     p.num_kb, c.nst, c.ring_bytes, g_trace));
+                                     p.num_kb, c.nst, c.ring_bytes, l2_ahead, g_trace));
   return B200_OK;
 }
 

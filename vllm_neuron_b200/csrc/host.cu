@@ -1,9 +1,11 @@
 // Host-side plumbing of libb200_paged.so: error strings, device probe, TMA descriptor encoding.
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <atomic>
 #include <mutex>
+#include <unordered_set>
 
 #include "common.cuh"
 
@@ -99,6 +101,18 @@ int make_tmap_2d_plain(CUtensorMap* out, const void* base, CUtensorMapDataType d
     return B200_ERR_DRIVER;
   }
   return 0;
+}
+
+void unify_carveout(const void* kern) {
+  static const int on = getenv("B200_CARVEOUT") ? atoi(getenv("B200_CARVEOUT")) : 0;
+  if (!on) return;
+  static std::mutex mu;
+  static std::unordered_set<const void*> done;
+  std::lock_guard<std::mutex> g(mu);
+  if (done.insert(kern).second) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaGetLastError();
+  }
 }
 
 int sm_count() {
