@@ -330,7 +330,10 @@ def run_b200(args, shape):
         "peak_source": peak_src, "algorithmic_bytes_per_launch": int(attn_bytes), "mean_us_per_launch": round(attn_ms * 1e3, 2),
         "timing": f"CUDA events around {attn_launches} graph-replayed launches (one per layer's KV pool per replay)",
         "mean_us_per_launch_eager": round(attn_ms_eager * 1e3, 2),
-        "share_of_step": round(shape.layers * attn_ms / ms_per_step, 4),
+        # serialised basis (every kernel timed alone, like the ncu launch list): comparable with profiles/*launches*.csv
+        "share_of_step": round(attn_cnt * attn_ms_eager / p_steps / per_step_ms, 4),
+        # in-graph basis: L launches at the graph-replayed duration over the measured step (PDL overlaps the other kernels)
+        "share_of_step_in_graph": round(shape.layers * attn_ms / ms_per_step, 4),
         "step": {"weights_bytes": int(wbytes), "kv_bytes": int(kvbytes),
                  "min_ms_at_peak": round((wbytes + kvbytes) / hbm_peak / 1e6, 4),
                  "frac_of_step_roofline": round((wbytes + kvbytes) / hbm_peak / 1e6 / ms_per_step, 4)},
