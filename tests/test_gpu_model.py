@@ -13,12 +13,12 @@ from parity_util import device_to_logical_pool, make_vllm_config, sched_output
 pytestmark = pytest.mark.gpu
 
 
-def _run(quant, steps=12, use_graph=True):
+def _run(quant, steps=12, use_graph=True, preset="tiny-test"):
     from vllm_neuron_b200.config import PRESETS
     from vllm_neuron_b200.model import B200CausalLM, random_init_full_weights
     from vllm_neuron_b200.worker.b200_model_runner import B200ModelRunner
 
-    shape = PRESETS["tiny-test"]
+    shape = PRESETS[preset]
     bs, mml, mns, nb = 32, 256, 4, 40
     weights = random_init_full_weights(shape, seed=3, std=0.05)
     override = {} if quant == "bf16" else {"quantized": True, "quantization_dtype": "f8e4m3" if quant == "fp8" else "int8",
@@ -123,9 +123,11 @@ def _rms(x):
     return x.float().pow(2).mean().sqrt().item()
 
 
-@pytest.mark.parametrize("quant", ["bf16", "fp8", "int8", "int8_wo"])
-def test_greedy_tokens_match_oracle(quant):
-    runner, model, ref, outs, ref_outs, margins, live, blocks = _run(quant)
+@pytest.mark.parametrize("quant,preset", [("bf16", "tiny-test"), ("fp8", "tiny-test"), ("int8", "tiny-test"),
+                                          ("int8_wo", "tiny-test"), ("bf16", "tiny-qwen"), ("int8_wo", "tiny-qwen")])
+def test_greedy_tokens_match_oracle(quant, preset):
+    """tiny-qwen = BASELINE config 4's traits at test size: GQA group of 5, qkv bias, INT8 weight-only, ragged vocab."""
+    runner, model, ref, outs, ref_outs, margins, live, blocks = _run(quant, preset=preset)
     keys = sorted(outs)
     flat_got = [t for k in keys for t in outs[k]]
     flat_ref = [t for k in keys for t in ref_outs[k]]

@@ -89,33 +89,74 @@ def bench_gemm(shapes=None, kinds=("fp8", "bf16"), pdl=True, splits=(0,)):
     for kind in kinds:
         for m, n, k in shapes:
             eb = 2 if kind == "bf16" else 1
+            dtc = {"bf16": 0, "fp8": 1, "int8wo": 4}[kind]
             copies = max(2, int(300e6 // (n * k * eb)) + 1)
             if kind == "bf16":
                 ws_ = [torch.randn(n, k, device="cuda", dtype=torch.bfloat16) for _ in range(copies)]
                 a = torch.randn(m, k, device="cuda", dtype=torch.bfloat16)
                 sa = sw = None
+            elif kind == "int8wo":
+                ws_ = [torch.randint(-127, 128, (n, k), device="cuda", dtype=torch.int8) for _ in range(copies)]
+                a = torch.randn(m, k, device="cuda", dtype=torch.bfloat16)
+                sa, sw = None, torch.ones(n, device="cuda")
             else:
                 ws_ = [torch.randn(n, k, device="cuda", dtype=torch.bfloat16).to(torch.float8_e4m3fn) for _ in range(copies)]
                 a = torch.randn(m, k, device="cuda", dtype=torch.bfloat16).to(torch.float8_e4m3fn)
                 sa = torch.ones(m, device="cuda")
                 sw = torch.ones(n, device="cuda")
             out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
-            nbytes = ops.gemm_workspace_bytes(m, n, k, 0 if kind == "bf16" else 1, 0)
+            nbytes = ops.gemm_workspace_bytes(m, n, k, dtc, 0)
             wsp = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device="cuda")  # stream-K counters start at zero
             for sk in splits:
                 try:
-                    plan = ops.gemm_decode_plan(m, n, k, 0 if kind == "bf16" else 1, split_k=sk)
+                    plan = ops.gemm_decode_plan(m, n, k, dtc, split_k=sk)
                 except Exception:
                     continue
                 fns = [(lambda w=w: ops.gemm(a, w, sa, sw, out=out, workspace=wsp, split_k=sk)) for w in ws_]
                 ms = time_calls(fns, iters=5)
-                alg = n * k * eb + n * 4 + m * k * eb + m * 4 + 2 * m * n
+                alg = n * k * eb + n * 4 + m * k * (2 if kind == "int8wo" else eb) + m * 4 + 2 * m * n
                 gbs = alg / ms / 1e6
                 res.append({"kernel": f"gemm_{kind}", "pdl": pdl, "M": m, "N": n, "K": k, "split_k": sk, "us": round(ms * 1e3, 2),
                             "GBps": round(gbs, 1), "frac_hbm": round(gbs / HBM, 4),
                             "TFLOPs": round(2 * m * n * k / ms / 1e9, 1), "plan": plan})
                 print(res[-1], flush=True)
             del ws_
+    return res
+
+
+def bench_configs():
+    """Kernel-level numbers at the PER-GPU shard shapes of BASELINE configs 4 and 5 (one GPU stands in for one TP rank;
+    no collective is timed):
+      cfg5: Llama-3.3-70B FP8, TP=8 -> Hq=8, Hkv=1 per rank, B=64, context 2k..32k (flash-decoding split over the context);
+      cfg4: Qwen2.5-32B INT8 weight-only, TP=8, B=128 -> Hq=5, Hkv=1; linears 5120 x {896, 640->5120, 2x3456, 3456->5120}."""
+    res = []
+    for ctx in (2048, 4096, 8192, 16384, 32768):
+        layers = max(2, min(8, (1 << 30) // (64 * ctx * 2 * 128 * 2)))  # > 4x L2 of distinct KV per round
+        r = bench_attn(b=64, hq=8, hkv=1, d=128, ctx=ctx, layers=layers, quotas=(0,))
+        for x in r:
+            x["config"] = "cfg5 llama-3.3-70b tp8 shard"
+        res += r
+    r = bench_attn(b=128, hq=5, hkv=1, d=128, ctx=2048, layers=8, quotas=(0,))
+    for x in r:
+        x["config"] = "cfg4 qwen2.5-32b tp8 shard"
+    res += r
+    # cfg4 linears, weight-only int8 (bf16 activations), M = 128
+    m = 128
+    for n, k, name in ((896, 5120, "qkv"), (5120, 640, "o"), (6912, 5120, "gate_up"), (5120, 3456, "down"), (19008, 5120, "lm_head")):
+        copies = max(4, int(300e6 // (n * k)) + 1)
+        ws_ = [torch.randint(-127, 128, (n, k), device="cuda", dtype=torch.int8) for _ in range(copies)]
+        a = torch.randn(m, k, device="cuda", dtype=torch.bfloat16)
+        sw = torch.rand(n, device="cuda") * 1e-3
+        out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+        fns = [(lambda w=w: ops.gemm(a, w, None, sw, out=out)) for w in ws_]
+        ms = time_calls(fns, iters=5)
+        alg = n * k + n * 4 + m * k * 2 + 2 * m * n
+        gbs = alg / ms / 1e6
+        res.append({"kernel": "gemm_int8wo", "config": "cfg4 qwen2.5-32b tp8 shard", "linear": name, "M": m, "N": n, "K": k,
+                    "us": round(ms * 1e3, 2), "GBps": round(gbs, 1), "frac_hbm": round(gbs / HBM, 4),
+                    "plan": ops.gemm_decode_plan(m, n, k, 4)})
+        print(res[-1], flush=True)
+        del ws_
     return res
 
 
@@ -132,6 +173,11 @@ if __name__ == "__main__":
         out += bench_gemm()
         out += bench_gemm(kinds=("fp8",), pdl=False)
         ops.set_pdl(True)
+    if a.what == "gemmcmp":
+        out += bench_gemm(shapes=[(64, 4096, 4096), (128, 4096, 4096), (64, 28672, 4096), (128, 28672, 4096), (128, 6912, 5120),
+                                  (128, 5120, 640)], kinds=("fp8", "bf16", "int8wo"))
+    if a.what == "configs":
+        out += bench_configs()
     if a.what == "gemmsweep":
         out += bench_gemm(kinds=("fp8",), splits=(0, 1, 2, 3, 4, 5, 6, 7, 8))
     if a.json:

@@ -82,6 +82,8 @@ PRESETS = {
     "llama-3.3-70b": ModelShape("Llama-3.3-70B", 8192, 80, 64, 8, 128, 28672, 128256, 500000.0, _LLAMA3_SCALING, 1e-5),
     # unit-test size
     "tiny-test": ModelShape("tiny-test", 256, 2, 8, 2, 64, 512, 1024, 10000.0, None, 1e-5),
+    # unit-test size with Qwen2's traits: 5 query heads per kv head, qkv bias, vocab not a multiple of the GEMM tile
+    "tiny-qwen": ModelShape("tiny-qwen", 640, 2, 10, 2, 64, 1152, 1000, 1000000.0, None, 1e-6, True),
 }
 
 

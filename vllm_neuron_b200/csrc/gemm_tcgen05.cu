@@ -73,12 +73,18 @@ __device__ __forceinline__ void widen_w_tile(const uint8_t* __restrict__ raw, ui
     const uint4 v = *reinterpret_cast<const uint4*>(raw + row * 64 + c4 * 16);
     const uint32_t w[4] = {v.x, v.y, v.z, v.w};
     uint32_t o[8];
+    // int8 -> bf16 without the conversion unit: byte b (two's complement) XOR 0x80 = b + 128 as unsigned; dropped into the
+    // low mantissa byte of 2^23 it reads as the float 8388608 + 128 + b; subtracting 8388736 leaves float(b) exactly, and a
+    // value of at most 7 significant bits is its own bf16 truncation, so the high half-words ARE the bf16 codes.
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const int b0 = (int)(int8_t)(w[j] & 0xff), b1 = (int)(int8_t)((w[j] >> 8) & 0xff);
-      const int b2 = (int)(int8_t)((w[j] >> 16) & 0xff), b3 = (int)(int8_t)(w[j] >> 24);
-      o[2 * j] = pack_bf16((float)b0, (float)b1);
-      o[2 * j + 1] = pack_bf16((float)b2, (float)b3);
+      const uint32_t x = w[j] ^ 0x80808080u;
+      const float f0 = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7440)) - 8388736.f;
+      const float f1 = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7441)) - 8388736.f;
+      const float f2 = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7442)) - 8388736.f;
+      const float f3 = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7443)) - 8388736.f;
+      o[2 * j] = __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632);
+      o[2 * j + 1] = __byte_perm(__float_as_uint(f2), __float_as_uint(f3), 0x7632);
     }
     uint8_t* rowp = dst + (row >> 3) * 1024 + (row & 7) * 128;
     *reinterpret_cast<uint4*>(rowp + (((2 * c4) ^ (row & 7)) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
@@ -243,8 +249,8 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? GEMM_THREADS + 128 : GEMM_T
   uint64_t* full = reinterpret_cast<uint64_t*>(raw_ring + (WO ? (size_t)NSTAGES * RAW_TILE : 0));
   uint64_t* empty = full + NSTAGES;
   uint64_t* full_raw = empty + NSTAGES;   // weight-only: raw tile landed
-  uint64_t* empty_raw = full_raw + NSTAGES;  // weight-only: raw tile widened (128 arrivals)
-  uint64_t* full_cvt = empty_raw + NSTAGES;  // weight-only: bf16 operand tile written (128 arrivals)
+  uint64_t* empty_raw = full_raw + NSTAGES;  // weight-only: raw tile widened
+  uint64_t* full_cvt = empty_raw + NSTAGES;  // weight-only: bf16 operand tile written
   uint64_t* tfull = full_cvt + NSTAGES;   // [2] accumulator stage ready for the epilogue
   uint64_t* tempty = tfull + 2;        // [2] accumulator stage drained
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
@@ -264,8 +270,8 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? GEMM_THREADS + 128 : GEMM_T
       mbar_init(&empty[s], 1);
       if (WO) {
         mbar_init(&full_raw[s], 1);
-        mbar_init(&empty_raw[s], 128);
-        mbar_init(&full_cvt[s], 128);
+        mbar_init(&empty_raw[s], 1);
+        mbar_init(&full_cvt[s], 1);
       }
     }
     mbar_init(&tfull[0], 1);
@@ -369,8 +375,11 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? GEMM_THREADS + 128 : GEMM_T
       if (i >= NSTAGES) mbar_wait(&empty[s], ((i / NSTAGES) - 1) & 1);
       widen_w_tile(raw_ring + (size_t)s * RAW_TILE, smem + (size_t)s * STAGE, ct);
       fence_proxy_async();
-      mbar_arrive(&full_cvt[s]);
-      mbar_arrive(&empty_raw[s]);
+      named_bar_sync(2, 128);
+      if (ct == 0) {
+        mbar_arrive(&full_cvt[s]);
+        mbar_arrive(&empty_raw[s]);
+      }
     }
   } else {
     // epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31; lane = weight row of the tile
@@ -474,7 +483,7 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? GEMM_THREADS + 128 : GEMM_T
 constexpr int DEC_MAX_ST = 12;
 
 template <int KIND, int BM, int EPI>
-__global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
+__global__ void __launch_bounds__(GEMM_THREADS, 2)
     gemm_decode_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap a_map,
                        GemmEpilogue ep, int M, int N, int num_kb, int nst, int ring_bytes, int l2_ahead,
                        unsigned long long* __restrict__ trace) {
@@ -523,13 +532,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
     tma_prefetch_desc(&w_map);
     tma_prefetch_desc(&a_map);
     for (int s = 0; s < nst; ++s) {
-      mbar_init(&full_w[s], WO ? 128 : 1);  // weight-only: every widening thread arrives after its writes
+      mbar_init(&full_w[s], 1);  // weight-only: one arrival after all 128 widening threads have fenced and met
       mbar_init(&empty_w[s], 1);
       mbar_init(&full_a[s], 1);
       mbar_init(&empty_a[s], 1);
       if (WO) {
         mbar_init(&full_raw[s], 1);
-        mbar_init(&empty_raw[s], 128);
+        mbar_init(&empty_raw[s], 1);
       }
     }
     mbar_init(tfull, 1);
@@ -686,8 +695,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM <= 64 ? 2 : 1))
         if (i >= nst) mbar_wait(&empty_w[s], ph ^ 1);  // the MMAs that read the previous contents have retired
         widen_w_tile(raw_ring + (size_t)s * RAW_TILE, w_ring + (size_t)s * W_TILE, et);
         fence_proxy_async();  // generic-proxy writes -> visible to the tensor core (async proxy)
-        mbar_arrive(&full_w[s]);
-        mbar_arrive(&empty_raw[s]);
+        named_bar_sync(1, 128);  // all 128 threads have written and fenced: ONE arrival per barrier (128 arrivals on
+        if (et == 0) {           // one shared-memory word serialise and cost more than the widening itself)
+          mbar_arrive(&full_w[s]);
+          mbar_arrive(&empty_raw[s]);
+        }
         if (++s == nst) {
           s = 0;
           ph ^= 1;
@@ -963,9 +975,13 @@ int plan_decode(DecodeCfg& best, int M, int n_tiles, int num_kb, int split_k, bo
   }
   static const int force_occ = getenv("B200_GEMM_FORCE_OCC") ? atoi(getenv("B200_GEMM_FORCE_OCC")) : 0;  // tuning aid
   const int sms = sm_count();
-  const size_t budget = (BM <= 64 && force_occ != 1) ? SMEM_TWO_PER_SM : SMEM_ONE_PER_SM;
-  const int per_sm = budget == SMEM_TWO_PER_SM ? 2 : 1;
   bool found = false;
+  // two CTAs per SM (half the shared memory each) or one with all of it: M <= 64 always fits two; M = 65..128 (32 KB
+  // activation + weight per stage, 64 KB of split-K partials) is tried both ways and the cost model decides
+  for (int per_sm = 2; per_sm >= 1; --per_sm) {
+  if (per_sm == 2 && force_occ == 1) continue;
+  if (per_sm == 1 && BM <= 64 && force_occ != 1) continue;
+  const size_t budget = per_sm == 2 ? SMEM_TWO_PER_SM : SMEM_ONE_PER_SM;
   for (int S = 1; S <= 8; ++S) {
     if (split_k != 0 && S != split_k) continue;
     if (S > num_kb) break;
@@ -1000,7 +1016,10 @@ int plan_decode(DecodeCfg& best, int M, int n_tiles, int num_kb, int split_k, bo
     const int sm_used = ctas < sms ? ctas : sms;
     int on_busiest = (ctas + sm_used - 1) / sm_used;
     const int resident = on_busiest < per_sm ? on_busiest : per_sm;
-    const double rate_sm = resident * c.nst * stage_bytes / 1.55;  // bytes per us
+    // ... and one CTA never ingests more than ~52 KB/us however deep its ring is (measured at M = 128, one CTA per SM,
+    // 7 stages: 0.55 us per 32 KB stage; two co-resident CTAs reach ~94 KB/us together)
+    double rate_sm = resident * c.nst * stage_bytes / 1.55;  // bytes per us
+    if (rate_sm > resident * 52e3) rate_sm = resident * 52e3;
     const double t_sm = on_busiest * nk * stage_bytes / rate_sm;
     const double t_chip = (double)n_tiles * num_kb * stage_bytes / 9.5e6;
     const double t_hbm = (double)n_tiles * num_kb * (KIND == KIND_WO8 ? RAW_TILE : W_TILE_BYTES) / 6.2e6;
@@ -1015,6 +1034,7 @@ int plan_decode(DecodeCfg& best, int M, int n_tiles, int num_kb, int split_k, bo
       best = c;
       found = true;
     }
+  }
   }
   if (!found) {
     set_last_error("gemm: no decode configuration fits (n_tiles %d, k-blocks %d, split_k %d)", n_tiles, num_kb, split_k);
