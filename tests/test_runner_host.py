@@ -26,6 +26,7 @@ def test_new_request_takes_lowest_free_row_and_mirrors_blocks():
 def test_cached_request_block_append_and_resume_replace():
     r = _runner()
     r._update_states(sched_output(new_reqs=[("a", list(range(40)), [7, 3], 0)]))
+    r.requests["a"].prefilled = 40                                                  # what execute_model's prefill leaves
     r.requests["a"].output_token_ids.append(11)
     upd = r._update_states(sched_output(cached=[("a", [5])]))
     assert r.requests["a"].block_ids == [7, 3, 5] and upd == [(0, 2, 5)]          # RUNNER:461-466
