@@ -85,3 +85,40 @@ def sched_output(new_reqs=(), cached=(), finished=()):
         total_num_scheduled_tokens=sum(num_sched.values()), finished_req_ids=set(finished),
         scheduled_spec_decode_tokens={}, free_encoder_mm_hashes=[],
     )
+
+
+def export_hf_checkpoint(full_weights, shape, out_dir, *, shards=2, lm_head=True):
+    """Write the B200 weight dictionary (model.random_init_full_weights layout) as an HF Llama/Qwen2 safetensors
+    checkpoint: separate q/k/v and gate/up tensors under the HF names, split over `shards` files + index json."""
+    import json
+    import os
+
+    from safetensors.torch import save_file
+
+    qd, kd, I = shape.num_q_heads * shape.head_dim, shape.num_kv_heads * shape.head_dim, shape.intermediate
+    sd = {"model.embed_tokens.weight": full_weights["embed"], "model.norm.weight": full_weights["final_norm"]}
+    if lm_head:
+        sd["lm_head.weight"] = full_weights["lm_head"]
+    for li in range(shape.layers):
+        lw, p = full_weights["layers"][li], f"model.layers.{li}."
+        q, k, v = lw["wqkv"].split([qd, kd, kd])
+        g, u = lw["wgu"].split([I, I])
+        sd.update({p + "self_attn.q_proj.weight": q, p + "self_attn.k_proj.weight": k, p + "self_attn.v_proj.weight": v,
+                   p + "self_attn.o_proj.weight": lw["wo"], p + "mlp.gate_proj.weight": g, p + "mlp.up_proj.weight": u,
+                   p + "mlp.down_proj.weight": lw["wdown"], p + "input_layernorm.weight": lw["input_norm"],
+                   p + "post_attention_layernorm.weight": lw["post_norm"]})
+        if "bqkv" in lw:
+            bq, bk, bv = lw["bqkv"].split([qd, kd, kd])
+            sd.update({p + "self_attn.q_proj.bias": bq, p + "self_attn.k_proj.bias": bk, p + "self_attn.v_proj.bias": bv})
+    os.makedirs(out_dir, exist_ok=True)
+    names = sorted(sd)
+    weight_map = {}
+    for s in range(shards):
+        fn = f"model-{s + 1:05d}-of-{shards:05d}.safetensors"
+        part = {n: sd[n].contiguous().clone() for n in names[s::shards]}
+        save_file(part, os.path.join(out_dir, fn))
+        weight_map.update({n: fn for n in part})
+    if shards > 1:
+        with open(os.path.join(out_dir, "model.safetensors.index.json"), "w") as f:
+            json.dump({"metadata": {}, "weight_map": weight_map}, f)
+    return out_dir

@@ -297,3 +297,55 @@ def test_chunked_prefill_matches_whole_prompt_prefill():
     r2.requests["p"].output_token_ids[:] = r1.requests["p"].output_token_ids[:1]
     d2 = r2.execute_model(sched_output(cached=[("p", None)]))
     assert len(d1.sampled_token_ids[0]) == 1 and len(d2.sampled_token_ids[0]) == 1
+
+
+@pytest.mark.parametrize("quant_override", [
+    {},
+    {"quantized": True, "quantization_dtype": "f8e4m3", "quantization_type": "per_channel_symmetric"},
+    {"quantized": True, "quantization_dtype": "int8", "quantization_type": "per_channel_symmetric", "weight_only": True,
+     "modules_to_not_convert": ["lm_head"]},
+])
+def test_checkpoint_load_matches_in_memory_weights(tmp_path, quant_override):
+    """load_model from an HF safetensors directory (and, when quantised, through the quantise-once
+    `quantized_checkpoints_path` round trip, LOADER:237-239) must give the SAME device weights as the in-memory
+    dictionary: prefill + decode logits bit-identical."""
+    from parity_util import export_hf_checkpoint
+    from vllm_neuron_b200.config import PRESETS
+    from vllm_neuron_b200.model import B200CausalLM, random_init_full_weights
+    from vllm_neuron_b200.worker.b200_model_runner import B200ModelRunner
+
+    shape = PRESETS["tiny-qwen"]
+    weights = random_init_full_weights(shape, seed=9, std=0.05)
+    hf = export_hf_checkpoint(weights, shape, str(tmp_path / "hf"))
+    override = dict(quant_override)
+    if override:
+        override["quantized_checkpoints_path"] = str(tmp_path / "q")
+    prompt = torch.randint(0, shape.vocab, (45,), generator=torch.Generator().manual_seed(2)).tolist()
+
+    def run(from_checkpoint):
+        cfg = make_vllm_config(shape, max_num_seqs=2, max_model_len=128, num_gpu_blocks_override=9, override=override)
+        cfg.model_config.hf_config.architectures = ["Qwen2ForCausalLM"]
+        model = None
+        if from_checkpoint:
+            cfg.model_config.model = hf
+            cfg.load_config.load_format = "auto"
+        r = B200ModelRunner(cfg, torch.device("cuda"), model=model)
+        r.load_model()
+        if not from_checkpoint:
+            r.model = B200CausalLM(shape, weights, quant=r.b200_config.quant_mode, quant_lm_head=r._quant_lm_head,
+                                   num_blocks=9, max_num_seqs=2, max_model_len=128)
+        r.initialize_kv_cache(num_blocks=9)
+        o1 = r.execute_model(sched_output(new_reqs=[("p", prompt, [4, 6], 0)]))
+        l1 = r.model.last_logits.float().cpu().clone()
+        o2 = r.execute_model(sched_output(cached=[("p", None)]))
+        l2 = r.model.last_logits.float().cpu().clone()
+        return o1.sampled_token_ids, o2.sampled_token_ids, l1, l2
+
+    a, b = run(False), run(True)
+    if override:  # second start reads the saved quantised state dict back
+        import os
+
+        assert os.path.exists(os.path.join(override["quantized_checkpoints_path"], "model.safetensors.index.json"))
+        b = run(True)
+    assert a[0] == b[0] and a[1] == b[1]
+    assert torch.equal(a[2], b[2]) and torch.equal(a[3], b[3])

@@ -104,6 +104,7 @@ class B200Config:
     quantization_dtype: str = "int8"     # "int8" | "f8e4m3"
     weight_only: bool = False
     modules_to_not_convert: tuple = ()
+    quantized_checkpoints_path: str | None = None   # LOADER:890-891: where the once-quantised state dict lives
     ignored: dict = field(default_factory=dict)
 
     @property
@@ -186,10 +187,10 @@ def build_config(*, tensor_parallel_size: int, max_num_seqs: int, max_model_len:
     if "quantized" in merged:  # LOADER:885-898
         cfg.update(
             quantized=merged.pop("quantized", False),
+            quantized_checkpoints_path=merged.pop("quantized_checkpoints_path", None),
             quantization_type=merged.pop("quantization_type", "per_tensor_symmetric"),
             quantization_dtype=merged.pop("quantization_dtype", "int8"),
         )
-        merged.pop("quantized_checkpoints_path", None)
     cfg.update(merged)
     cfg = handle_pa_num_blocks(num_gpu_blocks_override, cfg, override)
     cfg = validate_config(enable_prefix_caching, max_model_len, block_size, max_num_seqs, num_gpu_blocks_override, cfg)

@@ -109,7 +109,13 @@ class _Linear:
 
     def __init__(self, w_full: torch.Tensor, quant: str, device, row_slices=None, col_slice=None, bias=None):
         # quantise the FULL weight first (per-channel scales are properties of the un-sharded matrix), then shard
-        if quant in ("fp8", "int8", "int8_wo"):
+        if isinstance(w_full, tuple):  # (q, scale) from a quantised checkpoint (loader.py): not quantised again
+            wq, ws = w_full
+            want = {"fp8": torch.float8_e4m3fn, "int8": torch.int8, "int8_wo": torch.int8}.get(quant)
+            if wq.dtype != want:
+                raise ValueError(f"quantised checkpoint holds {wq.dtype} weights but the configured mode is {quant!r}")
+            wq, ws = wq.to(device), ws.float().to(device)
+        elif quant in ("fp8", "int8", "int8_wo"):
             wq, ws = quantize_weight(w_full, "fp8" if quant == "fp8" else "int8")  # on the master weight's device
             wq, ws = wq.to(device), ws.to(device)
         else:
@@ -191,7 +197,7 @@ class B200CausalLM:
                     "down": _Linear(lw["wdown"], quant, dev, col_slice=plan["down_cols"]),
                 }
             )
-            if isinstance(full_weights, _LazyRandomWeights):
+            if hasattr(full_weights, "drop"):  # lazy sources (random init, checkpoint reader) free the layer's host copy
                 full_weights.drop(li)
         self.cos, self.sin = rope_tables(self.d, max_model_len, shape.rope_theta, shape.rope_scaling, dev)
         # ---- KV pools: per layer [2(K,V)][num_blocks][Hkv_local][bs][D] bf16; block 0 is vLLM's null block

@@ -116,9 +116,32 @@ class B200ModelRunner:
         self.is_block_kv_layout = cfg.is_block_kv_layout
         self.is_prefix_caching = cfg.is_prefix_caching
         self._load_dummy = True if load_dummy_weights else getattr(self.vllm_config.load_config, "load_format", "dummy") == "dummy"
-        if not self._load_dummy:
-            raise NotImplementedError(
-                "checkpoint loading is not built yet (SURVEY 8(f)-4); run with load_format='dummy' (random-init weights)")
+        from ..loader import check_modules_to_not_convert
+
+        self._quant_lm_head = check_modules_to_not_convert(cfg.modules_to_not_convert, self.shape)
+        self._weights = None if self._load_dummy else self._open_checkpoint(cfg)
+
+    def _open_checkpoint(self, cfg: B200Config):
+        """HF checkpoint directory -> lazy weight source (loader.py).  With `quantized` + `quantized_checkpoints_path`
+        the weights are quantised once, saved there and read back from there on later starts (LOADER:237-239)."""
+        import os
+
+        from ..loader import HFCheckpointWeights, save_quantized_checkpoint
+
+        path = self.model_config.model
+        tie = bool(getattr(self.model_config.hf_config, "tie_word_embeddings", False))
+        qpath = cfg.quantized_checkpoints_path if cfg.quantized else None
+        if qpath:
+            if not os.path.exists(os.path.join(qpath, "model.safetensors.index.json")):
+                if self.tp_rank == 0:
+                    kind = "fp8" if cfg.quant_mode == "fp8" else "int8"
+                    logger.info("quantising %s (%s, per channel) into %s", path, kind, qpath)
+                    save_quantized_checkpoint(HFCheckpointWeights(path, self.shape, tie_word_embeddings=tie), qpath, kind,
+                                              cfg.modules_to_not_convert)
+                if self.tp_group is not None:
+                    torch.distributed.barrier(group=self.tp_group)
+            path = qpath
+        return HFCheckpointWeights(path, self.shape, tie_word_embeddings=tie)
 
     def weight_bytes_estimate(self) -> int:
         """Per-rank bytes of the weights that initialize_kv_cache will materialise (used to size the KV budget)."""
@@ -157,7 +180,8 @@ class B200ModelRunner:
         self.num_blocks = int(num_blocks)
         if self.model is None:
             self.model = B200CausalLM(
-                self.shape, None, quant=self.b200_config.quant_mode, num_blocks=self.num_blocks,
+                self.shape, self._weights, quant=self.b200_config.quant_mode, quant_lm_head=self._quant_lm_head,
+                num_blocks=self.num_blocks,
                 max_num_seqs=self.max_num_reqs, max_model_len=self.max_model_len, block_size=self.block_size,
                 device=self.device, tp_rank=self.tp_rank, tp_size=self.tp_size, tp_group=self.tp_group,
                 seed=getattr(self.model_config, "seed", 0) or 0,
