@@ -1,0 +1,83 @@
+"""End to end through the real vLLM engine: `vllm.LLM(...)` discovers the plugin through the `vllm.platform_plugins`
+entry point, B200Platform rewrites the config (null block +1, worker, scheduler), the continuous-batching scheduler feeds
+B200Worker.execute_model, weights come from an HF safetensors checkpoint -- and the greedy tokens vLLM hands back must be
+the CPU oracle's (teacher-forced with the engine's own tokens, so one near-tie cannot cascade).
+
+This is the reference's offline integration test (test/e2e/offline/offline_integration_test.py:145-155, greedy text on
+Neuron hardware) restated with seeded random weights and the oracle as the judge."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _engine(tmp_path, quant):
+    out = tmp_path / "engine.json"
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "vllm_engine_e2e.py"), "--out", str(out), "--quant", quant,
+                        "--model-dir", str(tmp_path / "model")], cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
+    assert p.returncode == 0, "vLLM engine run failed:\n" + p.stdout[-3000:] + "\n" + p.stderr[-6000:]
+    return json.loads(out.read_text())
+
+
+def _oracle_check(res, quant, band):
+    from oracle import index_ref, llama_ref
+    from vllm_neuron_b200.config import PRESETS
+    from vllm_neuron_b200.model import random_init_full_weights
+
+    shape, bs, mml = PRESETS[res["preset"]], res["block_size"], res["max_model_len"]
+    weights = random_init_full_weights(shape, seed=res["seed"], std=res["std"])
+    nb = 1 + sum(-(-(len(p) + len(res["outputs"][k])) // bs) for k, p in res["prompts"].items())
+    ref = llama_ref.RefLlama(
+        llama_ref.RefConfig(shape.hidden, shape.layers, shape.num_q_heads, shape.num_kv_heads, shape.head_dim,
+                            shape.intermediate, shape.vocab, shape.rope_theta, shape.rope_scaling, shape.rms_eps,
+                            shape.qkv_bias, quant, mml, bs), weights, nb)
+    nxt, checked, near_ties, bad = 1, 0, 0, []
+    for k, prompt in res["prompts"].items():
+        got = res["outputs"][k]
+        blocks = list(range(nxt, nxt + -(-(len(prompt) + len(got)) // bs)))
+        nxt += len(blocks)
+        row = index_ref.prefill_index(len(prompt), blocks, 0, bs, mml)
+        _, logits = ref.prefill(torch.tensor(prompt), torch.tensor(row["block_table"]), torch.tensor(row["slot_mapping"]), 0)
+        for i, tok in enumerate(got):
+            lg = logits.float().reshape(-1, shape.vocab)[-1]
+            top2 = lg.topk(2)
+            margin, std = (top2.values[0] - top2.values[1]).item(), lg.std().item()
+            if int(top2.indices[0]) == tok:
+                checked += 1
+            elif lg[tok].item() >= top2.values[0].item() - band * std:
+                near_ties += 1  # the engine picked a token whose oracle logit is inside the error band of the maximum
+            else:
+                bad.append((k, i, tok, int(top2.indices[0]), margin / std))
+            if i + 1 == len(got):
+                break
+            d = index_ref.decode_index(len(prompt), i + 1, blocks, bs, mml)  # feed the ENGINE's token
+            _, logits = ref.decode(torch.tensor([tok]), torch.tensor(d["position_ids"]), torch.tensor(d["slot_mapping"]),
+                                   torch.tensor([d["block_table"]]), torch.tensor([d["full_context_len"]]))
+    return checked, near_ties, bad
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("quant,band", [("bf16", 0.05), ("fp8", 0.6)])
+def test_vllm_engine_greedy_tokens_match_oracle(tmp_path, quant, band):
+    """band: bf16 = the 5 % of the logit spread bar of test_gpu_model (max logit error); fp8 W8A8 = 6 x the measured
+    quantisation-noise rms (~0.1 of the spread, test_gpu_model) -- the same margin guard as the model parity test."""
+    res = _engine(tmp_path, quant)
+    assert res["platform"].endswith("B200Platform"), res["platform"]
+    assert res["gpu_launches"] > 0
+    want_len = {k: 8 if k == "b" else 24 for k in res["prompts"]}
+    assert {k: len(v) for k, v in res["outputs"].items()} == want_len
+    assert all(v == "length" for v in res["finish_reason"].values())
+    checked, near_ties, bad = _oracle_check(res, quant, band)
+    total = sum(want_len.values())
+    print(f"[{quant}] engine tokens: {checked} equal to the oracle's argmax, {near_ties} inside the error band, {len(bad)} outside")
+    assert not bad, bad
+    assert checked >= (0.9 if quant == "bf16" else 0.7) * total
+    # "d" repeats a's first 64 tokens: vLLM's prefix cache must have served two full blocks
+    nc = res["num_cached_tokens"].get("d")
+    assert nc is None or nc >= 64, res["num_cached_tokens"]

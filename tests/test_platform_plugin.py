@@ -119,3 +119,27 @@ def test_worker_surface():
               "take_draft_token_ids", "add_lora", "remove_lora", "pin_lora", "list_loras", "profile", "sample_tokens",
               "get_cache_block_size_bytes", "shutdown"):
         assert callable(getattr(B200Worker, m)), m
+
+
+def test_async_scheduling_is_switched_off(platform, monkeypatch):
+    """vLLM 0.22 enables async scheduling by default (two batches in flight, tokens taken from sample_tokens); the
+    prefill-or-decode policy is synchronous like the reference's (PLAT:119-121), so the platform turns it off."""
+    monkeypatch.delenv("DISABLE_NEURON_CUSTOM_SCHEDULER", raising=False)
+    monkeypatch.delenv("DISABLE_B200_CUSTOM_SCHEDULER", raising=False)
+    cfg = _cfg()
+    cfg.scheduler_config.async_scheduling = True
+    platform.check_and_update_config(cfg)
+    assert cfg.scheduler_config.async_scheduling is False
+
+
+def test_worker_hands_the_step_output_to_sample_tokens():
+    """Batch-queue engine loops read the ModelRunnerOutput from sample_tokens(), the plain loop from execute_model()."""
+    from vllm_neuron_b200.worker.b200_worker import B200Worker
+
+    w = B200Worker.__new__(B200Worker)
+    w.is_driver_worker = True
+    w.model_runner = SimpleNamespace(execute_model=lambda so: ("out", so))
+    assert w.execute_model("s1") == ("out", "s1")
+    assert w.sample_tokens(None) == ("out", "s1") and w.sample_tokens(None) is None
+    w.is_driver_worker = False
+    assert w.execute_model("s2") is None and w.sample_tokens(None) is None  # WORKER:65-69

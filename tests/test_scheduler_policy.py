@@ -37,3 +37,22 @@ def test_stop_rules():
     assert _stop(num_output_tokens=16, min_tokens=32) == "length"
     assert _stop(num_tokens=2048) == "length"
     assert _stop(pooling=True) is None and _stop(pooling=True, has_pooler_output=True) == "stop"
+
+
+def test_stop_check_on_a_real_vllm_request():
+    """The installed vLLM (0.2x) keeps the EOS id on SamplingParams, 0.11 kept it on the Request (SCHED:149): the
+    wrapper must work on the real object.  min_tokens holds a stop token back; the cap still wins."""
+    from vllm import SamplingParams
+    from vllm.v1.request import Request, RequestStatus
+
+    from vllm_neuron_b200.core.scheduler import check_stop_with_min_tokens
+
+    sp = SamplingParams(temperature=0, max_tokens=3, min_tokens=2, stop_token_ids=[7])
+    r = Request(request_id="x", prompt_token_ids=[1, 2, 3], sampling_params=sp, pooling_params=None)
+    r.append_output_token_ids(7)
+    assert check_stop_with_min_tokens(r, 100) is False
+    r.append_output_token_ids(7)
+    assert check_stop_with_min_tokens(r, 100) is True and r.status == RequestStatus.FINISHED_STOPPED and r.stop_reason == 7
+    r2 = Request(request_id="y", prompt_token_ids=[1, 2, 3], sampling_params=SamplingParams(max_tokens=50), pooling_params=None)
+    r2.append_output_token_ids(5)
+    assert check_stop_with_min_tokens(r2, 4) is True and r2.status == RequestStatus.FINISHED_LENGTH_CAPPED

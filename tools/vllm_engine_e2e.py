@@ -1,0 +1,113 @@
+"""Drive the REAL vLLM engine (vllm.LLM) through the plugin: entry-point discovery -> B200Platform ->
+ContinuousBatchingB200Scheduler -> B200Worker -> B200ModelRunner.execute_model -> libb200_paged.so, loading an HF
+safetensors checkpoint written here from seeded random weights.  Prints / writes one JSON object with the prompts and
+the greedy tokens vLLM returned; tests/test_gpu_vllm_engine.py checks them against the CPU oracle.
+
+usage: python tools/vllm_engine_e2e.py [--out FILE] [--quant bf16|fp8|int8|int8_wo] [--preset tiny-test] [--max-tokens 24]
+(the reference's equivalent: examples/offline_inference + test/e2e/offline/offline_integration_test.py:145-155)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def ensure_entry_point() -> None:
+    """vLLM finds platform plugins through importlib.metadata; without a pip install the in-tree egg-info (made by
+    `setup.py egg_info`, git-ignored) on sys.path provides the `vllm.platform_plugins` entry."""
+    if not os.path.exists(os.path.join(ROOT, "vllm_neuron_b200.egg-info", "entry_points.txt")):
+        subprocess.check_call([sys.executable, "setup.py", "-q", "egg_info"], cwd=ROOT)
+
+
+def write_model_dir(shape, path: str, seed: int, std: float) -> str:
+    from parity_util import export_hf_checkpoint
+    from vllm_neuron_b200.model import random_init_full_weights
+
+    export_hf_checkpoint(random_init_full_weights(shape, seed=seed, std=std), shape, path, shards=2)
+    arch = "Qwen2ForCausalLM" if shape.qkv_bias else "LlamaForCausalLM"
+    cfg = {"architectures": [arch], "model_type": "qwen2" if shape.qkv_bias else "llama", "hidden_size": shape.hidden,
+           "num_hidden_layers": shape.layers, "num_attention_heads": shape.num_q_heads,
+           "num_key_value_heads": shape.num_kv_heads, "head_dim": shape.head_dim, "intermediate_size": shape.intermediate,
+           "vocab_size": shape.vocab, "rope_theta": shape.rope_theta, "rms_norm_eps": shape.rms_eps,
+           "max_position_embeddings": 4096, "torch_dtype": "bfloat16", "tie_word_embeddings": False, "hidden_act": "silu",
+           "bos_token_id": 1, "eos_token_id": 2}
+    with open(os.path.join(path, "config.json"), "w") as f:
+        json.dump(cfg, f)
+    return path
+
+
+def make_prompts(vocab: int):
+    import torch
+
+    g = torch.Generator().manual_seed(77)
+    r = lambda n: torch.randint(3, vocab, (n,), generator=g).tolist()  # noqa: E731  (3..: never the eos id)
+    a = r(70)
+    # five requests for four batch lines: "e" waits in the scheduler; "d" shares two full blocks with "a" (prefix cache)
+    return {"a": a, "b": r(33), "c": r(5), "d": a[:64] + r(9), "e": r(40)}
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default=None)
+    ap.add_argument("--quant", default="bf16", choices=["bf16", "fp8", "int8", "int8_wo"])
+    ap.add_argument("--preset", default="tiny-test")
+    ap.add_argument("--max-tokens", type=int, default=24)
+    ap.add_argument("--seed", type=int, default=3)
+    ap.add_argument("--std", type=float, default=0.05)
+    ap.add_argument("--model-dir", default=None)
+    args = ap.parse_args()
+
+    os.environ.setdefault("VLLM_ENABLE_V1_MULTIPROCESSING", "0")  # engine core in-process: one traceback, one GPU context
+    os.environ.setdefault("VLLM_PLUGINS", "b200")
+    ensure_entry_point()
+    from vllm_neuron_b200.config import PRESETS
+
+    shape = PRESETS[args.preset]
+    mdir = write_model_dir(shape, args.model_dir or tempfile.mkdtemp(prefix="b200_e2e_"), args.seed, args.std)
+    override = {}
+    if args.quant != "bf16":
+        override = {"quantized": True, "quantization_type": "per_channel_symmetric",
+                    "quantization_dtype": "f8e4m3" if args.quant == "fp8" else "int8"}
+        if args.quant == "int8_wo":
+            override["weight_only"] = True
+
+    from vllm import LLM, SamplingParams
+    from vllm.platforms import current_platform
+
+    llm = LLM(model=mdir, skip_tokenizer_init=True, dtype="bfloat16", max_model_len=256, max_num_seqs=4, block_size=32,
+              enable_prefix_caching=True, num_gpu_blocks_override=48,
+              additional_config={"override_neuron_config": override})
+    prompts = make_prompts(shape.vocab)
+    sps = {k: SamplingParams(temperature=0.0, max_tokens=8 if k == "b" else args.max_tokens, ignore_eos=True,
+                             detokenize=False) for k in prompts}
+    keys = list(prompts)
+    outs = llm.generate([{"prompt_token_ids": prompts[k]} for k in keys], [sps[k] for k in keys], use_tqdm=False)
+    from vllm_neuron_b200 import ops
+
+    res = {
+        "platform": type(current_platform).__module__ + "." + type(current_platform).__name__,
+        "quant": args.quant, "preset": args.preset, "seed": args.seed, "std": args.std, "block_size": 32,
+        "max_model_len": 256, "prompts": prompts,
+        "outputs": {k: list(o.outputs[0].token_ids) for k, o in zip(keys, outs)},
+        "num_cached_tokens": {k: getattr(o, "num_cached_tokens", None) for k, o in zip(keys, outs)},
+        "finish_reason": {k: o.outputs[0].finish_reason for k, o in zip(keys, outs)},
+        "gpu_launches": ops.launch_count(),
+    }
+    line = json.dumps(res)
+    if args.out:
+        with open(args.out, "w") as f:
+            f.write(line)
+    print(line)
+
+
+if __name__ == "__main__":
+    main()

@@ -63,11 +63,13 @@ def check_stop_with_min_tokens(request, max_model_len: int, pooler_output=None) 
     sp = request.sampling_params
     if not request.pooling_params:
         assert sp is not None
+    # vLLM 0.11 keeps the EOS id on the Request (SCHED:149), 0.2x on its SamplingParams (None when ignore_eos)
+    eos = request.eos_token_id if hasattr(request, "eos_token_id") else getattr(sp, "eos_token_id", None)
     r = stop_reason(
         num_tokens=request.num_tokens, num_output_tokens=request.num_output_tokens, max_tokens=request.max_tokens,
         max_model_len=max_model_len, min_tokens=getattr(sp, "min_tokens", 0) if sp else 0,
         last_token_id=request.output_token_ids[-1] if request.output_token_ids else -1,
-        eos_token_id=request.eos_token_id, ignore_eos=getattr(sp, "ignore_eos", False) if sp else False,
+        eos_token_id=eos, ignore_eos=getattr(sp, "ignore_eos", False) if sp else False,
         stop_token_ids=getattr(sp, "stop_token_ids", ()) if sp else (), pooling=bool(request.pooling_params),
         has_pooler_output=pooler_output is not None)
     if r is None:

@@ -90,6 +90,11 @@ class B200Platform(Platform):
             except Exception:  # read-only in some vLLM versions
                 sched_cfg.enable_chunked_prefill = False
             sched_cfg.max_num_batched_tokens = DEFAULT_MAX_NUM_BATCHED_TOKENS
+            if getattr(sched_cfg, "async_scheduling", False):
+                # vLLM >= 0.2x turns async scheduling on by default; the prefill-or-decode policy needs each step's
+                # tokens and finishes before the next schedule() (the reference is synchronous too, PLAT:119-121)
+                logger.info("Disabling async scheduling: the continuous-batching scheduler is synchronous")
+                sched_cfg.async_scheduling = False
             if not sched_cfg.max_num_seqs:
                 sched_cfg.max_num_seqs = DEFAULT_MAX_NUM_SEQS
             if not cache_config.enable_prefix_caching:

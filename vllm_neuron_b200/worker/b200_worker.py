@@ -103,15 +103,29 @@ class B200Worker(WorkerBase):
     def compile_or_warm_up_model(self):
         """Captures the decode CUDA graph for the full batch so the first request does not pay for it."""
         self.model_runner.warm_up()
-        return None
+        try:  # vLLM >= 0.2x: the executor takes max() over the workers' CompilationTimes
+            from vllm.v1.worker.worker_base import CompilationTimes
+
+            return CompilationTimes(language_model=0.0, encoder=0.0)
+        except ImportError:
+            return None
+
+    def update_max_model_len(self, max_model_len: int) -> None:
+        self.model_config.max_model_len = max_model_len
+        if self.model_runner is not None:
+            self.model_runner.max_model_len = max_model_len
 
     # ------------------------------------------------------------------ the step
     def execute_model(self, scheduler_output):
         output = self.model_runner.execute_model(scheduler_output)
-        return output if self.is_driver_worker else None  # WORKER:65-69
+        self._last_output = output if self.is_driver_worker else None
+        return self._last_output  # WORKER:65-69
 
     def sample_tokens(self, grammar_output=None):
-        return None  # sampling happens inside execute_model (on-device greedy)
+        """Sampling already happened on the device inside execute_model.  vLLM's batch-queue engine loop ignores
+        execute_model's return value and takes the step's ModelRunnerOutput from here instead."""
+        out, self._last_output = getattr(self, "_last_output", None), None
+        return out
 
     def take_draft_token_ids(self):
         return None
