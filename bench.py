@@ -458,6 +458,7 @@ def run_e2e(args, shape, model, bt_host, dev, rank, world, group, barrier, n_sta
 
 
 def main():
+    os.environ.setdefault("VLLM_LOGGING_LEVEL", "ERROR")  # stdout carries ONE JSON line: no plugin-loader chatter
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=64)

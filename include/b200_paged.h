@@ -125,7 +125,9 @@ int b200_paged_attn_prefill(const void* q, int64_t q_token_stride, const void* k
  *   its first use and is left zeroed by every call; one workspace may serve all GEMMs issued on one stream. */
 size_t b200_gemm_workspace_bytes(int M, int N, int K, int ab_dtype, int split_k);
 /* The decode schedule (M <= 128) chosen on the current device for a shape: out6 = {cluster size S, CTAs per SM, weight
- * ring depth, activation ring depth, CTAs the chip holds at once, dynamic shared memory bytes}.  Needs a device. */
+ * ring depth, activation ring depth, CTAs the chip holds at once, dynamic shared memory bytes}.  Needs a device.
+ * silu_mul selects the epilogue variant planned for: 0 linear, 1 SiLU*mul (b200_gemm_silu_mul), 2 RoPE + KV write
+ * (b200_gemm_rope_kv_write). */
 int b200_gemm_decode_plan(int M, int N, int K, int ab_dtype, int split_k, int silu_mul, int has_residual, int* out6);
 /* Profiling aid: with a non-NULL device buffer ([#CTAs][8] uint64) every decode-schedule GEMM CTA records %globaltimer
  * at its phase boundaries (tools/gemm_trace.py); NULL (default) switches it off. */
@@ -148,6 +150,17 @@ int b200_gemm_int8_wo(const void* a_bf16, const void* w_int8, void* out, const f
 int b200_gemm_silu_mul(const void* a, const void* w_gu, void* out_act, const float* a_scale, const float* w_scale,
                        const void* bias, float* group_amax, int M, int N2, int K, int ab_dtype, int split_k,
                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* qkv projection with RoPE and the KV-cache write fused into its epilogue: b200_gemm (bf16 out, no residual) followed by
+ * b200_rope_kv_write on its output, in ONE launch when the decode schedule splits K over a cluster (the token's owner
+ * holds whole heads; rotate-half partner = lane ^ D/8), else as the two launches.  Same bits either way: qkv_out keeps
+ * rotated q, un-rotated k and v; rotated k and v land in the pools at slot_mapping[t] (slot < 0 skipped).
+ * Replaces the qkv linear + rotary + KV scatter inside NxDI's decoder layer (model_loader.py:336-348). */
+int b200_gemm_rope_kv_write(const void* a, const void* w, void* qkv_out, const float* a_scale, const float* w_scale,
+                            const void* bias, int M, int N, int K, int ab_dtype, int split_k, void* workspace,
+                            size_t workspace_bytes, const int64_t* positions, const float* cos_table,
+                            const float* sin_table, int max_pos, void* k_pool, void* v_pool, const int64_t* slot_mapping,
+                            int Hq, int Hkv, int D, int block_size, int num_blocks, void* stream);
 
 /* ---------------------------------------------------------------- glue kernels of the decoder step */
 /* y = x * rsqrt(mean(x^2)+eps) * w (fp32 math).  Writes any of: out_bf16 [T][H]; out_q [T][H] (q_dtype FP8/INT8)

@@ -205,3 +205,53 @@ def test_gemm_silu_mul_matches_unfused(ops, kind, m, i, k, ctas):
         qw, sw = quant_ref.quantize_act_per_token(act.cpu(), qk)
         assert torch.equal(s1.cpu(), sw)
         assert torch.equal(q1.cpu().view(torch.uint8), qw.view(torch.uint8))
+
+
+@pytest.mark.parametrize("kind", ["bf16", "fp8", "int8_wo"])
+@pytest.mark.parametrize("m,hq,hkv,d,k,split", [
+    (64, 32, 8, 128, 4096, 0),   # cfg3 qkv: auto split (cluster of 5) -> fused epilogue
+    (64, 4, 1, 128, 4096, 0),    # cfg3 TP=8 shard
+    (37, 8, 2, 64, 256, 2),      # D=64: two heads per 128-row tile, q/k/v heads mixed inside one warp; ragged M
+    (128, 10, 2, 64, 640, 4),    # tiny-qwen traits (GQA 5, bias) at M=128
+    (64, 8, 2, 64, 256, 1),      # no split: library falls back to GEMM + rope kernel
+    (200, 8, 2, 64, 256, 0),     # prefill-sized (stream-K): fallback
+])
+def test_gemm_rope_kv_write_matches_two_launches(ops, kind, m, hq, hkv, d, k, split):
+    """b200_gemm_rope_kv_write == b200_gemm followed by b200_rope_kv_write, bit for bit: the qkv row (rotated q,
+    un-rotated k, v) and both KV pools (slots < 0 skipped, untouched blocks stay zero)."""
+    g = torch.Generator().manual_seed(5)
+    n, bs, nb, max_pos = (hq + 2 * hkv) * d, 32, 40, 512
+    w = torch.randn(n, k, generator=g) * 0.05
+    a = torch.randn(m, k, generator=g)
+    bias = (torch.randn(n, generator=g) * 0.1).bfloat16().cuda() if hq == 10 else None
+    if kind == "bf16":
+        aq, a_s, wq, w_s = a.bfloat16().cuda(), None, w.bfloat16().cuda(), None
+    elif kind == "fp8":
+        wq, w_s = quant_ref.quantize_weight_per_channel(w.bfloat16(), "fp8")
+        aq, a_s = quant_ref.quantize_act_per_token(a.bfloat16(), "fp8")
+        aq, a_s, wq, w_s = aq.cuda(), a_s.cuda(), wq.cuda(), w_s.cuda()
+    else:
+        wq, w_s = quant_ref.quantize_weight_per_channel(w.bfloat16(), "int8")
+        aq, a_s, wq, w_s = a.bfloat16().cuda(), None, wq.cuda(), w_s.cuda()
+    pos = torch.randint(0, max_pos, (m,), generator=g)
+    slots = (torch.randperm((nb - 1) * bs, generator=g)[:m] + bs)
+    slots[::7] = -1  # padding rows
+    pos[3] = max_pos + 5  # clamped
+    pos, slots = pos.cuda(), slots.cuda()
+    inv = 1.0 / (10000.0 ** (torch.arange(0, d, 2).float() / d))
+    ang = torch.arange(max_pos).float()[:, None] * inv[None, :]
+    cos, sin = ang.cos().cuda().contiguous(), ang.sin().cuda().contiguous()
+
+    def pools():
+        return (torch.zeros((nb, hkv, bs, d), dtype=torch.bfloat16, device="cuda"),
+                torch.zeros((nb, hkv, bs, d), dtype=torch.bfloat16, device="cuda"))
+
+    kp1, vp1 = pools()
+    ref = ops.gemm(aq, wq, a_s, w_s, bias, split_k=split)
+    ops.rope_kv_write(ref, pos, cos, sin, kp1, vp1, slots, hq)
+    kp2, vp2 = pools()
+    got = ops.gemm_rope_kv_write(aq, wq, pos, cos, sin, kp2, vp2, slots, hq, a_s, w_s, bias, split_k=split)
+    torch.cuda.synchronize()
+    assert torch.equal(got.view(torch.int16), ref.view(torch.int16))
+    assert torch.equal(kp2.view(torch.int16), kp1.view(torch.int16)) and torch.equal(vp2.view(torch.int16), vp1.view(torch.int16))
+    assert kp1.abs().sum().item() > 0 and (kp2[0] == 0).all()

@@ -22,10 +22,14 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 
 
 def ensure_entry_point() -> None:
-    """vLLM finds platform plugins through importlib.metadata; without a pip install the in-tree egg-info (made by
-    `setup.py egg_info`, git-ignored) on sys.path provides the `vllm.platform_plugins` entry."""
-    if not os.path.exists(os.path.join(ROOT, "vllm_neuron_b200.egg-info", "entry_points.txt")):
-        subprocess.check_call([sys.executable, "setup.py", "-q", "egg_info"], cwd=ROOT)
+    """vLLM finds platform plugins through importlib.metadata; without a pip install, an egg-info directory (made by
+    `setup.py egg_info` into a scratch directory that is put on sys.path -- nothing is written into the repo) provides
+    the `vllm.platform_plugins` entry."""
+    base = os.path.join(tempfile.gettempdir(), "b200_plugin_entry_point")
+    if not os.path.exists(os.path.join(base, "vllm_neuron_b200.egg-info", "entry_points.txt")):
+        os.makedirs(base, exist_ok=True)
+        subprocess.check_call([sys.executable, "setup.py", "-q", "egg_info", "--egg-base", base], cwd=ROOT)
+    sys.path.insert(0, base)
 
 
 def write_model_dir(shape, path: str, seed: int, std: float) -> str:

@@ -46,6 +46,8 @@ SIGNATURES = {
     "b200_gemm": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _sz, _p]),
     "b200_gemm_int8_wo": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _sz, _p]),
     "b200_gemm_silu_mul": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _sz, _p]),
+    "b200_gemm_rope_kv_write": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _sz, _p, _p, _p, _i, _p, _p, _p,
+                                     _i, _i, _i, _i, _i, _p]),
     "b200_rmsnorm": (_i, [_p, _p, _p, _p, _p, _i, _i, _f, _i, _p]),
     "b200_silu_mul": (_i, [_p, _p, _p, _p, _i, _i, _i, _p]),
     "b200_quantize_per_token": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _p]),

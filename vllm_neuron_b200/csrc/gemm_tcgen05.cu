@@ -92,7 +92,9 @@ __device__ __forceinline__ void widen_w_tile(const uint8_t* __restrict__ raw, ui
   }
 }
 
-enum { EPI_LINEAR = 0, EPI_SILU_MUL = 1 };
+// EPI_ROPE: EPI_LINEAR whose split-K owner epilogue also rotates q/k and scatters k/v (decode kernel, S > 1 only); its own
+// instantiation so the plain linears keep their register budget (80 vs 137)
+enum { EPI_LINEAR = 0, EPI_SILU_MUL = 1, EPI_ROPE = 2 };
 
 struct GemmEpilogue {
   const float* a_scale;
@@ -102,6 +104,19 @@ struct GemmEpilogue {
   void* out;
   int out_f32;
   float* group_amax;  // EPI_SILU_MUL: [M][N/32] max |act| over the 16 channels of each interleaved row group
+  // EPI_ROPE (decode kernel with a split-K cluster only; b200_gemm_rope_kv_write): the output row is a packed qkv row
+  // [Hq*D | Hkv*D | Hkv*D]; the token's owner rotates q and k (rotate-half, same roundings as rope_kv_write_kernel)
+  // and scatters k, v into the block-KV pools by slot.
+  struct RopeKv {
+    const int64_t* positions;
+    const int64_t* slot_mapping;
+    const float* cos_t;
+    const float* sin_t;
+    __nv_bfloat16* k_pool;
+    __nv_bfloat16* v_pool;
+    long long num_slots;
+    int max_pos, Hq, Hkv, D, bs;
+  } rope;
 };
 
 // out = ((acc * a_scale) * w_scale + bias) + residual, every step rounded on its own (no FMA contraction), so that the
@@ -482,6 +497,83 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? GEMM_THREADS + 128 : GEMM_T
 // float4 row groups and stores whole 256 B output rows.
 constexpr int DEC_MAX_ST = 12;
 
+// Split-K owner epilogue with RoPE + KV scatter fused (b200_gemm_rope_kv_write; host guarantees N == (Hq + 2 Hkv) * D,
+// N % 128 == 0, D in {64, 128}, bf16 out, no residual).  Thread (tq, t4) finishes tokens tq, tq+4, ... of this CTA's
+// slab and holds dims d0 .. d0+3 of one head; its rotate-half partner (d0 +- D/2) sits in lane ^ (D/8).  The position /
+// slot words and the cos / sin rows of up to RI tokens are loaded up front, back to back, so the loop pays two L2 round
+// trips in total instead of two per token (the output stores would otherwise fence the next token's loads).
+// Roundings are those of rope_kv_write_kernel: bf16(y), products and sums rounded separately.
+__device__ __forceinline__ void rope_reduce_store(const GemmEpilogue& ep, const float* __restrict__ red, int S, int tp_max,
+                                                  int m_lo, int cnt, int tq, int t4, int n0, int N,
+                                                  const float* __restrict__ a_s, const float (&w4)[4],
+                                                  const float (&b4)[4], bool hb) {
+  constexpr int RI = 4;
+  const auto& rp = ep.rope;
+  const int half = rp.D >> 1;
+  const int head = n0 / rp.D, d0 = n0 - head * rp.D;
+  const bool hi_half = d0 >= half, roped = head < rp.Hq + rp.Hkv, is_q = head < rp.Hq, is_k = roped && !is_q;
+  const int dcol = hi_half ? d0 - half : d0;
+  __nv_bfloat16* pool = is_k ? rp.k_pool : rp.v_pool;
+  const int kh = head - rp.Hq - (is_k ? 0 : rp.Hkv);
+  for (int base = tq; base < cnt; base += 4 * RI) {  // warp-uniform trip counts: every lane reaches the shuffles
+    long long pos[RI], slot[RI];
+    float4 c4[RI], s4[RI];
+#pragma unroll
+    for (int i = 0; i < RI; ++i) {
+      const int ml = base + 4 * i, m = m_lo + (ml < cnt ? ml : base);
+      pos[i] = __ldg(rp.positions + m);
+      slot[i] = __ldg(rp.slot_mapping + m);
+    }
+#pragma unroll
+    for (int i = 0; i < RI; ++i) {
+      if (pos[i] < 0) pos[i] = 0;
+      if (pos[i] >= rp.max_pos) pos[i] = rp.max_pos - 1;
+      c4[i] = __ldg(reinterpret_cast<const float4*>(rp.cos_t + pos[i] * half + dcol));
+      s4[i] = __ldg(reinterpret_cast<const float4*>(rp.sin_t + pos[i] * half + dcol));
+    }
+#pragma unroll
+    for (int i = 0; i < RI; ++i) {
+      const int ml = base + 4 * i;
+      if (ml >= cnt) break;
+      const int m = m_lo + ml;
+      float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        if (q < S) {
+          const float4 p = *reinterpret_cast<const float4*>(red + ((size_t)q * tp_max + ml) * GEMM_BN + 4 * t4);
+          sum.x += p.x;
+          sum.y += p.y;
+          sum.z += p.z;
+          sum.w += p.w;
+        }
+      }
+      const float as = a_s[m];
+      const float acc[4] = {sum.x, sum.y, sum.z, sum.w};
+      const float cc[4] = {c4[i].x, c4[i].y, c4[i].z, c4[i].w}, ss[4] = {s4[i].x, s4[i].y, s4[i].z, s4[i].w};
+      float xb[4], pr[4], o[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e)  // what the qkv row holds after the plain GEMM
+        xb[e] = __bfloat162float(__float2bfloat16_rn(scaled_value(acc[e], as, w4[e], hb, b4[e], false, 0.f)));
+#pragma unroll
+      for (int e = 0; e < 4; ++e) pr[e] = __shfl_xor_sync(0xffffffffu, xb[e], half >> 2);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float a = __fmul_rn(xb[e], cc[e]), b = __fmul_rn(pr[e], ss[e]);
+        o[e] = !roped ? xb[e] : hi_half ? __fadd_rn(a, b) : __fsub_rn(a, b);
+      }
+      const uint2 rot = make_uint2(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]));
+      // the qkv row keeps what the unfused pair leaves there: rotated q, un-rotated k, v
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + (int64_t)m * N + n0) =
+          is_q ? rot : make_uint2(pack_bf16(xb[0], xb[1]), pack_bf16(xb[2], xb[3]));
+      if (!is_q && slot[i] >= 0 && slot[i] < rp.num_slots) {
+        const long long blk = slot[i] / rp.bs;
+        const int off = (int)(slot[i] - blk * rp.bs);
+        *reinterpret_cast<uint2*>(pool + ((blk * rp.Hkv + kh) * rp.bs + off) * rp.D + d0) = rot;
+      }
+    }
+  }
+}
+
 template <int KIND, int BM, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 2)
     gemm_decode_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap a_map,
@@ -722,7 +814,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 2)
         float f[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) f[j] = KIND == KIND_I8 ? (float)(int32_t)v[j] : __uint_as_float(v[j]);
-        epilogue_chunk_staged<EPI>(ep, f, cc * 16, M, n, n < N, N, lane, a_s, w_sc, bias_v, resid_s + nl, GEMM_BN);
+        epilogue_chunk_staged<EPI == EPI_ROPE ? (int)EPI_LINEAR : EPI>(ep, f, cc * 16, M, n, n < N, N, lane, a_s, w_sc, bias_v,
+                                                                        resid_s + nl, GEMM_BN);
       }
     } else {
       // TMEM -> local staging tile [token][128 rows] (the ring is dead: every MMA of this CTA has retired) ...
@@ -763,9 +856,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, 2)
     cluster_arrive_relaxed();
     if (warp >= 2) {
       const int n0 = n_tile * GEMM_BN + 4 * t4;
-      const bool hb = ep.bias != nullptr, hr = EPI == EPI_LINEAR && ep.residual != nullptr;
+      const bool hb = ep.bias != nullptr, hr = EPI != EPI_SILU_MUL && ep.residual != nullptr;
+      bool rope_done = false;
+      if constexpr (EPI == EPI_ROPE) {
+        rope_reduce_store(ep, red, S, tp_max, m_lo, m_hi - m_lo, tq, t4, n0, N, a_s, w4, b4, hb);
+        rope_done = true;
+      }
 #pragma unroll 2
-      for (int ml = tq; ml < m_hi - m_lo; ml += 4) {
+      for (int ml = tq; ml < m_hi - m_lo && !rope_done; ml += 4) {
         const int m = m_lo + ml;
         float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -794,7 +892,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 2)
         y[1] = scaled_value(sum.y, as, w4[1], hb, b4[1], hr, rs[1]);
         y[2] = scaled_value(sum.z, as, w4[2], hb, b4[2], hr, rs[2]);
         y[3] = scaled_value(sum.w, as, w4[3], hb, b4[3], hr, rs[3]);
-        if constexpr (EPI == EPI_LINEAR) {
+        if constexpr (EPI != EPI_SILU_MUL) {
           if ((N & 3) == 0 && n0 + 3 < N) {
             if (ep.out_f32)
               *reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.out) + (int64_t)m * N + n0) =
@@ -1067,6 +1165,14 @@ int dispatch_gemm(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilog
   return launch_decode<KIND, 128, EPI>(wm, am, ep, M, N, p, split_k, stream);
 }
 
+template <int KIND>
+int launch_rope(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilogue& ep, int M, int N, const GemmPlan& p,
+                int split_k, cudaStream_t stream) {
+  if (p.bm == 32) return launch_decode<KIND, 32, EPI_ROPE>(wm, am, ep, M, N, p, split_k, stream);
+  if (p.bm == 64) return launch_decode<KIND, 64, EPI_ROPE>(wm, am, ep, M, N, p, split_k, stream);
+  return launch_decode<KIND, 128, EPI_ROPE>(wm, am, ep, M, N, p, split_k, stream);
+}
+
 int gemm_common(const void* a, const void* w, const GemmEpilogue& ep, int epi, int M, int N, int K, int ab_dtype,
                 int split_k, void* workspace, size_t workspace_bytes, void* stream) {
   B200_REQUIRE(a && w && ep.out, "gemm: null pointer");
@@ -1097,6 +1203,13 @@ int gemm_common(const void* a, const void* w, const GemmEpilogue& ep, int epi, i
   rc = make_tmap_2d(&am, a, dt, eb, (uint64_t)K, (uint64_t)M, (uint64_t)K * eb, bk, p.bm);
   if (rc) return rc;
   cudaStream_t s = (cudaStream_t)stream;
+  if (epi == EPI_ROPE) {  // decode schedule only (b200_gemm_rope_kv_write checked the plan)
+    B200_REQUIRE(p.decode, "gemm: the RoPE epilogue exists in the decode schedule only");
+    if (ab_dtype == B200_BF16) return launch_rope<KIND_F16>(wm, am, ep, M, N, p, split_k, s);
+    if (ab_dtype == B200_FP8_E4M3) return launch_rope<KIND_F8F6F4>(wm, am, ep, M, N, p, split_k, s);
+    if (wo) return launch_rope<KIND_WO8>(wm, am, ep, M, N, p, split_k, s);
+    return launch_rope<KIND_I8>(wm, am, ep, M, N, p, split_k, s);
+  }
   if (epi == EPI_LINEAR) {
     if (ab_dtype == B200_BF16) return dispatch_gemm<KIND_F16, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, split_k, s);
     if (ab_dtype == B200_FP8_E4M3) return dispatch_gemm<KIND_F8F6F4, EPI_LINEAR>(wm, am, ep, workspace, M, N, p, split_k, s);
@@ -1133,7 +1246,12 @@ int b200_gemm_decode_plan(int M, int N, int K, int ab_dtype, int split_k, int si
   if (rc) return rc;
   DecodeCfg c{};
   const bool r = has_residual != 0;
-  if (silu_mul) {
+  if (silu_mul == 2) {  // the qkv GEMM with the RoPE / KV-write epilogue
+    rc = ab_dtype == B200_BF16 ? query_plan<KIND_F16, EPI_ROPE>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
+         : ab_dtype == B200_FP8_E4M3 ? query_plan<KIND_F8F6F4, EPI_ROPE>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
+         : ab_dtype == B200_INT8_WO  ? query_plan<KIND_WO8, EPI_ROPE>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
+                                     : query_plan<KIND_I8, EPI_ROPE>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r);
+  } else if (silu_mul) {
     rc = ab_dtype == B200_BF16 ? query_plan<KIND_F16, EPI_SILU_MUL>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
          : ab_dtype == B200_FP8_E4M3 ? query_plan<KIND_F8F6F4, EPI_SILU_MUL>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
          : ab_dtype == B200_INT8_WO  ? query_plan<KIND_WO8, EPI_SILU_MUL>(c, p.bm, M, p.n_tiles, p.num_kb, split_k, r)
@@ -1168,6 +1286,35 @@ int b200_gemm(const void* a, const void* w, void* out, const float* a_scale, con
   GemmEpilogue ep{a_scale, w_scale, (const __nv_bfloat16*)bias, (const __nv_bfloat16*)residual, out, out_dtype == B200_F32,
                   nullptr};
   return gemm_common(a, w, ep, EPI_LINEAR, M, N, K, ab_dtype, split_k, workspace, workspace_bytes, stream);
+}
+
+int b200_gemm_rope_kv_write(const void* a, const void* w, void* qkv_out, const float* a_scale, const float* w_scale,
+                            const void* bias, int M, int N, int K, int ab_dtype, int split_k, void* workspace,
+                            size_t workspace_bytes, const int64_t* positions, const float* cos_table,
+                            const float* sin_table, int max_pos, void* k_pool, void* v_pool, const int64_t* slot_mapping,
+                            int Hq, int Hkv, int D, int block_size, int num_blocks, void* stream) {
+  B200_REQUIRE(positions && cos_table && sin_table && k_pool && v_pool && slot_mapping, "gemm_rope_kv_write: null pointer");
+  B200_REQUIRE(N == (Hq + 2 * Hkv) * D, "gemm_rope_kv_write: N=%d is not (Hq + 2 Hkv) * D = %d", N, (Hq + 2 * Hkv) * D);
+  GemmEpilogue ep{a_scale, w_scale, (const __nv_bfloat16*)bias, nullptr, qkv_out, 0, nullptr};
+  // The rotation lives in the split-K owner's epilogue of the decode kernel (a token's whole head in one warp).  Every
+  // other schedule (one CTA per tile, the stream-K prefill kernel, odd head sizes) runs the GEMM, then the RoPE/scatter
+  // kernel: same bits either way.
+  bool fused = false;
+  if (M <= 128 && (D == 64 || D == 128) && N % GEMM_BN == 0 && max_pos > 0 &&
+      (ab_dtype == B200_BF16 || ab_dtype == B200_FP8_E4M3 || ab_dtype == B200_INT8 || ab_dtype == B200_INT8_WO)) {
+    int plan6[6];
+    if (b200_gemm_decode_plan(M, N, K, ab_dtype, split_k, 2, 0, plan6) == B200_OK && plan6[0] > 1) fused = true;
+  }
+  static const bool no_fuse = getenv("B200_NO_ROPE_FUSION") != nullptr;  // A/B aid
+  if (fused && !no_fuse) {
+    ep.rope = {positions, slot_mapping, cos_table, sin_table, (__nv_bfloat16*)k_pool, (__nv_bfloat16*)v_pool,
+               (long long)num_blocks * block_size, max_pos, Hq, Hkv, D, block_size};
+    return gemm_common(a, w, ep, EPI_ROPE, M, N, K, ab_dtype, split_k, workspace, workspace_bytes, stream);
+  }
+  int rc = gemm_common(a, w, ep, EPI_LINEAR, M, N, K, ab_dtype, split_k, workspace, workspace_bytes, stream);
+  if (rc) return rc;
+  return b200_rope_kv_write(qkv_out, positions, cos_table, sin_table, max_pos, k_pool, v_pool, slot_mapping, M, Hq, Hkv, D,
+                            block_size, num_blocks, stream);
 }
 
 int b200_gemm_int8_wo(const void* a_bf16, const void* w_int8, void* out, const float* w_scale, const void* bias,

@@ -275,9 +275,11 @@ class B200CausalLM:
         n_layers = len(self.layers)
         h, hs = self._norm(x, self.layers[0]["input_norm"])
         for li, L in enumerate(self.layers):
-            qkv = self._linear(L["qkv"], h, hs)
             kp, vp = self.kv[li][0], self.kv[li][1]
-            ops.rope_kv_write(qkv, positions, self.cos, self.sin, kp, vp, slot_mapping, self.hq)
+            # qkv projection with RoPE + KV-cache write in its epilogue (one launch in the decode schedule)
+            lq = L["qkv"]
+            qkv = ops.gemm_rope_kv_write(h, lq.w, positions, self.cos, self.sin, kp, vp, slot_mapping, self.hq, hs, lq.scale,
+                                         lq.bias, workspace=self.gemm_ws)
             a = attn_fn(qkv[:, :qd].unflatten(1, (self.hq, self.d)), kp, vp, q)
             if q is None:
                 a = (a.reshape(t, qd), None)

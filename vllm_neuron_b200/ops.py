@@ -303,6 +303,34 @@ def gemm(a, w, a_scale=None, w_scale=None, bias=None, residual=None, out=None, o
     return out
 
 
+def gemm_rope_kv_write(a, w, positions, cos, sin, k_pool, v_pool, slot_mapping, num_q_heads: int, a_scale=None,
+                       w_scale=None, bias=None, split_k=0, workspace=None):
+    """qkv[M, (Hq+2Hkv)*D] = gemm(a, w, ...) with rope_kv_write fused into the GEMM epilogue when the decode schedule
+    allows (one launch), else GEMM + rope_kv_write inside the library (two launches); identical bits.  Returns qkv."""
+    _cuda(a, w, a_scale, w_scale, bias, positions, cos, sin, k_pool, v_pool, slot_mapping)
+    m, k = a.shape
+    n, k2 = w.shape
+    nb, hkv, bs, d = k_pool.shape
+    assert k == k2 and a.is_contiguous() and w.is_contiguous() and n == (num_q_heads + 2 * hkv) * d
+    assert cos.dtype == torch.float32 and cos.shape[1] == d // 2 and cos.is_contiguous() and sin.is_contiguous()
+    assert positions.dtype == torch.int64 and slot_mapping.dtype == torch.int64
+    dt = _gemm_dtype(a, w)
+    out = torch.empty((m, n), dtype=torch.bfloat16, device=a.device)
+    if workspace is None:
+        workspace = gemm_workspace(m, n, k, dt, a.device, split_k)
+    with _k(f"gemm_rope_kv_{_DTN[dt]}[{m}x{n}x{k}]"):
+        check(
+            _cabi.load().b200_gemm_rope_kv_write(
+                _ptr(a), _ptr(w), _ptr(out), _ptr(a_scale), _ptr(w_scale), _ptr(bias), m, n, k, dt, split_k,
+                _ptr(workspace), 0 if workspace is None else workspace.numel() * workspace.element_size(),
+                _ptr(positions), _ptr(cos), _ptr(sin), cos.shape[0], _ptr(k_pool), _ptr(v_pool), _ptr(slot_mapping),
+                num_q_heads, hkv, d, bs, nb, _stream(),
+            ),
+            "b200_gemm_rope_kv_write",
+        )
+    return out
+
+
 def interleave_gate_up(w_gu, *others):
     """Row permutation expected by gemm_silu_mul: [gate(I); up(I)] -> groups of 32 rows = 16 gate rows followed by the
     16 up rows of the same channels.  Applied (load time) to the weight and to every per-row companion (scale, bias)."""
