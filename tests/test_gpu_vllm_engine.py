@@ -16,11 +16,11 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _engine(tmp_path, quant):
+def _engine(tmp_path, quant, *extra):
     out = tmp_path / "engine.json"
     env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
     p = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "vllm_engine_e2e.py"), "--out", str(out), "--quant", quant,
-                        "--model-dir", str(tmp_path / "model")], cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
+                        "--model-dir", str(tmp_path / "model"), *extra], cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
     assert p.returncode == 0, "vLLM engine run failed:\n" + p.stdout[-3000:] + "\n" + p.stderr[-6000:]
     return json.loads(out.read_text())
 
@@ -81,3 +81,16 @@ def test_vllm_engine_greedy_tokens_match_oracle(tmp_path, quant, band):
     # "d" repeats a's first 64 tokens: vLLM's prefix cache must have served two full blocks
     nc = res["num_cached_tokens"].get("d")
     assert nc is None or nc >= 64, res["num_cached_tokens"]
+
+
+@pytest.mark.gpu
+def test_vllm_engine_native_scheduler_chunked_prefill(tmp_path):
+    """DISABLE_NEURON_CUSTOM_SCHEDULER=1 (PLAT:176-187): vLLM's own scheduler cuts the prompts into 48-token chunks and
+    mixes prefill chunks with decodes in one step (RUNNER:654-679, 938-1051); tokens must still be the oracle's."""
+    res = _engine(tmp_path, "bf16", "--native-scheduler")
+    assert res["native_scheduler"] and res["platform"].endswith("B200Platform")
+    assert {k: len(v) for k, v in res["outputs"].items()} == {k: 8 if k == "b" else 24 for k in res["prompts"]}
+    checked, near_ties, bad = _oracle_check(res, "bf16", 0.05)
+    print(f"[native scheduler] engine tokens: {checked} equal to the oracle's argmax, {near_ties} inside the band, {len(bad)} outside")
+    assert not bad, bad
+    assert checked >= 0.9 * sum(len(v) for v in res["outputs"].values())

@@ -68,10 +68,15 @@ def main() -> None:
     ap.add_argument("--seed", type=int, default=3)
     ap.add_argument("--std", type=float, default=0.05)
     ap.add_argument("--model-dir", default=None)
+    ap.add_argument("--native-scheduler", action="store_true",
+                    help="vLLM's own scheduler with chunked prefill (DISABLE_NEURON_CUSTOM_SCHEDULER=1, RUNNER:654-679): "
+                         "prompts are cut into 48-token chunks and prefill chunks share steps with decodes")
     args = ap.parse_args()
 
     os.environ.setdefault("VLLM_ENABLE_V1_MULTIPROCESSING", "0")  # engine core in-process: one traceback, one GPU context
     os.environ.setdefault("VLLM_PLUGINS", "b200")
+    if args.native_scheduler:
+        os.environ["DISABLE_NEURON_CUSTOM_SCHEDULER"] = "1"
     ensure_entry_point()
     from vllm_neuron_b200.config import PRESETS
 
@@ -89,6 +94,7 @@ def main() -> None:
 
     llm = LLM(model=mdir, skip_tokenizer_init=True, dtype="bfloat16", max_model_len=256, max_num_seqs=4, block_size=32,
               enable_prefix_caching=True, num_gpu_blocks_override=48,
+              **({"enable_chunked_prefill": True, "max_num_batched_tokens": 48} if args.native_scheduler else {}),
               additional_config={"override_neuron_config": override})
     prompts = make_prompts(shape.vocab)
     sps = {k: SamplingParams(temperature=0.0, max_tokens=8 if k == "b" else args.max_tokens, ignore_eos=True,
@@ -99,7 +105,7 @@ def main() -> None:
 
     res = {
         "platform": type(current_platform).__module__ + "." + type(current_platform).__name__,
-        "quant": args.quant, "preset": args.preset, "seed": args.seed, "std": args.std, "block_size": 32,
+        "native_scheduler": bool(args.native_scheduler), "quant": args.quant, "preset": args.preset, "seed": args.seed, "std": args.std, "block_size": 32,
         "max_model_len": 256, "prompts": prompts,
         "outputs": {k: list(o.outputs[0].token_ids) for k, o in zip(keys, outs)},
         "num_cached_tokens": {k: getattr(o, "num_cached_tokens", None) for k, o in zip(keys, outs)},
