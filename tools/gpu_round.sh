@@ -6,7 +6,7 @@ mkdir -p gpurun_out
 want() { [[ " $* " == *" $1 "* ]] ; }
 ARGS=" $* "
 if [[ "$ARGS" == *" tests "* ]]; then
-  for f in test_gpu_kv test_gpu_glue test_gpu_attn test_gpu_gemm test_gpu_sampling test_gpu_model; do
+  for f in test_gpu_kv test_gpu_glue test_gpu_attn test_gpu_gemm test_gpu_sampling test_gpu_model test_gpu_vllm_engine; do
     timeout 600 python -m pytest tests/$f.py -q -m gpu --timeout 300 -s > gpurun_out/$f.log 2>&1
     echo "$f exit=$?" | tee -a gpurun_out/summary.txt
     tail -15 gpurun_out/$f.log
