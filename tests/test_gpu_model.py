@@ -13,14 +13,14 @@ from parity_util import device_to_logical_pool, make_vllm_config, sched_output
 pytestmark = pytest.mark.gpu
 
 
-def _run(quant, steps=12, use_graph=True, preset="tiny-test"):
+def _run(quant, steps=12, use_graph=True, preset="tiny-test", std=0.05):
     from vllm_neuron_b200.config import PRESETS
     from vllm_neuron_b200.model import B200CausalLM, random_init_full_weights
     from vllm_neuron_b200.worker.b200_model_runner import B200ModelRunner
 
     shape = PRESETS[preset]
     bs, mml, mns, nb = 32, 256, 4, 40
-    weights = random_init_full_weights(shape, seed=3, std=0.05)
+    weights = random_init_full_weights(shape, seed=3, std=std)
     override = {} if quant == "bf16" else {"quantized": True, "quantization_dtype": "f8e4m3" if quant == "fp8" else "int8",
                                             "quantization_type": "per_channel_symmetric"}
     if quant == "int8_wo":
