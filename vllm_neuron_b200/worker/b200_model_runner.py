@@ -43,6 +43,7 @@ class CachedRequest:
     sampling_params: object = None
     rng: object = None  # per-request numpy Generator (SamplingParams.seed), created on first stochastic draw
     prefilled: int = 0  # prompt tokens whose K/V are in the cache (prefix-cache hits + chunks computed so far)
+    samp_row: tuple | None = None  # (top_k, top_p, temperature) by the reference's rule; fixed per request, computed once
 
     @property
     def num_tokens(self) -> int:
@@ -88,6 +89,7 @@ class B200ModelRunner:
         add = getattr(vllm_config, "additional_config", None) or {}
         ods = (add.get("override_neuron_config") or {}).get("on_device_sampling_config") or {}
         self.global_topk = int(ods.get("global_topk", 0)) if isinstance(ods, dict) else int(getattr(ods, "global_topk", 0))
+        self._max_topk: int | None = None
         self._rng = np.random.Generator(np.random.PCG64(getattr(self.model_config, "seed", 0) or 0))
 
     # ------------------------------------------------------------------ config / load / KV allocation
@@ -227,10 +229,12 @@ class B200ModelRunner:
         cached = so.scheduled_cached_reqs
         resumed = getattr(cached, "resumed_req_ids", None)
         legacy_resumed = getattr(cached, "resumed_from_preemption", None)
+        requests, new_ids = self.requests, cached.new_block_ids
         for i, req_id in enumerate(cached.req_ids):
-            st = self.requests[req_id]
-            new_blocks = _first_group(cached.new_block_ids[i]) if cached.new_block_ids else None
-            is_resumed = (req_id in resumed) if resumed is not None else bool(legacy_resumed and legacy_resumed[i])
+            st = requests[req_id]
+            nb = new_ids[i] if new_ids else None
+            new_blocks = None if nb is None else _first_group(nb)
+            is_resumed = (req_id in resumed) if resumed else bool(legacy_resumed and legacy_resumed[i])
             if not is_resumed:
                 if new_blocks:
                     start = len(st.block_ids)
@@ -261,11 +265,13 @@ class B200ModelRunner:
         """(top_k, top_p, temperature) of one request by the reference's rule: top_k outside (0, max_topk) -> max_topk
         (= min(global_topk or vocab, 256)); temperature 0 -> top_k 1, temperature 1.0 (greedy)."""
         sp = st.sampling_params
-        gv = getattr(self.model_config, "get_vocab_size", None)
-        vocab = gv() if callable(gv) else self.model_shape().vocab
-        max_topk = min(self.global_topk or vocab, _MAX_SAMPLING_TOP_K)
         if sp is None:
             return (1.0, 1.0, 1.0)
+        if self._max_topk is None:
+            gv = getattr(self.model_config, "get_vocab_size", None)
+            vocab = gv() if callable(gv) else self.model_shape().vocab
+            self._max_topk = min(self.global_topk or vocab, _MAX_SAMPLING_TOP_K)
+        max_topk = self._max_topk
         k = getattr(sp, "top_k", 0) or 0
         top_k = k if 0 < k < max_topk else max_topk
         top_p = float(getattr(sp, "top_p", 1.0))
@@ -290,8 +296,16 @@ class B200ModelRunner:
 
     def _sampling_inputs(self, sts: list[CachedRequest]):
         """None when every request of the batch is greedy (argmax path); else host lists (params rows, uniforms)."""
-        rows = [self.sampling_row(st) for st in sts]
-        if all(r[0] == 1.0 for r in rows):
+        rows = []
+        greedy = True
+        for st in sts:  # a request's SamplingParams never change: its row is computed on first use (256 us -> 6 us at B=64)
+            r = st.samp_row
+            if r is None:
+                r = st.samp_row = self.sampling_row(st)
+            if r[0] != 1.0:
+                greedy = False
+            rows.append(r)
+        if greedy:
             return None
         return rows, [self._draw_uniform(st) if r[0] != 1.0 else 0.0 for st, r in zip(sts, rows)]
 
