@@ -126,3 +126,18 @@ def test_vllm_engine_cfg1_tinyllama_64_greedy_steps(tmp_path):
     print(f"[cfg1] engine tokens: {checked} equal to the oracle's argmax, {near_ties} inside the band, {len(bad)} outside")
     assert not bad, bad
     assert checked >= 0.9 * 256
+
+
+@pytest.mark.gpu
+def test_vllm_engine_tensor_parallel_2(tmp_path):
+    """tensor_parallel_size=2 under vLLM's multi-process executor: one B200Worker process per GPU, NCCL process group from
+    vLLM's own init, the plugin found in the spawned workers, the NVLink exchange kernel between them (SURVEY 8(e));
+    only the driver worker returns the ModelRunnerOutput (WORKER:65-69).  Tokens must be the oracle's."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    res = _engine(tmp_path, "bf16", "--tp", "2")
+    assert res["tp"] == 2 and res["platform"].endswith("B200Platform")
+    checked, near_ties, bad = _oracle_check(res, "bf16", 0.05)
+    print(f"[tp2] engine tokens: {checked} equal to the oracle's argmax, {near_ties} inside the band, {len(bad)} outside")
+    assert not bad, bad
+    assert checked >= 0.9 * sum(len(v) for v in res["outputs"].values())

@@ -143,3 +143,13 @@ def test_worker_hands_the_step_output_to_sample_tokens():
     assert w.sample_tokens(None) == ("out", "s1") and w.sample_tokens(None) is None
     w.is_driver_worker = False
     assert w.execute_model("s2") is None and w.sample_tokens(None) is None  # WORKER:65-69
+
+
+def test_device_communicator_class_resolves(platform):
+    """TP>1 under vLLM's multi-process executor builds the TP GroupCoordinator with this class; CudaCommunicator asserts a
+    builtin CUDA platform (custom all-reduce), the base communicator is plain torch.distributed on the device group."""
+    import importlib
+
+    mod, _, name = platform.get_device_communicator_cls().rpartition(".")
+    cls = getattr(importlib.import_module(mod), name)
+    assert hasattr(cls, "all_reduce") and hasattr(cls, "all_gather")

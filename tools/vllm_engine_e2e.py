@@ -30,6 +30,8 @@ def ensure_entry_point() -> None:
         os.makedirs(base, exist_ok=True)
         subprocess.check_call([sys.executable, "setup.py", "-q", "egg_info", "--egg-base", base], cwd=ROOT)
     sys.path.insert(0, base)
+    # worker processes of the multi-GPU executor are spawned: they find the plugin (and this repo) through PYTHONPATH
+    os.environ["PYTHONPATH"] = os.pathsep.join([base, ROOT, os.environ.get("PYTHONPATH", "")]).rstrip(os.pathsep)
 
 
 def write_model_dir(shape, path: str, seed: int, std: float) -> str:
@@ -134,6 +136,7 @@ def main() -> None:
     ap.add_argument("--seed", type=int, default=3)
     ap.add_argument("--std", type=float, default=0.05)
     ap.add_argument("--model-dir", default=None)
+    ap.add_argument("--tp", type=int, default=1, help="tensor_parallel_size: one B200Worker process per GPU (vLLM mp executor)")
     ap.add_argument("--cfg1", action="store_true",
                     help="BASELINE configs[0]: TinyLlama-1.1B shape, max_num_seqs 4, block 32, max_model_len 2048, prefix "
                          "caching, 4096 blocks (reference README.md:37,45), 64 greedy tokens per sequence")
@@ -172,6 +175,7 @@ def main() -> None:
     from vllm.platforms import current_platform
 
     llm = LLM(model=mdir, skip_tokenizer_init=True, dtype="bfloat16", max_model_len=mml, max_num_seqs=4, block_size=32,
+              tensor_parallel_size=args.tp,
               enable_prefix_caching=True, num_gpu_blocks_override=nblocks,
               **({"enable_chunked_prefill": True, "max_num_batched_tokens": 48} if args.native_scheduler else {}),
               additional_config={"override_neuron_config": override})
@@ -184,7 +188,7 @@ def main() -> None:
 
     res = {
         "platform": type(current_platform).__module__ + "." + type(current_platform).__name__,
-        "native_scheduler": bool(args.native_scheduler), "quant": args.quant, "preset": args.preset, "seed": args.seed, "std": args.std, "block_size": 32,
+        "native_scheduler": bool(args.native_scheduler), "tp": args.tp, "quant": args.quant, "preset": args.preset, "seed": args.seed, "std": args.std, "block_size": 32,
         "max_model_len": mml, "prompts": prompts,
         "outputs": {k: list(o.outputs[0].token_ids) for k, o in zip(keys, outs)},
         "num_cached_tokens": {k: getattr(o, "num_cached_tokens", None) for k, o in zip(keys, outs)},

@@ -111,7 +111,9 @@ class B200Platform(Platform):
 
     @classmethod
     def get_device_communicator_cls(cls) -> str:
-        return "vllm.distributed.device_communicators.cuda_communicator.CudaCommunicator"
+        # torch.distributed (NCCL) on the TP device group; the hot-path exchange is this plugin's own NVLink kernel
+        # (tp_comm.py), so vLLM's CudaCommunicator (custom all-reduce, asserts a builtin CUDA platform) is not wanted
+        return "vllm.distributed.device_communicators.base_device_communicator.DeviceCommunicatorBase"
 
     @classmethod
     def is_pin_memory_available(cls) -> bool:
