@@ -56,3 +56,30 @@ def test_stop_check_on_a_real_vllm_request():
     r2 = Request(request_id="y", prompt_token_ids=[1, 2, 3], sampling_params=SamplingParams(max_tokens=50), pooling_params=None)
     r2.append_output_token_ids(5)
     assert check_stop_with_min_tokens(r2, 4) is True and r2.status == RequestStatus.FINISHED_LENGTH_CAPPED
+
+
+def test_request_wrapper_equals_the_pure_rule():
+    """check_stop_with_min_tokens (written out on the Request's fields for speed) == stop_reason over a grid of states."""
+    import itertools
+    from types import SimpleNamespace
+
+    from vllm.v1.request import RequestStatus
+
+    from vllm_neuron_b200.core.scheduler import check_stop_with_min_tokens, stop_reason
+
+    for n_out, max_tokens, min_tokens, last, ignore_eos, stop_ids, n_prompt in itertools.product(
+            (0, 1, 3, 5), (3, 100), (0, 4), (2, 7, 9), (False, True), ((), (7,)), (4, 98)):
+        outs = [1] * (n_out - 1) + [last] if n_out else []
+        sp = SimpleNamespace(min_tokens=min_tokens, ignore_eos=ignore_eos, stop_token_ids=list(stop_ids), eos_token_id=2)
+        req = SimpleNamespace(sampling_params=sp, pooling_params=None, num_output_tokens=n_out, num_tokens=n_prompt + n_out,
+                              max_tokens=max_tokens, output_token_ids=outs, status=None, stop_reason=None)
+        want = stop_reason(num_tokens=n_prompt + n_out, num_output_tokens=n_out, max_tokens=max_tokens, max_model_len=100,
+                           min_tokens=min_tokens, last_token_id=outs[-1] if outs else -1, eos_token_id=2,
+                           ignore_eos=ignore_eos, stop_token_ids=stop_ids)
+        got = check_stop_with_min_tokens(req, 100)
+        assert got == (want is not None), (n_out, max_tokens, min_tokens, last, ignore_eos, stop_ids, n_prompt)
+        if want == "length":
+            assert req.status == RequestStatus.FINISHED_LENGTH_CAPPED
+        elif want is not None:
+            assert req.status == RequestStatus.FINISHED_STOPPED
+            assert req.stop_reason == (want[1] if isinstance(want, tuple) else None)

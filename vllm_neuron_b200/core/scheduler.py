@@ -56,31 +56,47 @@ def _vllm_scheduler_base():
     return Scheduler
 
 
-def check_stop_with_min_tokens(request, max_model_len: int, pooler_output=None) -> bool:
-    """Request-object wrapper over `stop_reason` (same signature as SCHED:130)."""
-    from vllm.v1.request import RequestStatus
+_REQUEST_STATUS = None
 
+
+def check_stop_with_min_tokens(request, max_model_len: int, pooler_output=None) -> bool:
+    """SCHED:130-166 on a vLLM Request (same signature): `stop_reason`'s rule written out on the object's fields -- this
+    runs once per request per step inside the engine loop, so no keyword packing and no per-call import."""
+    global _REQUEST_STATUS
+    if _REQUEST_STATUS is None:
+        from vllm.v1.request import RequestStatus
+
+        _REQUEST_STATUS = RequestStatus
     sp = request.sampling_params
-    if not request.pooling_params:
+    pooling = request.pooling_params
+    if not pooling:
         assert sp is not None
-    # vLLM 0.11 keeps the EOS id on the Request (SCHED:149), 0.2x on its SamplingParams (None when ignore_eos)
-    eos = request.eos_token_id if hasattr(request, "eos_token_id") else getattr(sp, "eos_token_id", None)
-    r = stop_reason(
-        num_tokens=request.num_tokens, num_output_tokens=request.num_output_tokens, max_tokens=request.max_tokens,
-        max_model_len=max_model_len, min_tokens=getattr(sp, "min_tokens", 0) if sp else 0,
-        last_token_id=request.output_token_ids[-1] if request.output_token_ids else -1,
-        eos_token_id=eos, ignore_eos=getattr(sp, "ignore_eos", False) if sp else False,
-        stop_token_ids=getattr(sp, "stop_token_ids", ()) if sp else (), pooling=bool(request.pooling_params),
-        has_pooler_output=pooler_output is not None)
-    if r is None:
+    n_out = request.num_output_tokens
+    if request.num_tokens >= max_model_len or n_out >= request.max_tokens:
+        request.status = _REQUEST_STATUS.FINISHED_LENGTH_CAPPED
+        return True
+    if pooling:
+        if pooler_output is not None:
+            request.status = _REQUEST_STATUS.FINISHED_STOPPED
+            return True
         return False
-    if r == "length":
-        request.status = RequestStatus.FINISHED_LENGTH_CAPPED
-    else:
-        request.status = RequestStatus.FINISHED_STOPPED
-        if isinstance(r, tuple):
-            request.stop_reason = r[1]
-    return True
+    min_tokens = sp.min_tokens
+    if min_tokens > 0 and n_out < min_tokens:
+        return False
+    out = request.output_token_ids
+    last = out[-1] if out else -1
+    if not sp.ignore_eos:
+        # vLLM 0.11 keeps the EOS id on the Request (SCHED:149), 0.2x on its SamplingParams (None when ignore_eos)
+        eos = request.eos_token_id if hasattr(request, "eos_token_id") else getattr(sp, "eos_token_id", None)
+        if last == eos:
+            request.status = _REQUEST_STATUS.FINISHED_STOPPED
+            return True
+    stop_ids = sp.stop_token_ids
+    if stop_ids and last in stop_ids:
+        request.status = _REQUEST_STATUS.FINISHED_STOPPED
+        request.stop_reason = last
+        return True
+    return False
 
 
 def _build_scheduler_cls():
