@@ -349,3 +349,51 @@ def test_checkpoint_load_matches_in_memory_weights(tmp_path, quant_override):
         b = run(True)
     assert a[0] == b[0] and a[1] == b[1]
     assert torch.equal(a[2], b[2]) and torch.equal(a[3], b[3])
+
+
+def test_resume_after_preemption_recomputes_into_new_blocks():
+    """A request that vLLM preempted and resumes (resumed_req_ids; block ids REPLACED, RUNNER:467-471) has no K/V in its
+    new blocks: the runner must prefill prompt + generated tokens into them and sample the next token -- the same token
+    (within the bf16 bar: prefill and decode GEMM schedules differ) the un-preempted request produces."""
+    from vllm_neuron_b200.config import PRESETS
+    from vllm_neuron_b200.model import B200CausalLM, random_init_full_weights
+    from vllm_neuron_b200.worker.b200_model_runner import B200ModelRunner
+
+    shape = PRESETS["tiny-test"]
+    weights = random_init_full_weights(shape, seed=4, std=0.05)
+    prompt = torch.randint(0, shape.vocab, (45,), generator=torch.Generator().manual_seed(6)).tolist()
+
+    def make():
+        cfg = make_vllm_config(shape, max_num_seqs=2, max_model_len=128, num_gpu_blocks_override=12)
+        model = B200CausalLM(shape, weights, quant="bf16", num_blocks=12, max_num_seqs=2, max_model_len=128)
+        r = B200ModelRunner(cfg, torch.device("cuda"), model=model)
+        r.load_model(load_dummy_weights=True)
+        r.initialize_kv_cache(num_blocks=12)
+        return r, model
+
+    r1, m1 = make()
+    toks = r1.execute_model(sched_output(new_reqs=[("p", prompt, [4, 6], 0)])).sampled_token_ids[0]
+    for _ in range(4):
+        toks += r1.execute_model(sched_output(cached=[("p", None)])).sampled_token_ids[0]
+    want_logits = m1.last_logits.float().cpu().clone()
+
+    r2, m2 = make()
+    r2.execute_model(sched_output(new_reqs=[("p", prompt, [4, 6], 0)]))
+    for i in range(3):
+        r2.requests["p"].output_token_ids[:] = toks[: i + 1]
+        r2.execute_model(sched_output(cached=[("p", None)]))
+    r2.requests["p"].output_token_ids[:] = toks[:4]
+    so = sched_output(cached=[("p", [7, 8])])
+    so.scheduled_cached_reqs.resumed_req_ids = {"p"}
+    so.num_scheduled_tokens["p"] = so.total_num_scheduled_tokens = 49  # prompt + the four generated tokens
+    out = r2.execute_model(so)
+    got_logits = m2.last_logits.float().cpu()
+    std = want_logits.std().item()
+    assert (got_logits - want_logits).pow(2).mean().sqrt().item() < 1e-2 * std
+    top2 = want_logits.topk(2, dim=-1).values
+    if (top2[0, 0] - top2[0, 1]).item() > 0.05 * std:
+        assert out.sampled_token_ids == [[toks[4]]]
+    # the new blocks now hold the sequence's K/V; and decoding carries on from them
+    assert (m2.kv[0][:, [7, 8]] != 0).any() and r2.requests["p"].num_tokens == 50
+    nxt = r2.execute_model(sched_output(cached=[("p", None)]))
+    assert len(nxt.sampled_token_ids[0]) == 1

@@ -37,6 +37,10 @@ def test_cached_request_block_append_and_resume_replace():
     so.scheduled_cached_reqs.resumed_req_ids = {"a"}
     upd = r._update_states(so)
     assert r.requests["a"].block_ids == [20, 21] and upd == [(0, 0, 20), (0, 1, 21)]  # RUNNER:467-471 (replace)
+    # preemption = recompute: the generated token joins the tokens the next step prefills into the new (empty) blocks
+    st = r.requests["a"]
+    assert st.prompt_token_ids == list(range(40)) + [11] and st.output_token_ids == [] and st.prefilled == 0
+    assert st.num_tokens == 41
 
 
 def test_finished_request_frees_its_row():

@@ -244,6 +244,14 @@ class B200ModelRunner:
                 assert new_blocks is not None
                 st.block_ids = list(new_blocks)  # RUNNER:467-471: replace after preemption
                 updates += [(st.row, c, b) for c, b in enumerate(st.block_ids)]
+                # vLLM preempts by recomputation: the new blocks are empty, so everything generated so far joins what the
+                # next step prefills (the scheduler schedules all of those tokens) and the step samples the next token.
+                # (Cannot happen under the validated block budget -- max_num_seqs x max_model_len always fits, LOADER:845-859
+                # -- but a mirrored block list without its K/V would decode garbage.)
+                st.prompt_token_ids = st.prompt_token_ids + st.output_token_ids
+                st.output_token_ids = []
+                nct = getattr(cached, "num_computed_tokens", None)
+                st.prefilled = st.num_computed_tokens = int(nct[i]) if nct else 0
             if st.prefilled >= len(st.prompt_token_ids):
                 st.num_computed_tokens = st.num_tokens - 1
         return updates
