@@ -85,10 +85,13 @@ class B200Platform(Platform):
             assert cache_config.block_size is not None, "When vLLM V1 native scheduler is enabled, block_size must be set."
         else:
             sched_cfg.scheduler_cls = SCHEDULER_CLS
-            try:
-                sched_cfg.chunked_prefill_enabled = False
-            except Exception:  # read-only in some vLLM versions
-                sched_cfg.enable_chunked_prefill = False
+            # vLLM 0.11 names the switch chunked_prefill_enabled (PLAT:181), 0.2x enable_chunked_prefill
+            for name in ("chunked_prefill_enabled", "enable_chunked_prefill"):
+                if hasattr(sched_cfg, name):
+                    try:
+                        setattr(sched_cfg, name, False)
+                    except Exception:  # a read-only property in some versions
+                        pass
             sched_cfg.max_num_batched_tokens = DEFAULT_MAX_NUM_BATCHED_TOKENS
             if getattr(sched_cfg, "async_scheduling", False):
                 # vLLM >= 0.2x turns async scheduling on by default; the prefill-or-decode policy needs each step's
