@@ -230,6 +230,8 @@ class B200ModelRunner:
         resumed = getattr(cached, "resumed_req_ids", None)
         legacy_resumed = getattr(cached, "resumed_from_preemption", None)
         requests, new_ids = self.requests, cached.new_block_ids
+        if not resumed and not legacy_resumed and (not new_ids or new_ids.count(None) == len(new_ids)):
+            return updates  # steady decode step: nobody got a block (31 of 32 steps at block size 32), nothing to mirror
         for i, req_id in enumerate(cached.req_ids):
             st = requests[req_id]
             nb = new_ids[i] if new_ids else None
