@@ -335,57 +335,83 @@ __global__ void embedding_kernel(const int64_t* __restrict__ tokens, const uint4
   for (int i = threadIdx.x; i < nvec; i += blockDim.x) out[(int64_t)t * nvec + i] = table[tok * nvec + i];
 }
 
-// first index of the row maximum (ties -> lowest index)
-__global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ logits, int64_t row_stride,
-                                                      float* __restrict__ out_val, int64_t* __restrict__ out_idx, int V,
-                                                      int64_t idx_offset) {
+// first index of the row maximum (ties -> lowest index).  A row (128 K fp32 logits, just written by lm_head, so mostly
+// L2 hits) is cut into ARGMAX_CL slices scanned by the CTAs of one thread-block cluster with 128-bit loads; every CTA
+// reduces its slice and stores (max, index) into the shared memory of cluster rank 0, which picks the row's winner.
+// (One 1024-thread CTA per row with scalar loads took 37 us in the decode graph: 64 CTAs cannot pull 33 MB quickly.)
+constexpr int ARGMAX_CL = 8;
+constexpr int ARGMAX_THREADS = 256;
+
+__device__ __forceinline__ void argmax_take(float& best, int& bi, float x, int i) {
+  if (x > best || (x == best && i < bi)) {
+    best = x;
+    bi = i;
+  }
+}
+
+__global__ void __launch_bounds__(ARGMAX_THREADS) argmax_kernel(const float* __restrict__ logits, int64_t row_stride,
+                                                                float* __restrict__ out_val, int64_t* __restrict__ out_idx,
+                                                                int V, int64_t idx_offset) {
   griddep_launch();
   griddep_wait();
   __shared__ float sv[32];
   __shared__ int si[32];
-  int t = blockIdx.x;
+  __shared__ float cv[ARGMAX_CL];  // rank 0: one candidate per cluster rank
+  __shared__ int ci[ARGMAX_CL];
+  const int nr = (int)cluster_nctarank(), rk = (int)cluster_ctarank();
+  const int t = blockIdx.x / nr;
   const float* r = logits + (int64_t)t * row_stride;
   float best = -INFINITY;
   int bi = 0x7fffffff;
-  for (int i = threadIdx.x; i < V; i += blockDim.x) {
-    float x = r[i];
-    if (x > best || (x == best && i < bi)) {
-      best = x;
-      bi = i;
-    }
+  // slice [lo, hi) of this rank, in units of 4 floats when the row is 16-byte aligned; the ragged tail goes to the last rank
+  const bool vec = (reinterpret_cast<uintptr_t>(r) & 15) == 0;
+  const int nv = vec ? V >> 2 : 0;
+  const int lo = (int)((long long)nv * rk / nr), hi = (int)((long long)nv * (rk + 1) / nr);
+  const float4* r4 = reinterpret_cast<const float4*>(r);
+#pragma unroll 4
+  for (int i = lo + threadIdx.x; i < hi; i += ARGMAX_THREADS) {
+    const float4 x = r4[i];
+    argmax_take(best, bi, x.x, 4 * i);
+    argmax_take(best, bi, x.y, 4 * i + 1);
+    argmax_take(best, bi, x.z, 4 * i + 2);
+    argmax_take(best, bi, x.w, 4 * i + 3);
   }
+  if (rk == nr - 1)
+    for (int i = 4 * nv + threadIdx.x; i < V; i += ARGMAX_THREADS) argmax_take(best, bi, r[i], i);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
-    float ov = __shfl_xor_sync(0xffffffffu, best, o);
-    int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-    if (ov > best || (ov == best && oi < bi)) {
-      best = ov;
-      bi = oi;
-    }
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    argmax_take(best, bi, ov, oi);
   }
-  int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
   if (l == 0) {
     sv[w] = best;
     si[w] = bi;
   }
   __syncthreads();
   if (w == 0) {
-    int nw = blockDim.x >> 5;
-    best = l < nw ? sv[l] : -INFINITY;
-    bi = l < nw ? si[l] : 0x7fffffff;
+    constexpr int NW = ARGMAX_THREADS / 32;
+    best = l < NW ? sv[l] : -INFINITY;
+    bi = l < NW ? si[l] : 0x7fffffff;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-      float ov = __shfl_xor_sync(0xffffffffu, best, o);
-      int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      if (ov > best || (ov == best && oi < bi)) {
-        best = ov;
-        bi = oi;
-      }
+      const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      argmax_take(best, bi, ov, oi);
     }
-    if (l == 0) {
-      if (out_val) out_val[t] = best;
-      out_idx[t] = idx_offset + (bi == 0x7fffffff ? 0 : bi);
+    if (l == 0) {  // candidate of this rank -> rank 0's shared memory (DSMEM store; rank 0 stores locally the same way)
+      st_cluster_f32(mapa_shared(smem_u32(&cv[rk]), 0u), best);
+      st_cluster_f32(mapa_shared(smem_u32(&ci[rk]), 0u), __int_as_float(bi));
     }
+  }
+  cluster_sync_all();  // release / acquire: the candidates are visible to rank 0
+  if (rk == 0 && threadIdx.x == 0) {
+    best = -INFINITY;
+    bi = 0x7fffffff;
+    for (int q = 0; q < nr; ++q) argmax_take(best, bi, cv[q], ci[q]);
+    if (out_val) out_val[t] = best;
+    out_idx[t] = idx_offset + (bi == 0x7fffffff ? 0 : bi);
   }
 }
 
@@ -537,7 +563,10 @@ int b200_argmax(const float* logits, int64_t row_stride, float* out_val, int64_t
   B200_REQUIRE(logits && out_idx, "argmax: null pointer");
   B200_REQUIRE(V > 0, "argmax: V must be positive");
   if (T <= 0) return B200_OK;
-  B200_CUDA_OK(launch_kernel(argmax_kernel, dim3(T), dim3(1024), 0, (cudaStream_t)stream, logits, row_stride, out_val, out_idx, V, idx_offset));
+  // short rows (unit-test vocabularies) do not need the cluster; the headline vocabulary gets ARGMAX_CL CTAs per row
+  const int cl = V >= 16384 ? ARGMAX_CL : 1;
+  B200_CUDA_OK(launch_kernel_cluster(argmax_kernel, dim3(T * cl), dim3(ARGMAX_THREADS), 0, cl, (cudaStream_t)stream, logits,
+                                     row_stride, out_val, out_idx, V, idx_offset));
   return B200_OK;
 }
 
