@@ -1,6 +1,7 @@
 """Oracle (test infrastructure): block-KV paged attention, decode and prefix-cached prefill.
 
-PARITY UNPINNED for the arithmetic (the reference runs it inside NxDI).  The
+Arithmetic pinned through llama_ref to HF transformers' eager attention (tests/test_oracle_hf_pin.py; the reference
+runs it inside NxDI).  The
 *inputs* follow the reference's host contract exactly:
   block_tables [B, max_model_len // bs] right-padded with 0 (RUNNER:746-752, 812-817),
   full_context_lens = position + 1, computed_context_lens = position (RUNNER:786-787)

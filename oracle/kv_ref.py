@@ -1,6 +1,6 @@
 """Oracle (test infrastructure): block-KV cache write, RoPE, and small glue ops.
 
-PARITY UNPINNED for the arithmetic (see oracle/__init__.py): the reference's KV
+Arithmetic (RoPE, RMSNorm, SiLU) pinned through llama_ref to HF transformers (see oracle/__init__.py): the reference's KV
 write happens inside NxDI's compiled graph.  What the reference fixes -- and what
 this file restates -- is the *indexing contract* of its host side:
   * slot = block_id * block_size + offset   (RUNNER:757-763, 819-823)

@@ -1,6 +1,6 @@
 """Oracle (test infrastructure): one Llama/Qwen2 decoder forward over the block-KV cache.
 
-PARITY UNPINNED for the arithmetic.  This is the CPU restatement of what the
+Arithmetic PINNED to HF transformers (tests/golden/hf_golden.json, tests/test_oracle_hf_pin.py).  This is the CPU restatement of what the
 reference's ``self.model(...)`` call (RUNNER:517-530 -> LOADER:336-348) does inside
 NxDI: embedding -> L x (RMSNorm -> qkv -> RoPE -> KV write by slot_mapping -> paged
 attention via block_tables -> o_proj -> +res -> RMSNorm -> gate/up -> SiLU*up -> down
@@ -34,6 +34,10 @@ class RefConfig:
     quant: str = "bf16"  # "bf16" | "fp8" (W8A8 per-channel) | "int8" (W8A8) | "int8_wo"
     max_pos: int = 2048
     block_size: int = 32
+    # dtype of activations and of the KV pools.  bf16 = the rounding points of the CUDA path (what the GPU tests compare
+    # with); float32 = no intermediate rounding, used only by tests/test_oracle_hf_pin.py to pin the ALGORITHM (RoPE
+    # convention, GQA mapping, norm placement, paged gather, causal mask, quantisation rule) against HF transformers.
+    act_dtype: torch.dtype = torch.bfloat16
 
 
 class RefLinear:
@@ -57,7 +61,8 @@ class RefLinear:
             self.wq = self.wq.to(torch.float64)
         return self
 
-    def __call__(self, x, residual=None, out_dtype=torch.bfloat16):
+    def __call__(self, x, residual=None, out_dtype=None):
+        out_dtype = x.dtype if out_dtype is None else out_dtype
         if self.quant == "bf16":
             return quant_ref.gemm_ref(x, self.w, self.bias, residual, out_dtype)
         if self.quant == "int8_wo":
@@ -87,13 +92,13 @@ class RefLlama:
             )
         self.cos, self.sin = kv_ref.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling)
         shp = (num_blocks, cfg.block_size, cfg.num_kv_heads, cfg.head_dim)
-        self.k_pools = [torch.zeros(shp, dtype=torch.bfloat16) for _ in range(cfg.layers)]
-        self.v_pools = [torch.zeros(shp, dtype=torch.bfloat16) for _ in range(cfg.layers)]
+        self.k_pools = [torch.zeros(shp, dtype=cfg.act_dtype) for _ in range(cfg.layers)]
+        self.v_pools = [torch.zeros(shp, dtype=cfg.act_dtype) for _ in range(cfg.layers)]
 
     def _forward(self, tokens, positions, slot_mapping, attn):
         c = self.cfg
         t = tokens.numel()
-        x = self.embed[tokens.reshape(-1)]
+        x = self.embed[tokens.reshape(-1)].to(c.act_dtype)
         qd, kd = c.num_q_heads * c.head_dim, c.num_kv_heads * c.head_dim
         scale = c.head_dim**-0.5
         for li, L in enumerate(self.layers):
@@ -127,10 +132,12 @@ class RefLlama:
         logits = self._logits(x)
         return kv_ref.argmax_ref(logits), logits
 
-    def prefill(self, prompt_tokens, block_table_row, slot_mapping_sliced, computed_len: int):
+    def prefill(self, prompt_tokens, block_table_row, slot_mapping_sliced, computed_len: int, all_logits: bool = False):
         """Batch-1 prefix-cached prefill (SCHED:116).  ``prompt_tokens`` is the FULL prompt as the
         reference passes it (RUNNER:721); only the uncached suffix is computed; ``slot_mapping_sliced``
-        is the reference's slice that starts at the first uncached token (RUNNER:757-763)."""
+        is the reference's slice that starts at the first uncached token (RUNNER:757-763).
+        all_logits: return the logits of every computed position [S_new, V] (teacher-forced replay in the tests)
+        instead of the last one (what the reference samples from, LOADER:350-365)."""
         s = prompt_tokens.numel()
         new = prompt_tokens[computed_len:]
         positions = torch.arange(computed_len, s)
@@ -140,5 +147,5 @@ class RefLlama:
             return attn_ref.paged_attention_prefill_ref(q, kp, vp, block_table_row, computed_len, scale)
 
         x = self._forward(new, positions, slots, attn)
-        logits = self._logits(x[-1:])
+        logits = self._logits(x if all_logits else x[-1:])
         return kv_ref.argmax_ref(logits), logits

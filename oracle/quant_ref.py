@@ -1,7 +1,8 @@
 """Oracle (test infrastructure): symmetric per-channel weight quantisation and the W8A8 /
 weight-only GEMMs.
 
-PARITY UNPINNED (see oracle/__init__.py).  The reference only forwards config keys
+GEMM arithmetic pinned through llama_ref to HF transformers (+ fake-quant hooks); the quantisation RULE itself has no
+external reference (see oracle/__init__.py).  The reference only forwards config keys
 (`quantized`, `quantization_type`, `quantization_dtype`; LOADER:885-898) to NxDI.
 Restated from the published symmetric scheme:
   scale[n] = amax_k |W[n,k]| / qmax     qmax = 127 (int8) | 448 (OCP e4m3fn)

@@ -2,7 +2,8 @@
 
 Reference side that IS visible and pinned (tests/golden/index_golden.json "sampling" cases, generated from
 RUNNER:1106-1140): the [B,3] (top_k, top_p, temperature) rows -> oracle/index_ref.sampling_params_rows.
-The sampler itself lives in NxDI (`self.model.sample`, LOADER:367-382; absent here) -> PARITY UNPINNED; this file
+The sampler itself lives in NxDI (`self.model.sample`, LOADER:367-382; absent here); the kept-token set / probabilities are pinned to vLLM's own top-k / top-p filter
+(tests/test_oracle_sampling.py), the inverse-CDF draw has no reference (device RNG); this file
 restates the published top-k / temperature / top-p / multinomial scheme in the exact fp32, sequential order the CUDA
 kernels use (csrc/sampling.cu), with the caller's uniform u[b] in place of the device RNG:
   candidates = the 256 largest logits, (value desc, index asc);  k = clamp(top_k, 1, #candidates)

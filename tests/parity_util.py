@@ -87,14 +87,9 @@ def sched_output(new_reqs=(), cached=(), finished=()):
     )
 
 
-def export_hf_checkpoint(full_weights, shape, out_dir, *, shards=2, lm_head=True):
-    """Write the B200 weight dictionary (model.random_init_full_weights layout) as an HF Llama/Qwen2 safetensors
-    checkpoint: separate q/k/v and gate/up tensors under the HF names, split over `shards` files + index json."""
-    import json
-    import os
-
-    from safetensors.torch import save_file
-
+def hf_state_dict(full_weights, shape, *, lm_head=True):
+    """The B200 weight dictionary (model.random_init_full_weights layout) under HF Llama/Qwen2 parameter names:
+    fused qkv / gate-up rows split back into q/k/v and gate/up tensors."""
     qd, kd, I = shape.num_q_heads * shape.head_dim, shape.num_kv_heads * shape.head_dim, shape.intermediate
     sd = {"model.embed_tokens.weight": full_weights["embed"], "model.norm.weight": full_weights["final_norm"]}
     if lm_head:
@@ -110,6 +105,18 @@ def export_hf_checkpoint(full_weights, shape, out_dir, *, shards=2, lm_head=True
         if "bqkv" in lw:
             bq, bk, bv = lw["bqkv"].split([qd, kd, kd])
             sd.update({p + "self_attn.q_proj.bias": bq, p + "self_attn.k_proj.bias": bk, p + "self_attn.v_proj.bias": bv})
+    return sd
+
+
+def export_hf_checkpoint(full_weights, shape, out_dir, *, shards=2, lm_head=True):
+    """Write the B200 weight dictionary as an HF Llama/Qwen2 safetensors checkpoint: separate q/k/v and gate/up tensors
+    under the HF names, split over `shards` files + index json."""
+    import json
+    import os
+
+    from safetensors.torch import save_file
+
+    sd = hf_state_dict(full_weights, shape, lm_head=lm_head)
     os.makedirs(out_dir, exist_ok=True)
     names = sorted(sd)
     weight_map = {}

@@ -60,3 +60,30 @@ def test_merging_shards_equals_unsharded():
     a, _ = S.sample_candidates_ref(val, idx, params, u)
     b, _ = S.sample_candidates_ref(gv, gi, params, u)
     assert np.array_equal(a, b)
+
+
+def test_kept_distribution_matches_vllm_sampler_filter():
+    """Pin the sampler oracle to vLLM's own top-k / top-p filter -- what the reference's CPU sampling path runs
+    (RUNNER:1142-1239 -> vllm.v1.sample.sampler.Sampler -> apply_top_k_top_p): for rows of (top_k, top_p, temperature)
+    the oracle, swept over a grid of uniforms, must draw exactly the tokens vLLM's filter keeps, each with the
+    probability of vLLM's masked softmax (the inverse-CDF draw itself has no reference: the device RNG is NxDI's)."""
+    import torch
+    from vllm.v1.sample.ops.topk_topp_sampler import apply_top_k_top_p_pytorch
+
+    b, v, grid = 6, 3000, 2048
+    x = _logits(b, v, 5)
+    params = np.array([[40, 0.9, 0.8], [256, 0.5, 1.0], [5, 1.0, 1.3], [100, 0.95, 0.6], [256, 1.0, 1.0], [17, 0.3, 2.0]],
+                      dtype=np.float32)
+    val, idx = S.topk_candidates_ref(x)
+    want = apply_top_k_top_p_pytorch(torch.tensor(x) / torch.tensor(params[:, 2:3]), torch.tensor(params[:, 0]).long(),
+                                     torch.tensor(params[:, 1]), allow_cpu_sync=True).softmax(dim=-1).numpy()
+    us = ((np.arange(grid) + 0.5) / grid).astype(np.float32)
+    for r in range(b):
+        ids, _ = S.sample_candidates_ref(np.repeat(val[r:r + 1], grid, 0), np.repeat(idx[r:r + 1], grid, 0),
+                                         np.repeat(params[r:r + 1], grid, 0), us)
+        freq = np.bincount(ids, minlength=v) / grid
+        kept = np.nonzero(want[r] > 0)[0]
+        # support: every drawn token is kept by vLLM; every kept token heavier than one grid cell is drawn
+        assert set(np.nonzero(freq)[0]) <= set(kept), (r, set(np.nonzero(freq)[0]) - set(kept))
+        assert all(freq[t] > 0 for t in kept if want[r, t] > 2.0 / grid)
+        assert np.abs(freq - want[r]).max() <= 2.0 / grid, (r, np.abs(freq - want[r]).max())

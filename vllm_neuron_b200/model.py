@@ -54,13 +54,17 @@ def quantize_weight(w: torch.Tensor, kind: str):
     return q.contiguous(), scale.contiguous()
 
 
-def random_init_full_weights(shape: ModelShape, seed: int = 0, device="cpu", std: float = 0.02):
+def random_init_full_weights(shape: ModelShape, seed: int = 0, device="cpu", std: float = 0.02,
+                             resid_std: float | None = None):
     """Random-init weights of the architecture (HF init: N(0, 0.02^2), norms = 1), full (un-sharded), bf16.
-    Generated on CPU with a seeded generator so every rank / the oracle sees identical values."""
+    Generated on CPU with a seeded generator so every rank / the oracle sees identical values.
+    resid_std: std of the two projections that write into the residual stream (o_proj, down_proj); None = std.
+    (GPT-2 / Megatron / lit-gpt initialise them with std / sqrt(2 L); the same draws are scaled, so a given seed
+    names the same network up to that factor.)"""
     g = torch.Generator(device="cpu").manual_seed(seed)
 
-    def rnd(*s):
-        return (torch.randn(*s, generator=g, dtype=torch.float32) * std).to(torch.bfloat16).to(device)
+    def rnd(*s, sd=None):
+        return (torch.randn(*s, generator=g, dtype=torch.float32) * (std if sd is None else sd)).to(torch.bfloat16).to(device)
 
     qd, kd = shape.num_q_heads * shape.head_dim, shape.num_kv_heads * shape.head_dim
     w = {"embed": rnd(shape.vocab, shape.hidden), "lm_head": rnd(shape.vocab, shape.hidden),
@@ -70,9 +74,9 @@ def random_init_full_weights(shape: ModelShape, seed: int = 0, device="cpu", std
             "input_norm": torch.ones(shape.hidden, dtype=torch.bfloat16, device=device),
             "post_norm": torch.ones(shape.hidden, dtype=torch.bfloat16, device=device),
             "wqkv": rnd(qd + 2 * kd, shape.hidden),
-            "wo": rnd(shape.hidden, qd),
+            "wo": rnd(shape.hidden, qd, sd=resid_std),
             "wgu": rnd(2 * shape.intermediate, shape.hidden),
-            "wdown": rnd(shape.hidden, shape.intermediate),
+            "wdown": rnd(shape.hidden, shape.intermediate, sd=resid_std),
         }
         if shape.qkv_bias:
             lw["bqkv"] = rnd(qd + 2 * kd)
