@@ -13,7 +13,7 @@ from parity_util import device_to_logical_pool, make_vllm_config, sched_output
 pytestmark = pytest.mark.gpu
 
 
-def _run(quant, steps=12, use_graph=True, preset="tiny-test", std=0.05):
+def _run(quant, steps=12, use_graph=True, preset="tiny-test", std=0.05, widen_once=False):
     from vllm_neuron_b200.config import PRESETS
     from vllm_neuron_b200.model import B200CausalLM, random_init_full_weights
     from vllm_neuron_b200.worker.b200_model_runner import B200ModelRunner
@@ -39,6 +39,12 @@ def _run(quant, steps=12, use_graph=True, preset="tiny-test", std=0.05):
                             shape.qkv_bias, quant, mml, bs),
         weights, nb + 1)
 
+    if widen_once:  # large shapes: keep the oracle's weights in its accumulate dtype instead of widening per call
+        for L in ref.layers:
+            for name in ("qkv", "o", "gate_up", "down"):
+                L[name].prepare_f64()
+        ref.lm_head.prepare_f64()
+
     g = torch.Generator().manual_seed(1234)
     free = (torch.randperm(nb, generator=g) + 1).tolist()
     prompts = {"a": torch.randint(0, shape.vocab, (70,), generator=g).tolist(),
@@ -54,6 +60,11 @@ def _run(quant, steps=12, use_graph=True, preset="tiny-test", std=0.05):
                                 shape.intermediate, shape.vocab, shape.rope_theta, shape.rope_scaling, shape.rms_eps,
                                 shape.qkv_bias, "bf16", mml, bs),
             weights, nb + 1)
+        if widen_once:
+            for L in ref_hp.layers:
+                for name in ("qkv", "o", "gate_up", "down"):
+                    L[name].prepare_f64()
+            ref_hp.lm_head.prepare_f64()
 
     def record(logits, hp_logits):
         stats["gpu"].append(model.last_logits.float().cpu().clone())
@@ -127,12 +138,23 @@ def _rms(x):
                                           ("int8_wo", "tiny-test"), ("bf16", "tiny-qwen"), ("int8_wo", "tiny-qwen")])
 def test_greedy_tokens_match_oracle(quant, preset):
     """tiny-qwen = BASELINE config 4's traits at test size: GQA group of 5, qkv bias, INT8 weight-only, ragged vocab."""
-    runner, model, ref, outs, ref_outs, margins, live, blocks = _run(quant, preset=preset)
+    _check_against_oracle(quant, *_run(quant, preset=preset))
+
+
+def test_fp8_parity_at_headline_width():
+    """FP8 W8A8 at the HEADLINE shapes (BASELINE configs[2]): hidden 4096, 32 q / 8 kv heads of 128, intermediate 14336,
+    vocabulary 128256, llama3 RoPE scaling, HF init scale -- the GEMM tiles, split-K plans, attention head geometry and
+    the 128256-wide lm_head / argmax the bench runs, two layers deep so the CPU oracle finishes in minutes.  Same bars
+    as the tiny model: as close to the unquantised oracle as the quantised oracle is, tokens equal outside the band."""
+    _check_against_oracle("fp8", *_run("fp8", steps=3, preset="llama-3.1-8b-2l", std=0.02, widen_once=True), min_tokens=12)
+
+
+def _check_against_oracle(quant, runner, model, ref, outs, ref_outs, margins, live, blocks, min_tokens=40):
     keys = sorted(outs)
     flat_got = [t for k in keys for t in outs[k]]
     flat_ref = [t for k in keys for t in ref_outs[k]]
     flat_margin = [m for k in keys for m in margins[k]]
-    assert len(flat_got) == len(flat_ref) == len(flat_margin) and len(flat_got) > 40
+    assert len(flat_got) == len(flat_ref) == len(flat_margin) and len(flat_got) > min_tokens
     mism = [i for i, (a, b) in enumerate(zip(flat_got, flat_ref)) if a != b]
     st = model.stats
     std = _rms(st["ref"] - st["ref"].mean())
@@ -174,8 +196,21 @@ def test_kv_cache_contents_bit_exact_bf16():
     vd = device_to_logical_pool(model.kv[0][1]).cpu()
     k_match = (kd[used].view(torch.int16) == ref.k_pools[0][used].view(torch.int16)).float().mean().item()
     v_match = (vd[used].view(torch.int16) == ref.v_pools[0][used].view(torch.int16)).float().mean().item()
-    # GEMM accumulation order differs (tcgen05 vs CPU), so bf16 roundings can flip on rare elements; slots must agree
+    # The KV write itself is bit-exact (tests/test_gpu_kv.py: same qkv in, identical pools out).  Here the qkv rows come
+    # from the tcgen05 GEMM, whose fp32 accumulation order differs from the oracle's fp64 sum: a value within that
+    # distance of a bf16 rounding boundary lands on the neighbouring code.  So: >= 99.5 % of the elements identical, and
+    # every other V element exactly ONE bf16 code away (an indexing error would show as arbitrary differences).
     assert k_match > 0.995 and v_match > 0.995, (k_match, v_match)
+
+    def ulp_dist(a, b):  # distance in bf16 codes (sign-magnitude bits mapped to a monotone integer line)
+        ia, ib = a.view(torch.int16).int(), b.view(torch.int16).int()
+        ia = torch.where(ia < 0, -(ia & 0x7FFF), ia)
+        ib = torch.where(ib < 0, -(ib & 0x7FFF), ib)
+        return (ia - ib).abs().max().item()
+
+    assert ulp_dist(vd[used], ref.v_pools[0][used]) <= 1
+    # K went through the rotation after the flip: x1*cos - x2*sin can cancel, so one input code may become a few
+    assert ulp_dist(kd[used], ref.k_pools[0][used]) <= 8
     assert (kd[0] == 0).all() and (vd[0] == 0).all()  # null block never written
     unused = [b for b in range(1, model.num_blocks) if b not in used]
     assert (kd[unused] == 0).all()  # nothing leaked outside the allocated blocks

@@ -80,6 +80,9 @@ PRESETS = {
     "qwen2.5-32b": ModelShape("Qwen2.5-32B", 5120, 64, 40, 8, 128, 27648, 152064, 1000000.0, None, 1e-6, True),
     # configs[4]
     "llama-3.3-70b": ModelShape("Llama-3.3-70B", 8192, 80, 64, 8, 128, 28672, 128256, 500000.0, _LLAMA3_SCALING, 1e-5),
+    # parity at the headline WIDTH: Llama-3.1-8B's per-layer dimensions (and vocabulary), two layers deep, so the CPU
+    # oracle still finishes in minutes (tests/test_gpu_model.py::test_fp8_parity_at_headline_width)
+    "llama-3.1-8b-2l": ModelShape("Llama-3.1-8B-2L", 4096, 2, 32, 8, 128, 14336, 128256, 500000.0, _LLAMA3_SCALING, 1e-5),
     # unit-test size
     "tiny-test": ModelShape("tiny-test", 256, 2, 8, 2, 64, 512, 1024, 10000.0, None, 1e-5),
     # unit-test size with Qwen2's traits: 5 query heads per kv head, qkv bias, vocab not a multiple of the GEMM tile
