@@ -49,7 +49,7 @@ def attn_algorithmic_bytes(ctx_lens, hq, hkv, d, kv_bytes=2):
 
 def step_algorithmic_bytes(shape, quant, b, ctx, tp=1):
     """Weights + KV that one decode step must stream from HBM per GPU (lower bound used for the step roofline)."""
-    wb = 1 if quant in ("fp8", "int8") else 2
+    wb = 1 if quant in ("fp8", "int8", "int8_wo") else 2
     qd, kd = shape.num_q_heads * shape.head_dim, shape.num_kv_heads * shape.head_dim
     per_layer = ((qd + 2 * kd) * shape.hidden + shape.hidden * qd + 2 * shape.intermediate * shape.hidden
                  + shape.hidden * shape.intermediate) * wb
@@ -60,49 +60,76 @@ def step_algorithmic_bytes(shape, quant, b, ctx, tp=1):
 
 # ---------------------------------------------------------------------------------------------- clocks
 class ClockSampler:
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock / power / throttle reasons of this rank's GPU, sampled through NVML from a thread of THIS process every
+    few milliseconds across warm-up and the timed region (nvidia-smi -lms cannot place a sample inside a 60 ms region).
+    `mark()` brackets the timed region; the record reports the samples taken inside it (falling back to all samples)."""
 
-    def __init__(self, gpu_index: int):
-        self.idx = gpu_index
-        self.proc = None
+    REASONS = (("hw_slowdown", "nvmlClocksEventReasonHwSlowdown"), ("hw_thermal_slowdown", "nvmlClocksEventReasonHwThermalSlowdown"),
+               ("sw_thermal_slowdown", "nvmlClocksEventReasonSwThermalSlowdown"), ("sw_power_cap", "nvmlClocksEventReasonSwPowerCap"),
+               ("hw_power_brake", "nvmlClocksEventReasonHwPowerBrakeSlowdown"))
+
+    def __init__(self, gpu_index: int, period_s: float = 0.004):
+        self.idx, self.period = gpu_index, period_s
+        self.samples, self.marks, self.err, self._stop, self._th = [], [], None, False, None
+
+    def _loop(self):
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            # LOCAL_RANK indexes the visible devices; NVML indexes physical ones
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = self.idx
+            if vis:
+                ids = [v.strip() for v in vis.split(",") if v.strip()]
+                if self.idx < len(ids) and ids[self.idx].isdigit():
+                    phys = int(ids[self.idx])
+            h = nv.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            masks = [(n, getattr(nv, a)) for n, a in self.REASONS if hasattr(nv, a)]
+            while not self._stop:
+                t = time.perf_counter()
+                mhz = float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                try:
+                    r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                except Exception:
+                    r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                try:
+                    pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+                except Exception:
+                    pw = None
+                self.samples.append((t, mhz, pw, tuple(n for n, m in masks if r & m)))
+                time.sleep(self.period)
+        except Exception as e:  # no NVML: the record says so, the bench goes on
+            self.err = f"{type(e).__name__}: {e}"
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.idx)],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-        except Exception:
-            self.proc = None
+        import threading
+
+        self._th = threading.Thread(target=self._loop, daemon=True)
+        self._th.start()
         return self
 
+    def mark(self):
+        self.marks.append(time.perf_counter())
+
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            out, _ = self.proc.communicate(timeout=5)
-        except Exception:
-            self.proc.kill()
-            out = ""
-        sm, mx, pw, reasons = [], [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in out.splitlines():
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 8:
-                continue
-            try:
-                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
-            except ValueError:
-                continue
-            for n, v in zip(names, f[4:8]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm),
-                "reasons": sorted(reasons)}
+        self._stop = True
+        if self._th is not None:
+            self._th.join(timeout=2)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [self.err or "no samples"]}
+        inside = self.samples
+        if len(self.marks) >= 2:
+            sel = [x for x in self.samples if self.marks[0] <= x[0] <= self.marks[-1]]
+            inside = sel or self.samples
+        sm = [x[1] for x in inside]
+        pw = [x[2] for x in inside if x[2] is not None]
+        reasons = sorted({n for x in inside for n in x[3]})
+        return {"sm_mhz": statistics.median(sm), "sm_min_mhz": min(sm), "sm_max_mhz": getattr(self, "max_mhz", max(sm)),
+                "power_w_max": max(pw) if pw else None, "samples": len(inside), "samples_total": len(self.samples),
+                "source": "NVML, in-process thread, timed region" if inside is not self.samples else "NVML, whole run",
+                "reasons": reasons}
 
 
 # ---------------------------------------------------------------------------------------------- CPU leg (oracle)
@@ -207,7 +234,7 @@ def run_reference(args, shape):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": args.quant, "data": "synthetic (random-init weights, random KV, random tokens)",
-        "config": workload_config(args, shape, 1),
+        "config": workload_config(args, shape, args.gpus),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -216,12 +243,115 @@ def run_reference(args, shape):
 
 
 def workload_config(args, shape, tp):
+    kind = {"bf16": "bf16", "fp8": "fp8 per-channel W8A8", "int8": "int8 per-channel W8A8",
+            "int8_wo": "int8 per-channel weight-only"}[args.quant]
     return {
-        "workload": f"{shape.name} {args.quant} per-channel W8A8 block-KV paged decode" if args.quant != "bf16"
-        else f"{shape.name} bf16 block-KV paged decode",
+        "workload": f"{shape.name} {kind} block-KV paged decode",
         "global_batch": args.batch, "context": args.ctx, "block_size": BS, "parallelism": f"tp{tp}",
         "kv_dtype": "bf16", "l2": "inputs larger than L2 (weights + KV streamed per step >> 126 MB)",
     }
+
+
+def fill_kv_pools(model, shape, rank, world, blocks=None):
+    """Synthetic KV ~ N(0,1) (seed 11), drawn per (layer, GLOBAL kv head): a rank of a TP=N run holds exactly
+    the values the TP=1 pool holds for its heads, so runs at different N work on the same data (and can be compared).
+    blocks: only these block ids (the parity check's scratch blocks); None = the whole pool.  Block 0 stays zero."""
+    import torch
+
+    dev = model.device
+    g = torch.Generator(device=dev)
+    for li, kv in enumerate(model.kv):
+        for hl in range(model.hkv):
+            g.manual_seed(11 + 1009 * li + (rank * model.hkv + hl))
+            n = kv.shape[1] if blocks is None else len(blocks)
+            vals = torch.randn((2, n, kv.shape[3], kv.shape[4]), generator=g, device=dev, dtype=torch.float32).to(kv.dtype)
+            if blocks is None:
+                kv[:, :, hl] = vals
+            else:
+                kv[:, blocks, hl] = vals
+        if blocks is None:
+            kv[:, 0].zero_()  # null block
+
+
+def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, ctx=96):
+    """TP=N against TP=1 in this very process, before the timed region: rank 0 also builds the SAME weights un-sharded
+    (weights depend on (seed, tensor, layer) only); both models run `steps` teacher-forced decode steps of the whole
+    batch from the same state (context `ctx`, scratch blocks 1 .. B*nblk filled with the same per-global-head values).
+    The TP=N sampled ids must equal TP=1's wherever TP=1's own top-2 margin is outside 8x the measured logit rms
+    difference; otherwise every rank exits with status 3.  Returns the record that goes into the JSON line."""
+    import torch
+    import torch.distributed as dist
+
+    from vllm_neuron_b200.model import B200CausalLM
+
+    if args.tp_check == "off":
+        return {"tp_check": "off"}
+    b = args.batch
+    nblk = -(-(ctx + steps + 1) // BS)
+    blocks = list(range(1, b * nblk + 1))
+    bt = torch.zeros_like(model.block_table)
+    bt[:, :nblk] = torch.tensor(blocks, dtype=torch.int32, device=dev).reshape(b, nblk)
+    wb = 1 if args.quant != "bf16" else 2
+    qd, kd = shape.num_q_heads * shape.head_dim, shape.num_kv_heads * shape.head_dim
+    need = ((qd + 2 * kd + qd) * shape.hidden + 3 * shape.intermediate * shape.hidden) * wb * shape.layers \
+        + shape.vocab * shape.hidden * (wb + 2) + shape.layers * 2 * (b * nblk + 1) * kd * BS * 2 + (6 << 30)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    ref = None
+    if rank == 0:
+        free, _ = torch.cuda.mem_get_info(dev)
+        if free < need:
+            status[0] = 2
+        else:
+            ref = B200CausalLM(shape, None, quant=args.quant, num_blocks=b * nblk + 1, max_num_seqs=b,
+                               max_model_len=nblk * BS, block_size=BS, device=dev, seed=0)
+    dist.broadcast(status, src=0)
+    if int(status.item()) == 2:
+        return {"tp_check": f"skipped: the un-sharded model ({need / 2**30:.0f} GiB) does not fit beside rank 0's shard"}
+    fill_kv_pools(model, shape, rank, world, blocks=blocks)
+    model.block_table.copy_(bt)
+    tok = torch.randint(0, shape.vocab, (b,), generator=torch.Generator().manual_seed(4321)).to(dev)
+    if ref is not None:
+        fill_kv_pools(ref, shape, 0, 1, blocks=blocks)
+        ref.block_table.copy_(bt[:, :ref.max_blocks])
+    rec = {"tp_check": "ok", "steps": steps, "context": ctx, "tokens_compared": 0, "tokens_equal": 0, "logit_rms_err": [],
+           "logit_std": []}
+    for st in range(steps):
+        bufs.tokens.copy_(tok)
+        model.num_tokens.fill_(ctx + st + 1)
+        got = model.decode_step(b, advance=False, use_graph=False).clone()
+        l_tp = model.last_logits.float()
+        if ref is not None:
+            rb = ref.decode_buffers(b)
+            rb.tokens.copy_(tok)
+            ref.num_tokens.fill_(ctx + st + 1)
+            want = ref.decode_step(b, advance=False, use_graph=False).clone()
+            l_ref = ref.last_logits.float()
+            shard = l_ref[:, model.vocab_offset: model.vocab_offset + l_tp.shape[1]]
+            err = (l_tp - shard).pow(2).mean().sqrt().item()
+            std = l_ref.std().item()
+            top2 = l_ref.topk(2, dim=-1).values
+            margin = top2[:, 0] - top2[:, 1]
+            bad = (got != want) & (margin > 8 * err)
+            rec["tokens_compared"] += b
+            rec["tokens_equal"] += int((got == want).sum().item())
+            rec["logit_rms_err"].append(round(err, 5))
+            rec["logit_std"].append(round(std, 4))
+            bar = 0.03 if args.quant in ("bf16", "int8_wo") else 0.3
+            if bad.any() or not err < bar * std:
+                status[0] = 3
+                rec["tp_check"] = (f"FAILED at step {st}: {int(bad.sum().item())} tokens differ outside the margin guard, logit rms "
+                                   f"err {err:.3e} vs std {std:.3f}")
+            tok = want  # teacher-force both models with the TP=1 tokens
+        dist.broadcast(tok, src=0)
+        dist.broadcast(status, src=0)
+        if int(status.item()) == 3:
+            if rank == 0:
+                print(json.dumps({"error": "tp parity check failed", "parity": rec}), flush=True)
+            sys.stdout.flush()
+            os._exit(3)
+    del ref
+    torch.cuda.empty_cache()
+    return rec
 
 
 # ---------------------------------------------------------------------------------------------- B200 arm
@@ -235,8 +365,6 @@ def run_b200(args, shape):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO") and not os.environ.get("B200_KEEP_NCCL_DEBUG"):
-        os.environ["NCCL_DEBUG"] = "WARN"  # NCCL's banner goes to stdout, which must carry exactly one JSON line
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch N>1 with torchrun (one rank per GPU)"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -259,10 +387,7 @@ def run_b200(args, shape):
     perm = torch.randperm(num_blocks - 1, generator=torch.Generator().manual_seed(7)) + 1
     bt_host = perm.reshape(b, max_blocks).to(torch.int32)
     model.block_table.copy_(bt_host)
-    g = torch.Generator(device=dev).manual_seed(11)
-    for kv in model.kv:
-        kv.normal_(generator=g)
-        kv[:, 0].zero_()  # null block
+    fill_kv_pools(model, shape, rank, world)
     tok_host = torch.randint(0, shape.vocab, (b,), generator=torch.Generator().manual_seed(1234))
     bufs = model.decode_buffers(b)
     bufs.tokens.copy_(tok_host)
@@ -274,21 +399,29 @@ def run_b200(args, shape):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # ---- N > 1: correctness of this very model before anything is timed (TP=N vs TP=1 on rank 0, same weights)
+    parity = tp_parity_check(args, shape, model, bufs, rank, world, dev, group) if world > 1 else None
+    model.block_table.copy_(bt_host)
+    bufs.tokens.copy_(tok_host)
+
     # ---- device-resident decode: CUDA-graph replay, the sampled token and the length advance on the device
+    clocks = ClockSampler(local).start()
     l0 = ops.launch_count()
+    model.num_tokens.fill_(n0)
     model.decode_step(b, advance=True, use_graph=True)  # captures (one eager warm-up pass + one capture pass) and replays
     launches_per_step = (ops.launch_count() - l0) // 2
     model.num_tokens.fill_(n0)
     for _ in range(w_steps):
         model.decode_step(b, advance=True, use_graph=True)
     barrier()
-    clocks = ClockSampler(local).start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clocks.mark()
     e0.record()
     for _ in range(k_steps):
         model.decode_step(b, advance=True, use_graph=True)
     e1.record()
     barrier()
+    clocks.mark()
     ms = e0.elapsed_time(e1)
     clk = clocks.stop()
     if world > 1:
@@ -350,9 +483,10 @@ def run_b200(args, shape):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": k_steps, "warmup": w_steps,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": args.quant, "data": "synthetic (random-init weights, N(0,1) KV pool, random tokens, permuted block ids)",
-            "config": dict(workload_config(args, shape, world), mean_context_in_timed_region=mean_ctx,
-                           max_model_len=max_model_len, num_blocks=num_blocks, cuda_graph=True),
-            "clocks": clk, "e2e": e2e, "gpu_launches": launches_per_step * k_steps,
+            "config": workload_config(args, shape, world),  # the same dict the reference arm prints
+            "run": {"mean_context_in_timed_region": mean_ctx, "max_model_len": max_model_len, "num_blocks": num_blocks,
+                    "cuda_graph": True},
+            "clocks": clk, "parity": parity, "e2e": e2e, "gpu_launches": launches_per_step * k_steps,
             "launches_per_step": launches_per_step, "roofline": roofline, "cpu_baseline": cpu, "kernels": kernels,
         }
         print(json.dumps(line), flush=True)
@@ -418,6 +552,8 @@ def run_e2e(args, shape, model, bt_host, dev, rank, world, group, barrier, n_sta
     override = {} if args.quant == "bf16" else {
         "quantized": True, "quantization_dtype": "f8e4m3" if args.quant == "fp8" else "int8",
         "quantization_type": "per_channel_symmetric"}
+    if args.quant == "int8_wo":
+        override["weight_only"] = True
     cfg = make_vllm_config(shape, max_num_seqs=b, max_model_len=model.max_model_len,
                            num_gpu_blocks_override=model.num_blocks, tp=world, override=override)
     runner = B200ModelRunner(cfg, dev, model=model, tp_rank=rank, tp_size=world, tp_group=group)
@@ -465,7 +601,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--model", default="llama-3.1-8b")
-    ap.add_argument("--quant", default="fp8", choices=["bf16", "fp8", "int8"])
+    ap.add_argument("--quant", default="fp8", choices=["bf16", "fp8", "int8", "int8_wo"])
+    ap.add_argument("--tp-check", default="auto", choices=["auto", "off"],
+                    help="N>1: before timing, 4 teacher-forced decode steps of the TP=N model against a TP=1 model of the "
+                         "same weights on rank 0 (exit 3 on a mismatch outside the margin guard); off skips it")
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--ctx", type=int, default=2048)
     ap.add_argument("--e2e-steps", type=int, default=32)

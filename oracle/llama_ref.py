@@ -38,18 +38,19 @@ class RefConfig:
     # with); float32 = no intermediate rounding, used only by tests/test_oracle_hf_pin.py to pin the ALGORITHM (RoPE
     # convention, GQA mapping, norm placement, paged gather, causal mask, quantisation rule) against HF transformers.
     act_dtype: torch.dtype = torch.bfloat16
+    quant_type: str = "per_channel_symmetric"  # or "per_tensor_symmetric" (LOADER:893-895)
 
 
 class RefLinear:
-    def __init__(self, w, quant: str, bias=None):
+    def __init__(self, w, quant: str, bias=None, tensor_rows=None):
         self.quant = quant
         self.bias = bias
         if quant == "bf16":
             self.w = w
         elif quant in ("fp8", "int8"):
-            self.wq, self.ws = quant_ref.quantize_weight_per_channel(w, quant)
+            self.wq, self.ws = quant_ref.quantize_weight_per_channel(w, quant, tensor_rows)
         elif quant == "int8_wo":
-            self.wq, self.ws = quant_ref.quantize_weight_per_channel(w, "int8")
+            self.wq, self.ws = quant_ref.quantize_weight_per_channel(w, "int8", tensor_rows)
         else:
             raise ValueError(quant)
 
@@ -77,17 +78,24 @@ class RefLlama:
         q = cfg.quant
         self.embed = weights["embed"]
         self.final_norm = weights["final_norm"]
-        self.lm_head = RefLinear(weights["lm_head"], q if quant_lm_head else "bf16")
+        pt = cfg.quant_type == "per_tensor_symmetric"
+        assert pt or cfg.quant_type == "per_channel_symmetric", cfg.quant_type
+        qd, kd, it = cfg.num_q_heads * cfg.head_dim, cfg.num_kv_heads * cfg.head_dim, cfg.intermediate
+        tr_qkv = [(0, qd), (qd, qd + kd), (qd + kd, qd + 2 * kd)] if pt else None  # q / k / v are separate HF tensors
+        tr_gu = [(0, it), (it, 2 * it)] if pt else None
+        tr_h = [(0, cfg.hidden)] if pt else None
+        self.lm_head = RefLinear(weights["lm_head"], q if quant_lm_head else "bf16",
+                                 tensor_rows=[(0, cfg.vocab)] if pt else None)
         self.layers = []
         for lw in weights["layers"]:
             self.layers.append(
                 {
                     "input_norm": lw["input_norm"],
                     "post_norm": lw["post_norm"],
-                    "qkv": RefLinear(lw["wqkv"], q, lw.get("bqkv")),
-                    "o": RefLinear(lw["wo"], q),
-                    "gate_up": RefLinear(lw["wgu"], q),
-                    "down": RefLinear(lw["wdown"], q),
+                    "qkv": RefLinear(lw["wqkv"], q, lw.get("bqkv"), tr_qkv),
+                    "o": RefLinear(lw["wo"], q, tensor_rows=tr_h),
+                    "gate_up": RefLinear(lw["wgu"], q, tensor_rows=tr_gu),
+                    "down": RefLinear(lw["wdown"], q, tensor_rows=tr_h),
                 }
             )
         self.cos, self.sin = kv_ref.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling)

@@ -20,8 +20,12 @@ FP8_MAX = 448.0
 INT8_MAX = 127.0
 
 
-def _quant_rows(x32, kind: str):
+def _quant_rows(x32, kind: str, tensor_rows=None):
     amax = x32.abs().amax(dim=-1)
+    if tensor_rows is not None:  # per_tensor_symmetric: each listed row range (one original tensor) shares one scale
+        amax = amax.clone()
+        for a, b in tensor_rows:
+            amax[a:b] = amax[a:b].max()
     qmax = FP8_MAX if kind == "fp8" else INT8_MAX
     scale = torch.div(amax, torch.full_like(amax, qmax)).float()  # tensor/tensor: true IEEE division
     scale = torch.where(amax > 0, scale, torch.ones_like(scale))
@@ -35,9 +39,10 @@ def _quant_rows(x32, kind: str):
     return q, scale
 
 
-def quantize_weight_per_channel(w, kind: str):
-    """w [N, K] (bf16/fp32) -> (Wq [N,K] fp8|int8, scale [N] fp32)."""
-    return _quant_rows(w.float(), kind)
+def quantize_weight_per_channel(w, kind: str, tensor_rows=None):
+    """w [N, K] (bf16/fp32) -> (Wq [N,K] fp8|int8, scale [N] fp32).  tensor_rows: 'per_tensor_symmetric' (the
+    reference's default quantization_type, LOADER:893-895) -- one scale per listed row range, kept as scale[n]."""
+    return _quant_rows(w.float(), kind, tensor_rows)
 
 
 def quantize_act_per_token(x, kind: str):

@@ -13,7 +13,8 @@ from parity_util import device_to_logical_pool, make_vllm_config, sched_output
 pytestmark = pytest.mark.gpu
 
 
-def _run(quant, steps=12, use_graph=True, preset="tiny-test", std=0.05, widen_once=False):
+def _run(quant, steps=12, use_graph=True, preset="tiny-test", std=0.05, widen_once=False,
+         quant_type="per_channel_symmetric"):
     from vllm_neuron_b200.config import PRESETS
     from vllm_neuron_b200.model import B200CausalLM, random_init_full_weights
     from vllm_neuron_b200.worker.b200_model_runner import B200ModelRunner
@@ -22,12 +23,13 @@ def _run(quant, steps=12, use_graph=True, preset="tiny-test", std=0.05, widen_on
     bs, mml, mns, nb = 32, 256, 4, 40
     weights = random_init_full_weights(shape, seed=3, std=std)
     override = {} if quant == "bf16" else {"quantized": True, "quantization_dtype": "f8e4m3" if quant == "fp8" else "int8",
-                                            "quantization_type": "per_channel_symmetric"}
+                                            "quantization_type": quant_type}
     if quant == "int8_wo":
         override["weight_only"] = True
     cfg = make_vllm_config(shape, max_num_seqs=mns, max_model_len=mml, num_gpu_blocks_override=nb + 1, override=override,
                            enforce_eager=not use_graph)
-    model = B200CausalLM(shape, weights, quant=quant, num_blocks=nb + 1, max_num_seqs=mns, max_model_len=mml)
+    model = B200CausalLM(shape, weights, quant=quant, num_blocks=nb + 1, max_num_seqs=mns, max_model_len=mml,
+                         quant_type=quant_type)
     runner = B200ModelRunner(cfg, torch.device("cuda"), model=model)
     runner.load_model(load_dummy_weights=True)
     runner.initialize_kv_cache(num_blocks=nb + 1)
@@ -36,7 +38,7 @@ def _run(quant, steps=12, use_graph=True, preset="tiny-test", std=0.05, widen_on
     ref = llama_ref.RefLlama(
         llama_ref.RefConfig(shape.hidden, shape.layers, shape.num_q_heads, shape.num_kv_heads, shape.head_dim,
                             shape.intermediate, shape.vocab, shape.rope_theta, shape.rope_scaling, shape.rms_eps,
-                            shape.qkv_bias, quant, mml, bs),
+                            shape.qkv_bias, quant, mml, bs, quant_type=quant_type),
         weights, nb + 1)
 
     if widen_once:  # large shapes: keep the oracle's weights in its accumulate dtype instead of widening per call
@@ -139,6 +141,17 @@ def _rms(x):
 def test_greedy_tokens_match_oracle(quant, preset):
     """tiny-qwen = BASELINE config 4's traits at test size: GQA group of 5, qkv bias, INT8 weight-only, ragged vocab."""
     _check_against_oracle(quant, *_run(quant, preset=preset))
+
+
+@pytest.mark.parametrize("quant", ["fp8", "int8_wo"])
+def test_per_tensor_symmetric_matches_oracle(quant):
+    """quantization_type = per_tensor_symmetric, the reference's default (LOADER:893-895): one scale per original tensor
+    (q / k / v, gate / up separately), carried through the same per-row scale vector."""
+    res = _run(quant, steps=6, quant_type="per_tensor_symmetric")
+    model = res[1]
+    sc = model.layers[0]["o"].scale
+    assert torch.all(sc == sc[0])  # one scale for the whole o_proj
+    _check_against_oracle(quant, *res, min_tokens=20)
 
 
 def test_fp8_parity_at_headline_width():

@@ -116,3 +116,37 @@ def test_runner_load_model_opens_checkpoint_and_quantises_once(tmp_path):
     r3 = B200ModelRunner(cfg, torch.device("cpu"))
     r3.load_model()
     assert r3._weights is None
+
+
+def test_per_tensor_symmetric_scales_follow_the_original_tensors():
+    """quantization_type per_tensor_symmetric (the reference's default, LOADER:893-895): one scale per ORIGINAL tensor
+    (q, k, v and gate, up are separate HF tensors), identical between the product quantiser and the oracle's."""
+    import torch
+
+    from oracle import quant_ref
+    from vllm_neuron_b200.model import quantize_weight
+
+    w = (torch.randn(96, 64, generator=torch.Generator().manual_seed(2)) * 0.05).to(torch.bfloat16)
+    rows = [(0, 64), (64, 80), (80, 96)]
+    for kind in ("fp8", "int8"):
+        q, s = quantize_weight(w, kind, rows)
+        for a, b in rows:
+            amax = w[a:b].float().abs().max()
+            assert torch.all(s[a:b] == s[a]) and abs(s[a].item() - amax.item() / (448.0 if kind == "fp8" else 127.0)) < 1e-9
+        q2, s2 = quant_ref.quantize_weight_per_channel(w, kind, rows)
+        assert torch.equal(s, s2) and torch.equal(q.view(torch.uint8), q2.view(torch.uint8))
+        qc, sc = quantize_weight(w, kind)
+        assert not torch.all(sc[:64] == sc[0])  # per channel differs
+
+
+def test_quantization_type_default_and_validation():
+    import pytest
+
+    from vllm_neuron_b200.config import build_config
+
+    kw = dict(tensor_parallel_size=1, max_num_seqs=2, max_model_len=64, block_size=32, enable_prefix_caching=True,
+              num_gpu_blocks_override=None)
+    cfg = build_config(override={"quantized": True, "quantization_dtype": "f8e4m3"}, **kw)
+    assert cfg.quantization_type == "per_tensor_symmetric"  # the reference's default
+    with pytest.raises(ValueError):
+        build_config(override={"quantized": True, "quantization_type": "blockwise"}, **kw)

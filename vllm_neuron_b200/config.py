@@ -195,6 +195,10 @@ def build_config(*, tensor_parallel_size: int, max_num_seqs: int, max_model_len:
             quantization_dtype=merged.pop("quantization_dtype", "int8"),
         )
     cfg.update(merged)
+    if cfg.get("quantized") and cfg.get("quantization_type", "per_channel_symmetric") not in (
+            "per_channel_symmetric", "per_tensor_symmetric"):
+        raise ValueError(f"quantization_type {cfg['quantization_type']!r} is not supported on the B200 path "
+                         "(per_channel_symmetric or per_tensor_symmetric)")
     cfg = handle_pa_num_blocks(num_gpu_blocks_override, cfg, override)
     cfg = validate_config(enable_prefix_caching, max_model_len, block_size, max_num_seqs, num_gpu_blocks_override, cfg)
     known = {f for f in B200Config.__dataclass_fields__ if f != "ignored"}

@@ -181,15 +181,19 @@ def check_modules_to_not_convert(modules_to_not_convert, shape: ModelShape) -> b
     return not mods
 
 
-def save_quantized_checkpoint(src: "HFCheckpointWeights", out_dir: str, kind: str, modules_to_not_convert=()) -> str:
-    """Quantise an HF checkpoint once (symmetric, per output channel; kind 'fp8' | 'int8') and write it as one safetensors
+def save_quantized_checkpoint(src: "HFCheckpointWeights", out_dir: str, kind: str, modules_to_not_convert=(),
+                              quant_type: str = "per_channel_symmetric") -> str:
+    """Quantise an HF checkpoint once (symmetric, per output channel or per tensor; kind 'fp8' | 'int8') and write it as one safetensors
     file per decoder layer + model.safetensors.index.json.  Counterpart of save_quantized_state_dict (LOADER:237-239);
     the result is what `quantized_checkpoints_path` points at."""
     from safetensors.torch import save_file
 
-    from .model import quantize_weight
+    from .model import QUANT_TYPES, quantize_weight
 
     assert kind in ("fp8", "int8")
+    if quant_type not in QUANT_TYPES:
+        raise ValueError(f"quantization_type {quant_type!r} is not supported on the B200 path (one of {QUANT_TYPES})")
+    per_tensor = quant_type == "per_tensor_symmetric"
     os.makedirs(out_dir, exist_ok=True)
     weight_map: dict[str, str] = {}
 
@@ -202,7 +206,7 @@ def save_quantized_checkpoint(src: "HFCheckpointWeights", out_dir: str, kind: st
         if skip_quantization(name, modules_to_not_convert):
             out[name + ".weight"] = w.to(torch.bfloat16)
         else:
-            q, s = quantize_weight(w.to(torch.bfloat16), kind)
+            q, s = quantize_weight(w.to(torch.bfloat16), kind, [(0, w.shape[0])] if per_tensor else None)
             out[name + ".weight"], out[name + ".scale"] = q, s
 
     top = {"model.embed_tokens.weight": src._get("model.embed_tokens.weight").to(torch.bfloat16),
@@ -221,6 +225,6 @@ def save_quantized_checkpoint(src: "HFCheckpointWeights", out_dir: str, kind: st
                 out[p + f"self_attn.{n}_proj.bias"] = src._get(p + f"self_attn.{n}_proj.bias").to(torch.bfloat16)
         put(out, f"model-layer-{li:05d}.safetensors")
     with open(os.path.join(out_dir, "model.safetensors.index.json"), "w") as f:
-        json.dump({"metadata": {"quantization_dtype": kind, "quantization_type": "per_channel_symmetric"},
+        json.dump({"metadata": {"quantization_dtype": kind, "quantization_type": quant_type},
                    "weight_map": weight_map}, f)
     return out_dir

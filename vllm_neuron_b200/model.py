@@ -38,11 +38,21 @@ def rope_tables(head_dim: int, max_pos: int, theta: float, scaling: dict | None,
     return ang.cos().float().contiguous().to(device), ang.sin().float().contiguous().to(device)
 
 
-def quantize_weight(w: torch.Tensor, kind: str):
-    """Offline symmetric per-output-channel quantisation (load time, not the hot path).
-    scale[n] = amax|W[n,:]| / qmax;  fp8: cast RNE saturating to e4m3fn (qmax 448);  int8: round-half-even, clamp 127."""
+QUANT_TYPES = ("per_channel_symmetric", "per_tensor_symmetric")  # LOADER:893-895 (the reference's default is per tensor)
+
+
+def quantize_weight(w: torch.Tensor, kind: str, tensor_rows=None):
+    """Offline symmetric weight quantisation (load time, not the hot path).
+    scale[n] = amax|W[n,:]| / qmax;  fp8: cast RNE saturating to e4m3fn (qmax 448);  int8: round-half-even, clamp 127.
+    tensor_rows = None: per output channel.  tensor_rows = [(r0, r1), ...]: 'per_tensor_symmetric' -- every listed row
+    range is one original tensor (q / k / v, gate / up of a fused matrix) and shares ONE scale, still stored as scale[n]
+    so the GEMM epilogue is the same code."""
     w32 = w.float()
     amax = w32.abs().amax(dim=-1)
+    if tensor_rows is not None:
+        amax = amax.clone()
+        for a, b in tensor_rows:
+            amax[a:b] = amax[a:b].max()
     qmax = 448.0 if kind == "fp8" else 127.0
     # tensor / tensor is a true IEEE division on both CPU and CUDA (tensor / python-scalar may become a reciprocal multiply)
     scale = torch.where(amax > 0, torch.div(amax, torch.full_like(amax, qmax)), torch.ones_like(amax)).float()
@@ -111,7 +121,8 @@ def merge_sharded_argmax(vals: torch.Tensor, idxs: torch.Tensor, vocab: int) -> 
 class _Linear:
     """One (possibly TP-sharded, possibly quantised) weight with its per-channel scale."""
 
-    def __init__(self, w_full: torch.Tensor, quant: str, device, row_slices=None, col_slice=None, bias=None):
+    def __init__(self, w_full: torch.Tensor, quant: str, device, row_slices=None, col_slice=None, bias=None,
+                 tensor_rows=None):
         # quantise the FULL weight first (per-channel scales are properties of the un-sharded matrix), then shard
         if isinstance(w_full, tuple):  # (q, scale) from a quantised checkpoint (loader.py): not quantised again
             wq, ws = w_full
@@ -120,7 +131,7 @@ class _Linear:
                 raise ValueError(f"quantised checkpoint holds {wq.dtype} weights but the configured mode is {quant!r}")
             wq, ws = wq.to(device), ws.float().to(device)
         elif quant in ("fp8", "int8", "int8_wo"):
-            wq, ws = quantize_weight(w_full, "fp8" if quant == "fp8" else "int8")  # on the master weight's device
+            wq, ws = quantize_weight(w_full, "fp8" if quant == "fp8" else "int8", tensor_rows)  # on the master weight's device
             wq, ws = wq.to(device), ws.to(device)
         else:
             wq, ws = w_full.to(device), None
@@ -162,8 +173,12 @@ class B200CausalLM:
     def __init__(self, shape: ModelShape, full_weights: dict | None, *, quant: str = "bf16", num_blocks: int,
                  max_num_seqs: int, max_model_len: int, block_size: int = 32, device="cuda", tp_rank: int = 0,
                  tp_size: int = 1, tp_group=None, quant_lm_head: bool = True, seed: int = 0,
-                 use_peer_exchange: bool = True):
+                 use_peer_exchange: bool = True, quant_type: str = "per_channel_symmetric"):
         assert quant in ("bf16", "fp8", "int8", "int8_wo"), f"unknown quant mode {quant!r}"
+        if quant_type not in QUANT_TYPES:
+            raise ValueError(f"quantization_type {quant_type!r} is not supported on the B200 path (one of {QUANT_TYPES})")
+        self.quant_type = quant_type
+        per_tensor = quant_type == "per_tensor_symmetric"
         assert shape.num_q_heads % tp_size == 0 and shape.num_kv_heads % tp_size == 0, "heads must divide TP"
         assert shape.intermediate % tp_size == 0 and shape.vocab % tp_size == 0
         ops.device_check(torch.device(device).index or 0)
@@ -186,7 +201,14 @@ class B200CausalLM:
         self.embed = full_weights["embed"].to(dev).contiguous()
         self.final_norm = full_weights["final_norm"].to(dev).contiguous()
         v0, v1 = plan["vocab_rows"]
-        self.lm_head = _Linear(full_weights["lm_head"], quant if quant_lm_head else "bf16", dev, row_slices=[(v0, v1)])
+        qd_f, kd_f, i_f = shape.num_q_heads * shape.head_dim, shape.num_kv_heads * shape.head_dim, shape.intermediate
+        # per-tensor scales belong to the ORIGINAL tensors (q / k / v and gate / up are separate HF tensors), not to the
+        # fused matrices or their TP shards
+        tr_qkv = [(0, qd_f), (qd_f, qd_f + kd_f), (qd_f + kd_f, qd_f + 2 * kd_f)] if per_tensor else None
+        tr_gu = [(0, i_f), (i_f, 2 * i_f)] if per_tensor else None
+        tr_h = [(0, shape.hidden)] if per_tensor else None
+        self.lm_head = _Linear(full_weights["lm_head"], quant if quant_lm_head else "bf16", dev, row_slices=[(v0, v1)],
+                               tensor_rows=[(0, shape.vocab)] if per_tensor else None)
         self.vocab_offset = v0
         self.layers = []
         for li in range(shape.layers):
@@ -195,10 +217,10 @@ class B200CausalLM:
                 {
                     "input_norm": lw["input_norm"].to(dev).contiguous(),
                     "post_norm": lw["post_norm"].to(dev).contiguous(),
-                    "qkv": _Linear(lw["wqkv"], quant, dev, row_slices=qkv_rows, bias=lw.get("bqkv")),
-                    "o": _Linear(lw["wo"], quant, dev, col_slice=plan["o_cols"]),
-                    "gu": _Linear(lw["wgu"], quant, dev, row_slices=gu_rows).interleave_gate_up(),
-                    "down": _Linear(lw["wdown"], quant, dev, col_slice=plan["down_cols"]),
+                    "qkv": _Linear(lw["wqkv"], quant, dev, row_slices=qkv_rows, bias=lw.get("bqkv"), tensor_rows=tr_qkv),
+                    "o": _Linear(lw["wo"], quant, dev, col_slice=plan["o_cols"], tensor_rows=tr_h),
+                    "gu": _Linear(lw["wgu"], quant, dev, row_slices=gu_rows, tensor_rows=tr_gu).interleave_gate_up(),
+                    "down": _Linear(lw["wdown"], quant, dev, col_slice=plan["down_cols"], tensor_rows=tr_h),
                 }
             )
             if hasattr(full_weights, "drop"):  # lazy sources (random init, checkpoint reader) free the layer's host copy

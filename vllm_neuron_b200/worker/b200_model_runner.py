@@ -134,12 +134,19 @@ class B200ModelRunner:
         tie = bool(getattr(self.model_config.hf_config, "tie_word_embeddings", False))
         qpath = cfg.quantized_checkpoints_path if cfg.quantized else None
         if qpath:
-            if not os.path.exists(os.path.join(qpath, "model.safetensors.index.json")):
+            # ONE decision for all ranks (a rank arriving after rank 0 has written the index must not skip the barrier):
+            # rank 0 looks, the answer is broadcast, every rank then takes the same branch
+            need = not os.path.exists(os.path.join(qpath, "model.safetensors.index.json"))
+            if self.tp_group is not None:
+                flag = torch.tensor([int(need)], dtype=torch.int32, device=self.device)
+                torch.distributed.broadcast(flag, src=torch.distributed.get_global_rank(self.tp_group, 0), group=self.tp_group)
+                need = bool(flag.item())
+            if need:
                 if self.tp_rank == 0:
                     kind = "fp8" if cfg.quant_mode == "fp8" else "int8"
-                    logger.info("quantising %s (%s, per channel) into %s", path, kind, qpath)
+                    logger.info("quantising %s (%s, %s) into %s", path, kind, cfg.quantization_type, qpath)
                     save_quantized_checkpoint(HFCheckpointWeights(path, self.shape, tie_word_embeddings=tie), qpath, kind,
-                                              cfg.modules_to_not_convert)
+                                              cfg.modules_to_not_convert, cfg.quantization_type)
                 if self.tp_group is not None:
                     torch.distributed.barrier(group=self.tp_group)
             path = qpath
@@ -183,6 +190,7 @@ class B200ModelRunner:
         if self.model is None:
             self.model = B200CausalLM(
                 self.shape, self._weights, quant=self.b200_config.quant_mode, quant_lm_head=self._quant_lm_head,
+                quant_type=self.b200_config.quantization_type if self.b200_config.quantized else "per_channel_symmetric",
                 num_blocks=self.num_blocks,
                 max_num_seqs=self.max_num_reqs, max_model_len=self.max_model_len, block_size=self.block_size,
                 device=self.device, tp_rank=self.tp_rank, tp_size=self.tp_size, tp_group=self.tp_group,
