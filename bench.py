@@ -289,7 +289,7 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
     b = args.batch
     nblk = -(-(ctx + steps + 1) // BS)
     blocks = list(range(1, b * nblk + 1))
-    bt = torch.zeros_like(model.block_table)
+    bt = torch.zeros_like(model.block_table[:b])
     bt[:, :nblk] = torch.tensor(blocks, dtype=torch.int32, device=dev).reshape(b, nblk)
     wb = 1 if args.quant != "bf16" else 2
     qd, kd = shape.num_q_heads * shape.head_dim, shape.num_kv_heads * shape.head_dim
@@ -308,22 +308,22 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
     if int(status.item()) == 2:
         return {"tp_check": f"skipped: the un-sharded model ({need / 2**30:.0f} GiB) does not fit beside rank 0's shard"}
     fill_kv_pools(model, shape, rank, world, blocks=blocks)
-    model.block_table.copy_(bt)
+    model.block_table[:b].copy_(bt)
     tok = torch.randint(0, shape.vocab, (b,), generator=torch.Generator().manual_seed(4321)).to(dev)
     if ref is not None:
         fill_kv_pools(ref, shape, 0, 1, blocks=blocks)
-        ref.block_table.copy_(bt[:, :ref.max_blocks])
+        ref.block_table[:b].copy_(bt[:, :ref.max_blocks])
     rec = {"tp_check": "ok", "steps": steps, "context": ctx, "tokens_compared": 0, "tokens_equal": 0, "logit_rms_err": [],
            "logit_std": []}
     for st in range(steps):
         bufs.tokens.copy_(tok)
-        model.num_tokens.fill_(ctx + st + 1)
+        model.num_tokens[:b].fill_(ctx + st + 1)
         got = model.decode_step(b, advance=False, use_graph=False).clone()
         l_tp = model.last_logits.float()
         if ref is not None:
             rb = ref.decode_buffers(b)
             rb.tokens.copy_(tok)
-            ref.num_tokens.fill_(ctx + st + 1)
+            ref.num_tokens[:b].fill_(ctx + st + 1)
             want = ref.decode_step(b, advance=False, use_graph=False).clone()
             l_ref = ref.last_logits.float()
             shard = l_ref[:, model.vocab_offset: model.vocab_offset + l_tp.shape[1]]
@@ -386,12 +386,12 @@ def run_b200(args, shape):
     # synthetic state: block ids = random permutation of [1, num_blocks) (seed 7), KV ~ N(0,1) (seed 11)
     perm = torch.randperm(num_blocks - 1, generator=torch.Generator().manual_seed(7)) + 1
     bt_host = perm.reshape(b, max_blocks).to(torch.int32)
-    model.block_table.copy_(bt_host)
+    model.block_table[:b].copy_(bt_host)
     fill_kv_pools(model, shape, rank, world)
     tok_host = torch.randint(0, shape.vocab, (b,), generator=torch.Generator().manual_seed(1234))
     bufs = model.decode_buffers(b)
     bufs.tokens.copy_(tok_host)
-    model.num_tokens.fill_(n0)
+    model.num_tokens[:b].fill_(n0)
     torch.cuda.synchronize()
 
     def barrier():
@@ -401,16 +401,16 @@ def run_b200(args, shape):
 
     # ---- N > 1: correctness of this very model before anything is timed (TP=N vs TP=1 on rank 0, same weights)
     parity = tp_parity_check(args, shape, model, bufs, rank, world, dev, group) if world > 1 else None
-    model.block_table.copy_(bt_host)
+    model.block_table[:b].copy_(bt_host)
     bufs.tokens.copy_(tok_host)
 
     # ---- device-resident decode: CUDA-graph replay, the sampled token and the length advance on the device
     clocks = ClockSampler(local).start()
     l0 = ops.launch_count()
-    model.num_tokens.fill_(n0)
+    model.num_tokens[:b].fill_(n0)
     model.decode_step(b, advance=True, use_graph=True)  # captures (one eager warm-up pass + one capture pass) and replays
     launches_per_step = (ops.launch_count() - l0) // 2
-    model.num_tokens.fill_(n0)
+    model.num_tokens[:b].fill_(n0)
     for _ in range(w_steps):
         model.decode_step(b, advance=True, use_graph=True)
     barrier()

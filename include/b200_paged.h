@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 6
+#define B200_ABI_VERSION 7
 
 enum {
   B200_OK = 0,
@@ -64,7 +64,15 @@ int b200_set_pdl(int enabled);
  * Outputs are int64 like the reference's tensors (ctx_lens int32 for the kernels). */
 int b200_build_decode_meta(const int32_t* block_table, int64_t bt_row_stride, const int32_t* row_ids,
                            const int32_t* num_tokens, int64_t* slot_mapping, int64_t* positions, int32_t* ctx_lens,
-                           int B, int max_blocks, int block_size, void* stream);
+                           int B, int max_blocks, int block_size, int num_spec, void* stream);
+/* num_spec = 1: slot_mapping is [B].  num_spec = k > 1 (EAGLE / fused speculation, model_runner.py:825-830):
+ * slot_mapping is [B][k] with slot_mapping[b][i] = slot_mapping[b][0] + i, built exactly like the reference's
+ * `slots.append(slots[0] + i)` (not re-derived through the block table); a padded row stays -1.
+ *
+ * model_loader.py:308-334 (_remask_fused_spec_output): accepted [B][T] int64 is 0-padded; entries past
+ * clamp(next_pos[b] - positions[b], 0, T) become -1 in out so that the runner strips them (model_runner.py:306-323). */
+int b200_remask_spec_output(const int64_t* accepted, const int64_t* next_pos, const int64_t* positions, int64_t* out, int B,
+                            int T, void* stream);
 /* Replaces model_runner.py:739-763 (+ :853-885): batch-1 prefill with a prefix-cache hit.
  * slot_mapping_out[i] for i in [0, max_model_len): slot of token (num_computed + i) while that
  * token < prompt_len, else -1 (the reference's slice [num_computed:] right-padded with -1).
@@ -189,6 +197,17 @@ int b200_topk_candidates(const float* logits, int64_t row_stride, float* cand_va
                          int64_t idx_offset, void* stream);
 int b200_sample_candidates(const float* cand_val, const int64_t* cand_idx, int groups, int B, const float* params,
                            const float* u, int64_t* out_ids, void* stream);
+/* Log-probabilities on device (the reference returns them from its CPU sampling path, model_runner.py:347-356, 1142-1239:
+ * vLLM's Sampler = raw log-softmax of the logits, the sampled token's rank, the top-n tokens).
+ * b200_row_lse: per row of the local vocab shard, out_max[b] = max_v logits[b][v], out_sumexp[b] = sum_v exp(logits - max)
+ *   (fixed reduction tree: bit-reproducible).  TP: one (max, sumexp) pair per shard, laid out [groups][B] for the gather.
+ * b200_gather_logprobs: with the sorted candidate lists of b200_topk_candidates ([groups][B][256]) and the sampled ids:
+ *   out_ids / out_logprobs [B][1 + num_logprobs] (int32 / fp32; column 0 = the sampled token, then the num_logprobs most
+ *   likely tokens, value desc / index asc), out_rank[b] = 1 + #tokens with a strictly larger logit. */
+int b200_row_lse(const float* logits, int64_t row_stride, float* out_max, float* out_sumexp, int B, int V, void* stream);
+int b200_gather_logprobs(const float* cand_val, const int64_t* cand_idx, int groups, int B, const int64_t* sampled,
+                         const float* row_max, const float* row_sumexp, int num_logprobs, int32_t* out_ids,
+                         float* out_logprobs, int32_t* out_rank, void* stream);
 /* Greedy sampling (reference: top_k=1, temperature=1.0 for temperature 0, model_runner.py:1126-1128).
  * out_idx[t] = idx_offset + first index of the row maximum; out_val[t] = that maximum (for TP merges). */
 int b200_argmax(const float* logits, int64_t row_stride, float* out_val, int64_t* out_idx, int T, int V,

@@ -186,3 +186,14 @@ def sampling_params_rows(params, max_num_seqs: int, max_topk: int):
             top_k[i] = 1
             temp[i] = 1.0
     return np.asarray([top_k, top_p, temp], dtype=np.float32).T.copy()
+
+
+def remask_fused_spec_output(accepted, next_pos, positions):
+    """LOADER:308-334 -- accepted tokens [B][T] arrive 0-padded from fused speculation; entries past the number of tokens
+    generated this step (next_pos - position, clamped to [0, T]) become -1 so the runner strips them."""
+    out = []
+    for row, nxt, pos in zip(accepted, next_pos, positions):
+        t = len(row)
+        cnt = min(max(nxt - pos, 0), t)
+        out.append(list(row[:cnt]) + [-1] * (t - cnt))
+    return out

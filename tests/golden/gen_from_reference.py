@@ -331,6 +331,89 @@ def gen_output_cases(RUNNER):
     return out
 
 
+def gen_remask_cases(LOADER):
+    """LOADER:308-334 (_remask_fused_spec_output): 0-padded accepted tokens -> -1 past the tokens generated this step."""
+    out = []
+    rng = random.Random(11)
+    for b, t in [(1, 1), (3, 4), (4, 8), (2, 3)]:
+        accepted = [[rng.randint(0, 31999) for _ in range(t)] for _ in range(b)]
+        positions = [rng.randint(0, 2000) for _ in range(b)]
+        counts = [rng.choice([-2, 0, 1, t - 1, t, t + 3]) for _ in range(b)]
+        next_pos = [p + c for p, c in zip(positions, counts)]
+        fused = [torch.tensor(accepted), torch.zeros(b, 1), torch.tensor(next_pos).unsqueeze(-1)]
+        inputs = {"position_ids": torch.tensor([[0, p] for p in positions])}
+        masked = LOADER.NeuronCausalLM._remask_fused_spec_output(None, fused, inputs)
+        out.append({"accepted": accepted, "positions": positions, "next_pos": next_pos, "masked": _tolist(masked)})
+    return out
+
+
+def gen_scheduler_cases():
+    """SCHED:59-166 run on plain objects: the stop rule on a grid of request states, can_schedule on a grid of queue sizes,
+    and schedule()'s queue movement around the (stubbed) base-scheduler call."""
+    from collections import deque
+
+    import vllm_neuron.core.scheduler as SCHED
+    from vllm.v1.request import RequestStatus
+
+    stop = []
+    rng = random.Random(5)
+    for _ in range(160):
+        n_out = rng.randint(1, 12)
+        prompt = rng.randint(1, 20)
+        eos = 2
+        last = rng.choice([2, 2, 7, 9, 11])
+        req = SimpleNamespace(
+            num_tokens=prompt + n_out, num_output_tokens=n_out, max_tokens=rng.choice([n_out - 1, n_out, n_out + 1, 64]),
+            pooling_params=None, eos_token_id=eos, output_token_ids=[5] * (n_out - 1) + [last], status=None, stop_reason=None,
+            sampling_params=SimpleNamespace(min_tokens=rng.choice([0, 0, n_out, n_out + 2]), ignore_eos=rng.choice([False, False, True]),
+                                            stop_token_ids=rng.choice([None, [], [7], [9, 11]]), eos_token_id=eos))
+        mml = rng.choice([prompt + n_out - 1, prompt + n_out, prompt + n_out + 1, 4096])
+        rec = {"num_tokens": req.num_tokens, "num_output_tokens": n_out, "max_tokens": req.max_tokens, "eos_token_id": eos,
+               "last_token": last, "min_tokens": req.sampling_params.min_tokens, "ignore_eos": req.sampling_params.ignore_eos,
+               "stop_token_ids": req.sampling_params.stop_token_ids, "max_model_len": mml}
+        rec["stopped"] = bool(SCHED.check_stop_with_min_tokens(req, mml))
+        rec["status"] = None if req.status is None else RequestStatus(req.status).name
+        rec["stop_reason"] = req.stop_reason
+        stop.append(rec)
+
+    can = []
+    for max_run in (1, 2, 4):
+        for n_run in range(0, max_run + 1):
+            for n_wait in range(0, 3):
+                fake = SimpleNamespace(running=[0] * n_run, waiting=[0] * n_wait, max_num_running_reqs=max_run,
+                                       scheduler_config=SimpleNamespace(max_model_len=2048))
+                can.append({"max_running": max_run, "running": n_run, "waiting": n_wait,
+                            "can": bool(SCHED.ContinuousBatchingNeuronScheduler.can_schedule(fake, None))})
+
+    sched = []
+    seen = {}
+
+    def base_schedule(self):  # stands in for vLLM's Scheduler.schedule: records what it is shown
+        seen["waiting"], seen["running"] = list(self.waiting), list(self.running)
+        return "OUT"
+
+    orig = SCHED.Scheduler.schedule
+    SCHED.Scheduler.schedule = base_schedule
+    try:
+        for max_run in (1, 2, 4, 8):
+            for n_run in range(0, max_run + 1):
+                for n_wait in (0, 1, 2, 5):
+                    obj = object.__new__(SCHED.ContinuousBatchingNeuronScheduler)
+                    obj.waiting = deque(f"w{i}" for i in range(n_wait))
+                    obj.running = [f"r{i}" for i in range(n_run)]
+                    obj.holdback_queue = deque()
+                    obj.max_num_running_reqs = max_run
+                    obj.scheduler_config = SimpleNamespace(max_model_len=2048)
+                    out = obj.schedule()
+                    assert out == "OUT"
+                    sched.append({"max_running": max_run, "running": n_run, "waiting": n_wait,
+                                  "base_saw_waiting": seen["waiting"], "base_saw_running": seen["running"],
+                                  "waiting_after": list(obj.waiting), "running_after": list(obj.running)})
+    finally:
+        SCHED.Scheduler.schedule = orig
+    return {"stop": stop, "can_schedule": can, "schedule": sched}
+
+
 def main():
     _install_shims()
     import vllm_neuron.worker.neuronx_distributed_model_loader as LOADER
@@ -343,6 +426,8 @@ def main():
         "platform": gen_platform_cases(),
         "sampling": gen_sampling_cases(RUNNER),
         "output": gen_output_cases(RUNNER),
+        "remask": gen_remask_cases(LOADER),
+        "scheduler": gen_scheduler_cases(),
     }
     with open(OUT, "w") as f:
         json.dump(golden, f, separators=(",", ":"))

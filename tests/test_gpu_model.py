@@ -159,10 +159,11 @@ def test_fp8_parity_at_headline_width():
     vocabulary 128256, llama3 RoPE scaling, HF init scale -- the GEMM tiles, split-K plans, attention head geometry and
     the 128256-wide lm_head / argmax the bench runs, two layers deep so the CPU oracle finishes in minutes.  Same bars
     as the tiny model: as close to the unquantised oracle as the quantised oracle is, tokens equal outside the band."""
-    _check_against_oracle("fp8", *_run("fp8", steps=3, preset="llama-3.1-8b-2l", std=0.02, widen_once=True), min_tokens=12)
+    _check_against_oracle("fp8", *_run("fp8", steps=3, preset="llama-3.1-8b-2l", std=0.02, widen_once=True), min_tokens=12,
+                          noise_bar=0.25)  # measured on B200: e4m3 noise at K = 4096 / 14336 is 0.18 of the logit spread
 
 
-def _check_against_oracle(quant, runner, model, ref, outs, ref_outs, margins, live, blocks, min_tokens=40):
+def _check_against_oracle(quant, runner, model, ref, outs, ref_outs, margins, live, blocks, min_tokens=40, noise_bar=None):
     keys = sorted(outs)
     flat_got = [t for k in keys for t in outs[k]]
     flat_ref = [t for k in keys for t in ref_outs[k]]
@@ -190,7 +191,8 @@ def _check_against_oracle(quant, runner, model, ref, outs, ref_outs, margins, li
         print(msg)
         assert e_gh < 1.15 * e_q, msg
         assert e_g < 1.5 * e_q, msg
-        assert e_q < (0.15 if quant == "fp8" else 0.05) * std, msg
+        # sanity bar on the size of the oracle's OWN quantisation noise (not a property of the CUDA path)
+        assert e_q < (noise_bar or (0.15 if quant == "fp8" else 0.05)) * std, msg
         if quant == "int8_wo":
             # weight-only: both sides multiply the SAME int8 codes with bf16 activations (no activation codes to flip),
             # so the CUDA path tracks the quantised oracle as closely as the bf16 model tracks its oracle

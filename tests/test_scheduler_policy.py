@@ -83,3 +83,71 @@ def test_request_wrapper_equals_the_pure_rule():
         elif want is not None:
             assert req.status == RequestStatus.FINISHED_STOPPED
             assert req.stop_reason == (want[1] if isinstance(want, tuple) else None)
+
+
+# ---------------------------------------------------------------- against the reference's own scheduler (goldens)
+def _golden_sched():
+    import json
+    import os
+
+    with open(os.path.join(os.path.dirname(__file__), "golden", "index_golden.json")) as f:
+        return json.load(f)["scheduler"]
+
+
+def test_stop_rule_matches_reference_goldens():
+    """check_stop_with_min_tokens against the outputs of the reference's own function (SCHED:130-166) on 160 request
+    states (tests/golden/gen_from_reference.py ran it)."""
+    from types import SimpleNamespace
+
+    from vllm.v1.request import RequestStatus
+
+    from vllm_neuron_b200.core.scheduler import check_stop_with_min_tokens
+
+    cases = _golden_sched()["stop"]
+    assert len(cases) >= 100 and {c["status"] for c in cases} >= {None, "FINISHED_STOPPED", "FINISHED_LENGTH_CAPPED"}
+    for c in cases:
+        n_out = c["num_output_tokens"]
+        req = SimpleNamespace(
+            num_tokens=c["num_tokens"], num_output_tokens=n_out, max_tokens=c["max_tokens"], pooling_params=None,
+            eos_token_id=c["eos_token_id"], output_token_ids=[5] * (n_out - 1) + [c["last_token"]], status=None, stop_reason=None,
+            sampling_params=SimpleNamespace(min_tokens=c["min_tokens"], ignore_eos=c["ignore_eos"],
+                                            stop_token_ids=c["stop_token_ids"], eos_token_id=c["eos_token_id"]))
+        assert check_stop_with_min_tokens(req, c["max_model_len"]) == c["stopped"], c
+        assert (None if req.status is None else RequestStatus(req.status).name) == c["status"], c
+        assert req.stop_reason == c["stop_reason"], c
+
+
+def test_can_schedule_and_queue_movement_match_reference_goldens():
+    """can_schedule and schedule()'s hold-back / hide-the-decodes queue movement against the reference's own class run on
+    plain deques with the base scheduler stubbed (SCHED:69-127)."""
+    from collections import deque
+    from types import SimpleNamespace
+
+    import vllm_neuron_b200.core.scheduler as S
+
+    g = _golden_sched()
+    cls = S.ContinuousBatchingB200Scheduler
+    for c in g["can_schedule"]:
+        fake = SimpleNamespace(running=[0] * c["running"], waiting=[0] * c["waiting"], max_num_running_reqs=c["max_running"])
+        assert cls.can_schedule(fake, None) == c["can"], c
+    seen = {}
+    base = cls.__mro__[1]
+    orig = base.schedule
+
+    def base_schedule(self):
+        seen["waiting"], seen["running"] = list(self.waiting), list(self.running)
+        return "OUT"
+
+    base.schedule = base_schedule
+    try:
+        for c in g["schedule"]:
+            obj = object.__new__(cls)
+            obj.waiting = deque(f"w{i}" for i in range(c["waiting"]))
+            obj.running = [f"r{i}" for i in range(c["running"])]
+            obj.holdback_queue = deque()
+            obj.max_num_running_reqs = c["max_running"]
+            assert obj.schedule() == "OUT"
+            assert seen["waiting"] == c["base_saw_waiting"] and seen["running"] == c["base_saw_running"], c
+            assert list(obj.waiting) == c["waiting_after"] and list(obj.running) == c["running_after"], c
+    finally:
+        base.schedule = orig

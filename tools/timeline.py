@@ -49,12 +49,12 @@ def main():
     model = B200CausalLM(shape, None, quant=a.quant, num_blocks=nb, max_num_seqs=a.batch, max_model_len=mml, device=f"cuda:{local}",
                          tp_rank=rank, tp_size=world, tp_group=group)
     perm = torch.randperm(nb - 1, generator=torch.Generator().manual_seed(7)) + 1
-    model.block_table.copy_(perm.reshape(a.batch, mb).to(torch.int32))
+    model.block_table[:a.batch].copy_(perm.reshape(a.batch, mb).to(torch.int32))
     for kv in model.kv:
         kv.normal_()
     bufs = model.decode_buffers(a.batch)
     bufs.tokens.copy_(torch.randint(0, shape.vocab, (a.batch,)))
-    model.num_tokens.fill_(a.ctx)
+    model.num_tokens[:a.batch].fill_(a.ctx)
     for _ in range(4):
         model.decode_step(a.batch, advance=True, use_graph=True)
     torch.cuda.synchronize()

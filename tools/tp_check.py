@@ -116,7 +116,7 @@ def check_model(group, rank, world, dev):
         gen = torch.Generator().manual_seed(9)
         outs = {id(m): [] for m in models}
         for m in models:
-            m.block_table.copy_((torch.arange(b * 8, dtype=torch.int32).reshape(b, 8) + 1).to(dev))
+            m.block_table[:b].copy_((torch.arange(b * 8, dtype=torch.int32).reshape(b, 8) + 1).to(dev))
         prompts = [torch.randint(0, shape.vocab, (40 + 7 * i,), generator=gen) for i in range(b)]
         firsts = {}
         for m in models:
@@ -133,7 +133,7 @@ def check_model(group, rank, world, dev):
         for m in models:
             bufs = m.decode_buffers(b)
             bufs.tokens.copy_(feed)
-            m.num_tokens.copy_(torch.tensor([p.numel() + 1 for p in prompts], dtype=torch.int32))
+            m.num_tokens[:b].copy_(torch.tensor([p.numel() + 1 for p in prompts], dtype=torch.int32))
             for _ in range(6):
                 tok = m.decode_step(b, advance=True, use_graph=not os.environ.get('TP_CHECK_EAGER')).clone()
                 outs[id(m)].append((tok, m.last_logits.float().clone()))

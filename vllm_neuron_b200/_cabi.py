@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200_paged.so")
 
 OK = 0
-ABI_VERSION = 6
+ABI_VERSION = 7
 BF16, FP8_E4M3, INT8, F32 = 0, 1, 2, 3
 
 _p = C.c_void_p
@@ -28,7 +28,8 @@ SIGNATURES = {
     "b200_device_check": (_i, [_i]),
     "b200_launch_count": (C.c_uint64, []),
     "b200_set_pdl": (_i, [_i]),
-    "b200_build_decode_meta": (_i, [_p, _i64, _p, _p, _p, _p, _p, _i, _i, _i, _p]),
+    "b200_build_decode_meta": (_i, [_p, _i64, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p]),
+    "b200_remask_spec_output": (_i, [_p, _p, _p, _p, _i, _i, _p]),
     "b200_build_prefill_meta": (_i, [_p, _i, _i, _p, _p, _i, _i, _p]),
     "b200_block_table_scatter": (_i, [_p, _i64, _p, _i, _i, _i, _p]),
     "b200_advance_decode": (_i, [_p, _p, _p, _p, _i, _p]),
@@ -55,6 +56,8 @@ SIGNATURES = {
     "b200_argmax": (_i, [_p, _i64, _p, _p, _i, _i, _i64, _p]),
     "b200_topk_candidates": (_i, [_p, _i64, _p, _p, _i, _i, _i64, _p]),
     "b200_sample_candidates": (_i, [_p, _p, _i, _i, _p, _p, _p, _p]),
+    "b200_row_lse": (_i, [_p, _i64, _p, _p, _i, _i, _p]),
+    "b200_gather_logprobs": (_i, [_p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _p]),
     "b200_allreduce_rmsnorm": (_i, [_p, _p, _p, _i, _i, _p, _p, _p, _p, _p, _i, _i, _f, _i, _p]),
 }
 

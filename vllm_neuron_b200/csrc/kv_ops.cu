@@ -9,7 +9,7 @@ namespace b200 {
 __global__ void build_decode_meta_kernel(const int32_t* __restrict__ block_table, int64_t bt_stride,
                                          const int32_t* __restrict__ row_ids, const int32_t* __restrict__ num_tokens,
                                          int64_t* __restrict__ slot_mapping, int64_t* __restrict__ positions,
-                                         int32_t* __restrict__ ctx_lens, int B, int max_blocks, int bs) {
+                                         int32_t* __restrict__ ctx_lens, int B, int max_blocks, int bs, int num_spec) {
   griddep_launch();
   griddep_wait();
   int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -19,9 +19,25 @@ __global__ void build_decode_meta_kernel(const int32_t* __restrict__ block_table
   int pos = n - 1;
   int64_t slot = -1;
   if (pos >= 0 && pos / bs < max_blocks) slot = (int64_t)block_table[(int64_t)r * bt_stride + pos / bs] * bs + pos % bs;
-  slot_mapping[b] = slot;
+  // speculation (model_runner.py:825-830): the row carries k consecutive slots, slots[0] + i -- NOT re-derived through the
+  // block table, exactly as the reference builds them; a padded row (-1) stays -1 throughout
+  for (int i = 0; i < num_spec; ++i) slot_mapping[(int64_t)b * num_spec + i] = slot < 0 ? -1 : slot + i;
   positions[b] = pos < 0 ? 0 : pos;
   ctx_lens[b] = n < 0 ? 0 : n;
+}
+
+// model_loader.py:308-334 (_remask_fused_spec_output): accepted tokens [B][T] arrive 0-padded; everything past the number
+// of tokens generated this step (next_pos - position, clamped to [0, T]) becomes -1 so the runner can strip it
+__global__ void remask_spec_output_kernel(const int64_t* __restrict__ accepted, const int64_t* __restrict__ next_pos,
+                                          const int64_t* __restrict__ positions, int64_t* __restrict__ out, int B, int T) {
+  griddep_launch();
+  griddep_wait();
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * T) return;
+  int b = i / T, t = i - b * T;
+  long long cnt = next_pos[b] - positions[b];
+  cnt = cnt < 0 ? 0 : cnt > T ? T : cnt;
+  out[i] = t < cnt ? accepted[i] : -1;
 }
 
 // model_runner.py:739-763 + 869-874: slot list over range(max_model_len) sliced at num_computed, -1 padded
@@ -424,12 +440,25 @@ extern "C" {
 
 int b200_build_decode_meta(const int32_t* block_table, int64_t bt_row_stride, const int32_t* row_ids,
                            const int32_t* num_tokens, int64_t* slot_mapping, int64_t* positions, int32_t* ctx_lens, int B,
-                           int max_blocks, int block_size, void* stream) {
+                           int max_blocks, int block_size, int num_spec, void* stream) {
   B200_REQUIRE(block_table && num_tokens && slot_mapping && positions && ctx_lens, "build_decode_meta: null pointer");
   B200_REQUIRE(B >= 0 && max_blocks > 0 && block_size > 0, "build_decode_meta: bad sizes B=%d max_blocks=%d bs=%d", B,
                max_blocks, block_size);
+  B200_REQUIRE(num_spec >= 1 && num_spec <= 64, "build_decode_meta: num_spec %d outside 1..64", num_spec);
   if (B == 0) return B200_OK;
-  B200_CUDA_OK(launch_kernel(build_decode_meta_kernel, dim3((B + 127) / 128), dim3(128), 0, (cudaStream_t)stream, block_table, bt_row_stride, row_ids, num_tokens, slot_mapping, positions, ctx_lens, B, max_blocks, block_size));
+  B200_CUDA_OK(launch_kernel(build_decode_meta_kernel, dim3((B + 127) / 128), dim3(128), 0, (cudaStream_t)stream, block_table,
+                             bt_row_stride, row_ids, num_tokens, slot_mapping, positions, ctx_lens, B, max_blocks, block_size,
+                             num_spec));
+  return B200_OK;
+}
+
+int b200_remask_spec_output(const int64_t* accepted, const int64_t* next_pos, const int64_t* positions, int64_t* out, int B,
+                            int T, void* stream) {
+  B200_REQUIRE(accepted && next_pos && positions && out, "remask_spec_output: null pointer");
+  B200_REQUIRE(B >= 0 && T > 0, "remask_spec_output: bad sizes B=%d T=%d", B, T);
+  if (B == 0) return B200_OK;
+  B200_CUDA_OK(launch_kernel(remask_spec_output_kernel, dim3((B * T + 127) / 128), dim3(128), 0, (cudaStream_t)stream, accepted,
+                             next_pos, positions, out, B, T));
   return B200_OK;
 }
 

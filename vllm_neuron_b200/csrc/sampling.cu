@@ -236,6 +236,119 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// ---------------------------------------------------------------- log-probabilities (RUNNER:347-356, 1142-1239)
+// The reference returns logprobs from vLLM's Sampler on full logits (raw log-softmax, the sampled token's rank, the top-n
+// tokens).  On device: one pass per row for (max, sum exp(x - max)) of the local vocab shard, then everything else comes
+// from the sorted 256-candidate lists b200_topk_candidates already produces.
+constexpr int LSE_THREADS = 512;
+__global__ void __launch_bounds__(LSE_THREADS) row_lse_kernel(const float* __restrict__ logits, int64_t row_stride,
+                                                               float* __restrict__ out_max, float* __restrict__ out_sum,
+                                                               int V) {
+  griddep_launch();
+  griddep_wait();
+  __shared__ float red[LSE_THREADS / 32];
+  __shared__ float bc;
+  const float* r = logits + (int64_t)blockIdx.x * row_stride;
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  float m = -INFINITY;
+  for (int i = threadIdx.x; i < V; i += LSE_THREADS) m = fmaxf(m, r[i]);
+  m = warp_max(m);
+  if (l == 0) red[w] = m;
+  __syncthreads();
+  if (w == 0) {
+    m = l < LSE_THREADS / 32 ? red[l] : -INFINITY;
+    m = warp_max(m);
+    if (l == 0) bc = m;
+  }
+  __syncthreads();
+  m = bc;
+  // fixed thread -> element map and a fixed reduction tree: the sum is bit-reproducible
+  float s = 0.f;
+  for (int i = threadIdx.x; i < V; i += LSE_THREADS) s += expf(r[i] - m);
+  s = warp_sum(s);
+  __syncthreads();
+  if (l == 0) red[w] = s;
+  __syncthreads();
+  if (w == 0) {
+    s = l < LSE_THREADS / 32 ? red[l] : 0.f;
+    s = warp_sum(s);
+    if (l == 0) {
+      out_max[blockIdx.x] = m;
+      out_sum[blockIdx.x] = s;
+    }
+  }
+}
+
+// One warp per row.  cand_* [groups][B][256] sorted (value desc, index asc) per group, row_max / row_sum [groups][B].
+// out_ids / out_logprobs [B][1 + n]: column 0 = the sampled token, columns 1..n = the n most likely tokens;
+// out_rank [B] = 1 + number of tokens with a strictly larger logit (vLLM's rank rule).  The sampled token always is a
+// candidate (the sampler draws from the candidates; the greedy token is candidate 0 of its shard).
+__global__ void __launch_bounds__(128) gather_logprobs_kernel(const float* __restrict__ cand_val,
+                                                              const int64_t* __restrict__ cand_idx, int groups, int B,
+                                                              const int64_t* __restrict__ sampled,
+                                                              const float* __restrict__ row_max,
+                                                              const float* __restrict__ row_sum, int n,
+                                                              int32_t* __restrict__ out_ids, float* __restrict__ out_lp,
+                                                              int32_t* __restrict__ out_rank) {
+  griddep_launch();
+  griddep_wait();
+  const int b = blockIdx.x * 4 + (threadIdx.x >> 5), l = threadIdx.x & 31;
+  if (b >= B) return;
+  float m = -INFINITY;
+  for (int g = 0; g < groups; ++g) m = fmaxf(m, row_max[(int64_t)g * B + b]);
+  float s = 0.f;
+  for (int g = 0; g < groups; ++g) s += row_sum[(int64_t)g * B + b] * expf(row_max[(int64_t)g * B + b] - m);
+  const float lse = m + logf(s);
+  const int64_t tok = sampled[b];
+  float xs = -INFINITY;
+  for (int g = 0; g < groups; ++g)
+    for (int j = l; j < SAMPLE_K; j += 32) {
+      const int64_t o = ((int64_t)g * B + b) * SAMPLE_K + j;
+      if (cand_idx[o] == tok) xs = cand_val[o];
+    }
+  xs = warp_max(xs);
+  int cnt = 0;
+  for (int g = 0; g < groups; ++g)
+    for (int j = l; j < SAMPLE_K; j += 32) {
+      const int64_t o = ((int64_t)g * B + b) * SAMPLE_K + j;
+      cnt += (cand_idx[o] >= 0 && cand_val[o] > xs) ? 1 : 0;
+    }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  if (l != 0) return;
+  const int64_t row = (int64_t)b * (1 + n);
+  out_ids[row] = (int32_t)tok;
+  out_lp[row] = xs - lse;
+  out_rank[b] = cnt + 1;
+  int head[16];
+  for (int g = 0; g < groups; ++g) head[g] = 0;
+  for (int j = 0; j < n; ++j) {  // k-way merge of the sorted shard lists: value desc, then index asc
+    int bg = -1;
+    float bv = -INFINITY;
+    int64_t bi = 0;
+    for (int g = 0; g < groups; ++g) {
+      if (head[g] >= SAMPLE_K) continue;
+      const int64_t o = ((int64_t)g * B + b) * SAMPLE_K + head[g];
+      const int64_t ci = cand_idx[o];
+      if (ci < 0) continue;
+      const float cv = cand_val[o];
+      if (bg < 0 || cv > bv || (cv == bv && ci < bi)) {
+        bg = g;
+        bv = cv;
+        bi = ci;
+      }
+    }
+    if (bg < 0) {
+      out_ids[row + 1 + j] = -1;
+      out_lp[row + 1 + j] = -INFINITY;
+    } else {
+      ++head[bg];
+      out_ids[row + 1 + j] = (int32_t)bi;
+      out_lp[row + 1 + j] = bv - lse;
+    }
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -261,6 +374,28 @@ int b200_sample_candidates(const float* cand_val, const int64_t* cand_idx, int g
   while (n2 < groups * SAMPLE_K) n2 <<= 1;
   B200_CUDA_OK(launch_kernel(sample_candidates_kernel, dim3(B), dim3(256), (size_t)n2 * 8, (cudaStream_t)stream, cand_val,
                              cand_idx, groups, B, params, u, out_ids));
+  return B200_OK;
+}
+
+int b200_row_lse(const float* logits, int64_t row_stride, float* out_max, float* out_sumexp, int B, int V, void* stream) {
+  B200_REQUIRE(logits && out_max && out_sumexp, "row_lse: null pointer");
+  B200_REQUIRE(V > 0, "row_lse: V must be positive");
+  if (B <= 0) return B200_OK;
+  B200_CUDA_OK(launch_kernel(row_lse_kernel, dim3(B), dim3(LSE_THREADS), 0, (cudaStream_t)stream, logits, row_stride, out_max,
+                             out_sumexp, V));
+  return B200_OK;
+}
+
+int b200_gather_logprobs(const float* cand_val, const int64_t* cand_idx, int groups, int B, const int64_t* sampled,
+                         const float* row_max, const float* row_sumexp, int num_logprobs, int32_t* out_ids,
+                         float* out_logprobs, int32_t* out_rank, void* stream) {
+  B200_REQUIRE(cand_val && cand_idx && sampled && row_max && row_sumexp && out_ids && out_logprobs && out_rank,
+               "gather_logprobs: null pointer");
+  B200_REQUIRE(groups >= 1 && groups <= 16, "gather_logprobs: groups %d outside 1..16", groups);
+  B200_REQUIRE(num_logprobs >= 0 && num_logprobs <= SAMPLE_K, "gather_logprobs: num_logprobs %d outside 0..256", num_logprobs);
+  if (B <= 0) return B200_OK;
+  B200_CUDA_OK(launch_kernel(gather_logprobs_kernel, dim3((B + 3) / 4), dim3(128), 0, (cudaStream_t)stream, cand_val, cand_idx,
+                             groups, B, sampled, row_max, row_sumexp, num_logprobs, out_ids, out_logprobs, out_rank));
   return B200_OK;
 }
 

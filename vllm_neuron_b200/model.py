@@ -167,6 +167,28 @@ class StepBuffers:
     sampled: torch.Tensor
     samp_params: torch.Tensor  # [b, 3] fp32 (top_k, top_p, temperature) -- RUNNER:1106-1140
     samp_u: torch.Tensor       # [b] fp32 uniforms in [0, 1) for the inverse-CDF draw
+    logprobs: tuple | None = None  # (ids int32 [b, 1+n], logprobs fp32 [b, 1+n], ranks int32 [b]) of the last step that asked
+
+
+GRAPH_CACHE_CAP = 24  # captured decode graphs kept (LRU); all share one memory pool
+
+
+def bucket_batch(b: int, max_num_seqs: int) -> int:
+    """Decode batches run at the next power of two (capped at max_num_seqs): few graphs, rows b.. are padding."""
+    bb = 1
+    while bb < b:
+        bb <<= 1
+    return min(bb, max_num_seqs)
+
+
+def bucket_ctx_blocks(n: int, max_blocks: int) -> int:
+    """Context bound (in blocks) handed to the attention split, rounded up with <= 12.5 % slack: multiples of 8 up to
+    128 blocks, then of 1/8 of the enclosing power of two."""
+    n = max(1, n)
+    step = 8
+    while step * 16 < n:
+        step <<= 1
+    return min(max_blocks, -(-n // step) * step)
 
 
 class B200CausalLM:
@@ -186,7 +208,9 @@ class B200CausalLM:
         self.tp_rank, self.tp_size, self.tp_group = tp_rank, tp_size, tp_group
         self.block_size, self.num_blocks = block_size, num_blocks
         self.max_num_seqs, self.max_model_len = max_num_seqs, max_model_len
-        self.max_blocks = max_model_len // block_size
+        # ceil: vLLM allocates ceil(tokens / block_size) blocks, so a max_model_len that is not a multiple of the block size
+        # still has a column for its last, partial block (the reference's floor, RUNNER:749,814, would drop it)
+        self.max_blocks = -(-max_model_len // block_size)
         self.hq = shape.num_q_heads // tp_size
         self.hkv = shape.num_kv_heads // tp_size
         self.d = shape.head_dim
@@ -230,10 +254,18 @@ class B200CausalLM:
         self.kv = [torch.zeros((2, num_blocks, self.hkv, block_size, self.d), dtype=torch.bfloat16, device=dev)
                    for _ in range(shape.layers)]
         # ---- persistent per-sequence state (rows = the reference's seq-id slots, RUNNER:130-136)
-        self.block_table = torch.zeros((max_num_seqs, self.max_blocks), dtype=torch.int32, device=dev)
-        self.num_tokens = torch.zeros((max_num_seqs,), dtype=torch.int32, device=dev)
+        # one extra row (index max_num_seqs): the PADDING row of bucketed decode batches -- num_tokens 0, so position -1,
+        # slot -1 (nothing written) and context length 0 (nothing read)
+        self.block_table = torch.zeros((max_num_seqs + 1, self.max_blocks), dtype=torch.int32, device=dev)
+        self.num_tokens = torch.zeros((max_num_seqs + 1,), dtype=torch.int32, device=dev)
+        self.pad_row = max_num_seqs
         self._decode_bufs: dict[int, StepBuffers] = {}
-        self._graphs: dict[tuple, tuple] = {}
+        from collections import OrderedDict
+
+        self._graphs: "OrderedDict[tuple, tuple]" = OrderedDict()
+        self._graph_pool = None
+        self._prefill_meta = None
+        self.last_logprobs = None
         self._alloc_workspaces()
         # TP exchange over NVLink peer memory (our kernel); NCCL stays for prefill-sized batches and the greedy merge
         self.tp_comm = None
@@ -323,9 +355,11 @@ class B200CausalLM:
             x, h, hs = self._row_parallel(L["down"], aq, a_s, x, nxt)
         return x
 
-    def _sample(self, x_rows, samp=None):
+    def _sample(self, x_rows, samp=None, num_logprobs: int | None = None):
         """final norm -> lm_head (fp32 logits of the local vocab shard) -> greedy argmax (TP: merge (val, idx)), or with
-        samp = (params [T,3], u [T]) the on-device top-k / top-p / temperature sampler (TP: candidates all-gathered)."""
+        samp = (params [T,3], u [T]) the on-device top-k / top-p / temperature sampler (TP: candidates all-gathered).
+        num_logprobs = n: also returns vLLM's LogprobsTensors triple (ids [T,1+n], logprobs [T,1+n], ranks [T]) computed
+        on the device from the candidate lists and one log-sum-exp pass (RUNNER:347-356; None = not requested)."""
         lm_q = _QKIND[self.lm_head.quant]
         if lm_q is None:
             h, hs = ops.rmsnorm(x_rows, self.final_norm, self.shape.rms_eps), None
@@ -333,7 +367,9 @@ class B200CausalLM:
             h, hs = ops.rmsnorm(x_rows, self.final_norm, self.shape.rms_eps, quant=lm_q)
         logits = self._linear(self.lm_head, h, hs, out_dtype=torch.float32)
         self.last_logits = logits  # kept for parity tests (a reference, no copy)
-        if samp is not None:
+        self.last_logprobs = None
+        cv = ci = None
+        if samp is not None or num_logprobs is not None:
             cv, ci = ops.topk_candidates(logits, idx_offset=self.vocab_offset)
             if self.tp_size > 1:
                 gv = torch.empty((self.tp_size, *cv.shape), dtype=cv.dtype, device=cv.device)
@@ -341,15 +377,27 @@ class B200CausalLM:
                 torch.distributed.all_gather_into_tensor(gv, cv, group=self.tp_group)
                 torch.distributed.all_gather_into_tensor(gi, ci, group=self.tp_group)
                 cv, ci = gv, gi
-            return ops.sample_candidates(cv, ci, samp[0], samp[1]), logits
-        if self.tp_size == 1:
-            return ops.argmax(logits), logits
-        val, idx = ops.argmax(logits, idx_offset=self.vocab_offset, want_val=True)
-        vals = torch.empty((self.tp_size, val.numel()), dtype=val.dtype, device=val.device)
-        idxs = torch.empty((self.tp_size, idx.numel()), dtype=idx.dtype, device=idx.device)
-        torch.distributed.all_gather_into_tensor(vals, val, group=self.tp_group)
-        torch.distributed.all_gather_into_tensor(idxs, idx, group=self.tp_group)
-        return merge_sharded_argmax(vals, idxs, self.shape.vocab), logits
+        if samp is not None:
+            ids = ops.sample_candidates(cv, ci, samp[0], samp[1])
+        elif self.tp_size == 1:
+            ids = ops.argmax(logits)
+        else:
+            val, idx = ops.argmax(logits, idx_offset=self.vocab_offset, want_val=True)
+            vals = torch.empty((self.tp_size, val.numel()), dtype=val.dtype, device=val.device)
+            idxs = torch.empty((self.tp_size, idx.numel()), dtype=idx.dtype, device=idx.device)
+            torch.distributed.all_gather_into_tensor(vals, val, group=self.tp_group)
+            torch.distributed.all_gather_into_tensor(idxs, idx, group=self.tp_group)
+            ids = merge_sharded_argmax(vals, idxs, self.shape.vocab)
+        if num_logprobs is not None:
+            m, se = ops.row_lse(logits)
+            if self.tp_size > 1:
+                gm = torch.empty((self.tp_size, m.numel()), dtype=m.dtype, device=m.device)
+                gs = torch.empty((self.tp_size, se.numel()), dtype=se.dtype, device=se.device)
+                torch.distributed.all_gather_into_tensor(gm, m, group=self.tp_group)
+                torch.distributed.all_gather_into_tensor(gs, se, group=self.tp_group)
+                m, se = gm, gs
+            self.last_logprobs = ops.gather_logprobs(cv, ci, ids, m, se, num_logprobs)
+        return ids, logits
 
     # ------------------------------------------------------------------ decode
     def decode_buffers(self, b: int) -> StepBuffers:
@@ -367,7 +415,8 @@ class B200CausalLM:
             )
         return self._decode_bufs[b]
 
-    def _decode_body(self, bufs: StepBuffers, max_ctx_blocks: int, advance: bool, sampled: bool = False):
+    def _decode_body(self, bufs: StepBuffers, max_ctx_blocks: int, advance: bool, sampled: bool = False,
+                     num_logprobs: int | None = None):
         b = bufs.tokens.numel()
         # index construction on device (RUNNER:765-832): positions, slot_mapping, context lengths
         ops.build_decode_meta(self.block_table, bufs.row_ids, self.num_tokens, bufs.slot_mapping, bufs.positions,
@@ -379,46 +428,56 @@ class B200CausalLM:
                                          row_ids=bufs.row_ids, max_blocks=max_ctx_blocks, quant=quant)
 
         x = self._layers(x, bufs.positions, bufs.slot_mapping, attn)
-        ids, _ = self._sample(x, (bufs.samp_params, bufs.samp_u) if sampled else None)
+        ids, _ = self._sample(x, (bufs.samp_params, bufs.samp_u) if sampled else None, num_logprobs)
         bufs.sampled.copy_(ids)
         if advance:  # device-side twin of RUNNER:325-339 so the captured step can be replayed back to back
             ops.advance_decode(bufs.sampled, bufs.tokens, self.num_tokens, bufs.row_ids)
         return bufs.sampled
 
     def decode_step(self, b: int, *, max_ctx_blocks: int | None = None, advance: bool = False, use_graph: bool = False,
-                    sampled: bool = False):
+                    sampled: bool = False, num_logprobs: int | None = None):
         """One decode step for the `b` rows in decode_buffers(b).row_ids; inputs already on the device:
         bufs.tokens (last sampled token per row), self.num_tokens[row] (= prompt + outputs incl. that token).
-        sampled=True draws with bufs.samp_params / bufs.samp_u instead of the greedy argmax."""
+        sampled=True draws with bufs.samp_params / bufs.samp_u instead of the greedy argmax; num_logprobs=n leaves the
+        LogprobsTensors triple in self.last_logprobs.
+        Captured graphs are cached per (b, context bound, advance, sampled, num_logprobs) in an LRU of GRAPH_CACHE_CAP
+        entries that share ONE memory pool; callers bucket b and the context bound (bucket_batch / bucket_ctx_blocks)."""
         bufs = self.decode_buffers(b)
         mcb = self.max_blocks if max_ctx_blocks is None else max_ctx_blocks
         if not use_graph:
-            return self._decode_body(bufs, mcb, advance, sampled)
-        key = (b, mcb, advance, sampled)
-        if key not in self._graphs:
+            return self._decode_body(bufs, mcb, advance, sampled, num_logprobs)
+        key = (b, mcb, advance, sampled, num_logprobs)
+        hit = self._graphs.get(key)
+        if hit is None:
             nt = self.num_tokens.clone()
             tk = bufs.tokens.clone()
             s = torch.cuda.Stream()
             s.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(s):  # warm-up outside capture (function attributes, NCCL channels)
-                self._decode_body(bufs, mcb, advance, sampled)
+                self._decode_body(bufs, mcb, advance, sampled, num_logprobs)
             torch.cuda.current_stream().wait_stream(s)
             torch.cuda.synchronize()
             self.num_tokens.copy_(nt)
             bufs.tokens.copy_(tk)
+            while len(self._graphs) >= GRAPH_CACHE_CAP:  # least recently used graph goes; its memory returns to the pool
+                self._graphs.popitem(last=False)
+            if self._graph_pool is None:
+                self._graph_pool = torch.cuda.graph_pool_handle()
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                self._decode_body(bufs, mcb, advance, sampled)
+            with torch.cuda.graph(g, pool=self._graph_pool):
+                self._decode_body(bufs, mcb, advance, sampled, num_logprobs)
             self.num_tokens.copy_(nt)
             bufs.tokens.copy_(tk)
-            self._graphs[key] = (g, self.last_logits)
-        g, self.last_logits = self._graphs[key]
+            hit = self._graphs[key] = (g, self.last_logits, self.last_logprobs)
+        else:
+            self._graphs.move_to_end(key)
+        g, self.last_logits, self.last_logprobs = hit
         g.replay()
         return bufs.sampled
 
     # ------------------------------------------------------------------ prefill (batch 1, prefix-cached)
     def prefill(self, row: int, new_tokens: torch.Tensor, prompt_len: int, computed_len: int, samp=None,
-                sample: bool = True):
+                sample: bool = True, num_logprobs: int | None = None):
         """Compute the uncached suffix `new_tokens` (device int64 [prompt_len - computed_len]) of one request whose
         block ids are already in block_table[row]; returns the sampled next token (device int64 [1]).
         samp = (params [1,3], u [1]) selects the on-device sampler instead of greedy.
@@ -426,9 +485,10 @@ class B200CausalLM:
         cached prefix); sample=False for a chunk that does not finish the prompt (no lm_head, returns None)."""
         s_new = prompt_len - computed_len
         assert new_tokens.numel() == s_new and s_new > 0
-        dev = self.device
-        slot_full = torch.empty(self.max_model_len, dtype=torch.int64, device=dev)
-        pos_full = torch.empty(self.max_model_len, dtype=torch.int64, device=dev)
+        if self._prefill_meta is None:  # allocated once (max_model_len int64 each), reused by every prefill / chunk
+            self._prefill_meta = (torch.empty(self.max_model_len, dtype=torch.int64, device=self.device),
+                                  torch.empty(self.max_model_len, dtype=torch.int64, device=self.device))
+        slot_full, pos_full = self._prefill_meta
         bt_row = self.block_table[row]
         ops.build_prefill_meta(bt_row, prompt_len, computed_len, slot_full, pos_full, self.block_size)
         slots, positions = slot_full[:s_new], pos_full[:s_new]
@@ -441,7 +501,7 @@ class B200CausalLM:
         self.num_tokens[row] = prompt_len
         if not sample:
             return None
-        ids, _ = self._sample(x[-1:].contiguous(), samp)
+        ids, _ = self._sample(x[-1:].contiguous(), samp, num_logprobs)
         return ids
 
     def kv_bytes_per_block(self) -> int:

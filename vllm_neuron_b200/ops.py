@@ -93,16 +93,19 @@ def launch_count() -> int:
 # ------------------------------------------------------------------ index construction
 def build_decode_meta(block_table, row_ids, num_tokens, slot_mapping, positions, ctx_lens, block_size: int):
     """block_table int32 [rows, max_blocks]; row_ids int32 [B] or None; num_tokens int32 [rows];
-    outputs: slot_mapping int64 [B], positions int64 [B], ctx_lens int32 [B]."""
+    outputs: slot_mapping int64 [B] (or [B, k]: k consecutive slots per row for speculation, RUNNER:825-830),
+    positions int64 [B], ctx_lens int32 [B]."""
     _cuda(block_table, num_tokens, slot_mapping)
     assert block_table.dtype == torch.int32 and num_tokens.dtype == torch.int32
     assert slot_mapping.dtype == torch.int64 and positions.dtype == torch.int64 and ctx_lens.dtype == torch.int32
-    b = slot_mapping.numel()
+    b = positions.numel()
+    num_spec = 1 if slot_mapping.dim() == 1 else slot_mapping.shape[1]
+    assert slot_mapping.is_contiguous() and slot_mapping.numel() == b * num_spec
     with _k("build_decode_meta"):
         check(
             _cabi.load().b200_build_decode_meta(
                 _ptr(block_table), block_table.stride(0), _ptr(row_ids), _ptr(num_tokens), _ptr(slot_mapping),
-                _ptr(positions), _ptr(ctx_lens), b, block_table.shape[1], block_size, _stream(),
+                _ptr(positions), _ptr(ctx_lens), b, block_table.shape[1], block_size, num_spec, _stream(),
             ),
             "b200_build_decode_meta",
         )
@@ -118,6 +121,17 @@ def build_prefill_meta(block_table_row, prompt_len: int, num_computed: int, slot
         ),
         "b200_build_prefill_meta",
     )
+
+
+def remask_spec_output(accepted, next_pos, positions):
+    """LOADER:308-334: accepted int64 [B, T] 0-padded -> -1 past clamp(next_pos - positions, 0, T) tokens per row."""
+    _cuda(accepted, next_pos, positions)
+    b, t = accepted.shape
+    assert accepted.dtype == next_pos.dtype == positions.dtype == torch.int64 and accepted.is_contiguous()
+    out = torch.empty_like(accepted)
+    check(_cabi.load().b200_remask_spec_output(_ptr(accepted), _ptr(next_pos), _ptr(positions), _ptr(out), b, t, _stream()),
+          "b200_remask_spec_output")
+    return out
 
 
 def block_table_scatter(block_table, updates):
@@ -477,6 +491,37 @@ def sample_candidates(cand_val, cand_idx, params, u, out=None):
         check(_cabi.load().b200_sample_candidates(_ptr(cand_val), _ptr(cand_idx), g, b, _ptr(params), _ptr(u), _ptr(out),
                                                   _stream()), "b200_sample_candidates")
     return out
+
+
+def row_lse(logits):
+    """logits fp32 [B, V] -> (row max [B], sum exp(x - max) [B]) of the local vocab shard."""
+    _cuda(logits)
+    b, v = logits.shape
+    assert logits.dtype == torch.float32 and logits.stride(1) == 1
+    m = torch.empty((b,), dtype=torch.float32, device=logits.device)
+    s = torch.empty((b,), dtype=torch.float32, device=logits.device)
+    with _k("row_lse"):
+        check(_cabi.load().b200_row_lse(_ptr(logits), logits.stride(0), _ptr(m), _ptr(s), b, v, _stream()), "b200_row_lse")
+    return m, s
+
+
+def gather_logprobs(cand_val, cand_idx, sampled, row_max, row_sumexp, num_logprobs: int):
+    """cand_* [B,256] or [groups,B,256]; row_max / row_sumexp [B] or [groups,B]; sampled int64 [B].
+    -> (ids int32 [B, 1+n], logprobs fp32 [B, 1+n], ranks int32 [B]) in vLLM's LogprobsTensors layout."""
+    _cuda(cand_val, cand_idx, sampled, row_max, row_sumexp)
+    if cand_val.dim() == 2:
+        cand_val, cand_idx, row_max, row_sumexp = cand_val.unsqueeze(0), cand_idx.unsqueeze(0), row_max.unsqueeze(0), row_sumexp.unsqueeze(0)
+    g, b, k = cand_val.shape
+    assert k == SAMPLE_K and cand_val.is_contiguous() and cand_idx.is_contiguous() and row_max.is_contiguous()
+    assert row_max.shape == (g, b) and row_sumexp.shape == (g, b) and row_sumexp.is_contiguous() and sampled.dtype == torch.int64
+    ids = torch.empty((b, 1 + num_logprobs), dtype=torch.int32, device=cand_val.device)
+    lp = torch.empty((b, 1 + num_logprobs), dtype=torch.float32, device=cand_val.device)
+    rk = torch.empty((b,), dtype=torch.int32, device=cand_val.device)
+    with _k("gather_logprobs"):
+        check(_cabi.load().b200_gather_logprobs(_ptr(cand_val), _ptr(cand_idx), g, b, _ptr(sampled), _ptr(row_max),
+                                                _ptr(row_sumexp), num_logprobs, _ptr(ids), _ptr(lp), _ptr(rk), _stream()),
+              "b200_gather_logprobs")
+    return ids, lp, rk
 
 
 def allreduce_rmsnorm(peer_bufs, peer_flags, epoch, rank, world, t, h, norm_w, eps, quant=None, want_bf16=False):

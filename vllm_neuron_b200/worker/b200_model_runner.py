@@ -23,7 +23,7 @@ import torch
 
 from .. import ops
 from ..config import B200Config, ModelShape, build_config
-from ..model import B200CausalLM
+from ..model import B200CausalLM, bucket_batch, bucket_ctx_blocks
 
 logger = logging.getLogger(__name__)
 
@@ -58,6 +58,40 @@ def _first_group(block_ids):
         assert len(block_ids) == 1, "exactly one KV cache group is supported"
         return list(block_ids[0])
     return list(block_ids)
+
+
+def check_sampling_params(sp, req_id="?") -> None:
+    """Admission check.  The device sampler implements what the reference's on-device sampler takes -- (top_k, top_p,
+    temperature) rows with top_k <= 256 (RUNNER:1106-1140) -- plus seeds, min_tokens / stop handling in the scheduler, and
+    log-probabilities.  Everything else vLLM's CPU Sampler would apply on the reference's CPU path (RUNNER:1142-1239) has
+    no device implementation here; a request asking for it is REJECTED instead of being sampled without it."""
+    if sp is None:
+        return
+    bad = []
+    for name, neutral in (("repetition_penalty", 1.0), ("presence_penalty", 0.0), ("frequency_penalty", 0.0), ("min_p", 0.0)):
+        v = getattr(sp, name, neutral)
+        if v is not None and float(v) != neutral:
+            bad.append(f"{name}={v}")
+    for name in ("logit_bias", "bad_words", "allowed_token_ids", "logits_processors", "structured_outputs", "guided_decoding"):
+        v = getattr(sp, name, None)
+        if v:
+            bad.append(name)
+    if getattr(sp, "prompt_logprobs", None) is not None:
+        bad.append("prompt_logprobs")
+    lp = getattr(sp, "logprobs", None)
+    if lp is not None and not (0 <= int(lp) <= _MAX_SAMPLING_TOP_K):
+        bad.append(f"logprobs={lp} (0..{_MAX_SAMPLING_TOP_K})")
+    if bad:
+        raise ValueError(f"request {req_id}: sampling parameters not supported by the B200 device sampler: {', '.join(bad)} "
+                         "(supported: temperature, top_k <= 256, top_p, seed, min_tokens, stop conditions, logprobs <= 256)")
+
+
+def _logprob_bucket(n: int) -> int:
+    """Requested top-n log-probabilities run at 1 / 5 / 20 / 256 columns (few graph variants; vLLM reads what it needs)."""
+    for c in (1, 5, 20):
+        if n <= c:
+            return c
+    return _MAX_SAMPLING_TOP_K
 
 
 class B200ModelRunner:
@@ -162,14 +196,29 @@ class B200ModelRunner:
         return (per_layer * sh.layers + sh.vocab * sh.hidden * wb) // tp + sh.vocab * sh.hidden * 2
 
     def warm_up(self) -> None:
-        """Capture the full-batch decode graph ahead of the first request (reference: compile/warm-up is NxDI's)."""
+        """Capture the decode graphs the first requests will hit: the full-batch bucket at the smallest and the largest
+        context bound (reference: compile / warm-up is NxDI's).  Other (batch bucket, context bound) pairs are captured on
+        first use into the same memory pool; the cache is an LRU of model.GRAPH_CACHE_CAP graphs."""
         if self.model is None or not self.use_cuda_graph:
             return
-        saved = self.model.num_tokens.clone()
-        self.model.num_tokens.fill_(0)  # pos = -1 -> slot -1: nothing is written
-        self.model.decode_step(self.max_num_reqs, use_graph=True)
-        self.model.num_tokens.copy_(saved)
+        from ..model import bucket_batch, bucket_ctx_blocks
+
+        m = self.model
+        saved = m.num_tokens.clone()
+        m.num_tokens.fill_(0)  # pos = -1 -> slot -1: nothing is written
+        bb = bucket_batch(self.max_num_reqs, self.max_num_reqs)
+        for mcb in sorted({bucket_ctx_blocks(1, m.max_blocks), m.max_blocks}):
+            m.decode_step(bb, max_ctx_blocks=mcb, use_graph=True)
+        m.num_tokens.copy_(saved)
         torch.cuda.synchronize()
+
+    def graph_pool_reserve_bytes(self) -> int:
+        """HBM the shared CUDA-graph pool may grow to (activations + fp32 logits of the largest decode batch, with slack
+        for fragmentation across bucket sizes); taken out of the KV budget in B200Worker.determine_available_memory."""
+        sh, b = self.model_shape(), self.max_num_reqs
+        tp = self.tp_size
+        per_step = b * (sh.vocab // tp) * 4 + b * (4 * sh.hidden + 3 * sh.intermediate // tp + 2 * sh.hidden) * 2
+        return 3 * per_step + (256 << 20)
 
     def get_kv_cache_spec(self):
         """RUNNER:361-379 hands vLLM ONE spec under 'layer'; we register one per decoder layer with the per-rank
@@ -202,9 +251,8 @@ class B200ModelRunner:
         n = self.max_num_reqs
         self._pin_tokens = torch.zeros(n, dtype=torch.int64).pin_memory()
         self._pin_rows = torch.zeros(n, dtype=torch.int32).pin_memory()
-        self._pin_ntok = torch.zeros(n, dtype=torch.int32).pin_memory()
-        self._pin_upd = torch.zeros((max(64, 4 * n), 3), dtype=torch.int32).pin_memory()
-        self._dev_upd = torch.zeros_like(self._pin_upd, device=self.device)
+        self._pin_ntok = torch.zeros(n + 1, dtype=torch.int32).pin_memory()  # + the padding row (always 0 tokens)
+        self._dev_upd = torch.zeros((max(64, 4 * n), 3), dtype=torch.int32, device=self.device)
         self._pin_out = torch.zeros(n, dtype=torch.int64).pin_memory()
         self._pin_samp = torch.ones((n, 3), dtype=torch.float32).pin_memory()
         self._pin_u = torch.zeros(n, dtype=torch.float32).pin_memory()
@@ -230,6 +278,7 @@ class B200ModelRunner:
             self.free_rows.discard(row)
             self.req_to_row[nr.req_id] = row
             blocks = _first_group(nr.block_ids) or []
+            check_sampling_params(getattr(nr, "sampling_params", None), nr.req_id)
             st = CachedRequest(nr.req_id, list(nr.prompt_token_ids), [], blocks, nr.num_computed_tokens, row,
                                getattr(nr, "sampling_params", None))
             self.requests[nr.req_id] = st
@@ -270,11 +319,13 @@ class B200ModelRunner:
         if not updates:
             return
         n = len(updates)
-        if n > self._pin_upd.shape[0]:
-            self._pin_upd = torch.zeros((2 * n, 3), dtype=torch.int32).pin_memory()
-            self._dev_upd = torch.zeros_like(self._pin_upd, device=self.device)
-        self._pin_upd[:n] = torch.tensor(updates, dtype=torch.int32)
-        self._dev_upd[:n].copy_(self._pin_upd[:n], non_blocking=True)
+        if n > self._dev_upd.shape[0]:
+            self._dev_upd = torch.zeros((2 * n, 3), dtype=torch.int32, device=self.device)
+        # a FRESH pinned tensor per push: the copy is asynchronous and a step made only of partial prefill chunks never
+        # synchronises, so a reused staging buffer could be rewritten by the host before the previous step's DMA has read
+        # it (the caching host allocator keeps this block alive until the copy has executed on the stream)
+        host = torch.tensor(updates, dtype=torch.int32).pin_memory()
+        self._dev_upd[:n].copy_(host, non_blocking=True)
         ops.block_table_scatter(self.model.block_table, self._dev_upd[:n])
         self.h2d_bytes_last += n * 12
 
@@ -327,6 +378,47 @@ class B200ModelRunner:
             return None
         return rows, [self._draw_uniform(st) if r[0] != 1.0 else 0.0 for st, r in zip(sts, rows)]
 
+    @staticmethod
+    def _num_logprobs(sts) -> int | None:
+        """None when no request of this part asked for log-probabilities, else the bucketed column count."""
+        want = [int(lp) for lp in (getattr(st.sampling_params, "logprobs", None) for st in sts) if lp is not None]
+        return _logprob_bucket(max(want)) if want else None
+
+    def _logprobs_to_host(self, parts):
+        """Start the D2H copies of the parts' LogprobsTensors triples (before the step's single synchronize)."""
+        if not any(t is not None for _, t in parts):
+            return None
+        out = []
+        for rows, t in parts:
+            if t is None:
+                out.append((rows, None))
+                continue
+            host = tuple(x[:rows].to("cpu", non_blocking=True) for x in t)
+            self.d2h_bytes_last += sum(h.numel() * h.element_size() for h in host)
+            out.append((rows, host))
+        return out
+
+    @staticmethod
+    def _logprobs_lists(parts):
+        """vLLM's LogprobsLists over the step's sampled rows (RUNNER:347-349 `logprobs_tensors.tolists()`); parts that
+        did not compute log-probabilities contribute -inf rows (their requests did not ask)."""
+        if parts is None:
+            return None
+        import numpy as np
+        from vllm.v1.outputs import LogprobsLists
+
+        width = max(h[0].shape[1] for _, h in parts if h is not None)
+        ids, lps, rks = [], [], []
+        for rows, h in parts:
+            i = np.full((rows, width), -1, dtype=np.int32)
+            l = np.full((rows, width), -np.inf, dtype=np.float32)
+            r = np.zeros((rows,), dtype=np.int32)
+            if h is not None:
+                w = h[0].shape[1]
+                i[:, :w], l[:, :w], r[:] = h[0].numpy(), h[1].numpy(), h[2].numpy()
+            ids.append(i); lps.append(l); rks.append(r)
+        return LogprobsLists(np.concatenate(ids), np.concatenate(lps), np.concatenate(rks))
+
     # ------------------------------------------------------------------ the step
     @torch.inference_mode()
     def execute_model(self, scheduler_output, intermediate_tensors=None):
@@ -340,6 +432,7 @@ class B200ModelRunner:
 
         req_ids: list[str] = []
         pending: list[torch.Tensor] = []
+        lp_parts: list[tuple] = []  # (rows, LogprobsTensors triple or None) per pending part
         no_sample: list[str] = []  # requests whose chunk did not finish the prompt (reference: -1 rows, RUNNER:1060-1064)
         # ---- prefill: one request at a time (SCHED:116 guarantees batch 1; several are processed in turn).  A chunk
         # (vLLM's native scheduler, RUNNER:654-679) is a prefill of tokens [prefilled, prefilled + n) against the cached
@@ -364,11 +457,13 @@ class B200ModelRunner:
                 u_d = torch.tensor(samp[1], dtype=torch.float32).pin_memory().to(self.device, non_blocking=True)
                 self.h2d_bytes_last += 16
                 samp = (sp_d, u_d)
-            tok = self.model.prefill(st.row, new_d, end, st.prefilled, samp, sample=last)
+            nlp = self._num_logprobs([st]) if last else None
+            tok = self.model.prefill(st.row, new_d, end, st.prefilled, samp, sample=last, num_logprobs=nlp)
             st.prefilled = end
             st.num_computed_tokens = end
             if last:
                 pending.append(tok)
+                lp_parts.append((1, self.model.last_logprobs))
                 req_ids.append(st.req_id)
             else:
                 no_sample.append(st.req_id)
@@ -381,36 +476,55 @@ class B200ModelRunner:
             sts = [reqs[rid] for rid in dec_ids]
             rows = [st.row for st in sts]
             ntok = [len(st.prompt_token_ids) + len(st.output_token_ids) for st in sts]
+            # the batch runs at its bucket size bb >= b: rows b.. point at the model's padding row (0 tokens: slot -1,
+            # context 0), so one captured graph serves every batch size of the bucket
+            bb = bucket_batch(b, self.max_num_reqs) if self.use_cuda_graph else b
             self._np_tokens[:b] = [st.output_token_ids[-1] if st.output_token_ids else st.prompt_token_ids[-1] for st in sts]
             self._np_rows[:b] = rows
+            if bb > b:
+                self._np_tokens[b:bb] = 0
+                self._np_rows[b:bb] = self.model.pad_row
             self._np_ntok[rows] = ntok
             max_ctx = max(ntok)
-            bufs = self.model.decode_buffers(b)
-            bufs.tokens.copy_(self._pin_tokens[:b], non_blocking=True)
-            bufs.row_ids.copy_(self._pin_rows[:b], non_blocking=True)
+            bufs = self.model.decode_buffers(bb)
+            bufs.tokens.copy_(self._pin_tokens[:bb], non_blocking=True)
+            bufs.row_ids.copy_(self._pin_rows[:bb], non_blocking=True)
             self.model.num_tokens.copy_(self._pin_ntok, non_blocking=True)
-            self.h2d_bytes_last += b * 12 + self._pin_ntok.numel() * 4
+            self.h2d_bytes_last += bb * 12 + self._pin_ntok.numel() * 4
             samp = self._sampling_inputs(sts)
             if samp is not None:
                 self._np_samp[:b] = samp[0]
                 self._np_u[:b] = samp[1]
-                bufs.samp_params.copy_(self._pin_samp[:b], non_blocking=True)
-                bufs.samp_u.copy_(self._pin_u[:b], non_blocking=True)
-                self.h2d_bytes_last += b * 16
-            # bound the context split by the longest live context, rounded to 8 blocks so few graphs are captured
-            mcb = min(self.model.max_blocks, -(-(-(-max_ctx // self.block_size)) // 8) * 8)
-            pending.append(self.model.decode_step(b, max_ctx_blocks=mcb, use_graph=self.use_cuda_graph,
-                                                  sampled=samp is not None))
+                if bb > b:
+                    self._np_samp[b:bb] = (1.0, 1.0, 1.0)
+                    self._np_u[b:bb] = 0.0
+                bufs.samp_params.copy_(self._pin_samp[:bb], non_blocking=True)
+                bufs.samp_u.copy_(self._pin_u[:bb], non_blocking=True)
+                self.h2d_bytes_last += bb * 16
+            nlp = self._num_logprobs(sts)
+            # bound the context split by the longest live context, bucketed so few graphs are captured
+            mcb = bucket_ctx_blocks(-(-max_ctx // self.block_size), self.model.max_blocks)
+            out = self.model.decode_step(bb, max_ctx_blocks=mcb, use_graph=self.use_cuda_graph, sampled=samp is not None,
+                                         num_logprobs=nlp)
+            pending.append(out[:b])
+            lp_parts.append((b, self.model.last_logprobs))
             req_ids += dec_ids
         # ---- one D2H read of all sampled ids (the step's only sync point; RUNNER:304-306 `.tolist()`)
         sampled: list[list[int]] = []
+        logprobs = None
         if pending:
             ids = torch.cat(pending) if len(pending) > 1 else pending[0]
             n = ids.numel()
             self._pin_out[:n].copy_(ids, non_blocking=True)
+            lp_host = self._logprobs_to_host(lp_parts)
             torch.cuda.current_stream().synchronize()
             self.d2h_bytes_last += n * 8
             sampled = [[x] if x != -1 else [] for x in self._np_out[:n].tolist()]  # RUNNER:304-306: -1 is padding
+            logprobs = self._logprobs_lists(lp_host)
+        else:
+            # a step made only of partial prefill chunks reads nothing back: wait for its copies anyway, so the host can
+            # never run a whole step ahead of the device's view of the staging buffers
+            torch.cuda.current_stream().synchronize()
         for rid, row in zip(req_ids, sampled):
             self.requests[rid].output_token_ids.extend(row)  # RUNNER:325-339
         req_ids += no_sample  # partial chunks report no token this step
@@ -419,7 +533,7 @@ class B200ModelRunner:
             req_ids=req_ids,
             req_id_to_index={r: i for i, r in enumerate(req_ids)},
             sampled_token_ids=sampled,
-            logprobs=None,
+            logprobs=logprobs,  # RUNNER:347-356 (the reference fills them on its CPU-sampling path)
             prompt_logprobs_dict={},
             pooler_output=[],
         )

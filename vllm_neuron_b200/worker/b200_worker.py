@@ -78,11 +78,13 @@ class B200Worker(WorkerBase):
         self.model_runner.load_model(load_dummy_weights=load_dummy_weights)
 
     def determine_available_memory(self) -> int:
-        """Bytes the KV pools may take: free HBM x gpu_memory_utilization minus the (not yet materialised) weights.
+        """Bytes the KV pools may take: free HBM x gpu_memory_utilization minus the (not yet materialised) weights and the
+        reserve of the shared CUDA-graph pool.
         (The reference asks the Neuron runtime or assumes 20 GB, WORKER:51-63.)"""
         free, total = torch.cuda.mem_get_info(self.device)
         util = getattr(self.cache_config, "gpu_memory_utilization", 0.9)
-        budget = int(total * util) - (total - free) - self.model_runner.weight_bytes_estimate()
+        budget = (int(total * util) - (total - free) - self.model_runner.weight_bytes_estimate()
+                  - self.model_runner.graph_pool_reserve_bytes())
         return max(budget, 0)
 
     def get_kv_cache_spec(self):
