@@ -203,7 +203,7 @@ int b200_sample_candidates(const float* cand_val, const int64_t* cand_idx, int g
  *   (fixed reduction tree: bit-reproducible).  TP: one (max, sumexp) pair per shard, laid out [groups][B] for the gather.
  * b200_gather_logprobs: with the sorted candidate lists of b200_topk_candidates ([groups][B][256]) and the sampled ids:
  *   out_ids / out_logprobs [B][1 + num_logprobs] (int32 / fp32; column 0 = the sampled token, then the num_logprobs most
- *   likely tokens, value desc / index asc), out_rank[b] = 1 + #tokens with a strictly larger logit. */
+ *   likely tokens, value desc / index asc), out_rank[b] = #tokens whose logit is >= the sampled token's (itself included). */
 int b200_row_lse(const float* logits, int64_t row_stride, float* out_max, float* out_sumexp, int B, int V, void* stream);
 int b200_gather_logprobs(const float* cand_val, const int64_t* cand_idx, int groups, int B, const int64_t* sampled,
                          const float* row_max, const float* row_sumexp, int num_logprobs, int32_t* out_ids,

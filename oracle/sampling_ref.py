@@ -76,3 +76,21 @@ def sample_candidates_ref(cand_val: np.ndarray, cand_idx: np.ndarray, params: np
                 break
         ids[r] = i[pick]
     return ids, margin
+
+
+def logprobs_ref(logits: np.ndarray, sampled: np.ndarray, num_logprobs: int):
+    """vLLM's Sampler.compute_logprobs + gather_logprobs (vllm/v1/sample/sampler.py), which the reference's CPU sampling
+    path returns through ModelRunnerOutput.logprobs (RUNNER:347-356, 1142-1239): raw log-softmax of the fp32 logits,
+    column 0 = the sampled token, columns 1..n = the n most likely tokens (value desc, index asc on ties), rank = number
+    of entries >= the sampled token's log-probability.  Pinned to vLLM's own function in tests/test_oracle_sampling.py."""
+    x = logits.astype(np.float64)
+    m = x.max(axis=1, keepdims=True)
+    lse = m + np.log(np.exp(x - m).sum(axis=1, keepdims=True))
+    lp = x - lse
+    b = x.shape[0]
+    order = np.lexsort((np.arange(x.shape[1])[None, :].repeat(b, 0), -x), axis=1)[:, :num_logprobs]
+    tok = sampled.astype(np.int64)
+    ids = np.concatenate([tok[:, None], order], axis=1).astype(np.int32)
+    vals = np.take_along_axis(lp, ids.astype(np.int64), axis=1).astype(np.float32)
+    rank = (x >= np.take_along_axis(x, tok[:, None], axis=1)).sum(axis=1).astype(np.int32)
+    return ids, vals, rank

@@ -129,3 +129,42 @@ def test_rope_kv_write_bit_exact(ops, hq, hkv, d, t):
     assert torch.equal(q_got.view(torch.int16), q_want.view(torch.int16))
     assert torch.equal(device_to_logical_pool(kd).cpu().view(torch.int16), kp.view(torch.int16))
     assert torch.equal(device_to_logical_pool(vd).cpu().view(torch.int16), vp.view(torch.int16))
+
+
+def test_decode_meta_speculative_slots_match_golden(ops, golden_index):
+    """num_spec = k: slot_mapping [B, k] = slots[0] + i, the reference's EAGLE / fused-speculation rows (model_runner.py:825-830)."""
+    n = 0
+    for c in golden_index["index"]:
+        if c["kind"] != "decode" or c["tkg"] or not c["spec"]:
+            continue
+        bs, mml, k = c["block_size"], c["max_model_len"], c["spec"]
+        b = len(c["reqs"])
+        bt = torch.zeros((b + 1, mml // bs), dtype=torch.int32)
+        ntok = torch.zeros(b + 1, dtype=torch.int32)
+        for i, q in enumerate(c["reqs"]):
+            bt[i, : len(q["block_ids"])] = torch.tensor(q["block_ids"], dtype=torch.int32)
+            ntok[i] = q["prompt_len"] + len(q["output_token_ids"])
+        rows = torch.arange(b + 1, dtype=torch.int32)  # last row: padding (0 tokens) -> -1 in every column
+        d = "cuda"
+        slot = torch.empty((b + 1, k), dtype=torch.int64, device=d)
+        pos = torch.empty(b + 1, dtype=torch.int64, device=d)
+        ctx = torch.empty(b + 1, dtype=torch.int32, device=d)
+        ops.build_decode_meta(bt.to(d), rows.to(d), ntok.to(d), slot, pos, ctx, bs)
+        assert slot.cpu().tolist() == c["out"]["slot_mapping"] + [[-1] * k]
+        assert pos.cpu().tolist()[:b] == [p[0] for p in c["out"]["position_ids"]]
+        want = [index_ref.decode_index(q["prompt_len"], len(q["output_token_ids"]), q["block_ids"], bs, mml,
+                                       num_speculative_tokens=k)["slot_mapping"] for q in c["reqs"]]
+        assert slot.cpu().tolist()[:b] == want
+        n += 1
+    assert n >= 5
+
+
+def test_remask_spec_output_matches_golden(ops, golden_index):
+    """b200_remask_spec_output == the reference's _remask_fused_spec_output (model_loader.py:308-334) on its own outputs."""
+    assert len(golden_index["remask"]) >= 4
+    for c in golden_index["remask"]:
+        got = ops.remask_spec_output(torch.tensor(c["accepted"], dtype=torch.int64, device="cuda"),
+                                     torch.tensor(c["next_pos"], dtype=torch.int64, device="cuda"),
+                                     torch.tensor(c["positions"], dtype=torch.int64, device="cuda"))
+        assert got.cpu().tolist() == c["masked"]
+        assert got.cpu().tolist() == index_ref.remask_fused_spec_output(c["accepted"], c["next_pos"], c["positions"])

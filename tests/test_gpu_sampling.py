@@ -84,3 +84,33 @@ def test_sampler_statistics_at_vocab_size(ops):
     q = p[:kept] / p[:kept].sum()
     counts = torch.tensor([(ids == top.indices[j]).sum().item() for j in range(kept)], dtype=torch.float64) / n
     assert abs(counts.sum().item() - 1.0) < 1e-12 and (counts - q).abs().max() < 2e-3
+
+
+@pytest.mark.parametrize("groups,n", [(1, 1), (1, 5), (1, 20), (2, 5), (8, 256)])
+def test_logprobs_match_oracle(ops, groups, n):
+    """b200_row_lse + b200_gather_logprobs vs oracle/sampling_ref.logprobs_ref (pinned to vLLM's Sampler): token ids and
+    ranks identical (integer work), log-probabilities within 1e-5 (fp32 log-sum-exp over the vocabulary vs fp64)."""
+    b, vs = 33, 16384
+    v = vs * groups
+    x = _logits(b, v, 31 + groups, scale=2.5)
+    x[0, 5] = x[0, v - 9] = x[0].max() + 1.0           # tie at the top (rank counts both)
+    want_greedy = x.argmax(dim=1)
+    sampled = want_greedy.clone()
+    # half of the rows "sampled" a non-greedy candidate: the r-th most likely token
+    order = torch.argsort(x, dim=1, descending=True, stable=True)
+    for r in range(0, b, 2):
+        sampled[r] = order[r, (7 * r) % 200]
+    parts = [x[:, g * vs:(g + 1) * vs].contiguous().cuda() for g in range(groups)]
+    cands = [ops.topk_candidates(p, idx_offset=g * vs) for g, p in enumerate(parts)]
+    lses = [ops.row_lse(p) for p in parts]
+    cv = torch.stack([c[0] for c in cands]).contiguous()
+    ci = torch.stack([c[1] for c in cands]).contiguous()
+    m = torch.stack([l[0] for l in lses]).contiguous()
+    s = torch.stack([l[1] for l in lses]).contiguous()
+    if groups == 1:
+        cv, ci, m, s = cv[0], ci[0], m[0], s[0]
+    ids, lp, rk = ops.gather_logprobs(cv, ci, sampled.cuda(), m, s, n)
+    wi, wl, wr = S.logprobs_ref(x.numpy(), sampled.numpy(), n)
+    assert np.array_equal(ids.cpu().numpy(), wi)
+    assert np.array_equal(rk.cpu().numpy(), wr)
+    np.testing.assert_allclose(lp.cpu().numpy(), wl, rtol=0, atol=1e-5)

@@ -87,3 +87,28 @@ def test_kept_distribution_matches_vllm_sampler_filter():
         assert set(np.nonzero(freq)[0]) <= set(kept), (r, set(np.nonzero(freq)[0]) - set(kept))
         assert all(freq[t] > 0 for t in kept if want[r, t] > 2.0 / grid)
         assert np.abs(freq - want[r]).max() <= 2.0 / grid, (r, np.abs(freq - want[r]).max())
+
+
+def test_logprobs_oracle_matches_vllm_sampler():
+    """Pin logprobs_ref to vLLM's Sampler.compute_logprobs + gather_logprobs -- what the reference returns on its CPU
+    sampling path (RUNNER:347-356)."""
+    import torch
+    from vllm.v1.sample.sampler import Sampler
+
+    b, v, n = 9, 5000, 7
+    x = _logits(b, v, 21)
+    x[0, 3] = x[0, 77] = x[0].max() + 0.5  # tie at the top: both count towards the rank
+    sampled = np.array([3, 10, 4999, 0, 17, 100, 2500, 42, 77], dtype=np.int64)
+    sampled[1] = int(x[1].argmax())
+    lp = Sampler.compute_logprobs(torch.tensor(x))
+    with torch.compiler.set_stance("force_eager"):  # vLLM torch.compiles its rank count; no OpenMP toolchain needed here
+        want = Sampler.gather_logprobs(lp, n, torch.tensor(sampled))
+    ids, vals, rank = S.logprobs_ref(x, sampled, n)
+    assert np.array_equal(rank, want.selected_token_ranks.numpy())
+    assert np.array_equal(ids[:, 0], want.logprob_token_ids[:, 0].numpy())
+    np.testing.assert_allclose(vals, want.logprobs.numpy(), rtol=0, atol=2e-6)
+    # top-n ids: identical wherever the values are distinct (torch.topk's tie order is unspecified)
+    wi = want.logprob_token_ids.numpy()
+    for r in range(b):
+        distinct = np.concatenate([[True], np.diff(vals[r, 1:]) != 0]) & np.concatenate([np.diff(vals[r, 1:]) != 0, [True]])
+        assert np.array_equal(ids[r, 1:][distinct], wi[r, 1:][distinct])

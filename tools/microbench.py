@@ -160,6 +160,53 @@ def bench_configs():
     return res
 
 
+def bench_prefill():
+    """Prefill-side kernels of Llama-3.1-8B: gemm_streamk_kernel at M = 512 / 2048 / 8192 for
+    qkv / gate_up / down in bf16 and fp8 (TFLOP/s against the measured sustained bf16 cuBLAS figure), and
+    paged_attn_prefill_kernel at S_new + cached = 2048 (0 and 1024 cached tokens) and 8192."""
+    tf_peak = PEAKS.get("bf16_tflops_sustained", 1432.9)
+    res = []
+    for kind in ("bf16", "fp8"):
+        for m in (512, 2048, 8192):
+            for n, k, name in ((6144, 4096, "qkv"), (28672, 4096, "gate_up"), (4096, 14336, "down")):
+                if kind == "bf16":
+                    w = torch.randn(n, k, device="cuda", dtype=torch.bfloat16)
+                    a = torch.randn(m, k, device="cuda", dtype=torch.bfloat16)
+                    sa = sw = None
+                else:
+                    w = torch.randn(n, k, device="cuda", dtype=torch.bfloat16).to(torch.float8_e4m3fn)
+                    a = torch.randn(m, k, device="cuda", dtype=torch.bfloat16).to(torch.float8_e4m3fn)
+                    sa, sw = torch.ones(m, device="cuda"), torch.ones(n, device="cuda")
+                out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+                dtc = {"bf16": 0, "fp8": 1}[kind]
+                wsp = torch.zeros(max(ops.gemm_workspace_bytes(m, n, k, dtc, 0), 16), dtype=torch.uint8, device="cuda")
+                fns = [lambda: ops.gemm(a, w, sa, sw, out=out, workspace=wsp)] * 4
+                ms = time_calls(fns, iters=5)
+                tf = 2 * m * n * k / ms / 1e9
+                res.append({"kernel": f"gemm_streamk_{kind}", "linear": name, "M": m, "N": n, "K": k, "us": round(ms * 1e3, 1),
+                            "TFLOPs": round(tf, 1), "frac_bf16_sustained_peak": round(tf / tf_peak, 3)})
+                print(res[-1], flush=True)
+    hq, hkv, d, bs = 32, 8, 128, 32
+    for total, cached in ((2048, 0), (2048, 1024), (8192, 0), (8192, 4096)):
+        s_new = total - cached
+        nblk = total // bs
+        g = torch.Generator(device="cuda").manual_seed(3)
+        kp = torch.randn(nblk + 1, hkv, bs, d, generator=g, device="cuda", dtype=torch.bfloat16)
+        vp = torch.randn(nblk + 1, hkv, bs, d, generator=g, device="cuda", dtype=torch.bfloat16)
+        bt = (torch.randperm(nblk, generator=torch.Generator().manual_seed(1)) + 1).to(torch.int32).cuda()
+        q = torch.randn(s_new, hq, d, generator=g, device="cuda", dtype=torch.bfloat16)
+        out = torch.empty_like(q)
+        fns = [lambda: ops.paged_attn_prefill(q, kp, vp, bt, cached, d ** -0.5, out=out)] * 4
+        ms = time_calls(fns, iters=5)
+        # causal flops: every new token attends to cached + its own prefix: QK^T and PV, 2 flops per MAC
+        pairs = s_new * cached + s_new * (s_new + 1) // 2
+        tf = 4 * pairs * hq * d / ms / 1e9
+        res.append({"kernel": "paged_attn_prefill", "S_new": s_new, "cached": cached, "Hq": hq, "Hkv": hkv, "D": d,
+                    "us": round(ms * 1e3, 1), "TFLOPs_causal": round(tf, 1), "frac_bf16_sustained_peak": round(tf / tf_peak, 3)})
+        print(res[-1], flush=True)
+    return res
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("what", nargs="?", default="all")
@@ -178,6 +225,8 @@ if __name__ == "__main__":
                                   (128, 5120, 640)], kinds=("fp8", "bf16", "int8wo"))
     if a.what == "configs":
         out += bench_configs()
+    if a.what == "prefill":
+        out += bench_prefill()
     if a.what == "gemmsweep":
         out += bench_gemm(kinds=("fp8",), splits=(0, 1, 2, 3, 4, 5, 6, 7, 8))
     if a.json:

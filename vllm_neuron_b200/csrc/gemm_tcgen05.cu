@@ -574,8 +574,71 @@ __device__ __forceinline__ void rope_reduce_store(const GemmEpilogue& ep, const 
   }
 }
 
+// Weight-only (KIND_WO8) decode path, second version: the widened bf16 weight rows never touch shared memory.  Eight
+// converter warps (the four epilogue warps plus warps 6..9, two per TMEM lane quarter, alternating k-blocks) read their
+// weight row's 64 raw int8 out of the TMA tile (64B swizzle: conflict-free 16-byte row reads), widen them in registers and
+// park the row as 32 packed bf16x2 columns in a TMEM slot with tcgen05.st; the MMA takes its A operand straight from TMEM
+// (tcgen05.mma with a tensor-memory A).  Shared memory holds only the raw int8 ring (8 KB a stage) and the activation
+// ring, so the rings are twice as deep as with a widened copy in shared memory, there is no generic-proxy -> async-proxy
+// fence on the way to the tensor core, and the MMA reads half as many shared-memory bytes.
+constexpr int WO_CONV_WARPS = 8;
+constexpr int WO_THREADS = 64 + 32 * WO_CONV_WARPS;
+constexpr uint32_t WO_TMEM_COLS = 256;  // accumulator (BM columns, >= 32) + widened-weight slots of 32 columns each
+template <int BM>
+__host__ __device__ constexpr int wo_slots() { return (int)(WO_TMEM_COLS - (BM < 32 ? 32 : BM)) / 32; }
+
+// 64 raw int8 of one weight row (already in registers) -> 32 packed bf16x2 words, K order
+__device__ __forceinline__ void widen_row64(const uint4 (&raw)[4], uint32_t (&o)[32]) {
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const uint32_t w[4] = {raw[c].x, raw[c].y, raw[c].z, raw[c].w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {  // same exact bit trick as widen_w_tile
+      const uint32_t x = w[j] ^ 0x80808080u;
+      const float f0 = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7440)) - 8388736.f;
+      const float f1 = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7441)) - 8388736.f;
+      const float f2 = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7442)) - 8388736.f;
+      const float f3 = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7443)) - 8388736.f;
+      o[c * 8 + 2 * j] = __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632);
+      o[c * 8 + 2 * j + 1] = __byte_perm(__float_as_uint(f2), __float_as_uint(f3), 0x7632);
+    }
+  }
+}
+
+// One converter warp: k-blocks first, first + 2, ... of this CTA's stream; `quarter` = warp id % 4 = the TMEM lane quarter
+// (and so the 32 weight rows) this warp may touch.  Raw tile s = i % nst in shared memory (TMA, 64B swizzle: the 16-byte
+// chunk c of row r sits at chunk c ^ ((r >> 1) & 3)), TMEM slot t = i % NW.
+template <int BM>
+__device__ __forceinline__ void wo_convert(const uint8_t* __restrict__ raw_ring, uint64_t* full_raw, uint64_t* empty_raw,
+                                           uint64_t* full_w, uint64_t* empty_w, uint32_t tmem_w0, int nk, int nst,
+                                           int first, int quarter, int lane) {
+  constexpr int NW = wo_slots<BM>();
+  const int row = quarter * 32 + lane;
+  const int sw = (row >> 1) & 3;
+  for (int i = first; i < nk; i += 2) {
+    const int s = i % nst, t = i % NW;
+    mbar_wait(&full_raw[s], (uint32_t)(i / nst) & 1u);
+    if (i >= NW) mbar_wait(&empty_w[t], (uint32_t)(i / NW - 1) & 1u);  // the MMAs that read slot t have retired
+    tc_fence_after();
+    const uint8_t* rp = raw_ring + (size_t)s * RAW_TILE + row * 64;
+    uint4 raw[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) raw[c] = *reinterpret_cast<const uint4*>(rp + ((c ^ sw) << 4));
+    uint32_t o[32];
+    widen_row64(raw, o);
+    tmem_st_32x32b_x32(tmem_w0 + ((uint32_t)(quarter * 32) << 16) + (uint32_t)t * 32u, o);
+    tmem_st_wait();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) {
+      mbar_arrive(&full_w[t]);
+      mbar_arrive(&empty_raw[s]);
+    }
+  }
+}
+
 template <int KIND, int BM, int EPI>
-__global__ void __launch_bounds__(GEMM_THREADS, 2)
+__global__ void __launch_bounds__(KIND == KIND_WO8 ? WO_THREADS : GEMM_THREADS, KIND == KIND_WO8 ? 1 : 2)
     gemm_decode_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap a_map,
                        GemmEpilogue ep, int M, int N, int num_kb, int nst, int ring_bytes, int l2_ahead,
                        unsigned long long* __restrict__ trace) {
@@ -583,13 +646,15 @@ __global__ void __launch_bounds__(GEMM_THREADS, 2)
   constexpr int BK_ELEMS = GEMM_BK_BYTES / T::ELEM;
   constexpr int W_TILE = GEMM_BN * GEMM_BK_BYTES;
   constexpr int A_TILE = BM * GEMM_BK_BYTES;
-  constexpr uint32_t TMEM_COLS = BM < 32 ? 32 : BM;
+  constexpr bool WO = KIND == KIND_WO8;
+  constexpr uint32_t ACC_COLS = BM < 32 ? 32 : BM;
+  constexpr uint32_t TMEM_COLS = WO ? WO_TMEM_COLS : ACC_COLS;
+  constexpr int NW = wo_slots<BM>();  // weight-only: widened-weight slots in TMEM
   // optional per-CTA time stamps (b200_gemm_set_trace; tools/gemm_trace.py): 0 start, 1 producer past the dependency,
   // 2 first stage landed, 3 last MMA retired, 4 partials pushed, 5 cluster barrier passed, 6 outputs stored
 #define B200_STAMP(k) do { if (trace) trace[(size_t)blockIdx.x * 8 + (k)] = globaltimer_ns(); } while (0)
   if (threadIdx.x == 0) B200_STAMP(0);
   constexpr uint32_t IDESC = umma_idesc(T::CFMT, T::ABFMT, GEMM_BN, BM);
-  constexpr bool WO = KIND == KIND_WO8;
   constexpr int MK = KIND == KIND_WO8 ? (int)KIND_F16 : KIND;
 
   extern __shared__ uint8_t smem_raw[];
@@ -597,10 +662,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 2)
   const int S = (int)cluster_nctarank(), r = (int)cluster_ctarank();
   const int tp_max = (M + S - 1) / S;                                   // most tokens one rank owns
   const int m_lo = (int)((long long)M * r / S), m_hi = (int)((long long)M * (r + 1) / S);  // tokens this rank finishes
+  // ring_bytes = max(the rings the staging tile may alias once they are dead, the staging tile):
+  //   W8A8 / bf16:  [w_ring: nst x 16 KB | ring_bytes][a_ring: nst x A_TILE]
+  //   weight-only:  [a_ring: nst x A_TILE][raw_ring: nst x 8 KB | together ring_bytes]   (no widened copy in smem)
   uint8_t* w_ring = smem;
-  uint8_t* a_ring = smem + ring_bytes;  // ring_bytes = max(nst weight stages, the staging tile)
+  uint8_t* a_ring = WO ? smem : smem + ring_bytes;
   uint8_t* raw_ring = a_ring + (size_t)nst * A_TILE;  // weight-only: nst raw int8 tiles
-  float* red = reinterpret_cast<float*>(raw_ring + (WO ? (size_t)nst * RAW_TILE : 0));  // [S][tp_max][128] (S > 1)
+  float* red = reinterpret_cast<float*>(WO ? smem + ring_bytes : raw_ring);  // [S][tp_max][128] (S > 1)
   float* a_s = red + (S > 1 ? (size_t)S * tp_max * GEMM_BN : 0);         // [BM] per-token scales
   __nv_bfloat16* resid_s = reinterpret_cast<__nv_bfloat16*>(a_s + BM);  // [owned tokens][128] (iff residual)
   uint64_t* full_w = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(resid_s) +
@@ -623,14 +691,15 @@ __global__ void __launch_bounds__(GEMM_THREADS, 2)
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&w_map);
     tma_prefetch_desc(&a_map);
-    for (int s = 0; s < nst; ++s) {
-      mbar_init(&full_w[s], 1);  // weight-only: one arrival after all 128 widening threads have fenced and met
+    for (int s = 0; s < (WO && NW > nst ? NW : nst); ++s) {
+      // weight-only: full_w / empty_w guard the TMEM weight slots (one arrival per quarter warp of the converting group)
+      mbar_init(&full_w[s], WO ? 4 : 1);
       mbar_init(&empty_w[s], 1);
       mbar_init(&full_a[s], 1);
       mbar_init(&empty_a[s], 1);
       if (WO) {
         mbar_init(&full_raw[s], 1);
-        mbar_init(&empty_raw[s], 1);
+        mbar_init(&empty_raw[s], 4);
       }
     }
     mbar_init(tfull, 1);
@@ -711,31 +780,49 @@ __global__ void __launch_bounds__(GEMM_THREADS, 2)
     __syncwarp();  // lanes 1..31 park here
   } else if (warp == 1) {
     int s = 0, ph = 0;
+    int t = 0, pht = 0;  // weight-only: TMEM weight slot / its parity
     for (int i = 0; i < nk; ++i) {
-      mbar_wait(&full_w[s], ph);
+      mbar_wait(&full_w[WO ? t : s], WO ? pht : ph);
       if (trace && lane == 0 && i < 8) trace[(size_t)gridDim.x * 8 + (size_t)blockIdx.x * 16 + i] = globaltimer_ns();
       mbar_wait(&full_a[s], ph);
       if (trace && lane == 0 && i < 8) trace[(size_t)gridDim.x * 8 + (size_t)blockIdx.x * 16 + 8 + i] = globaltimer_ns();
       tc_fence_after();
       if (lane == 0) {
         if (i == 0) B200_STAMP(2);
-        const uint32_t wa = smem_u32(w_ring + (size_t)s * W_TILE);
         const uint32_t aa = smem_u32(a_ring + (size_t)s * A_TILE);
+        if constexpr (WO) {
+          // A operand = the widened weight rows in TMEM slot t: lane = weight row, 8 columns (16 bf16 of K) per UMMA_K
+          const uint32_t wt = tmem_base + ACC_COLS + (uint32_t)t * 32u;
 #pragma unroll
-        for (int kk = 0; kk < GEMM_BK_BYTES / 32; ++kk)  // UMMA_K = 32 bytes of K
-          umma_ss<MK>(tmem_base, umma_desc_sw128(wa + kk * 32), umma_desc_sw128(aa + kk * 32), IDESC,
-                      (uint32_t)((i | kk) != 0));
-        tc_commit(&empty_a[s]);
-        tc_commit(&empty_w[s]);
+          for (int kk = 0; kk < GEMM_BK_BYTES / 32; ++kk)
+            umma_ts_f16(tmem_base, wt + kk * 8, umma_desc_sw128(aa + kk * 32), IDESC, (uint32_t)((i | kk) != 0));
+          tc_commit(&empty_a[s]);
+          tc_commit(&empty_w[t]);
+        } else {
+          const uint32_t wa = smem_u32(w_ring + (size_t)s * W_TILE);
+#pragma unroll
+          for (int kk = 0; kk < GEMM_BK_BYTES / 32; ++kk)  // UMMA_K = 32 bytes of K
+            umma_ss<MK>(tmem_base, umma_desc_sw128(wa + kk * 32), umma_desc_sw128(aa + kk * 32), IDESC,
+                        (uint32_t)((i | kk) != 0));
+          tc_commit(&empty_a[s]);
+          tc_commit(&empty_w[s]);
+        }
       }
       __syncwarp();
       if (++s == nst) {
         s = 0;
         ph ^= 1;
       }
+      if (++t == NW) {
+        t = 0;
+        pht ^= 1;
+      }
     }
     if (lane == 0) tc_commit(tfull);
     __syncwarp();
+  } else if (WO && warp >= 6) {
+    // weight-only: the second converter group (odd k-blocks); see wo_convert below
+    wo_convert<BM>(raw_ring, full_raw, empty_raw, full_w, empty_w, tmem_base + ACC_COLS, nk, nst, 1, warp & 3, lane);
   } else {
     // ---- epilogue warps, part 1: stage the epilogue operands while the ring streams
     griddep_wait();
@@ -779,24 +866,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 2)
     named_bar_sync(1, 128);
 
     if constexpr (WO) {
-      // ---- weight-only: these 128 threads widen every raw int8 tile into the bf16 operand tile the MMA reads.
-      // The raw tiles were requested before the dependency resolved, so the first ones are usually waiting here.
-      int s = 0, ph = 0;
-      for (int i = 0; i < nk; ++i) {
-        mbar_wait(&full_raw[s], ph);
-        if (i >= nst) mbar_wait(&empty_w[s], ph ^ 1);  // the MMAs that read the previous contents have retired
-        widen_w_tile(raw_ring + (size_t)s * RAW_TILE, w_ring + (size_t)s * W_TILE, et);
-        fence_proxy_async();  // generic-proxy writes -> visible to the tensor core (async proxy)
-        named_bar_sync(1, 128);  // all 128 threads have written and fenced: ONE arrival per barrier (128 arrivals on
-        if (et == 0) {           // one shared-memory word serialise and cost more than the widening itself)
-          mbar_arrive(&full_w[s]);
-          mbar_arrive(&empty_raw[s]);
-        }
-        if (++s == nst) {
-          s = 0;
-          ph ^= 1;
-        }
-      }
+      // ---- weight-only: the first converter group (even k-blocks).  The raw tiles were requested before the dependency
+      // resolved, so the first ones are usually waiting here.
+      wo_convert<BM>(raw_ring, full_raw, empty_raw, full_w, empty_w, tmem_base + ACC_COLS, nk, nst, 0, lg, lane);
     }
 
     // ---- part 2: the accumulator is final
@@ -848,13 +920,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 2)
   __syncwarp();
   if (threadIdx.x == 64) B200_STAMP(4);
   if (S > 1) {
-    if (warp < 2) cluster_wait();  // phase 1 for the warps that do not push
-    if (warp >= 2 && m_hi > m_lo) mbar_wait(red_full, 0);  // the S partials of this CTA's tokens have landed
+    if (warp < 2 || warp >= 6) cluster_wait();  // phase 1 for the warps that do not push
+    if (warp >= 2 && warp < 6 && m_hi > m_lo) mbar_wait(red_full, 0);  // the S partials of this CTA's tokens have landed
     if (threadIdx.x == 64) B200_STAMP(5);
     // phase 2: nobody may exit while a peer's copy still reads its staging tile; arriving here means "all copies INTO
     // me are complete", so once every CTA has arrived every copy OUT of everyone is complete too
     cluster_arrive_relaxed();
-    if (warp >= 2) {
+    if (warp >= 2 && warp < 6) {
       const int n0 = n_tile * GEMM_BN + 4 * t4;
       const bool hb = ep.bias != nullptr, hr = EPI != EPI_SILU_MUL && ep.residual != nullptr;
       bool rope_done = false;
@@ -1030,18 +1102,28 @@ struct DecodeCfg {
 
 // ring depth that fits `budget` bytes
 bool decode_rings(int bm, int M, int S, int nk, bool resid, size_t budget, DecodeCfg& c, bool wo = false) {
-  const int a_tile = bm * GEMM_BK_BYTES + (wo ? RAW_TILE : 0);  // weight-only: one raw int8 tile rides with every stage
+  // per stage: the activation tile plus the weight tile as it sits in shared memory -- 16 KB of operand-ready rows, or
+  // (weight-only) the 8 KB raw int8 tile: the widened rows live in TMEM
+  const int a_tile = bm * GEMM_BK_BYTES;
+  const int w_tile = wo ? RAW_TILE : W_TILE_BYTES;
   const int tp_max = (M + S - 1) / S;
   const size_t red = S > 1 ? (size_t)S * tp_max * GEMM_BN * 4 : 0;
   const size_t fixed = 1024 + red + (size_t)bm * 8 + (resid ? (size_t)(S > 1 ? tp_max : bm) * GEMM_BN * 2 : 0) + 768;
-  if (budget < fixed + (size_t)(a_tile + W_TILE_BYTES)) return false;
-  int n = (int)((budget - fixed) / (size_t)(a_tile + W_TILE_BYTES));
+  const size_t stage = S > 1 ? (size_t)bm * GEMM_BN * 4 : 0;  // the partial tile is staged over the dead ring(s)
+  if (budget < fixed + (size_t)(a_tile + w_tile) || budget < fixed + stage) return false;
+  int n = (int)((budget - fixed) / (size_t)(a_tile + w_tile));
   if (n > DEC_MAX_ST) n = DEC_MAX_ST;
   if (n > nk) n = nk;
   if (n < 1) return false;
   c.nst = n;
+  if (wo) {  // [a_ring][raw_ring] together are what the staging tile aliases
+    size_t ring = (size_t)n * (a_tile + w_tile);
+    if (ring < stage) ring = stage;
+    c.ring_bytes = (int)ring;
+    c.smem = fixed + ring;
+    return c.smem <= budget;
+  }
   size_t ring = (size_t)n * W_TILE_BYTES;
-  const size_t stage = S > 1 ? (size_t)bm * GEMM_BN * 4 : 0;  // the partial tile is staged over the dead ring
   if (ring < stage) ring = stage;
   c.ring_bytes = (int)ring;
   c.smem = fixed + ring + (size_t)n * a_tile;
@@ -1077,8 +1159,8 @@ int plan_decode(DecodeCfg& best, int M, int n_tiles, int num_kb, int split_k, bo
   // two CTAs per SM (half the shared memory each) or one with all of it: M <= 64 always fits two; M = 65..128 (32 KB
   // activation + weight per stage, 64 KB of split-K partials) is tried both ways and the cost model decides
   for (int per_sm = 2; per_sm >= 1; --per_sm) {
-  if (per_sm == 2 && force_occ == 1) continue;
-  if (per_sm == 1 && BM <= 64 && force_occ != 1) continue;
+  if (per_sm == 2 && (force_occ == 1 || KIND == KIND_WO8)) continue;  // weight-only: 320 threads x ~126 registers, one CTA
+  if (per_sm == 1 && BM <= 64 && force_occ != 1 && KIND != KIND_WO8) continue;
   const size_t budget = per_sm == 2 ? SMEM_TWO_PER_SM : SMEM_ONE_PER_SM;
   for (int S = 1; S <= 8; ++S) {
     if (split_k != 0 && S != split_k) continue;
@@ -1090,7 +1172,7 @@ int plan_decode(DecodeCfg& best, int M, int n_tiles, int num_kb, int split_k, bo
     // clusters of 4 and 8 strand SMs (GPC packing): ask the runtime how many clusters one wave holds
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(n_tiles * S);
-    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.blockDim = dim3(KIND == KIND_WO8 ? WO_THREADS : GEMM_THREADS);
     cfg.dynamicSmemBytes = c.smem;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
@@ -1151,8 +1233,8 @@ int launch_decode(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilog
   if (rc) return rc;
   auto kern = gemm_decode_kernel<KIND, BM, EPI>;
   static const int l2_ahead = getenv("B200_GEMM_L2_AHEAD") ? atoi(getenv("B200_GEMM_L2_AHEAD")) : 0;  // tuning aid
-  B200_CUDA_OK(launch_kernel_cluster(kern, dim3(p.n_tiles * c.S), dim3(GEMM_THREADS), c.smem, c.S, stream, wm, am, ep, M, N,
-                                     p.num_kb, c.nst, c.ring_bytes, l2_ahead, g_trace));
+  B200_CUDA_OK(launch_kernel_cluster(kern, dim3(p.n_tiles * c.S), dim3(KIND == KIND_WO8 ? WO_THREADS : GEMM_THREADS), c.smem,
+                                     c.S, stream, wm, am, ep, M, N, p.num_kb, c.nst, c.ring_bytes, l2_ahead, g_trace));
   return B200_OK;
 }
 
@@ -1195,7 +1277,9 @@ int gemm_common(const void* a, const void* w, const GemmEpilogue& ep, int epi, i
   CUtensorMapDataType dt = eb == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
   int bk = GEMM_BK_BYTES / eb;
   CUtensorMap wm, am;
-  if (wo)  // raw int8 rows, 64 B of K per row and stage, no swizzle: the widening warps read them with plain loads
+  if (wo && p.decode)  // raw int8 rows, 64 B of K per row and stage, 64B swizzle: a converter thread reads its whole row
+    rc = make_tmap_2d_sw64(&wm, w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)K, (uint64_t)N, (uint64_t)K, bk, GEMM_BN);
+  else if (wo)  // stream-K: no swizzle, the widening warps read 16-byte pieces with plain loads
     rc = make_tmap_2d_plain(&wm, w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)K, (uint64_t)N, (uint64_t)K, bk, GEMM_BN);
   else
     rc = make_tmap_2d(&wm, w, dt, eb, (uint64_t)K, (uint64_t)N, (uint64_t)K * eb, bk, GEMM_BN);

@@ -103,6 +103,33 @@ int make_tmap_2d_plain(CUtensorMap* out, const void* base, CUtensorMapDataType d
   return 0;
 }
 
+int make_tmap_2d_sw64(CUtensorMap* out, const void* base, CUtensorMapDataType dt, uint32_t elem_bytes, uint64_t cols,
+                      uint64_t rows, uint64_t row_pitch_bytes, uint32_t box_cols, uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) {
+    set_last_error("cuTensorMapEncodeTiled entry point not available (no driver?)");
+    return B200_ERR_DRIVER;
+  }
+  if (((uintptr_t)base & 15) || (row_pitch_bytes & 15) || box_cols * elem_bytes != 64 || box_rows > 256) {
+    set_last_error("tensor map (64B swizzle): base %p pitch %llu box %ux%u elem %u violates TMA alignment rules", base,
+                   (unsigned long long)row_pitch_bytes, box_cols, box_rows, elem_bytes);
+    return B200_ERR_INVALID_ARG;
+  }
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {row_pitch_bytes};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled (64B swizzle) failed: CUresult %d (cols=%llu rows=%llu pitch=%llu box=%ux%u)",
+                   (int)r, (unsigned long long)cols, (unsigned long long)rows, (unsigned long long)row_pitch_bytes, box_cols,
+                   box_rows);
+    return B200_ERR_DRIVER;
+  }
+  return 0;
+}
+
 void unify_carveout(const void* kern) {
   static const int on = getenv("B200_CARVEOUT") ? atoi(getenv("B200_CARVEOUT")) : 0;
   if (!on) return;

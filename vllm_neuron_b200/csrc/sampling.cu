@@ -281,7 +281,8 @@ __global__ void __launch_bounds__(LSE_THREADS) row_lse_kernel(const float* __res
 
 // One warp per row.  cand_* [groups][B][256] sorted (value desc, index asc) per group, row_max / row_sum [groups][B].
 // out_ids / out_logprobs [B][1 + n]: column 0 = the sampled token, columns 1..n = the n most likely tokens;
-// out_rank [B] = 1 + number of tokens with a strictly larger logit (vLLM's rank rule).  The sampled token always is a
+// out_rank [B] = number of tokens whose logit is >= the sampled token's, itself included (vLLM's rank rule:
+// batched_count_greater_than is `(x >= value).sum(-1)`).  The sampled token always is a
 // candidate (the sampler draws from the candidates; the greedy token is candidate 0 of its shard).
 __global__ void __launch_bounds__(128) gather_logprobs_kernel(const float* __restrict__ cand_val,
                                                               const int64_t* __restrict__ cand_idx, int groups, int B,
@@ -311,7 +312,7 @@ __global__ void __launch_bounds__(128) gather_logprobs_kernel(const float* __res
   for (int g = 0; g < groups; ++g)
     for (int j = l; j < SAMPLE_K; j += 32) {
       const int64_t o = ((int64_t)g * B + b) * SAMPLE_K + j;
-      cnt += (cand_idx[o] >= 0 && cand_val[o] > xs) ? 1 : 0;
+      cnt += (cand_idx[o] >= 0 && cand_val[o] >= xs) ? 1 : 0;
     }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
@@ -319,7 +320,7 @@ __global__ void __launch_bounds__(128) gather_logprobs_kernel(const float* __res
   const int64_t row = (int64_t)b * (1 + n);
   out_ids[row] = (int32_t)tok;
   out_lp[row] = xs - lse;
-  out_rank[b] = cnt + 1;
+  out_rank[b] = cnt;
   int head[16];
   for (int g = 0; g < groups; ++g) head[g] = 0;
   for (int j = 0; j < n; ++j) {  // k-way merge of the sorted shard lists: value desc, then index asc
