@@ -46,8 +46,8 @@ __device__ __forceinline__ void bulk_1d(void* dst, const void* src, uint32_t byt
 }
 
 // units: one unit = one request of `req_bytes`; CTA c handles units [c*per, (c+1)*per)
-__global__ void __launch_bounds__(64) ingest(const __grid_constant__ CUtensorMap map, const uint8_t* base, int mode, int per,
-                                            int stages, int req_bytes, int kb_per_row, int box_rows, int box_bytes) {
+__global__ void __launch_bounds__(160) ingest(const __grid_constant__ CUtensorMap map, const uint8_t* base, int mode, int per,
+                                             int stages, int req_bytes, int kb_per_row, int box_rows, int box_bytes, int nprod) {
   extern __shared__ uint8_t raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full = (uint64_t*)(smem + (size_t)stages * req_bytes);
@@ -58,8 +58,10 @@ __global__ void __launch_bounds__(64) ingest(const __grid_constant__ CUtensorMap
   }
   __syncthreads();
   const long long u0 = (long long)blockIdx.x * per;
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < per; ++i) {
+  // producers: lane 0 of warps 0..nprod-1, request i belongs to producer i % nprod (does a CTA's TMA stream speed up when
+  // its requests come from several warps?); consumer: lane 0 of warp 4
+  if ((threadIdx.x & 31) == 0 && (int)(threadIdx.x >> 5) < nprod) {
+    for (int i = threadIdx.x >> 5; i < per; i += nprod) {
       const int s = i % stages;
       if (i >= stages) mbar_wait(&empty[s], ((i / stages) - 1) & 1);
       mbar_expect_tx(&full[s], req_bytes);
@@ -75,7 +77,7 @@ __global__ void __launch_bounds__(64) ingest(const __grid_constant__ CUtensorMap
         tma_2d(smem + (size_t)s * req_bytes, &map, &full[s], kb * box_bytes, (int)(rt * box_rows));
       }
     }
-  } else if (threadIdx.x == 32) {
+  } else if (threadIdx.x == 128) {
     for (int i = 0; i < per; ++i) {
       const int s = i % stages;
       mbar_wait(&full[s], (i / stages) & 1);
@@ -126,7 +128,9 @@ int main() {
       kb_per_row = (int)(pitch / c.box_bytes);
     }
     for (int per_sm = 1; per_sm <= 2; ++per_sm) {
+      for (int nprod : {1, 2, 4})
       for (int stages : {4, 8}) {
+        if (nprod > 1 && (stages != 8 || per_sm != 1)) continue;
         const size_t smem = (size_t)stages * req_bytes + 2 * stages * 8 + 1024;
         if (smem * per_sm > 226 * 1024) continue;
         const int grid = 148 * per_sm;
@@ -137,15 +141,15 @@ int main() {
         CK(cudaEventCreate(&e1));
         for (int it = 0; it < 2; ++it) {
           CK(cudaEventRecord(e0));
-          ingest<<<grid, 64, smem>>>(map, buf, c.mode, per, stages, req_bytes, kb_per_row, c.box_rows, c.box_bytes);
+          ingest<<<grid, 160, smem>>>(map, buf, c.mode, per, stages, req_bytes, kb_per_row, c.box_rows, c.box_bytes, nprod);
           CK(cudaEventRecord(e1));
           CK(cudaDeviceSynchronize());
         }
         float ms;
         CK(cudaEventElapsedTime(&ms, e0, e1));
         const double gb = (double)per * grid * req_bytes / 1e9;
-        printf("%-42s ctas/SM %d stages %d: %8.1f GB/s total, %6.1f GB/s per SM, %.2f cyc@1.9GHz per 128B\n", c.name, per_sm,
-               stages, gb / (ms * 1e-3), gb / (ms * 1e-3) / 148, 1.9e9 * (ms * 1e-3) / ((double)per * per_sm * req_bytes / 128));
+        printf("%-42s ctas/SM %d producers %d stages %d: %8.1f GB/s total, %6.1f GB/s per SM, %.2f cyc@1.9GHz per 128B\n", c.name, per_sm,
+               nprod, stages, gb / (ms * 1e-3), gb / (ms * 1e-3) / 148, 1.9e9 * (ms * 1e-3) / ((double)per * per_sm * req_bytes / 128));
       }
     }
   }
