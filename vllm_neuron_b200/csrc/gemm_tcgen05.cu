@@ -582,7 +582,8 @@ __device__ __forceinline__ void rope_reduce_store(const GemmEpilogue& ep, const 
 // ring, so the rings are twice as deep as with a widened copy in shared memory, there is no generic-proxy -> async-proxy
 // fence on the way to the tensor core, and the MMA reads half as many shared-memory bytes.
 constexpr int WO_CONV_WARPS = 8;
-constexpr int WO_THREADS = 64 + 32 * WO_CONV_WARPS;
+constexpr int WO_THREADS = 64 + 32 * WO_CONV_WARPS + 32;  // + the activation producer warp (last warp)
+constexpr int DEC_THREADS = GEMM_THREADS + 32;            // decode kernel: + the activation producer warp (warp 6)
 constexpr uint32_t WO_TMEM_COLS = 256;  // accumulator (BM columns, >= 32) + widened-weight slots of 32 columns each
 template <int BM>
 __host__ __device__ constexpr int wo_slots() { return (int)(WO_TMEM_COLS - (BM < 32 ? 32 : BM)) / 32; }
@@ -638,7 +639,7 @@ __device__ __forceinline__ void wo_convert(const uint8_t* __restrict__ raw_ring,
 }
 
 template <int KIND, int BM, int EPI>
-__global__ void __launch_bounds__(KIND == KIND_WO8 ? WO_THREADS : GEMM_THREADS, KIND == KIND_WO8 ? 1 : 2)
+__global__ void __launch_bounds__(KIND == KIND_WO8 ? WO_THREADS : DEC_THREADS, KIND == KIND_WO8 ? 1 : 2)
     gemm_decode_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap a_map,
                        GemmEpilogue ep, int M, int N, int num_kb, int nst, int ring_bytes, int l2_ahead,
                        unsigned long long* __restrict__ trace) {
@@ -650,6 +651,7 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? WO_THREADS : GEMM_THREADS, 
   constexpr uint32_t ACC_COLS = BM < 32 ? 32 : BM;
   constexpr uint32_t TMEM_COLS = WO ? WO_TMEM_COLS : ACC_COLS;
   constexpr int NW = wo_slots<BM>();  // weight-only: widened-weight slots in TMEM
+  constexpr int AP_WARP = WO ? 2 + WO_CONV_WARPS : 6;  // the activation producer: the last warp
   // optional per-CTA time stamps (b200_gemm_set_trace; tools/gemm_trace.py): 0 start, 1 producer past the dependency,
   // 2 first stage landed, 3 last MMA retired, 4 partials pushed, 5 cluster barrier passed, 6 outputs stored
 #define B200_STAMP(k) do { if (trace) trace[(size_t)blockIdx.x * 8 + (k)] = globaltimer_ns(); } while (0)
@@ -733,7 +735,6 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? WO_THREADS : GEMM_THREADS, 
   if (warp == 0) {
     if (lane == 0 && nk > 0) {
       const uint64_t pol_w = policy_evict_first();  // every weight byte is read once per step
-      const uint64_t pol_a = policy_evict_last();   // activations are re-read by every tile
       const int npre = nk < nst ? nk : nst;
       // weights do not depend on any kernel of the step: fill the ring with W tiles before the dependency resolves
       for (int i = 0; i < npre; ++i) {
@@ -751,17 +752,11 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? WO_THREADS : GEMM_THREADS, 
         const int pf_end = nk < npre + l2_ahead ? nk : npre + l2_ahead;
         for (int i = npre; i < pf_end; ++i) tma_prefetch_l2_2d(&w_map, (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN);
       }
-      griddep_wait();
-      B200_STAMP(1);
-      for (int i = 0; i < npre; ++i) {
-        mbar_expect_tx(&full_a[i], A_TILE);
-        tma_load_2d_hint(a_ring + (size_t)i * A_TILE, &a_map, &full_a[i], (kb0 + i) * BK_ELEMS, 0, pol_a);
-      }
+      // refills: weights only -- the activation tiles come from their own producer warp (AP_WARP).  One issuing thread
+      // sustains about one TMA box row per 5.5 cycles (tools/tma_ingest.cu: 128x64B boxes 21 GB/s per SM from one
+      // producer warp, 40 GB/s from two), so W and A boxes issued by the same thread queue behind each other.
       int s = 0, ph = 0;  // stage / parity of the empty barriers for refills
       for (int i = npre; i < nk; ++i) {
-        mbar_wait(&empty_a[s], ph);
-        mbar_expect_tx(&full_a[s], A_TILE);
-        tma_load_2d_hint(a_ring + (size_t)s * A_TILE, &a_map, &full_a[s], (kb0 + i) * BK_ELEMS, 0, pol_a);
         if constexpr (WO) {
           mbar_wait(&empty_raw[s], ph);
           mbar_expect_tx(&full_raw[s], RAW_TILE);
@@ -819,6 +814,24 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? WO_THREADS : GEMM_THREADS, 
       }
     }
     if (lane == 0) tc_commit(tfull);
+    __syncwarp();
+  } else if (warp == AP_WARP) {
+    // ---- activation producer: everything it loads was written by the previous kernel of the stream
+    if (lane == 0 && nk > 0) {
+      const uint64_t pol_a = policy_evict_last();  // activations are re-read by every tile
+      griddep_wait();
+      B200_STAMP(1);
+      int s = 0, ph = 1;  // first pass over the ring: the stages are free (parity-1 wait on a fresh barrier returns at once)
+      for (int i = 0; i < nk; ++i) {
+        mbar_wait(&empty_a[s], ph);
+        mbar_expect_tx(&full_a[s], A_TILE);
+        tma_load_2d_hint(a_ring + (size_t)s * A_TILE, &a_map, &full_a[s], (kb0 + i) * BK_ELEMS, 0, pol_a);
+        if (++s == nst) {
+          s = 0;
+          ph ^= 1;
+        }
+      }
+    }
     __syncwarp();
   } else if (WO && warp >= 6) {
     // weight-only: the second converter group (odd k-blocks); see wo_convert below
@@ -1172,7 +1185,7 @@ int plan_decode(DecodeCfg& best, int M, int n_tiles, int num_kb, int split_k, bo
     // clusters of 4 and 8 strand SMs (GPC packing): ask the runtime how many clusters one wave holds
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(n_tiles * S);
-    cfg.blockDim = dim3(KIND == KIND_WO8 ? WO_THREADS : GEMM_THREADS);
+    cfg.blockDim = dim3(KIND == KIND_WO8 ? WO_THREADS : DEC_THREADS);
     cfg.dynamicSmemBytes = c.smem;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
@@ -1233,7 +1246,7 @@ int launch_decode(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilog
   if (rc) return rc;
   auto kern = gemm_decode_kernel<KIND, BM, EPI>;
   static const int l2_ahead = getenv("B200_GEMM_L2_AHEAD") ? atoi(getenv("B200_GEMM_L2_AHEAD")) : 0;  // tuning aid
-  B200_CUDA_OK(launch_kernel_cluster(kern, dim3(p.n_tiles * c.S), dim3(KIND == KIND_WO8 ? WO_THREADS : GEMM_THREADS), c.smem,
+  B200_CUDA_OK(launch_kernel_cluster(kern, dim3(p.n_tiles * c.S), dim3(KIND == KIND_WO8 ? WO_THREADS : DEC_THREADS), c.smem,
                                      c.S, stream, wm, am, ep, M, N, p.num_kb, c.nst, c.ring_bytes, l2_ahead, g_trace));
   return B200_OK;
 }
