@@ -293,27 +293,41 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
     bt[:, :nblk] = torch.tensor(blocks, dtype=torch.int32, device=dev).reshape(b, nblk)
     wb = 1 if args.quant != "bf16" else 2
     qd, kd = shape.num_q_heads * shape.head_dim, shape.num_kv_heads * shape.head_dim
-    need = ((qd + 2 * kd + qd) * shape.hidden + 3 * shape.intermediate * shape.hidden) * wb * shape.layers \
-        + shape.vocab * shape.hidden * (wb + 2) + shape.layers * 2 * (b * nblk + 1) * kd * BS * 2 + (6 << 30)
-    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    # bytes of the un-sharded model on rank 0: per layer (weights + its scratch KV), the head (lm_head + bf16 embedding), and
+    # room for the loader's transients (one full bf16 + fp32 copy of the largest matrix while it is quantised)
+    per_layer = ((qd + 2 * kd + qd) * shape.hidden + 3 * shape.intermediate * shape.hidden) * wb \
+        + 2 * (b * nblk + 1) * kd * BS * 2
+    head = shape.vocab * shape.hidden * (wb + 2)
+    transient = 2 * shape.intermediate * shape.hidden * 6 + (8 << 30)
+    status = torch.zeros(2, dtype=torch.int32, device=dev)
     ref = None
     if rank == 0:
         free, _ = torch.cuda.mem_get_info(dev)
-        if free < need:
+        fit = int((free - head - transient) // per_layer) if free > head + transient else 0
+        status[1] = max(0, min(shape.layers, fit))
+        if int(status[1].item()) < 1:
             status[0] = 2
-        else:
-            ref = B200CausalLM(shape, None, quant=args.quant, num_blocks=b * nblk + 1, max_num_seqs=b,
-                               max_model_len=nblk * BS, block_size=BS, device=dev, seed=0)
     dist.broadcast(status, src=0)
-    if int(status.item()) == 2:
-        return {"tp_check": f"skipped: the un-sharded model ({need / 2**30:.0f} GiB) does not fit beside rank 0's shard"}
+    if int(status[0].item()) == 2:
+        return {"tp_check": "skipped: not even one layer of the un-sharded model fits beside rank 0's shard"}
+    # When the whole un-sharded model does not fit beside rank 0's shard and KV pool (70B with a 32k pool), both sides run
+    # the FIRST n layers + the head: weights depend on (seed, tensor, layer) only, so they are the same n layers.
+    n_chk = int(status[1].item())
+    from dataclasses import replace as _replace
+
+    all_layers, all_kv = model.layers, model.kv
+    model.layers, model.kv = all_layers[:n_chk], all_kv[:n_chk]
+    if rank == 0:
+        ref = B200CausalLM(_replace(shape, layers=n_chk), None, quant=args.quant, num_blocks=b * nblk + 1, max_num_seqs=b,
+                           max_model_len=nblk * BS, block_size=BS, device=dev, seed=0)
     fill_kv_pools(model, shape, rank, world, blocks=blocks)
     model.block_table[:b].copy_(bt)
     tok = torch.randint(0, shape.vocab, (b,), generator=torch.Generator().manual_seed(4321)).to(dev)
     if ref is not None:
         fill_kv_pools(ref, shape, 0, 1, blocks=blocks)
         ref.block_table[:b].copy_(bt[:, :ref.max_blocks])
-    rec = {"tp_check": "ok", "steps": steps, "context": ctx, "tokens_compared": 0, "tokens_equal": 0, "logit_rms_err": [],
+    rec = {"tp_check": "ok", "steps": steps, "context": ctx, "layers_checked": n_chk, "layers": shape.layers,
+           "tokens_compared": 0, "tokens_equal": 0, "logit_rms_err": [],
            "logit_std": []}
     for st in range(steps):
         bufs.tokens.copy_(tok)
@@ -344,14 +358,118 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
             tok = want  # teacher-force both models with the TP=1 tokens
         dist.broadcast(tok, src=0)
         dist.broadcast(status, src=0)
-        if int(status.item()) == 3:
+        if int(status[0].item()) == 3:
             if rank == 0:
                 print(json.dumps({"error": "tp parity check failed", "parity": rec}), flush=True)
             sys.stdout.flush()
             os._exit(3)
     del ref
+    model.layers, model.kv = all_layers, all_kv
     torch.cuda.empty_cache()
     return rec
+
+
+def measure_at(args, shape, model, bufs, bt_host, dev, rank, world, local, group, barrier, parity, max_model_len, num_blocks,
+               sweep=False):
+    """One bench line at context args.ctx on an already built model (KV pool, block table and weights resident)."""
+    import torch
+    import torch.distributed as dist
+
+    from vllm_neuron_b200 import ops
+    from vllm_neuron_b200.model import bucket_ctx_blocks
+
+    b, k_steps, w_steps, e_steps, p_steps = args.batch, args.steps, args.warmup, args.e2e_steps, 2
+    n0 = args.ctx - w_steps  # tokens per sequence before the first warm-up step; first timed step has ctx = args.ctx
+    # a sweep shares one pool sized for the longest context: bound the attention split by THIS context's blocks, as the
+    # model runner does for every step (bucket_ctx_blocks); the single-context run sizes max_model_len to the context
+    mcb = bucket_ctx_blocks(-(-(args.ctx + k_steps + w_steps + e_steps + p_steps + 2) // BS), model.max_blocks) if sweep else None
+    # ---- device-resident decode: CUDA-graph replay, the sampled token and the length advance on the device
+    clocks = ClockSampler(local).start()
+    l0 = ops.launch_count()
+    model.num_tokens[:b].fill_(n0)
+    model.decode_step(b, max_ctx_blocks=mcb, advance=True, use_graph=True)  # captures (one eager warm-up pass + one capture pass) and replays
+    launches_per_step = (ops.launch_count() - l0) // 2
+    model.num_tokens[:b].fill_(n0)
+    for _ in range(w_steps):
+        model.decode_step(b, max_ctx_blocks=mcb, advance=True, use_graph=True)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clocks.mark()
+    e0.record()
+    for _ in range(k_steps):
+        model.decode_step(b, max_ctx_blocks=mcb, advance=True, use_graph=True)
+    e1.record()
+    barrier()
+    clocks.mark()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop()
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / k_steps
+    value = b * k_steps / (ms * 1e-3)
+    mean_ctx = args.ctx + (k_steps - 1) / 2
+
+    # ---- end to end through execute_model (host inputs each step, sampled ids read back each step)
+    e2e = run_e2e(args, shape, model, bt_host, dev, rank, world, group, barrier, n_start=args.ctx + k_steps)
+
+    # ---- per-kernel device times (eager, CUDA events around every launch) for the roofline of the dominant kernel
+    n_prof = int(model.num_tokens[0].item())
+    with ops.kernel_timer() as kt:
+        for _ in range(p_steps):
+            model.decode_step(b, max_ctx_blocks=mcb, advance=True, use_graph=False)
+    ksum = kt.summary()
+    hbm_peak, peak_src = load_peaks()
+    attn_cnt, attn_ms_eager = ksum["paged_attn_decode"]
+    # The dominant kernel as it runs in the step: one launch per decoder layer over that layer's own KV pool (L x 545 MB
+    # streamed per replay, far beyond L2), captured once and replayed; CUDA events on the launching stream.
+    n_attn = int(model.num_tokens[0].item())
+    attn_ms, attn_launches = time_attention_in_graph(model, bufs, b, reps=8, max_blocks=mcb)
+    ctxs = [n_attn] * b
+    attn_bytes = attn_algorithmic_bytes(ctxs, model.hq, model.hkv, model.d)
+    achieved = attn_bytes / (attn_ms * 1e-3) / 1e9
+    kernels = {}
+    per_step_ms = 0.0
+    for name, (cnt, mean_ms) in sorted(ksum.items(), key=lambda kv: -kv[1][0] * kv[1][1]):
+        kernels[name] = {"launches_per_step": cnt / p_steps, "mean_us": round(mean_ms * 1e3, 2),
+                         "us_per_step": round(cnt * mean_ms * 1e3 / p_steps, 1)}
+        per_step_ms += cnt * mean_ms / p_steps
+    wbytes, kvbytes = step_algorithmic_bytes(shape, args.quant, b, mean_ctx, world)
+    roofline = {
+        "bound": "hbm", "kernel": "paged_attn_decode_kernel (+ split combine)", "achieved": round(achieved, 1),
+        "peak": hbm_peak, "unit": "GB/s", "frac": round(achieved / hbm_peak, 4),
+        # the committed ncu --set full capture is of the headline shape (8B, B=64, 2k, TP=1) only
+        "traffic": args.attn_traffic if (shape.name == "Llama-3.1-8B" and b == 64 and args.ctx == 2048 and world == 1) else None,
+        "peak_source": peak_src, "algorithmic_bytes_per_launch": int(attn_bytes), "mean_us_per_launch": round(attn_ms * 1e3, 2),
+        "timing": f"CUDA events around {attn_launches} graph-replayed launches (one per layer's KV pool per replay)",
+        "mean_us_per_launch_eager": round(attn_ms_eager * 1e3, 2),
+        # serialised basis (every kernel timed alone, like the ncu launch list): comparable with profiles/*launches*.csv
+        "share_of_step": round(attn_cnt * attn_ms_eager / p_steps / per_step_ms, 4),
+        # in-graph basis: L launches at the graph-replayed duration over the measured step (PDL overlaps the other kernels)
+        "share_of_step_in_graph": round(shape.layers * attn_ms / ms_per_step, 4),
+        "step": {"weights_bytes": int(wbytes), "kv_bytes": int(kvbytes),
+                 "min_ms_at_peak": round((wbytes + kvbytes) / hbm_peak / 1e6, 4),
+                 "frac_of_step_roofline": round((wbytes + kvbytes) / hbm_peak / 1e6 / ms_per_step, 4)},
+    }
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        steps_s, desc = time_cpu_step(shape, args.quant, b, args.ctx, threads, reps=args.cpu_reps)
+        cpu = {"value": b / statistics.median(steps_s), "unit": UNIT, "cores": threads, "kind": "port", "sample": desc}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": k_steps, "warmup": w_steps,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": args.quant, "data": "synthetic (random-init weights, N(0,1) KV pool, random tokens, permuted block ids)",
+        "config": workload_config(args, shape, world),  # the same dict the reference arm prints
+        "run": {"mean_context_in_timed_region": mean_ctx, "max_model_len": max_model_len, "num_blocks": num_blocks,
+                "cuda_graph": True},
+        "clocks": clk, "parity": parity, "e2e": e2e, "gpu_launches": launches_per_step * k_steps,
+        "launches_per_step": launches_per_step, "roofline": roofline, "cpu_baseline": cpu, "kernels": kernels,
+    }
+    return line
 
 
 # ---------------------------------------------------------------------------------------------- B200 arm
@@ -375,9 +493,10 @@ def run_b200(args, shape):
     ops.device_check(local)  # fails loudly without an sm_100 device / the CUDA library
 
     b, k_steps, w_steps, e_steps, p_steps = args.batch, args.steps, args.warmup, args.e2e_steps, 2
-    n0 = args.ctx - w_steps  # tokens per sequence before the first warm-up step; first timed step has ctx = args.ctx
-    assert n0 >= 1
-    n_end = args.ctx + k_steps + w_steps + e_steps + p_steps + 2
+    # --sweep-ctx: ONE model / KV pool sized for the longest context, one JSON line per context (BASELINE configs[4])
+    sweep = [int(c) for c in args.sweep_ctx.split(",")] if args.sweep_ctx else [args.ctx]
+    assert min(sweep) - w_steps >= 1
+    n_end = max(sweep) + k_steps + w_steps + e_steps + p_steps + 2
     max_model_len = -(-n_end // BS) * BS
     max_blocks = max_model_len // BS
     num_blocks = b * max_blocks + 1
@@ -391,7 +510,6 @@ def run_b200(args, shape):
     tok_host = torch.randint(0, shape.vocab, (b,), generator=torch.Generator().manual_seed(1234))
     bufs = model.decode_buffers(b)
     bufs.tokens.copy_(tok_host)
-    model.num_tokens[:b].fill_(n0)
     torch.cuda.synchronize()
 
     def barrier():
@@ -402,94 +520,14 @@ def run_b200(args, shape):
     # ---- N > 1: correctness of this very model before anything is timed (TP=N vs TP=1 on rank 0, same weights)
     parity = tp_parity_check(args, shape, model, bufs, rank, world, dev, group) if world > 1 else None
     model.block_table[:b].copy_(bt_host)
-    bufs.tokens.copy_(tok_host)
 
-    # ---- device-resident decode: CUDA-graph replay, the sampled token and the length advance on the device
-    clocks = ClockSampler(local).start()
-    l0 = ops.launch_count()
-    model.num_tokens[:b].fill_(n0)
-    model.decode_step(b, advance=True, use_graph=True)  # captures (one eager warm-up pass + one capture pass) and replays
-    launches_per_step = (ops.launch_count() - l0) // 2
-    model.num_tokens[:b].fill_(n0)
-    for _ in range(w_steps):
-        model.decode_step(b, advance=True, use_graph=True)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    clocks.mark()
-    e0.record()
-    for _ in range(k_steps):
-        model.decode_step(b, advance=True, use_graph=True)
-    e1.record()
-    barrier()
-    clocks.mark()
-    ms = e0.elapsed_time(e1)
-    clk = clocks.stop()
-    if world > 1:
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    ms_per_step = ms / k_steps
-    value = b * k_steps / (ms * 1e-3)
-    mean_ctx = args.ctx + (k_steps - 1) / 2
-
-    # ---- end to end through execute_model (host inputs each step, sampled ids read back each step)
-    e2e = run_e2e(args, shape, model, bt_host, dev, rank, world, group, barrier, n_start=args.ctx + k_steps)
-
-    # ---- per-kernel device times (eager, CUDA events around every launch) for the roofline of the dominant kernel
-    n_prof = int(model.num_tokens[0].item())
-    with ops.kernel_timer() as kt:
-        for _ in range(p_steps):
-            model.decode_step(b, advance=True, use_graph=False)
-    ksum = kt.summary()
-    hbm_peak, peak_src = load_peaks()
-    attn_cnt, attn_ms_eager = ksum["paged_attn_decode"]
-    # The dominant kernel as it runs in the step: one launch per decoder layer over that layer's own KV pool (L x 545 MB
-    # streamed per replay, far beyond L2), captured once and replayed; CUDA events on the launching stream.
-    n_attn = int(model.num_tokens[0].item())
-    attn_ms, attn_launches = time_attention_in_graph(model, bufs, b, reps=8)
-    ctxs = [n_attn] * b
-    attn_bytes = attn_algorithmic_bytes(ctxs, model.hq, model.hkv, model.d)
-    achieved = attn_bytes / (attn_ms * 1e-3) / 1e9
-    kernels = {}
-    per_step_ms = 0.0
-    for name, (cnt, mean_ms) in sorted(ksum.items(), key=lambda kv: -kv[1][0] * kv[1][1]):
-        kernels[name] = {"launches_per_step": cnt / p_steps, "mean_us": round(mean_ms * 1e3, 2),
-                         "us_per_step": round(cnt * mean_ms * 1e3 / p_steps, 1)}
-        per_step_ms += cnt * mean_ms / p_steps
-    wbytes, kvbytes = step_algorithmic_bytes(shape, args.quant, b, mean_ctx, world)
-    roofline = {
-        "bound": "hbm", "kernel": "paged_attn_decode_kernel (+ split combine)", "achieved": round(achieved, 1),
-        "peak": hbm_peak, "unit": "GB/s", "frac": round(achieved / hbm_peak, 4), "traffic": args.attn_traffic,
-        "peak_source": peak_src, "algorithmic_bytes_per_launch": int(attn_bytes), "mean_us_per_launch": round(attn_ms * 1e3, 2),
-        "timing": f"CUDA events around {attn_launches} graph-replayed launches (one per layer's KV pool per replay)",
-        "mean_us_per_launch_eager": round(attn_ms_eager * 1e3, 2),
-        # serialised basis (every kernel timed alone, like the ncu launch list): comparable with profiles/*launches*.csv
-        "share_of_step": round(attn_cnt * attn_ms_eager / p_steps / per_step_ms, 4),
-        # in-graph basis: L launches at the graph-replayed duration over the measured step (PDL overlaps the other kernels)
-        "share_of_step_in_graph": round(shape.layers * attn_ms / ms_per_step, 4),
-        "step": {"weights_bytes": int(wbytes), "kv_bytes": int(kvbytes),
-                 "min_ms_at_peak": round((wbytes + kvbytes) / hbm_peak / 1e6, 4),
-                 "frac_of_step_roofline": round((wbytes + kvbytes) / hbm_peak / 1e6 / ms_per_step, 4)},
-    }
-
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        threads = os.cpu_count() or 1
-        steps_s, desc = time_cpu_step(shape, args.quant, b, args.ctx, threads, reps=args.cpu_reps)
-        cpu = {"value": b / statistics.median(steps_s), "unit": UNIT, "cores": threads, "kind": "port", "sample": desc}
-
-    if rank == 0:
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": k_steps, "warmup": w_steps,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": args.quant, "data": "synthetic (random-init weights, N(0,1) KV pool, random tokens, permuted block ids)",
-            "config": workload_config(args, shape, world),  # the same dict the reference arm prints
-            "run": {"mean_context_in_timed_region": mean_ctx, "max_model_len": max_model_len, "num_blocks": num_blocks,
-                    "cuda_graph": True},
-            "clocks": clk, "parity": parity, "e2e": e2e, "gpu_launches": launches_per_step * k_steps,
-            "launches_per_step": launches_per_step, "roofline": roofline, "cpu_baseline": cpu, "kernels": kernels,
-        }
-        print(json.dumps(line), flush=True)
+    for ctx in sweep:
+        args.ctx = ctx
+        bufs.tokens.copy_(tok_host)
+        line = measure_at(args, shape, model, bufs, bt_host, dev, rank, world, local, group, barrier, parity,
+                          max_model_len, num_blocks, sweep=len(sweep) > 1)
+        if rank == 0:
+            print(json.dumps(line), flush=True)
     if world > 1:
         # Leave without tearing NCCL down: destroy_process_group() with captured graphs that hold NCCL kernels alive
         # hung the 2-GPU run (all ranks had finished and printed).  Everything measured is already out.
@@ -500,7 +538,7 @@ def run_b200(args, shape):
         os._exit(0)
 
 
-def time_attention_in_graph(model, bufs, b, reps):
+def time_attention_in_graph(model, bufs, b, reps, max_blocks=None):
     """Mean device time (ms) of one paged-attention decode launch (split kernel + merge) at the current context lengths:
     a CUDA graph holding one launch per layer (each on its own KV pool, as in the step) is replayed `reps` times between
     two events on the launching stream."""
@@ -517,7 +555,7 @@ def time_attention_in_graph(model, bufs, b, reps):
     def body():
         for kv in model.kv:
             ops.paged_attn_decode(q, kv[0], kv[1], model.block_table, bufs.ctx_lens, model.scale, workspace=model.attn_ws,
-                                  row_ids=bufs.row_ids, max_blocks=model.max_blocks, quant=quant)
+                                  row_ids=bufs.row_ids, max_blocks=max_blocks or model.max_blocks, quant=quant)
 
     s = torch.cuda.Stream()
     s.wait_stream(torch.cuda.current_stream())
@@ -607,6 +645,8 @@ def main():
                          "same weights on rank 0 (exit 3 on a mismatch outside the margin guard); off skips it")
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--ctx", type=int, default=2048)
+    ap.add_argument("--sweep-ctx", default="", help="comma-separated contexts measured on ONE model / KV pool sized for the "
+                    "longest (BASELINE configs[4]: 2048,4096,8192,16384,32768); one JSON line per context")
     ap.add_argument("--e2e-steps", type=int, default=32)
     ap.add_argument("--cpu-reps", type=int, default=3)
     ap.add_argument("--cpu-budget-s", type=float, default=150.0)
