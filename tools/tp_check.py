@@ -101,6 +101,70 @@ def bench_exchange(group, rank, world, dev, rows=64, hidden=4096, reps=64):
         print(f"exchange bench tp{world} rows {rows} hidden {hidden}: " + ", ".join(f"{k} {v:.2f} us" for k, v in res.items()), flush=True)
 
 
+def stress_exchange(group, rank, world, dev, epochs=102400, rows=64, hidden=4096):
+    """Concurrency stress of b200_allreduce_rmsnorm: `epochs` back-to-back exchanges inside replayed CUDA graphs (no host
+    sync between them, so ranks drift against each other freely), ragged row counts, eight rotating partial contents per
+    rank.  Every exchange adds per-row checksums of the reduced rows and of the normalised fp8 rows into device
+    accumulators; the expected sums come from NCCL all_gather + rank-order fp32 sum + b200_rmsnorm of each content.  A
+    stale or torn read (the previous use of the same A/B buffer held a different content) changes a checksum."""
+    comm = TpComm(group, rank, world, rows, hidden, dev)
+    w = (torch.randn(hidden, generator=torch.Generator().manual_seed(5)) * 0.1 + 1.0).to(torch.bfloat16).to(dev)
+    nvar, per_graph = 8, 64
+    g = torch.Generator(device=dev).manual_seed(77 + rank)
+    src = [torch.randn(rows, hidden, generator=g, device=dev, dtype=torch.float32).to(torch.bfloat16) for _ in range(nvar)]
+    want_x, want_h = [], []
+    for v in range(nvar):
+        allp = [torch.empty_like(src[v]) for _ in range(world)]
+        dist.all_gather(allp, src[v], group=group)
+        acc = torch.zeros(rows, hidden, dtype=torch.float32, device=dev)
+        for p_ in allp:
+            acc = acc + p_.float()
+        x = acc.to(torch.bfloat16)
+        hq, _ = ops.rmsnorm(x, w, 1e-5, quant="fp8")
+        want_x.append(x.view(torch.int16).long().sum(1))
+        want_h.append(hq.view(torch.uint8).long().sum(1))
+    total, bad = 0, 0
+    for t in (rows, 33, 7, 1, rows):
+        cx = torch.zeros(t, dtype=torch.int64, device=dev)
+        ch = torch.zeros(t, dtype=torch.int64, device=dev)
+
+        def body():
+            for e in range(per_graph):
+                i, part = comm.next_partial(t)
+                part.copy_(src[e % nvar][:t])
+                x, h, _ = comm.exchange(i, t, w, 1e-5, "fp8")
+                cx.add_(x.view(torch.int16).long().sum(1))
+                ch.add_(h.view(torch.uint8).long().sum(1))
+
+        s_ = torch.cuda.Stream()
+        s_.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s_):
+            body()
+        torch.cuda.current_stream().wait_stream(s_)
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            body()
+        reps = max(1, epochs // (5 * per_graph))
+        cx.zero_()
+        ch.zero_()
+        for _ in range(reps):
+            gr.replay()
+        torch.cuda.synchronize()
+        ex = sum(want_x[e % nvar][:t] for e in range(per_graph)) * reps
+        eh = sum(want_h[e % nvar][:t] for e in range(per_graph)) * reps
+        bad += int((cx != ex).sum().item()) + int((ch != eh).sum().item())
+        total += reps * per_graph
+        dist.barrier(group=group)
+    flag = torch.tensor([bad], device=dev)
+    dist.all_reduce(flag)
+    if rank == 0:
+        print(f"exchange stress tp{world}: {total} exchanges in replayed graphs, ragged T (64/33/7/1), "
+              f"{int(flag.item())} checksum mismatches over all ranks", flush=True)
+    assert int(flag.item()) == 0, "exchange stress: checksum mismatch"
+
+
 def check_model(group, rank, world, dev):
     from vllm_neuron_b200.config import ModelShape
 
@@ -174,6 +238,8 @@ def main():
         torch.cuda.synchronize()
         os._exit(0)
     check_exchange(group, rank, world, dev)
+    if "--stress" in sys.argv:
+        stress_exchange(group, rank, world, dev)
     check_model(group, rank, world, dev)
     dist.barrier()
     torch.cuda.synchronize()
