@@ -548,7 +548,7 @@ def time_attention_in_graph(model, bufs, b, reps, max_blocks=None):
 
     q = torch.randn((b, model.hq, model.d), generator=torch.Generator(device=model.device).manual_seed(13),
                     device=model.device, dtype=torch.float32).to(torch.bfloat16)
-    quant = None if model.quant == "bf16" else model.quant
+    quant = {"bf16": None, "int8_wo": None}.get(model.quant, model.quant)  # activation quantisation of the merge kernel
     ops.build_decode_meta(model.block_table, bufs.row_ids, model.num_tokens, bufs.slot_mapping, bufs.positions, bufs.ctx_lens,
                           model.block_size)
 
