@@ -277,10 +277,20 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
     """TP=N against TP=1 in this very process, before the timed region: rank 0 also builds the SAME weights un-sharded
     (weights depend on (seed, tensor, layer) only); both models run `steps` teacher-forced decode steps of the whole
     batch from the same state (context `ctx`, scratch blocks 1 .. B*nblk filled with the same per-global-head values).
-    The TP=N sampled ids must equal TP=1's wherever TP=1's own top-2 margin is outside 8x the measured logit rms
-    difference; otherwise every rank exits with status 3.  Returns the record that goes into the JSON line."""
+    Two passes, each on the first n layers + the head of both models:
+      shallow (n = 2), TIGHT bar -- a sharding / exchange / merge error is O(logit std) at any depth, while two layers of
+        rounding noise stay small: logit rms difference < 3 % of the logit std (bf16, weight-only) or 30 % (W8A8: each rank
+        quantises its row-parallel GEMM input over its own columns, so 8-bit codes differ from TP=1's);
+      deep (n = all layers, or as many as fit beside rank 0's shard and KV pool), depth-aware bar -- two differently
+        rounded computations decorrelate like sqrt(n): measured 0.42 std (8B fp8, 32 layers), 0.63 (70B fp8, 78 layers),
+        0.08 (32B weight-only, 64 layers) at TP=8; bar = min(1.0, 1.6 x base x sqrt(n / 2)), base 0.10 (W8A8) / 0.012.
+    In both passes the TP=N sampled ids must equal TP=1's wherever TP=1's own top-2 margin is outside 8x the measured rms
+    difference.  On failure every rank exits with status 3.  Returns the record that goes into the JSON line."""
+    import math
+
     import torch
     import torch.distributed as dist
+    from dataclasses import replace as _replace
 
     from vllm_neuron_b200.model import B200CausalLM
 
@@ -300,7 +310,6 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
     head = shape.vocab * shape.hidden * (wb + 2)
     transient = 2 * shape.intermediate * shape.hidden * 6 + (8 << 30)
     status = torch.zeros(2, dtype=torch.int32, device=dev)
-    ref = None
     if rank == 0:
         free, _ = torch.cuda.mem_get_info(dev)
         fit = int((free - head - transient) // per_layer) if free > head + transient else 0
@@ -310,62 +319,66 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
     dist.broadcast(status, src=0)
     if int(status[0].item()) == 2:
         return {"tp_check": "skipped: not even one layer of the un-sharded model fits beside rank 0's shard"}
-    # When the whole un-sharded model does not fit beside rank 0's shard and KV pool (70B with a 32k pool), both sides run
-    # the FIRST n layers + the head: weights depend on (seed, tensor, layer) only, so they are the same n layers.
-    n_chk = int(status[1].item())
-    from dataclasses import replace as _replace
-
+    n_fit = int(status[1].item())
+    w8a8 = args.quant in ("fp8", "int8")
+    tight = 0.3 if w8a8 else 0.03
+    base = 0.10 if w8a8 else 0.012
     all_layers, all_kv = model.layers, model.kv
-    model.layers, model.kv = all_layers[:n_chk], all_kv[:n_chk]
-    if rank == 0:
-        ref = B200CausalLM(_replace(shape, layers=n_chk), None, quant=args.quant, num_blocks=b * nblk + 1, max_num_seqs=b,
-                           max_model_len=nblk * BS, block_size=BS, device=dev, seed=0)
     fill_kv_pools(model, shape, rank, world, blocks=blocks)
     model.block_table[:b].copy_(bt)
-    tok = torch.randint(0, shape.vocab, (b,), generator=torch.Generator().manual_seed(4321)).to(dev)
-    if ref is not None:
-        fill_kv_pools(ref, shape, 0, 1, blocks=blocks)
-        ref.block_table[:b].copy_(bt[:, :ref.max_blocks])
-    rec = {"tp_check": "ok", "steps": steps, "context": ctx, "layers_checked": n_chk, "layers": shape.layers,
-           "tokens_compared": 0, "tokens_equal": 0, "logit_rms_err": [],
-           "logit_std": []}
-    for st in range(steps):
-        bufs.tokens.copy_(tok)
-        model.num_tokens[:b].fill_(ctx + st + 1)
-        got = model.decode_step(b, advance=False, use_graph=False).clone()
-        l_tp = model.last_logits.float()
-        if ref is not None:
-            rb = ref.decode_buffers(b)
-            rb.tokens.copy_(tok)
-            ref.num_tokens[:b].fill_(ctx + st + 1)
-            want = ref.decode_step(b, advance=False, use_graph=False).clone()
-            l_ref = ref.last_logits.float()
-            shard = l_ref[:, model.vocab_offset: model.vocab_offset + l_tp.shape[1]]
-            err = (l_tp - shard).pow(2).mean().sqrt().item()
-            std = l_ref.std().item()
-            top2 = l_ref.topk(2, dim=-1).values
-            margin = top2[:, 0] - top2[:, 1]
-            bad = (got != want) & (margin > 8 * err)
-            rec["tokens_compared"] += b
-            rec["tokens_equal"] += int((got == want).sum().item())
-            rec["logit_rms_err"].append(round(err, 5))
-            rec["logit_std"].append(round(std, 4))
-            bar = 0.03 if args.quant in ("bf16", "int8_wo") else 0.3
-            if bad.any() or not err < bar * std:
-                status[0] = 3
-                rec["tp_check"] = (f"FAILED at step {st}: {int(bad.sum().item())} tokens differ outside the margin guard, logit rms "
-                                   f"err {err:.3e} vs std {std:.3f}")
-            tok = want  # teacher-force both models with the TP=1 tokens
-        dist.broadcast(tok, src=0)
-        dist.broadcast(status, src=0)
-        if int(status[0].item()) == 3:
-            if rank == 0:
-                print(json.dumps({"error": "tp parity check failed", "parity": rec}), flush=True)
-            sys.stdout.flush()
-            os._exit(3)
-    del ref
+    rec = {"tp_check": "ok", "steps": steps, "context": ctx, "layers": shape.layers, "passes": []}
+    n_shallow = min(2, n_fit)
+    for n_chk, bar in ((n_shallow, tight), (n_fit, max(tight, min(1.0, 1.6 * base * math.sqrt(n_fit / 2))))):
+        if rec["passes"] and n_chk == rec["passes"][0]["layers_checked"]:
+            break
+        model.layers, model.kv = all_layers[:n_chk], all_kv[:n_chk]
+        ref = None
+        if rank == 0:
+            ref = B200CausalLM(_replace(shape, layers=n_chk), None, quant=args.quant, num_blocks=b * nblk + 1, max_num_seqs=b,
+                               max_model_len=nblk * BS, block_size=BS, device=dev, seed=0)
+            fill_kv_pools(ref, shape, 0, 1, blocks=blocks)
+            ref.block_table[:b].copy_(bt[:, :ref.max_blocks])
+        tok = torch.randint(0, shape.vocab, (b,), generator=torch.Generator().manual_seed(4321)).to(dev)
+        pr = {"layers_checked": n_chk, "bar_frac_of_std": round(bar, 3), "tokens_compared": 0, "tokens_equal": 0,
+              "logit_rms_err": [], "logit_std": []}
+        rec["passes"].append(pr)
+        for st in range(steps):
+            bufs.tokens.copy_(tok)
+            model.num_tokens[:b].fill_(ctx + st + 1)
+            got = model.decode_step(b, advance=False, use_graph=False).clone()
+            l_tp = model.last_logits.float()
+            if ref is not None:
+                rb = ref.decode_buffers(b)
+                rb.tokens.copy_(tok)
+                ref.num_tokens[:b].fill_(ctx + st + 1)
+                want = ref.decode_step(b, advance=False, use_graph=False).clone()
+                l_ref = ref.last_logits.float()
+                shard = l_ref[:, model.vocab_offset: model.vocab_offset + l_tp.shape[1]]
+                err = (l_tp - shard).pow(2).mean().sqrt().item()
+                std = l_ref.std().item()
+                top2 = l_ref.topk(2, dim=-1).values
+                margin = top2[:, 0] - top2[:, 1]
+                bad = (got != want) & (margin > 8 * err)
+                pr["tokens_compared"] += b
+                pr["tokens_equal"] += int((got == want).sum().item())
+                pr["logit_rms_err"].append(round(err, 5))
+                pr["logit_std"].append(round(std, 4))
+                if bad.any() or not err < bar * std:
+                    status[0] = 3
+                    rec["tp_check"] = (f"FAILED ({n_chk} layers) at step {st}: {int(bad.sum().item())} tokens differ outside the "
+                                       f"margin guard, logit rms err {err:.3e} vs std {std:.3f} (bar {bar:.2f} std)")
+                tok = want  # teacher-force both models with the TP=1 tokens
+            dist.broadcast(tok, src=0)
+            dist.broadcast(status, src=0)
+            if int(status[0].item()) == 3:
+                if rank == 0:
+                    print(json.dumps({"error": "tp parity check failed", "parity": rec}), flush=True)
+                sys.stdout.flush()
+                os._exit(3)
+        del ref
+        torch.cuda.empty_cache()
     model.layers, model.kv = all_layers, all_kv
-    torch.cuda.empty_cache()
+    rec["layers_checked"] = rec["passes"][-1]["layers_checked"]
     return rec
 
 

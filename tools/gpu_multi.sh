@@ -31,6 +31,6 @@ for f in sorted(glob.glob("gpurun_out/bench_*tp$N.json")):
         if "value" not in d: print(f, d); continue
         print(f.split("/")[-1], d["config"]["workload"][:40], "ctx", d["config"]["context"], "tok/s", round(d["value"]), "ms", round(d["ms_per_step"], 3),
               "e2e", round(d["e2e"]["value"]), "attn", d["roofline"]["frac"], "step", d["roofline"]["step"]["frac_of_step_roofline"],
-              "parity", (d.get("parity") or {}).get("tp_check"), (d.get("parity") or {}).get("layers_checked"))
+              "parity", (d.get("parity") or {}).get("tp_check"), [(p["layers_checked"], max(p["logit_rms_err"] or [0]), p["logit_std"][:1]) for p in (d.get("parity") or {}).get("passes", [])])
 PY
 cat gpurun_out/multi_summary.txt
