@@ -225,6 +225,14 @@ int b200_argmax(const float* logits, int64_t row_stride, float* out_val, int64_t
 int b200_allreduce_rmsnorm(const void* const* host_peer_bufs, void* const* host_peer_flags, uint32_t* epoch, int rank,
                            int world, void* x_out, const void* norm_w, void* out_bf16, void* out_q, float* out_scale, int T,
                            int H, float eps, int q_dtype, void* stream);
+/* Same exchange with the sum done INSIDE the NVSwitch (NVLS): mc_buf is the MULTICAST device address of the partial
+ * [T][H] bf16 (the address that maps every rank's replica; torch symmetric memory: handle.multicast_ptr + offset); the
+ * kernel issues one multimem.ld_reduce (bf16x2 add, fp32 accumulate) per 16 bytes, so a rank receives T*H*2 bytes
+ * instead of (world-1) x that.  Flags, epoch, outputs and the alternation rule as above.  The order of the additions is
+ * the switch's: identical bits on every rank, but not necessarily those of the rank-order sum (last bf16 bit). */
+int b200_allreduce_rmsnorm_nvls(const void* mc_buf, void* const* host_peer_flags, uint32_t* epoch, int rank, int world,
+                                void* x_out, const void* norm_w, void* out_bf16, void* out_q, float* out_scale, int T,
+                                int H, float eps, int q_dtype, void* stream);
 
 #ifdef __cplusplus
 }

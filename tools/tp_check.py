@@ -28,6 +28,7 @@ def check_exchange(group, rank, world, dev):
     rows, hidden = 64, 4096
     comm = TpComm(group, rank, world, rows, hidden, dev)
     w = (torch.randn(hidden, generator=torch.Generator().manual_seed(5)) * 0.1 + 1.0).to(torch.bfloat16).to(dev)
+    nvls_stats = [0, 0]
     for it, t in enumerate([64, 64, 33, 1, 64, 7]):
         for quant in (None, "fp8", "int8"):
             g = torch.Generator(device=dev).manual_seed(1000 * it + rank)
@@ -40,6 +41,17 @@ def check_exchange(group, rank, world, dev):
             for p in allp:  # rank order, fp32
                 acc = acc + p.float()
             want_x = acc.to(torch.bfloat16)
+            if comm.nvls:
+                # in-switch sum: fp32 additions in the switch's order -> at most the last bf16 bit of a few elements may
+                # differ from the rank-order sum; every rank must hold IDENTICAL bits
+                d = (x.view(torch.int16).int() - want_x.view(torch.int16).int()).abs()
+                nvls_stats[0] += int((d != 0).sum().item())
+                nvls_stats[1] += d.numel()
+                assert int(d.max().item()) <= 1, f"rank {rank} it {it}: NVLS sum differs by more than one bf16 ulp"
+                allx = [torch.empty_like(x) for _ in range(world)]
+                dist.all_gather(allx, x.contiguous(), group=group)
+                assert all(torch.equal(allx[0], a) for a in allx), "NVLS sums differ between ranks"
+                want_x = x
             assert torch.equal(x, want_x), f"rank {rank} it {it}: reduced rows differ ({(x.float() - want_x.float()).abs().max()})"
             if quant is None:
                 want_h = ops.rmsnorm(want_x, w, 1e-5)
@@ -55,12 +67,13 @@ def check_exchange(group, rank, world, dev):
             assert h is None and torch.all(x == world * (world + 1) / 2)
     torch.cuda.synchronize()
     if rank == 0:
-        print("exchange ok", flush=True)
+        print("exchange ok" + (f" (NVLS in-switch sum: {nvls_stats[0]} of {nvls_stats[1]} elements differ from the rank-order "
+                               f"sum by one bf16 ulp, identical on all ranks)" if comm.nvls else " (peer pull, bit-exact)"), flush=True)
 
 
-def bench_exchange(group, rank, world, dev, rows=64, hidden=4096, reps=64):
+def bench_exchange(group, rank, world, dev, rows=64, hidden=4096, reps=64, use_nvls=None):
     """Steady-state cost of one exchange (graph of `reps` exchanges, each preceded by a small local write of the partial)."""
-    comm = TpComm(group, rank, world, rows, hidden, dev)
+    comm = TpComm(group, rank, world, rows, hidden, dev, use_nvls=use_nvls)
     w = torch.ones(hidden, dtype=torch.bfloat16, device=dev)
     src = torch.randn(rows, hidden, device=dev).to(torch.bfloat16)
 
@@ -98,7 +111,7 @@ def bench_exchange(group, rank, world, dev, rows=64, hidden=4096, reps=64):
         torch.cuda.synchronize()
         res[name] = e0.elapsed_time(e1) * 1e3 / (5 * reps)
     if rank == 0:
-        print(f"exchange bench tp{world} rows {rows} hidden {hidden}: " + ", ".join(f"{k} {v:.2f} us" for k, v in res.items()), flush=True)
+        print(f"exchange bench tp{world} rows {rows} hidden {hidden} [{'NVLS' if comm.nvls else 'pull'}]: " + ", ".join(f"{k} {v:.2f} us" for k, v in res.items()), flush=True)
 
 
 def stress_exchange(group, rank, world, dev, epochs=102400, rows=64, hidden=4096):
@@ -120,6 +133,12 @@ def stress_exchange(group, rank, world, dev, epochs=102400, rows=64, hidden=4096
         for p_ in allp:
             acc = acc + p_.float()
         x = acc.to(torch.bfloat16)
+        if comm.nvls:  # the switch's own (deterministic) sum is the reference: one exchange per content, checked <= 1 ulp
+            i_, part_ = comm.next_partial(rows)
+            part_.copy_(src[v])
+            xs, _, _ = comm.exchange(i_, rows, w, 1e-5, "fp8")
+            assert int((xs.view(torch.int16).int() - x.view(torch.int16).int()).abs().max().item()) <= 1
+            x = xs.clone()
         hq, _ = ops.rmsnorm(x, w, 1e-5, quant="fp8")
         want_x.append(x.view(torch.int16).long().sum(1))
         want_h.append(hq.view(torch.uint8).long().sum(1))
@@ -160,7 +179,7 @@ def stress_exchange(group, rank, world, dev, epochs=102400, rows=64, hidden=4096
     flag = torch.tensor([bad], device=dev)
     dist.all_reduce(flag)
     if rank == 0:
-        print(f"exchange stress tp{world}: {total} exchanges in replayed graphs, ragged T (64/33/7/1), "
+        print(f"exchange stress tp{world} ({'NVLS' if comm.nvls else 'pull'}): {total} exchanges in replayed graphs, ragged T (64/33/7/1), "
               f"{int(flag.item())} checksum mismatches over all ranks", flush=True)
     assert int(flag.item()) == 0, "exchange stress: checksum mismatch"
 
@@ -233,7 +252,10 @@ def main():
     group = dist.group.WORLD
     ops.device_check(local)
     if "--bench" in sys.argv:
-        bench_exchange(group, rank, world, dev)
+        for hidden in (4096, 8192):
+            for rows in (64, 128):
+                for nv in (False, True):
+                    bench_exchange(group, rank, world, dev, rows=rows, hidden=hidden, use_nvls=nv)
         dist.barrier()
         torch.cuda.synchronize()
         os._exit(0)

@@ -12,6 +12,13 @@
 // and a rank can only overwrite buffer A after it has passed the entry barrier of the exchange on buffer B, by which time
 // every peer has finished reading A (same-stream order on the peer).
 // Flags carry a per-row epoch that only grows, so nothing is ever reset and a CUDA graph can replay the step.
+//
+// NVLS variant (b200_allreduce_rmsnorm_nvls): when the symmetric region also has a MULTICAST mapping (NVSwitch), step 2
+// is ONE multimem.ld_reduce per 16 bytes on the multicast address: the switch fetches the row from every rank, adds the
+// bf16 pairs with an fp32 accumulator and returns the rounded sum.  Each rank then receives T*H*2 bytes per exchange
+// instead of (world - 1) x that (3.5 MB -> 0.5 MB at hidden 4096, TP=8; 7 -> 1 MB at hidden 8192), which is what bounded
+// the pull at TP=8.  The order of the fp32 additions is the switch's, not rank order: sums may differ from the pull
+// variant in the last bf16 bit of a few elements; every rank still receives identical bits (checked in tools/tp_check.py).
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -25,6 +32,7 @@ constexpr int AR_MAXV = 4;  // 4 x 8 bf16 per thread -> H <= 8192
 struct ArPeers {
   const uint4* buf[AR_MAX_TP];  // rank p's partial [T][H] bf16
   uint32_t* flags[AR_MAX_TP];   // rank p's flag area: [rows][AR_MAX_TP] epochs, written by the peers
+  const uint4* mc_buf;          // NVLS: multicast address of the partial (all ranks' replicas), else null
 };
 
 // Flag traffic is RELAXED at system scope on purpose.  Measured on 2 x B200 (profiles/r01_tp_exchange_*.md): a
@@ -44,6 +52,15 @@ __device__ __forceinline__ uint32_t ld_flag_sys(const uint32_t* p) {
 __device__ __forceinline__ uint4 ld_peer(const uint4* p) {
   uint4 v;
   asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];\n"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+// in-switch sum over all replicas of 8 bf16 (fp32 accumulate, rounded back to bf16)
+__device__ __forceinline__ uint4 ld_reduce_mc(const uint4* p) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];\n"
                : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
                : "l"(p)
                : "memory");
@@ -76,7 +93,7 @@ __device__ __forceinline__ float ar_block_max(float v, float* sh) {
   return warp_max(r);
 }
 
-template <int QD>
+template <int QD, bool NVLS>
 __global__ void __launch_bounds__(AR_THREADS)
     allreduce_rmsnorm_kernel(ArPeers peers, uint32_t* __restrict__ epoch, int rank, int world, uint4* __restrict__ x_out,
                              const uint4* __restrict__ w, uint4* __restrict__ out_bf16, uint2* __restrict__ out_q,
@@ -111,25 +128,30 @@ __global__ void __launch_bounds__(AR_THREADS)
   for (int i = 0; i < AR_MAXV; ++i) {
     const int vi = threadIdx.x + i * AR_THREADS;
     if (vi < nvec) {
-      uint4 part[AR_MAX_TP];
-#pragma unroll
-      for (int p = 0; p < AR_MAX_TP; ++p)
-        if (p < world) part[p] = ld_peer(peers.buf[(dbg & 4) ? rank : p] + (size_t)t * nvec + vi);
-      float acc[8];
-#pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-#pragma unroll
-      for (int p = 0; p < AR_MAX_TP; ++p) {
-        if (p < world) {
-          float f[8];
-          unpack8f(part[p], f);
-#pragma unroll
-          for (int e = 0; e < 8; ++e) acc[e] = __fadd_rn(acc[e], f[e]);
-        }
-      }
       uint32_t pk[4];
+      if constexpr (NVLS) {
+        const uint4 r = ld_reduce_mc(peers.mc_buf + (size_t)t * nvec + vi);
+        pk[0] = r.x, pk[1] = r.y, pk[2] = r.z, pk[3] = r.w;
+      } else {
+        uint4 part[AR_MAX_TP];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) pk[e] = pack_bf16(acc[2 * e], acc[2 * e + 1]);
+        for (int p = 0; p < AR_MAX_TP; ++p)
+          if (p < world) part[p] = ld_peer(peers.buf[(dbg & 4) ? rank : p] + (size_t)t * nvec + vi);
+        float acc[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+#pragma unroll
+        for (int p = 0; p < AR_MAX_TP; ++p) {
+          if (p < world) {
+            float f[8];
+            unpack8f(part[p], f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] = __fadd_rn(acc[e], f[e]);
+          }
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) pk[e] = pack_bf16(acc[2 * e], acc[2 * e + 1]);
+      }
       const uint4 xr = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       x_out[(size_t)t * nvec + vi] = xr;
       unpack8f(xr, xv[i]);  // the norm sees the bf16 residual stream, like rmsnorm_kernel does
@@ -186,10 +208,11 @@ __global__ void __launch_bounds__(AR_THREADS)
 
 using namespace b200;
 
-extern "C" int b200_allreduce_rmsnorm(const void* const* host_peer_bufs, void* const* host_peer_flags, uint32_t* epoch,
-                                      int rank, int world, void* x_out, const void* norm_w, void* out_bf16, void* out_q,
-                                      float* out_scale, int T, int H, float eps, int q_dtype, void* stream) {
-  B200_REQUIRE(host_peer_bufs && host_peer_flags && epoch && x_out, "allreduce_rmsnorm: null pointer");
+namespace {
+int allreduce_common(const void* const* host_peer_bufs, void* const* host_peer_flags, const void* mc_buf, uint32_t* epoch,
+                     int rank, int world, void* x_out, const void* norm_w, void* out_bf16, void* out_q, float* out_scale,
+                     int T, int H, float eps, int q_dtype, void* stream) {
+  B200_REQUIRE(host_peer_flags && epoch && x_out && (host_peer_bufs || mc_buf), "allreduce_rmsnorm: null pointer");
   B200_REQUIRE(world >= 1 && world <= AR_MAX_TP && rank >= 0 && rank < world, "allreduce_rmsnorm: bad rank %d / world %d",
                rank, world);
   B200_REQUIRE(H > 0 && H % 8 == 0 && H <= 8 * AR_THREADS * AR_MAXV, "allreduce_rmsnorm: H=%d unsupported", H);
@@ -199,21 +222,41 @@ extern "C" int b200_allreduce_rmsnorm(const void* const* host_peer_bufs, void* c
   if (T <= 0) return B200_OK;
   ArPeers peers{};
   for (int p = 0; p < world; ++p) {
-    B200_REQUIRE(host_peer_bufs[p] && host_peer_flags[p], "allreduce_rmsnorm: null peer pointer %d", p);
-    peers.buf[p] = (const uint4*)host_peer_bufs[p];
+    B200_REQUIRE(host_peer_flags[p] && (mc_buf || host_peer_bufs[p]), "allreduce_rmsnorm: null peer pointer %d", p);
+    peers.buf[p] = mc_buf ? nullptr : (const uint4*)host_peer_bufs[p];
     peers.flags[p] = (uint32_t*)host_peer_flags[p];
   }
+  peers.mc_buf = (const uint4*)mc_buf;
   cudaStream_t s = (cudaStream_t)stream;
   static const int dbg = getenv("B200_AR_DEBUG") ? atoi(getenv("B200_AR_DEBUG")) : 0;  // timing experiments only
-  if (norm_w && q_dtype == B200_FP8_E4M3)
-    B200_CUDA_OK(launch_kernel(allreduce_rmsnorm_kernel<B200_FP8_E4M3>, dim3(T), dim3(AR_THREADS), 0, s, peers, epoch, rank,
-                               world, (uint4*)x_out, (const uint4*)norm_w, (uint4*)out_bf16, (uint2*)out_q, out_scale, H, eps, dbg));
-  else if (norm_w && q_dtype == B200_INT8)
-    B200_CUDA_OK(launch_kernel(allreduce_rmsnorm_kernel<B200_INT8>, dim3(T), dim3(AR_THREADS), 0, s, peers, epoch, rank,
-                               world, (uint4*)x_out, (const uint4*)norm_w, (uint4*)out_bf16, (uint2*)out_q, out_scale, H, eps, dbg));
-  else
-    B200_CUDA_OK(launch_kernel(allreduce_rmsnorm_kernel<B200_BF16>, dim3(T), dim3(AR_THREADS), 0, s, peers, epoch, rank,
-                               world, (uint4*)x_out, (const uint4*)norm_w, (uint4*)out_bf16, (uint2*)nullptr, (float*)nullptr,
-                               H, eps, dbg));
+#define B200_AR_LAUNCH(QD, NV, OQ, OS)                                                                                     \
+  B200_CUDA_OK(launch_kernel(allreduce_rmsnorm_kernel<QD, NV>, dim3(T), dim3(AR_THREADS), 0, s, peers, epoch, rank, world, \
+                             (uint4*)x_out, (const uint4*)norm_w, (uint4*)out_bf16, (uint2*)(OQ), (float*)(OS), H, eps, dbg))
+  const bool nv = mc_buf != nullptr;
+  if (norm_w && q_dtype == B200_FP8_E4M3) {
+    if (nv) B200_AR_LAUNCH(B200_FP8_E4M3, true, out_q, out_scale); else B200_AR_LAUNCH(B200_FP8_E4M3, false, out_q, out_scale);
+  } else if (norm_w && q_dtype == B200_INT8) {
+    if (nv) B200_AR_LAUNCH(B200_INT8, true, out_q, out_scale); else B200_AR_LAUNCH(B200_INT8, false, out_q, out_scale);
+  } else {
+    if (nv) B200_AR_LAUNCH(B200_BF16, true, nullptr, nullptr); else B200_AR_LAUNCH(B200_BF16, false, nullptr, nullptr);
+  }
+#undef B200_AR_LAUNCH
   return B200_OK;
+}
+}  // namespace
+
+extern "C" int b200_allreduce_rmsnorm(const void* const* host_peer_bufs, void* const* host_peer_flags, uint32_t* epoch,
+                                      int rank, int world, void* x_out, const void* norm_w, void* out_bf16, void* out_q,
+                                      float* out_scale, int T, int H, float eps, int q_dtype, void* stream) {
+  B200_REQUIRE(host_peer_bufs, "allreduce_rmsnorm: null pointer");
+  return allreduce_common(host_peer_bufs, host_peer_flags, nullptr, epoch, rank, world, x_out, norm_w, out_bf16, out_q,
+                          out_scale, T, H, eps, q_dtype, stream);
+}
+
+extern "C" int b200_allreduce_rmsnorm_nvls(const void* mc_buf, void* const* host_peer_flags, uint32_t* epoch, int rank,
+                                           int world, void* x_out, const void* norm_w, void* out_bf16, void* out_q,
+                                           float* out_scale, int T, int H, float eps, int q_dtype, void* stream) {
+  B200_REQUIRE(mc_buf, "allreduce_rmsnorm_nvls: null multicast pointer");
+  return allreduce_common(nullptr, host_peer_flags, mc_buf, epoch, rank, world, x_out, norm_w, out_bf16, out_q, out_scale, T,
+                          H, eps, q_dtype, stream);
 }

@@ -524,29 +524,33 @@ def gather_logprobs(cand_val, cand_idx, sampled, row_max, row_sumexp, num_logpro
     return ids, lp, rk
 
 
-def allreduce_rmsnorm(peer_bufs, peer_flags, epoch, rank, world, t, h, norm_w, eps, quant=None, want_bf16=False):
+def allreduce_rmsnorm(peer_bufs, peer_flags, epoch, rank, world, t, h, norm_w, eps, quant=None, want_bf16=False, mc_buf=0):
     """One-shot all-reduce over NVLink peer memory fused with RMSNorm (+ per-token quantisation).
-    peer_bufs / peer_flags: ctypes arrays of `world` device pointers (tp_comm.TpComm).  Returns (x, h_out, h_scale):
+    peer_bufs / peer_flags: ctypes arrays of `world` device pointers (tp_comm.TpComm).  mc_buf != 0: the multicast address
+    of the partial -- the sum is then done inside the NVSwitch (b200_allreduce_rmsnorm_nvls).  Returns (x, h_out, h_scale):
     x = the reduced bf16 residual stream; h_out = normed bf16 (quant None) or quantised tensor; h_scale = scales or None."""
     dev = epoch.device
     x = torch.empty((t, h), dtype=torch.bfloat16, device=dev)
     qd = _QDT[quant]
+    lib = _cabi.load()
+    if mc_buf:
+        fn, first, name = lib.b200_allreduce_rmsnorm_nvls, int(mc_buf), "b200_allreduce_rmsnorm_nvls"
+    else:
+        fn, first, name = lib.b200_allreduce_rmsnorm, peer_bufs, "b200_allreduce_rmsnorm"
     if norm_w is None:
         with _k("allreduce"):
-            check(_cabi.load().b200_allreduce_rmsnorm(peer_bufs, peer_flags, _ptr(epoch), rank, world, _ptr(x), 0, 0, 0, 0,
-                                                      t, h, float(eps), BF16, _stream()), "b200_allreduce_rmsnorm")
+            check(fn(first, peer_flags, _ptr(epoch), rank, world, _ptr(x), 0, 0, 0, 0, t, h, float(eps), BF16, _stream()), name)
         return x, None, None
     if qd == BF16:
         y = torch.empty_like(x)
         with _k("allreduce_rmsnorm"):
-            check(_cabi.load().b200_allreduce_rmsnorm(peer_bufs, peer_flags, _ptr(epoch), rank, world, _ptr(x), _ptr(norm_w),
-                                                      _ptr(y), 0, 0, t, h, float(eps), qd, _stream()), "b200_allreduce_rmsnorm")
+            check(fn(first, peer_flags, _ptr(epoch), rank, world, _ptr(x), _ptr(norm_w), _ptr(y), 0, 0, t, h, float(eps), qd,
+                     _stream()), name)
         return x, y, None
     q = torch.empty((t, h), dtype=_TORCH_Q[qd], device=dev)
     s = torch.empty((t,), dtype=torch.float32, device=dev)
     y = torch.empty_like(x) if want_bf16 else None
     with _k("allreduce_rmsnorm_quant"):
-        check(_cabi.load().b200_allreduce_rmsnorm(peer_bufs, peer_flags, _ptr(epoch), rank, world, _ptr(x), _ptr(norm_w),
-                                                  _ptr(y), _ptr(q), _ptr(s), t, h, float(eps), qd, _stream()),
-              "b200_allreduce_rmsnorm")
+        check(fn(first, peer_flags, _ptr(epoch), rank, world, _ptr(x), _ptr(norm_w), _ptr(y), _ptr(q), _ptr(s), t, h,
+                 float(eps), qd, _stream()), name)
     return x, q, s

@@ -4,6 +4,8 @@ torch.distributed's symmetric memory is used ONLY to obtain peer-mapped device m
 layout, every region mapped into every process); the exchange itself is our kernel (csrc/tp_allreduce.cu), not NCCL.
 Region layout (bytes):  [ partial A : rows*hidden bf16 | partial B : rows*hidden bf16 | flags : rows*8 uint32 ].
 The row-parallel GEMMs (o_proj, down_proj) write their outputs straight into partial A / B of the local region.
+Where the region also has a MULTICAST mapping (NVSwitch), the exchange kernel sums the ranks inside the switch
+(multimem.ld_reduce on `multicast_ptr`, b200_allreduce_rmsnorm_nvls); otherwise it pulls every peer's rows.
 """
 from __future__ import annotations
 
@@ -15,7 +17,9 @@ import torch
 class TpComm:
     FLAG_SLOTS = 8  # = AR_MAX_TP in csrc/tp_allreduce.cu
 
-    def __init__(self, group, rank: int, world: int, rows: int, hidden: int, device):
+    def __init__(self, group, rank: int, world: int, rows: int, hidden: int, device, use_nvls: bool | None = None):
+        import os
+
         import torch.distributed._symmetric_memory as symm_mem
 
         self.rank, self.world, self.rows, self.hidden = rank, world, rows, hidden
@@ -32,6 +36,12 @@ class TpComm:
         arr = C.c_void_p * world
         self._peer_bufs = [arr(*[b + i * part_bytes for b in base]) for i in range(2)]
         self._peer_flags = arr(*[b + 2 * part_bytes for b in base])
+        # NVLS: the region's multicast mapping (NVSwitch boxes; 0 where the fabric has none).  B200_AR_NVLS=0 keeps the pull.
+        mc = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
+        if use_nvls is None:
+            use_nvls = os.environ.get("B200_AR_NVLS", "1") != "0"
+        self.nvls = bool(mc) and use_nvls and world > 1
+        self._mc_bufs = [mc + i * part_bytes if self.nvls else 0 for i in range(2)]
         self.epoch = torch.zeros((rows,), dtype=torch.int32, device=device)
         self._next = 0
         torch.cuda.synchronize(device)
@@ -48,4 +58,4 @@ class TpComm:
         assert i == self._next, "exchange sites must alternate between the two partial buffers"
         self._next ^= 1
         return ops.allreduce_rmsnorm(self._peer_bufs[i], self._peer_flags, self.epoch, self.rank, self.world, t, self.hidden,
-                                     norm_w, eps, quant)
+                                     norm_w, eps, quant, mc_buf=self._mc_bufs[i])
