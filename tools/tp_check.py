@@ -24,9 +24,9 @@ from vllm_neuron_b200.model import B200CausalLM, random_init_full_weights  # noq
 from vllm_neuron_b200.tp_comm import TpComm  # noqa: E402
 
 
-def check_exchange(group, rank, world, dev):
+def check_exchange(group, rank, world, dev, use_nvls=None):
     rows, hidden = 64, 4096
-    comm = TpComm(group, rank, world, rows, hidden, dev)
+    comm = TpComm(group, rank, world, rows, hidden, dev, use_nvls=use_nvls)
     w = (torch.randn(hidden, generator=torch.Generator().manual_seed(5)) * 0.1 + 1.0).to(torch.bfloat16).to(dev)
     nvls_stats = [0, 0]
     for it, t in enumerate([64, 64, 33, 1, 64, 7]):
@@ -114,13 +114,13 @@ def bench_exchange(group, rank, world, dev, rows=64, hidden=4096, reps=64, use_n
         print(f"exchange bench tp{world} rows {rows} hidden {hidden} [{'NVLS' if comm.nvls else 'pull'}]: " + ", ".join(f"{k} {v:.2f} us" for k, v in res.items()), flush=True)
 
 
-def stress_exchange(group, rank, world, dev, epochs=102400, rows=64, hidden=4096):
+def stress_exchange(group, rank, world, dev, epochs=102400, rows=64, hidden=4096, use_nvls=None):
     """Concurrency stress of b200_allreduce_rmsnorm: `epochs` back-to-back exchanges inside replayed CUDA graphs (no host
     sync between them, so ranks drift against each other freely), ragged row counts, eight rotating partial contents per
     rank.  Every exchange adds per-row checksums of the reduced rows and of the normalised fp8 rows into device
     accumulators; the expected sums come from NCCL all_gather + rank-order fp32 sum + b200_rmsnorm of each content.  A
     stale or torn read (the previous use of the same A/B buffer held a different content) changes a checksum."""
-    comm = TpComm(group, rank, world, rows, hidden, dev)
+    comm = TpComm(group, rank, world, rows, hidden, dev, use_nvls=use_nvls)
     w = (torch.randn(hidden, generator=torch.Generator().manual_seed(5)) * 0.1 + 1.0).to(torch.bfloat16).to(dev)
     nvar, per_graph = 8, 64
     g = torch.Generator(device=dev).manual_seed(77 + rank)
@@ -259,9 +259,10 @@ def main():
         dist.barrier()
         torch.cuda.synchronize()
         os._exit(0)
-    check_exchange(group, rank, world, dev)
-    if "--stress" in sys.argv:
-        stress_exchange(group, rank, world, dev)
+    for nv in (False, True):  # both exchange variants, whatever the default of this world size is
+        check_exchange(group, rank, world, dev, use_nvls=nv)
+        if "--stress" in sys.argv:
+            stress_exchange(group, rank, world, dev, use_nvls=nv)
     check_model(group, rank, world, dev)
     dist.barrier()
     torch.cuda.synchronize()

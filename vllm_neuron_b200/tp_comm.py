@@ -39,7 +39,9 @@ class TpComm:
         # NVLS: the region's multicast mapping (NVSwitch boxes; 0 where the fabric has none).  B200_AR_NVLS=0 keeps the pull.
         mc = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
         if use_nvls is None:
-            use_nvls = os.environ.get("B200_AR_NVLS", "1") != "0"
+            # measured (profiles/r02_tp_exchange_nvls_v1.md): no gain at TP=2 (the pull moves the same bytes and is the
+            # bit-exact rank-order sum); +5..7 % whole-model tokens/s at TP=8, where the pull's 7x ingress contends
+            use_nvls = os.environ.get("B200_AR_NVLS", "1" if world >= 4 else "0") != "0"
         self.nvls = bool(mc) and use_nvls and world > 1
         self._mc_bufs = [mc + i * part_bytes if self.nvls else 0 for i in range(2)]
         self.epoch = torch.zeros((rows,), dtype=torch.int32, device=device)
