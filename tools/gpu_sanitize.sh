@@ -1,5 +1,8 @@
 #!/bin/bash
 # compute-sanitizer over the GPU parity tests that exercise the cluster / DSMEM / mbarrier / TMA code.
+# NOTE (round 2): on this GPU pool compute-sanitizer is closed by the operators ("runs under it have left GPUs needing a
+# reset"; gpurun_out/sanitize_*.log hold only that message, rc 86).  Concurrency evidence is therefore the stress test in
+# tools/tp_check.py --stress (102 400 exchanges, checksums) and the bounded-spin traps in the kernels.
 # usage: tools/gpu_sanitize.sh   (one gpurun call; logs -> gpurun_out/sanitize_*.log)
 mkdir -p gpurun_out
 CS=/usr/local/cuda/bin/compute-sanitizer
