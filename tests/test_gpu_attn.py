@@ -140,7 +140,11 @@ def test_decode_zero_context_row_is_zero(ops):
 
 @pytest.mark.parametrize(
     "s_new,computed,hq,hkv,d",
-    [(1, 0, 8, 2, 128), (33, 0, 8, 2, 128), (200, 96, 32, 8, 128), (64, 64, 32, 4, 64), (130, 1, 5, 1, 128), (1, 777, 8, 8, 64)],
+    [(1, 0, 8, 2, 128), (33, 0, 8, 2, 128), (200, 96, 32, 8, 128), (64, 64, 32, 4, 64), (130, 1, 5, 1, 128), (1, 777, 8, 8, 64),
+     # the tcgen05 kernel (>= 64 new tokens): several kv steps, odd GQA group (one CTA of the pair holds a single tile),
+     # one query head per kv head, cached prefixes that are not multiples of the 128-token step, D = 64
+     (513, 0, 8, 2, 128), (300, 1000, 10, 2, 128), (129, 37, 8, 8, 64), (128, 128, 4, 1, 128), (1024, 0, 32, 8, 128),
+     (700, 333, 32, 4, 64)],
 )
 def test_prefill_matches_oracle(ops, s_new, computed, hq, hkv, d):
     g = torch.Generator().manual_seed(17)

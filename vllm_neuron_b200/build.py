@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200_paged.so")
-SOURCES = ["host.cu", "kv_ops.cu", "paged_attn.cu", "gemm_tcgen05.cu", "tp_allreduce.cu", "sampling.cu"]
+SOURCES = ["host.cu", "kv_ops.cu", "paged_attn.cu", "paged_attn_prefill_tc.cu", "gemm_tcgen05.cu", "tp_allreduce.cu", "sampling.cu"]
 HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(os.path.dirname(HERE), "include", "b200_paged.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -40,6 +40,9 @@ int make_tmap_2d_sw64(CUtensorMap* out, const void* base, CUtensorMapDataType dt
 int make_tmap_2d_plain(CUtensorMap* out, const void* base, CUtensorMapDataType dt, uint32_t elem_bytes, uint64_t cols,
                        uint64_t rows, uint64_t row_pitch_bytes, uint32_t box_cols, uint32_t box_rows);
 int sm_count();
+// tcgen05 prefix-cached prefill attention (csrc/paged_attn_prefill_tc.cu); km / vm = the KV pools' tensor maps (pool_tmap)
+int launch_prefill_tc(const CUtensorMap& km, const CUtensorMap& vm, const void* q, int64_t q_stride, const int32_t* bt_row,
+                      void* out, int S_new, int computed_len, int Hq, int Hkv, int D, float scale, cudaStream_t stream);
 void count_launch(int n = 1);
 bool pdl_enabled();
 

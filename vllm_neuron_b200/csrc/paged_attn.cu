@@ -14,6 +14,8 @@
 #include <mutex>
 #include <unordered_map>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -778,6 +780,11 @@ int b200_paged_attn_prefill(const void* q, int64_t q_token_stride, const void* k
   rc = pool_tmap(v_pool, num_blocks, Hkv, D, &vm);
   if (rc) return rc;
   cudaStream_t s = (cudaStream_t)stream;
+  // prompts / chunks of >= 64 new tokens: the tcgen05 kernel (128-row query tiles in TMEM); shorter ones would leave most of
+  // a 128-row tile empty and keep the mma.sync kernel (64-row CTAs).  B200_PREFILL_LEGACY=1 forces the latter (A/B aid).
+  static const bool legacy = getenv("B200_PREFILL_LEGACY") != nullptr;
+  if (S_new >= 64 && !legacy && ((uintptr_t)q & 15) == 0 && (q_token_stride * 2) % 16 == 0)
+    return launch_prefill_tc(km, vm, q, q_token_stride, block_table_row, out, S_new, computed_len, Hq, Hkv, D, scale, s);
   if (D == 128)
     return launch_prefill<128>(km, vm, q, q_token_stride, block_table_row, out, S_new, computed_len, Hq, Hkv, scale, s);
   return launch_prefill<64>(km, vm, q, q_token_stride, block_table_row, out, S_new, computed_len, Hq, Hkv, scale, s);

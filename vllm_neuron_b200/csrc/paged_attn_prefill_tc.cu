@@ -1,0 +1,350 @@
+// Prefix-cached prefill attention on the 5th-generation tensor cores (tcgen05 + TMEM), one sequence per launch.
+//
+//   out[r][h] = softmax_k( q[r][h] . K[k] * scale  |  k <= computed_len + r ) V        (causal over cached prefix + new tokens)
+//
+// The reference builds the inputs of this step in `_prepare_prefix_caching_inputs`
+// (vllm_neuron/worker/neuronx_distributed_model_runner.py:739-763: block table row, slot mapping, `num_queries`,
+// `computed_context_lens`) and hands them to NxDI's prefix-caching attention; this kernel is the B200 side of that call
+// for prompts / chunks of >= 64 new tokens (shorter ones keep the mma.sync kernel in paged_attn.cu).
+//
+// CTA = one 128-row query tile of TWO query heads that share a kv head (GQA), so every K/V byte fetched from L2 feeds two
+// tiles; a K/V step is 128 tokens = four 32-token blocks gathered through the block table by TMA (128B swizzle) straight
+// into UMMA operand layout:
+//   S_t = Q_t K^T   : tcgen05.mma kind::f16, A = Q_t (smem, K-major), B = K step (smem, K-major: token rows)   -> TMEM fp32
+//   P_t = softmax   : one thread per query row (no shuffles): tcgen05.ld S, row max, exp2, row sum, bf16 P written back with
+//                     tcgen05.st INTO the columns S_t occupied (P aliases S, as in FlashAttention-4)
+//   O_t += P_t V    : tcgen05.mma, A = P_t FROM TENSOR MEMORY, B = V step (smem, MN-major: the TMA tile is already
+//                     [token][d]) -> TMEM fp32, accumulated over the whole K/V loop
+// TMEM: S0 | S1 | O0 | O1 = 4 x 128 columns.  The running maximum is "lazy": O and l are rescaled only when a row's maximum
+// grew by more than 8 (in log2 units), so exp2 arguments stay <= 8 and the O read-modify-write is rare.
+// Warp roles (352 threads): warps 0-3 softmax of tile 0, warps 4-7 softmax of tile 1 (warp w owns TMEM lanes 32*(w%4)..),
+// warp 8 = MMA issuer + TMEM owner (+ Q loads), warp 9 = K producer, warp 10 = V producer (two issuing warps: one thread
+// sustains ~1 TMA box row per 5.5 clk, profiles/r02_tma_ingest_v1.txt).
+// MMA issue order per step j:  PV0(j)  S0(j+1)  PV1(j)  S1(j+1)  -- tile 0's softmax of step j+1 overlaps tile 1's PV and
+// softmax of step j, and the other way round.
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int PF_BM = 128;   // query rows per tile
+constexpr int PF_BN = 128;   // kv tokens per step
+constexpr int PF_ST = 2;     // K / V stages
+constexpr int PF_THREADS = 256 + 3 * 32;
+constexpr int PF_BLK = 32;   // pa_block_size
+
+// MN-major, 128B-swizzled operand: 64 contiguous elements (128 B) of M/N per row, 8 K-rows per 1024 B atom;
+// LBO = byte distance between 64-element M/N atoms, SBO = byte distance between 8-row K groups
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]),
+        "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]),
+        "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16};\n" ::"r"(taddr),
+      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
+      "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+      : "memory");
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;\n" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int D>
+__global__ void __launch_bounds__(PF_THREADS, 1)
+    paged_attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
+                                 const __grid_constant__ CUtensorMap q_map, const int32_t* __restrict__ bt_row,
+                                 __nv_bfloat16* __restrict__ out, int S_new, int computed_len, int Hq, int Hkv,
+                                 float scale_log2) {
+  constexpr int NH = D / 64;                 // 64-element (128 B) halves of the head dimension
+  constexpr int HALF = PF_BN * 128;          // one [128 rows x 128 B] half tile = 16 KB
+  constexpr int TILE = NH * HALF;            // Q tile / K step / V step
+  constexpr uint32_t IDESC_S = umma_idesc(1, 1, PF_BM, PF_BN);
+  constexpr uint32_t IDESC_PV = umma_idesc(1, 1, PF_BM, D) | (1u << 16);  // B (= V) is MN-major
+  constexpr uint32_t TMEM_COLS = 512;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* q_s = smem;                               // [2 tiles][TILE]
+  uint8_t* k_s = q_s + 2 * TILE;                     // [PF_ST][TILE]
+  uint8_t* v_s = k_s + PF_ST * TILE;                 // [PF_ST][TILE]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(v_s + PF_ST * TILE);
+  uint64_t* q_full = bars;                           // 1
+  uint64_t* k_full = q_full + 1;                     // PF_ST
+  uint64_t* k_empty = k_full + PF_ST;
+  uint64_t* v_full = k_empty + PF_ST;
+  uint64_t* v_empty = v_full + PF_ST;
+  uint64_t* s_full = v_empty + PF_ST;                // 2 (per tile)
+  uint64_t* p_ready = s_full + 2;                    // 2
+  uint64_t* o_full = p_ready + 2;                    // 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int G = Hq / Hkv, pairs = (G + 1) >> 1;
+  const int kvh = blockIdx.y / pairs, pr = blockIdx.y - kvh * pairs;
+  const int head0 = kvh * G + 2 * pr;
+  const int ntile = (2 * pr + 1 < G) ? 2 : 1;
+  // heavy (late) query tiles first: the causal triangle makes tile x cost ~ (computed + 128 x) kv steps
+  const int q0 = ((int)gridDim.x - 1 - (int)blockIdx.x) * PF_BM;
+  const int q_hi = q0 + PF_BM < S_new ? q0 + PF_BM : S_new;  // one past the last valid row
+  const int kv_end = computed_len + q_hi;                    // keys [0, kv_end) are visible to some row of the tile
+  const int nsteps = (kv_end + PF_BN - 1) / PF_BN;
+  const int nblk_seq = (computed_len + S_new + PF_BLK - 1) / PF_BLK;  // valid entries of bt_row
+
+  if (warp == 8 && lane == 0) {
+    tma_prefetch_desc(&k_map);
+    tma_prefetch_desc(&v_map);
+    tma_prefetch_desc(&q_map);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < PF_ST; ++s) {
+      mbar_init(&k_full[s], 1);
+      mbar_init(&k_empty[s], 1);
+      mbar_init(&v_full[s], 1);
+      mbar_init(&v_empty[s], 1);
+    }
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(&s_full[t], 1);
+      mbar_init(&p_ready[t], 4);  // one arrival per softmax warp of the tile
+      mbar_init(&o_full[t], 1);
+    }
+    fence_mbar_init();
+    fence_proxy_async();
+  }
+  if (warp == 8) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  griddep_launch();
+  griddep_wait();  // q and the KV pool were written by the previous kernels of the stream (qkv GEMM, RoPE + KV write)
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 9 || warp == 10) {
+    // ---------------------------------------------------------------- K (warp 9) / V (warp 10) producer
+    if (lane == 0) {
+      const CUtensorMap* map = warp == 9 ? &k_map : &v_map;
+      uint8_t* ring = warp == 9 ? k_s : v_s;
+      uint64_t* full = warp == 9 ? k_full : v_full;
+      uint64_t* empty = warp == 9 ? k_empty : v_empty;
+      for (int j = 0; j < nsteps; ++j) {
+        const int s = j % PF_ST;
+        if (j >= PF_ST) mbar_wait(&empty[s], (uint32_t)(j / PF_ST - 1) & 1u);
+        mbar_expect_tx(&full[s], TILE);
+        uint8_t* dst = ring + (size_t)s * TILE;
+#pragma unroll
+        for (int b = 0; b < PF_BN / PF_BLK; ++b) {
+          const int bi = j * (PF_BN / PF_BLK) + b;
+          const int blk = bi < nblk_seq ? __ldg(bt_row + bi) : 0;  // past the sequence: the null block (masked anyway)
+          const int row = (blk * Hkv + kvh) * PF_BLK;
+#pragma unroll
+          for (int h = 0; h < NH; ++h) tma_load_2d(dst + h * HALF + b * (PF_BLK * 128), map, &full[s], h * 64, row);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 8) {
+    // ---------------------------------------------------------------- MMA issuer
+    if (lane == 0) {
+      mbar_expect_tx(q_full, (uint32_t)(ntile * TILE));
+      for (int t = 0; t < ntile; ++t)
+#pragma unroll
+        for (int h = 0; h < NH; ++h)
+          tma_load_2d(q_s + t * TILE + h * HALF, &q_map, q_full, (head0 + t) * D + h * 64, q0);
+      auto issue_s = [&](int t, int s) {
+        const uint32_t qa = smem_u32(q_s + t * TILE), ka = smem_u32(k_s + (size_t)s * TILE);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+          const uint32_t off = (uint32_t)(kk >> 2) * HALF + (uint32_t)(kk & 3) * 32;
+          umma_ss<KIND_F16>(tmem_base + (uint32_t)t * 128u, umma_desc_sw128(qa + off), umma_desc_sw128(ka + off), IDESC_S,
+                            (uint32_t)(kk != 0));
+        }
+        tc_commit(&s_full[t]);
+      };
+      auto issue_pv = [&](int t, int s, int j) {
+        const uint32_t va = smem_u32(v_s + (size_t)s * TILE);
+#pragma unroll
+        for (int kk = 0; kk < PF_BN / 16; ++kk)  // 16 tokens per UMMA_K: two 8-row groups of the [token][d] tile
+          umma_ts_f16(tmem_base + 256u + (uint32_t)t * 128u, tmem_base + (uint32_t)t * 128u + (uint32_t)kk * 8u,
+                      umma_desc_mn_sw128(va + kk * 2048, HALF, 1024), IDESC_PV, (uint32_t)((j | kk) != 0));
+      };
+      mbar_wait(q_full, 0);
+      mbar_wait(&k_full[0], 0);
+      tc_fence_after();
+      for (int t = 0; t < ntile; ++t) issue_s(t, 0);
+      tc_commit(&k_empty[0]);
+      for (int j = 0; j < nsteps; ++j) {
+        const int s = j % PF_ST, sn = (j + 1) % PF_ST;
+        const bool more = j + 1 < nsteps;
+        mbar_wait(&v_full[s], (uint32_t)(j / PF_ST) & 1u);
+        for (int t = 0; t < ntile; ++t) {
+          mbar_wait(&p_ready[t], (uint32_t)j & 1u);
+          tc_fence_after();
+          issue_pv(t, s, j);
+          if (t == ntile - 1) tc_commit(&v_empty[s]);
+          if (more) {
+            if (t == 0) {
+              mbar_wait(&k_full[sn], (uint32_t)((j + 1) / PF_ST) & 1u);
+              tc_fence_after();
+            }
+            issue_s(t, sn);
+            if (t == ntile - 1) tc_commit(&k_empty[sn]);
+          } else {
+            tc_commit(&o_full[t]);
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if ((warp >> 2) < ntile) {
+    // ---------------------------------------------------------------- softmax + epilogue of tile t, one row per thread
+    const int t = warp >> 2;
+    const int row = (warp & 3) * 32 + lane;
+    const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+    const uint32_t s_addr = lane_base + (uint32_t)t * 128u;        // S_t, and P_t over its first 64 columns
+    const uint32_t o_addr = lane_base + 256u + (uint32_t)t * 128u;
+    const int qpos = computed_len + q0 + row;
+    float m_used = -INFINITY, l = 0.f;
+    for (int j = 0; j < nsteps; ++j) {
+      mbar_wait(&s_full[t], (uint32_t)j & 1u);
+      tc_fence_after();
+      const int k0 = j * PF_BN;
+      const bool masked = k0 + PF_BN - 1 > computed_len + q0;  // some key of this step lies above some row's diagonal
+      // pass 1: row maximum of the raw scores
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < PF_BN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(s_addr + c * 32, v);
+        tmem_ld_wait();
+        if (masked) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, k0 + c * 32 + i <= qpos ? __uint_as_float(v[i]) : -INFINITY);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+        }
+      }
+      const float m_new = fmaxf(m_used, mx * scale_log2);
+      // lazy maximum: move it (and pay the O read-modify-write) only when it grew by more than 2^8
+      const bool grow = m_new > m_used + 8.f;
+      if (__any_sync(0xffffffffu, grow)) {
+        const float alpha = grow ? ex2_approx(m_used - m_new) : 1.f;  // m_used = -inf -> 0
+        if (grow) m_used = m_new;
+        l *= alpha;
+        if (j > 0) {
+#pragma unroll 1
+          for (int c = 0; c < D / 32; ++c) {
+            uint32_t v[32];
+            tmem_ld_32x32b_x32(o_addr + c * 32, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
+            tmem_st_32x32b_x32(o_addr + c * 32, v);
+          }
+          tmem_st_wait();
+        }
+      }
+      // pass 2: p = 2^(s*scale - m), row sum, bf16 P into the columns S occupied (chunk c of P lands on columns that
+      // chunk <= c of S has already been read from)
+#pragma unroll 1
+      for (int c = 0; c < PF_BN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(s_addr + c * 32, v);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float p0 = ex2_approx(fmaf(__uint_as_float(v[i]), scale_log2, -m_used));
+          float p1 = ex2_approx(fmaf(__uint_as_float(v[i + 1]), scale_log2, -m_used));
+          if (masked) {
+            if (k0 + c * 32 + i > qpos) p0 = 0.f;
+            if (k0 + c * 32 + i + 1 > qpos) p1 = 0.f;
+          }
+          l += p0 + p1;
+          pk[i >> 1] = pack_bf16(p0, p1);
+        }
+        tmem_st_32x32b_x16(s_addr + c * 16, pk);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_ready[t]);
+    }
+    // epilogue: O / l -> bf16 rows
+    mbar_wait(&o_full[t], 0);
+    tc_fence_after();
+    const float inv = l > 0.f ? 1.f / l : 0.f;
+    const bool ok = q0 + row < S_new;
+    __nv_bfloat16* dst = out + ((int64_t)(q0 + row) * Hq + head0 + t) * D;
+#pragma unroll 1
+    for (int c = 0; c < D / 32; ++c) {
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(o_addr + c * 32, v);
+      tmem_ld_wait();
+      if (ok) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 8) {
+          uint4 w;
+          w.x = pack_bf16(__uint_as_float(v[i]) * inv, __uint_as_float(v[i + 1]) * inv);
+          w.y = pack_bf16(__uint_as_float(v[i + 2]) * inv, __uint_as_float(v[i + 3]) * inv);
+          w.z = pack_bf16(__uint_as_float(v[i + 4]) * inv, __uint_as_float(v[i + 5]) * inv);
+          w.w = pack_bf16(__uint_as_float(v[i + 6]) * inv, __uint_as_float(v[i + 7]) * inv);
+          *reinterpret_cast<uint4*>(dst + c * 32 + i) = w;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+template <int D>
+static int launch_tc(const CUtensorMap& km, const CUtensorMap& vm, const CUtensorMap& qm, const int32_t* bt_row, void* out,
+                     int S_new, int computed_len, int Hq, int Hkv, float scale, cudaStream_t stream) {
+  auto kern = paged_attn_prefill_tc_kernel<D>;
+  constexpr size_t smem = (size_t)(2 + 2 * PF_ST) * (D / 64) * PF_BN * 128 + 256 + 1024;
+  static bool attr_done = false;
+  if (!attr_done) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_done = true;
+  }
+  const int G = Hq / Hkv;
+  dim3 grid((S_new + PF_BM - 1) / PF_BM, Hkv * ((G + 1) / 2));
+  B200_CUDA_OK(launch_kernel(kern, grid, dim3(PF_THREADS), smem, stream, km, vm, qm, bt_row, (__nv_bfloat16*)out, S_new,
+                             computed_len, Hq, Hkv, scale * 1.4426950408889634f));
+  return B200_OK;
+}
+
+int launch_prefill_tc(const CUtensorMap& km, const CUtensorMap& vm, const void* q, int64_t q_stride, const int32_t* bt_row,
+                      void* out, int S_new, int computed_len, int Hq, int Hkv, int D, float scale, cudaStream_t stream) {
+  // q rows as a 2D tensor [S_new][Hq*D] with the packed-qkv row pitch: box = 64 dims x 128 rows; rows past S_new read 0
+  CUtensorMap qm;
+  int rc = make_tmap_2d(&qm, q, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (uint64_t)Hq * D, (uint64_t)S_new,
+                        (uint64_t)q_stride * 2, 64, PF_BM);
+  if (rc) return rc;
+  if (D == 128) return launch_tc<128>(km, vm, qm, bt_row, out, S_new, computed_len, Hq, Hkv, scale, stream);
+  return launch_tc<64>(km, vm, qm, bt_row, out, S_new, computed_len, Hq, Hkv, scale, stream);
+}
+
+}  // namespace b200
