@@ -99,11 +99,12 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int G = Hq / Hkv, pairs = (G + 1) >> 1;
-  const int kvh = blockIdx.y / pairs, pr = blockIdx.y - kvh * pairs;
+  const int kvh = blockIdx.x / pairs, pr = blockIdx.x - kvh * pairs;
   const int head0 = kvh * G + 2 * pr;
   const int ntile = (2 * pr + 1 < G) ? 2 : 1;
-  // heavy (late) query tiles first: the causal triangle makes tile x cost ~ (computed + 128 x) kv steps
-  const int q0 = ((int)gridDim.x - 1 - (int)blockIdx.x) * PF_BM;
+  // longest-processing-time-first: CTAs are dispatched x-fastest, so y (slowest) walks the query tiles from the LAST one
+  // (the causal triangle makes tile i cost ~ computed/128 + i + 1 kv steps) and every head pair's heavy tiles start first
+  const int q0 = ((int)gridDim.y - 1 - (int)blockIdx.y) * PF_BM;
   const int q_hi = q0 + PF_BM < S_new ? q0 + PF_BM : S_new;  // one past the last valid row
   const int kv_end = computed_len + q_hi;                    // keys [0, kv_end) are visible to some row of the tile
   const int nsteps = (kv_end + PF_BN - 1) / PF_BN;
@@ -229,21 +230,27 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
       tc_fence_after();
       const int k0 = j * PF_BN;
       const bool masked = k0 + PF_BN - 1 > computed_len + q0;  // some key of this step lies above some row's diagonal
-      // pass 1: row maximum of the raw scores
-      float mx = -INFINITY;
+      // pass 1: row maximum of the raw scores; 64 columns per tcgen05.wait, four independent max chains
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll 1
-      for (int c = 0; c < PF_BN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(s_addr + c * 32, v);
+      for (int hc = 0; hc < PF_BN / 64; ++hc) {
+        uint32_t va[32], vb[32];
+        tmem_ld_32x32b_x32(s_addr + hc * 64, va);
+        tmem_ld_32x32b_x32(s_addr + hc * 64 + 32, vb);
         tmem_ld_wait();
         if (masked) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, k0 + c * 32 + i <= qpos ? __uint_as_float(v[i]) : -INFINITY);
+          for (int i = 0; i < 32; ++i) {
+            mx4[i & 3] = fmaxf(mx4[i & 3], k0 + hc * 64 + i <= qpos ? __uint_as_float(va[i]) : -INFINITY);
+            mx4[i & 3] = fmaxf(mx4[i & 3], k0 + hc * 64 + 32 + i <= qpos ? __uint_as_float(vb[i]) : -INFINITY);
+          }
         } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+          for (int i = 0; i < 32; ++i)
+            mx4[i & 3] = fmaxf(mx4[i & 3], fmaxf(__uint_as_float(va[i]), __uint_as_float(vb[i])));
         }
       }
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       const float m_new = fmaxf(m_used, mx * scale_log2);
       // lazy maximum: move it (and pay the O read-modify-write) only when it grew by more than 2^8
       const bool grow = m_new > m_used + 8.f;
@@ -264,27 +271,40 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
           tmem_st_wait();
         }
       }
-      // pass 2: p = 2^(s*scale - m), row sum, bf16 P into the columns S occupied (chunk c of P lands on columns that
-      // chunk <= c of S has already been read from)
+      // pass 2: p = 2^(s*scale - m), row sum (four independent chains), bf16 P into the columns S occupied: the 32 packed
+      // columns of half hc land on columns [32 hc, 32 hc + 32), all of which this thread has already read
+      float l4[4] = {0.f, 0.f, 0.f, 0.f};
+      const float neg_m = -m_used;
 #pragma unroll 1
-      for (int c = 0; c < PF_BN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(s_addr + c * 32, v);
+      for (int hc = 0; hc < PF_BN / 64; ++hc) {
+        uint32_t va[32], vb[32];
+        tmem_ld_32x32b_x32(s_addr + hc * 64, va);
+        tmem_ld_32x32b_x32(s_addr + hc * 64 + 32, vb);
         tmem_ld_wait();
-        uint32_t pk[16];
+        uint32_t pk[32];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          float p0 = ex2_approx(fmaf(__uint_as_float(v[i]), scale_log2, -m_used));
-          float p1 = ex2_approx(fmaf(__uint_as_float(v[i + 1]), scale_log2, -m_used));
+          float p0 = ex2_approx(fmaf(__uint_as_float(va[i]), scale_log2, neg_m));
+          float p1 = ex2_approx(fmaf(__uint_as_float(va[i + 1]), scale_log2, neg_m));
+          float p2 = ex2_approx(fmaf(__uint_as_float(vb[i]), scale_log2, neg_m));
+          float p3 = ex2_approx(fmaf(__uint_as_float(vb[i + 1]), scale_log2, neg_m));
           if (masked) {
-            if (k0 + c * 32 + i > qpos) p0 = 0.f;
-            if (k0 + c * 32 + i + 1 > qpos) p1 = 0.f;
+            const int kp = k0 + hc * 64 + i;
+            if (kp > qpos) p0 = 0.f;
+            if (kp + 1 > qpos) p1 = 0.f;
+            if (kp + 32 > qpos) p2 = 0.f;
+            if (kp + 33 > qpos) p3 = 0.f;
           }
-          l += p0 + p1;
+          l4[0] += p0;
+          l4[1] += p1;
+          l4[2] += p2;
+          l4[3] += p3;
           pk[i >> 1] = pack_bf16(p0, p1);
+          pk[16 + (i >> 1)] = pack_bf16(p2, p3);
         }
-        tmem_st_32x32b_x16(s_addr + c * 16, pk);
+        tmem_st_32x32b_x32(s_addr + hc * 32, pk);
       }
+      l += (l4[0] + l4[1]) + (l4[2] + l4[3]);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -330,7 +350,7 @@ static int launch_tc(const CUtensorMap& km, const CUtensorMap& vm, const CUtenso
     attr_done = true;
   }
   const int G = Hq / Hkv;
-  dim3 grid((S_new + PF_BM - 1) / PF_BM, Hkv * ((G + 1) / 2));
+  dim3 grid(Hkv * ((G + 1) / 2), (S_new + PF_BM - 1) / PF_BM);
   B200_CUDA_OK(launch_kernel(kern, grid, dim3(PF_THREADS), smem, stream, km, vm, qm, bt_row, (__nv_bfloat16*)out, S_new,
                              computed_len, Hq, Hkv, scale * 1.4426950408889634f));
   return B200_OK;
