@@ -160,13 +160,13 @@ def bench_configs():
     return res
 
 
-def bench_prefill():
+def bench_prefill(attn_only=False):
     """Prefill-side kernels of Llama-3.1-8B: gemm_streamk_kernel at M = 512 / 2048 / 8192 for
     qkv / gate_up / down in bf16 and fp8 (TFLOP/s against the measured sustained bf16 cuBLAS figure), and
     paged_attn_prefill_kernel at S_new + cached = 2048 (0 and 1024 cached tokens) and 8192."""
     tf_peak = PEAKS.get("bf16_tflops_sustained", 1432.9)
     res = []
-    for kind in ("bf16", "fp8"):
+    for kind in (() if attn_only else ("bf16", "fp8")):
         for m in (512, 2048, 8192):
             for n, k, name in ((6144, 4096, "qkv"), (28672, 4096, "gate_up"), (4096, 14336, "down")):
                 if kind == "bf16":
@@ -187,7 +187,10 @@ def bench_prefill():
                             "TFLOPs": round(tf, 1), "frac_bf16_sustained_peak": round(tf / tf_peak, 3)})
                 print(res[-1], flush=True)
     hq, hkv, d, bs = 32, 8, 128, 32
-    for total, cached in ((2048, 0), (2048, 1024), (8192, 0), (8192, 4096)):
+    cases = ((2048, 0), (2048, 1024), (8192, 0), (8192, 4096), (32768, 0))
+    if os.environ.get("PREFILL_CASES"):  # e.g. "8192:0" -- a single shape under ncu
+        cases = tuple(tuple(int(x) for x in c.split(":")) for c in os.environ["PREFILL_CASES"].split(","))
+    for total, cached in cases:
         s_new = total - cached
         nblk = total // bs
         g = torch.Generator(device="cuda").manual_seed(3)
@@ -225,6 +228,8 @@ if __name__ == "__main__":
                                   (128, 5120, 640)], kinds=("fp8", "bf16", "int8wo"))
     if a.what == "configs":
         out += bench_configs()
+    if a.what == "prefillattn":
+        out += bench_prefill(attn_only=True)
     if a.what == "prefill":
         out += bench_prefill()
     if a.what == "gemmsweep":
