@@ -17,7 +17,7 @@
 //                     [token][d]) -> TMEM fp32, accumulated over the whole K/V loop
 // TMEM: S0 | S1 | O0 | O1 = 4 x 128 columns.  The running maximum is "lazy": O and l are rescaled only when a row's maximum
 // grew by more than 8 (in log2 units), so exp2 arguments stay <= 8 and the O read-modify-write is rare.
-// Warp roles (352 threads): warps 0-3 softmax of tile 0, warps 4-7 softmax of tile 1 (warp w owns TMEM lanes 32*(w%4)..),
+// Warp roles (384 threads; setmaxnreg gives the softmax warpgroups 224 registers, the third warpgroup 56): warps 0-3 softmax of tile 0, warps 4-7 softmax of tile 1 (warp w owns TMEM lanes 32*(w%4)..),
 // warp 8 = MMA issuer + TMEM owner (+ Q loads), warp 9 = K producer, warp 10 = V producer (two issuing warps: one thread
 // sustains ~1 TMA box row per 5.5 clk, profiles/r02_tma_ingest_v1.txt).
 // MMA issue order per step j:  PV0(j)  S0(j+1)  PV1(j)  S1(j+1)  -- tile 0's softmax of step j+1 overlaps tile 1's PV and
@@ -29,7 +29,7 @@ namespace b200 {
 constexpr int PF_BM = 128;   // query rows per tile
 constexpr int PF_BN = 128;   // kv tokens per step
 constexpr int PF_ST = 2;     // K / V stages
-constexpr int PF_THREADS = 256 + 3 * 32;
+constexpr int PF_THREADS = 256 + 4 * 32;  // two softmax warpgroups + the MMA / producer warpgroup (its 4th warp idles)
 constexpr int PF_BLK = 32;   // pa_block_size
 
 // MN-major, 128B-swizzled operand: 64 contiguous elements (128 B) of M/N per row, 8 K-rows per 1024 B atom;
@@ -140,6 +140,10 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
   griddep_wait();  // q and the KV pool were written by the previous kernels of the stream (qkv GEMM, RoPE + KV write)
   const uint32_t tmem_base = *tmem_slot;
 
+  // register budget per role (setmaxnreg acts on whole warpgroups): the MMA / producer warpgroup keeps 56, the softmax
+  // threads -- who hold a 128-column score row each -- get 224
+  if (warp >= 8) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 56;\n");
   if (warp == 9 || warp == 10) {
     // ---------------------------------------------------------------- K (warp 9) / V (warp 10) producer
     if (lane == 0) {
@@ -216,7 +220,10 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
       }
     }
     __syncwarp();
-  } else if ((warp >> 2) < ntile) {
+  }
+  } else {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 224;\n");
+  if ((warp >> 2) < ntile) {
     // ---------------------------------------------------------------- softmax + epilogue of tile t, one row per thread
     const int t = warp >> 2;
     const int row = (warp & 3) * 32 + lane;
@@ -230,25 +237,28 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
       tc_fence_after();
       const int k0 = j * PF_BN;
       const bool masked = k0 + PF_BN - 1 > computed_len + q0;  // some key of this step lies above some row's diagonal
-      // pass 1: row maximum of the raw scores; 64 columns per tcgen05.wait, four independent max chains
-      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll 1
-      for (int hc = 0; hc < PF_BN / 64; ++hc) {
-        uint32_t va[32], vb[32];
-        tmem_ld_32x32b_x32(s_addr + hc * 64, va);
-        tmem_ld_32x32b_x32(s_addr + hc * 64 + 32, vb);
+      // the whole score row lives in registers: ONE pass over tensor memory, straight-line code after it
+      uint32_t sv[PF_BN];
+      auto load_scores = [&]() {
+        tmem_ld_32x32b_x32(s_addr, *reinterpret_cast<uint32_t(*)[32]>(&sv[0]));
+        tmem_ld_32x32b_x32(s_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&sv[32]));
+        tmem_ld_32x32b_x32(s_addr + 64, *reinterpret_cast<uint32_t(*)[32]>(&sv[64]));
+        tmem_ld_32x32b_x32(s_addr + 96, *reinterpret_cast<uint32_t(*)[32]>(&sv[96]));
         tmem_ld_wait();
-        if (masked) {
+        if (masked) {  // keys above the diagonal (and whatever stale bits a block past the sequence holds) -> -inf
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            mx4[i & 3] = fmaxf(mx4[i & 3], k0 + hc * 64 + i <= qpos ? __uint_as_float(va[i]) : -INFINITY);
-            mx4[i & 3] = fmaxf(mx4[i & 3], k0 + hc * 64 + 32 + i <= qpos ? __uint_as_float(vb[i]) : -INFINITY);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            mx4[i & 3] = fmaxf(mx4[i & 3], fmaxf(__uint_as_float(va[i]), __uint_as_float(vb[i])));
+          for (int i = 0; i < PF_BN; ++i)
+            if (k0 + i > qpos) sv[i] = 0xff800000u;
         }
+      };
+      load_scores();
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+      for (int i = 0; i < PF_BN; i += 8) {
+        mx4[0] = fmaxf(mx4[0], fmaxf(__uint_as_float(sv[i]), __uint_as_float(sv[i + 1])));
+        mx4[1] = fmaxf(mx4[1], fmaxf(__uint_as_float(sv[i + 2]), __uint_as_float(sv[i + 3])));
+        mx4[2] = fmaxf(mx4[2], fmaxf(__uint_as_float(sv[i + 4]), __uint_as_float(sv[i + 5])));
+        mx4[3] = fmaxf(mx4[3], fmaxf(__uint_as_float(sv[i + 6]), __uint_as_float(sv[i + 7])));
       }
       const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       const float m_new = fmaxf(m_used, mx * scale_log2);
@@ -258,7 +268,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
         const float alpha = grow ? ex2_approx(m_used - m_new) : 1.f;  // m_used = -inf -> 0
         if (grow) m_used = m_new;
         l *= alpha;
-        if (j > 0) {
+        if (j > 0) {  // rare after the first steps: the score registers are given up for the O tile and loaded again
 #pragma unroll 1
           for (int c = 0; c < D / 32; ++c) {
             uint32_t v[32];
@@ -269,42 +279,29 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
             tmem_st_32x32b_x32(o_addr + c * 32, v);
           }
           tmem_st_wait();
+          load_scores();
         }
       }
-      // pass 2: p = 2^(s*scale - m), row sum (four independent chains), bf16 P into the columns S occupied: the 32 packed
-      // columns of half hc land on columns [32 hc, 32 hc + 32), all of which this thread has already read
+      // p = 2^(s*scale - m), row sum on four independent chains, bf16 P over the first 64 columns S occupied
       float l4[4] = {0.f, 0.f, 0.f, 0.f};
       const float neg_m = -m_used;
-#pragma unroll 1
-      for (int hc = 0; hc < PF_BN / 64; ++hc) {
-        uint32_t va[32], vb[32];
-        tmem_ld_32x32b_x32(s_addr + hc * 64, va);
-        tmem_ld_32x32b_x32(s_addr + hc * 64 + 32, vb);
-        tmem_ld_wait();
-        uint32_t pk[32];
+      uint32_t pk[PF_BN / 2];
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float p0 = ex2_approx(fmaf(__uint_as_float(va[i]), scale_log2, neg_m));
-          float p1 = ex2_approx(fmaf(__uint_as_float(va[i + 1]), scale_log2, neg_m));
-          float p2 = ex2_approx(fmaf(__uint_as_float(vb[i]), scale_log2, neg_m));
-          float p3 = ex2_approx(fmaf(__uint_as_float(vb[i + 1]), scale_log2, neg_m));
-          if (masked) {
-            const int kp = k0 + hc * 64 + i;
-            if (kp > qpos) p0 = 0.f;
-            if (kp + 1 > qpos) p1 = 0.f;
-            if (kp + 32 > qpos) p2 = 0.f;
-            if (kp + 33 > qpos) p3 = 0.f;
-          }
-          l4[0] += p0;
-          l4[1] += p1;
-          l4[2] += p2;
-          l4[3] += p3;
-          pk[i >> 1] = pack_bf16(p0, p1);
-          pk[16 + (i >> 1)] = pack_bf16(p2, p3);
-        }
-        tmem_st_32x32b_x32(s_addr + hc * 32, pk);
+      for (int i = 0; i < PF_BN; i += 4) {
+        const float p0 = ex2_approx(fmaf(__uint_as_float(sv[i]), scale_log2, neg_m));
+        const float p1 = ex2_approx(fmaf(__uint_as_float(sv[i + 1]), scale_log2, neg_m));
+        const float p2 = ex2_approx(fmaf(__uint_as_float(sv[i + 2]), scale_log2, neg_m));
+        const float p3 = ex2_approx(fmaf(__uint_as_float(sv[i + 3]), scale_log2, neg_m));
+        l4[0] += p0;
+        l4[1] += p1;
+        l4[2] += p2;
+        l4[3] += p3;
+        pk[i >> 1] = pack_bf16(p0, p1);
+        pk[(i >> 1) + 1] = pack_bf16(p2, p3);
       }
       l += (l4[0] + l4[1]) + (l4[2] + l4[3]);
+      tmem_st_32x32b_x32(s_addr, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+      tmem_st_32x32b_x32(s_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -333,6 +330,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
         }
       }
     }
+  }
   }
   tc_fence_before();
   __syncthreads();
