@@ -210,6 +210,46 @@ def bench_prefill(attn_only=False):
     return res
 
 
+def bench_ttft(quant="fp8", prompts=(512, 2048, 8192)):
+    """Time to first token of one request through the model's prefill path (embedding -> 32 layers with the stream-K GEMMs,
+    fused RoPE / KV write, tcgen05 prefill attention -> last-row lm_head -> argmax), Llama-3.1-8B, random-init weights."""
+    from vllm_neuron_b200.config import PRESETS
+    from vllm_neuron_b200.model import B200CausalLM
+
+    shape = PRESETS["llama-3.1-8b"]
+    mml = max(prompts) + 32
+    nb = mml // 32 + 2
+    model = B200CausalLM(shape, None, quant=quant, num_blocks=nb, max_num_seqs=1, max_model_len=mml, device="cuda", seed=0)
+    model.block_table[0, : nb - 1] = torch.arange(1, nb, dtype=torch.int32, device="cuda")
+    res = []
+    for n in prompts:
+        toks = torch.randint(0, shape.vocab, (n,), generator=torch.Generator().manual_seed(n)).cuda()
+        for cached in (0, n // 2):
+            new = toks[cached:]
+            model.prefill(0, new, n, cached)  # warm-up (plans, tensor maps)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = 3
+            e0.record()
+            for _ in range(reps):
+                tok = model.prefill(0, new, n, cached)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / reps
+            # dense flops of the new tokens: 2 x params(layers + head row) x tokens + attention
+            qd, kd = shape.num_q_heads * shape.head_dim, shape.num_kv_heads * shape.head_dim
+            per_tok = 2 * shape.layers * ((qd + 2 * kd) * shape.hidden + shape.hidden * qd + 3 * shape.intermediate * shape.hidden)
+            s_new = n - cached
+            attn = 4 * (s_new * cached + s_new * (s_new + 1) // 2) * shape.num_q_heads * shape.head_dim * shape.layers
+            tf = (per_tok * s_new + attn) / ms / 1e9
+            res.append({"kernel": "ttft_prefill", "model": shape.name, "quant": quant, "prompt": n, "cached_prefix": cached,
+                        "ms": round(ms, 3), "prefill_tokens_per_s": round(s_new / ms * 1e3), "TFLOPs": round(tf, 1),
+                        "frac_bf16_sustained_peak": round(tf / PEAKS.get("bf16_tflops_sustained", 1432.9), 3),
+                        "first_token": int(tok)})
+            print(res[-1], flush=True)
+    return res
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("what", nargs="?", default="all")
@@ -228,6 +268,8 @@ if __name__ == "__main__":
                                   (128, 5120, 640)], kinds=("fp8", "bf16", "int8wo"))
     if a.what == "configs":
         out += bench_configs()
+    if a.what == "ttft":
+        out += bench_ttft()
     if a.what == "prefillattn":
         out += bench_prefill(attn_only=True)
     if a.what == "prefill":
