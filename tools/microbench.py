@@ -218,9 +218,10 @@ def bench_ttft(quant="fp8", prompts=(512, 2048, 8192)):
 
     shape = PRESETS["llama-3.1-8b"]
     mml = max(prompts) + 32
-    nb = mml // 32 + 2
+    mb = -(-mml // 32)
+    nb = mb + 1
     model = B200CausalLM(shape, None, quant=quant, num_blocks=nb, max_num_seqs=1, max_model_len=mml, device="cuda", seed=0)
-    model.block_table[0, : nb - 1] = torch.arange(1, nb, dtype=torch.int32, device="cuda")
+    model.block_table[0, :mb] = torch.arange(1, mb + 1, dtype=torch.int32, device="cuda")
     res = []
     for n in prompts:
         toks = torch.randint(0, shape.vocab, (n,), generator=torch.Generator().manual_seed(n)).cuda()
