@@ -242,6 +242,124 @@ __device__ __forceinline__ void epilogue_chunk_staged(const GemmEpilogue& ep, co
   }
 }
 
+// Stream-K (prefill) epilogue of one 16-token chunk, transposed through a per-warp shared-memory tile so that global
+// memory sees 16-byte vectors instead of one 2-byte element per lane:
+//   TMEM hands lane l the weight row n0w + l of 16 tokens; the warp writes the scaled values (a_scale, w_scale, bias
+//   applied, fp32) as xp[token][row] (pitch XP_PITCH floats), then lane (token = l / 4 + 8 it, rows 8 (l % 4) ..) adds the
+//   residual it loads as one 16-byte vector and stores 8 bf16 (or 8 fp32).  Per lane and chunk: 16 st.shared + 2 x
+//   (2 ld.shared.v4 + ld.global.v4 + st.global.v4) instead of 16 x (4 scalar global loads + a 2-byte store) -- measured
+//   on Llama-3.1-8B prefill (profiles/r02_ttft_breakdown_*.txt): o_proj 322 us, down 392 us at M = 2048 before.
+// Same roundings as scaled_value().  EPI_SILU_MUL: the activation of 16 channels x 16 tokens goes through the tile as
+// bf16 and leaves as one 16-byte store per lane.
+constexpr int XP_PITCH = 36;                       // floats; 36 keeps the float4 reads of a quarter-warp on distinct banks
+constexpr int XP_WARP_FLOATS = 16 * XP_PITCH;      // one warp's tile
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk_xpose(const GemmEpilogue& ep, const float (&v)[16], int m_base, int ml_base,
+                                                     int M, int n0w, int N, int lane, const float* a_s, float w_sc,
+                                                     float bias_v, float* xp) {
+  const bool hb = ep.bias != nullptr, hr = ep.residual != nullptr;
+  const int n = n0w + lane;
+  const bool n_ok = n < N;
+  if constexpr (EPI == EPI_LINEAR) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      float y = __fmul_rn(__fmul_rn(v[j], a_s[ml_base + j]), w_sc);
+      if (hb) y = __fadd_rn(y, bias_v);
+      xp[j * XP_PITCH + lane] = y;
+    }
+    __syncwarp();
+    const bool vec = (N & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0 &&
+                     (!hr || (reinterpret_cast<uintptr_t>(ep.residual) & 15) == 0);
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const int mm = it * 8 + (lane >> 2), c8 = (lane & 3) * 8;
+      const int m = m_base + mm, nn = n0w + c8;
+      if (m >= M || nn >= N) continue;
+      const float4 lo = *reinterpret_cast<const float4*>(xp + mm * XP_PITCH + c8);
+      const float4 hi = *reinterpret_cast<const float4*>(xp + mm * XP_PITCH + c8 + 4);
+      float y[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+      const int64_t off = (int64_t)m * N + nn;
+      if (vec) {
+        if (hr) {
+          const uint4 rv = *reinterpret_cast<const uint4*>(ep.residual + off);
+          const __nv_bfloat162* rh = reinterpret_cast<const __nv_bfloat162*>(&rv);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            y[2 * e] = __fadd_rn(y[2 * e], __low2float(rh[e]));
+            y[2 * e + 1] = __fadd_rn(y[2 * e + 1], __high2float(rh[e]));
+          }
+        }
+        if (ep.out_f32) {
+          float* o = reinterpret_cast<float*>(ep.out) + off;
+          *reinterpret_cast<float4*>(o) = make_float4(y[0], y[1], y[2], y[3]);
+          *reinterpret_cast<float4*>(o + 4) = make_float4(y[4], y[5], y[6], y[7]);
+        } else {
+          *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + off) =
+              make_uint4(pack_bf16(y[0], y[1]), pack_bf16(y[2], y[3]), pack_bf16(y[4], y[5]), pack_bf16(y[6], y[7]));
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          if (nn + e < N) {
+            float z = y[e];
+            if (hr) z = __fadd_rn(z, __bfloat162float(ep.residual[off + e]));
+            if (ep.out_f32)
+              reinterpret_cast<float*>(ep.out)[off + e] = z;
+            else
+              reinterpret_cast<__nv_bfloat16*>(ep.out)[off + e] = __float2bfloat16_rn(z);
+          }
+        }
+      }
+    }
+    __syncwarp();  // the tile is rewritten by the next chunk
+  } else {
+    // this lane's row: gate (lane < 16) or up (lane >= 16) of channel ch; both rounded to bf16 like the unfused path
+    const int I = N >> 1, n_groups = N >> 5;
+    float mine[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      float y = __fmul_rn(__fmul_rn(v[j], a_s[ml_base + j]), w_sc);
+      if (hb) y = __fadd_rn(y, bias_v);
+      mine[j] = (m_base + j < M && n_ok) ? __bfloat162float(__float2bfloat16_rn(y)) : 0.f;
+    }
+    const bool hi_half = lane >= 16;  // lanes < 16 finish tokens 0..7 of the chunk, lanes >= 16 finish tokens 8..15
+    __nv_bfloat16* xb = reinterpret_cast<__nv_bfloat16*>(xp);  // [16 tokens][16 channels] bf16
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float send = hi_half ? mine[j] : mine[j + 8];
+      const float got = __shfl_xor_sync(0xffffffffu, send, 16);
+      const float g = hi_half ? got : mine[j];
+      const float u = hi_half ? mine[j + 8] : got;
+      const int mm = (hi_half ? 8 : 0) + j;
+      const bool ok = m_base + mm < M && n_ok;
+      const float a = silu_mul_bf16(g, u);
+      xb[mm * 16 + (lane & 15)] = __float2bfloat16_rn(a);
+      float x = ok ? fabsf(a) : 0.f;  // max over the 16 channels of the group (one half-warp)
+#pragma unroll
+      for (int o = 1; o < 16; o <<= 1) x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, o));
+      if ((lane & 15) == 0 && ok) ep.group_amax[(int64_t)(m_base + mm) * n_groups + (n0w >> 5)] = x;
+    }
+    __syncwarp();
+    {
+      const int mm = lane >> 1, c8 = (lane & 1) * 8;
+      const int m = m_base + mm;
+      const int ch = (n0w >> 5) * 16 + c8;
+      if (m < M && n0w < N) {  // N2 % 32 == 0: a 32-row group is inside N or outside as a whole
+        const uint4 val = *reinterpret_cast<const uint4*>(xb + mm * 16 + c8);
+        __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(ep.out) + (int64_t)m * I + ch;
+        if ((I & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0) {
+          *reinterpret_cast<uint4*>(dst) = val;
+        } else {
+          const __nv_bfloat16* sv = reinterpret_cast<const __nv_bfloat16*>(&val);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) dst[e] = sv[e];
+        }
+      }
+    }
+    __syncwarp();
+  }
+}
+
 template <int KIND, int BM, int NSTAGES, int EPI>
 __global__ void __launch_bounds__(KIND == KIND_WO8 ? GEMM_THREADS + 128 : GEMM_THREADS, 1)
     gemm_streamk_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap a_map,
@@ -270,6 +388,8 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? GEMM_THREADS + 128 : GEMM_T
   uint64_t* tempty = tfull + 2;        // [2] accumulator stage drained
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
   int* fix_flag = reinterpret_cast<int*>(tmem_slot + 1);
+  float* a_s_tile = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(fix_flag + 1) + 15) & ~uintptr_t(15));  // [BM]
+  float* xpose = a_s_tile + BM;  // [4 epilogue warps][16][XP_PITCH]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int P = gridDim.x, c = blockIdx.x;
@@ -412,6 +532,15 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? GEMM_THREADS + 128 : GEMM_T
       const int nl = lg * 32 + lane;
       const int n = n_tile * GEMM_BN + nl;
       const bool n_ok = n < N;
+      const int n0w = n_tile * GEMM_BN + lg * 32;
+      float* xp = xpose + lg * XP_WARP_FLOATS;
+      // per-tile epilogue operands: the token scales of this m-tile in shared memory, this lane's channel scale / bias in
+      // registers (the MMAs of the tile are still running)
+      named_bar_sync(1, 128);  // the previous segment's readers of a_s_tile are done
+      for (int m = et; m < BM; m += 128) a_s_tile[m] = (ep.a_scale && m0 + m < M) ? ep.a_scale[m0 + m] : 1.f;
+      const float w_sc = (ep.w_scale && n_ok) ? ep.w_scale[n] : 1.f;
+      const float bias_v = (ep.bias && n_ok) ? __bfloat162float(ep.bias[n]) : 0.f;
+      named_bar_sync(1, 128);
       mbar_wait(&tfull[as], (seg >> 1) & 1);
       tc_fence_after();
       const uint32_t acc = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(as * BM);
@@ -425,7 +554,7 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? GEMM_THREADS + 128 : GEMM_T
 #pragma unroll
         for (int j = 0; j < 16; ++j) f[j] = KIND == KIND_I8 ? (float)(int32_t)v[j] : __uint_as_float(v[j]);
         if (complete) {
-          epilogue_chunk<EPI>(ep, f, m0 + cc * 16, M, n, n_ok, N, lane);
+          if (m0 + cc * 16 < M) epilogue_chunk_xpose<EPI>(ep, f, m0 + cc * 16, cc * 16, M, n0w, N, lane, a_s_tile, w_sc, bias_v, xp);
         } else {
 #pragma unroll
           for (int j = 0; j < 16; ++j) slot[(size_t)(cc * 16 + j) * GEMM_BN + nl] = f[j];
@@ -461,7 +590,7 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? GEMM_THREADS + 128 : GEMM_T
 #pragma unroll
               for (int j = 0; j < 16; ++j) f[j] += __ldcg(ps + (size_t)(mb + j) * GEMM_BN);
             }
-            epilogue_chunk<EPI>(ep, f, m0 + mb, M, n, n_ok, N, lane);
+            if (m0 + mb < M) epilogue_chunk_xpose<EPI>(ep, f, m0 + mb, mb, M, n0w, N, lane, a_s_tile, w_sc, bias_v, xp);
           }
         }
       }
@@ -1054,7 +1183,7 @@ int w_elem_bytes(int dt) { return dt == B200_BF16 ? 2 : 1; }
 constexpr int stages_for(int bm, bool wo = false) { return bm == 32 ? 10 : bm == 64 ? 8 : bm == 128 ? 6 : wo ? 3 : 4; }
 constexpr size_t smem_for(int bm, bool wo = false) {
   return (size_t)stages_for(bm, wo) * (GEMM_BN * GEMM_BK_BYTES + bm * GEMM_BK_BYTES + (wo ? RAW_TILE : 0)) +
-         (5 * stages_for(bm, wo) + 4) * 8 + 8 + 1024;
+         (5 * stages_for(bm, wo) + 4) * 8 + 8 + 16 + (size_t)bm * 4 + 4 * XP_WARP_FLOATS * 4 + 1024;
 }
 
 // split_k: decode = cluster size along K (0 = auto; 1, 2, 4, 8); stream-K = cap on the persistent CTAs (0 = one per SM)
