@@ -711,7 +711,7 @@ __device__ __forceinline__ void rope_reduce_store(const GemmEpilogue& ep, const 
 // ring, so the rings are twice as deep as with a widened copy in shared memory, there is no generic-proxy -> async-proxy
 // fence on the way to the tensor core, and the MMA reads half as many shared-memory bytes.
 constexpr int WO_CONV_WARPS = 8;
-constexpr int WO_THREADS = 64 + 32 * WO_CONV_WARPS + 3 * 32;  // + two activation producer warps and a second weight producer
+constexpr int WO_THREADS = 64 + 32 * WO_CONV_WARPS + 32;  // + the activation producer warp (last warp)
 constexpr int DEC_THREADS = GEMM_THREADS + 32;            // decode kernel: + the activation producer warp (warp 6)
 constexpr uint32_t WO_TMEM_COLS = 256;  // accumulator (BM columns, >= 32) + widened-weight slots of 32 columns each
 template <int BM>
@@ -780,12 +780,7 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? WO_THREADS : DEC_THREADS, K
   constexpr uint32_t ACC_COLS = BM < 32 ? 32 : BM;
   constexpr uint32_t TMEM_COLS = WO ? WO_TMEM_COLS : ACC_COLS;
   constexpr int NW = wo_slots<BM>();  // weight-only: widened-weight slots in TMEM
-  constexpr int AP_WARP = WO ? 2 + WO_CONV_WARPS : 6;  // the (first) activation producer
-  // Weight-only at M = 128 is bound by how fast ONE thread can issue TMA boxes (~5.5 clk per box row: a 128-row raw tile
-  // and a 128-row activation tile cost 0.36 us each per k-block, profiles/r02_tma_ingest_v1.txt), so that schedule gets
-  // two issuing warps per operand, each taking every other k-block: warp 0 + warp AP_WARP+2 (weights), AP_WARP +
-  // AP_WARP+1 (activations).  The W8A8 / bf16 kernels keep one each (they run two CTAs per SM and are HBM-bound).
-  constexpr int NP = WO ? 2 : 1;
+  constexpr int AP_WARP = WO ? 2 + WO_CONV_WARPS : 6;  // the activation producer: the last warp
   // optional per-CTA time stamps (b200_gemm_set_trace; tools/gemm_trace.py): 0 start, 1 producer past the dependency,
   // 2 first stage landed, 3 last MMA retired, 4 partials pushed, 5 cluster barrier passed, 6 outputs stored
 #define B200_STAMP(k) do { if (trace) trace[(size_t)blockIdx.x * 8 + (k)] = globaltimer_ns(); } while (0)
@@ -866,29 +861,43 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? WO_THREADS : DEC_THREADS, K
   float w_sc = 1.f, bias_v = 0.f;        // S == 1: row nl
   float w4[4] = {1.f, 1.f, 1.f, 1.f}, b4[4] = {0.f, 0.f, 0.f, 0.f};  // S > 1: rows 4*t4 + e
 
-  if (warp == 0 || (NP == 2 && warp == AP_WARP + 2)) {
-    const int pi = warp == 0 ? 0 : 1;  // producer index: k-blocks i = pi, pi + NP, ...
+  if (warp == 0) {
     if (lane == 0 && nk > 0) {
       const uint64_t pol_w = policy_evict_first();  // every weight byte is read once per step
       const int npre = nk < nst ? nk : nst;
-      // weights do not depend on any kernel of the step: fill the ring with W tiles before the dependency resolves;
-      // once the ring is full, refills wait for the stage to drain (stage i % nst, parity of its previous use)
-      for (int i = pi; i < nk; i += NP) {
-        const int s = i % nst;
+      // weights do not depend on any kernel of the step: fill the ring with W tiles before the dependency resolves
+      for (int i = 0; i < npre; ++i) {
         if constexpr (WO) {
-          if (i >= nst) mbar_wait(&empty_raw[s], (uint32_t)(i / nst - 1) & 1u);
+          mbar_expect_tx(&full_raw[i], RAW_TILE);
+          tma_load_2d_hint(raw_ring + (size_t)i * RAW_TILE, &w_map, &full_raw[i], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
+        } else {
+          mbar_expect_tx(&full_w[i], W_TILE);
+          tma_load_2d_hint(w_ring + (size_t)i * W_TILE, &w_map, &full_w[i], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
+        }
+      }
+      // ... and pull the next `l2_ahead` weight tiles of this CTA's stream into L2: HBM is idle while the predecessor
+      // (a small glue kernel, or the tail of a GEMM) drains, so by the time the ring recycles these loads are L2 hits
+      {
+        const int pf_end = nk < npre + l2_ahead ? nk : npre + l2_ahead;
+        for (int i = npre; i < pf_end; ++i) tma_prefetch_l2_2d(&w_map, (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN);
+      }
+      // refills: weights only -- the activation tiles come from their own producer warp (AP_WARP).  One issuing thread
+      // sustains about one TMA box row per 5.5 cycles (tools/tma_ingest.cu: 128x64B boxes 21 GB/s per SM from one
+      // producer warp, 40 GB/s from two), so W and A boxes issued by the same thread queue behind each other.
+      int s = 0, ph = 0;  // stage / parity of the empty barriers for refills
+      for (int i = npre; i < nk; ++i) {
+        if constexpr (WO) {
+          mbar_wait(&empty_raw[s], ph);
           mbar_expect_tx(&full_raw[s], RAW_TILE);
           tma_load_2d_hint(raw_ring + (size_t)s * RAW_TILE, &w_map, &full_raw[s], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
         } else {
-          if (i >= nst) mbar_wait(&empty_w[s], (uint32_t)(i / nst - 1) & 1u);
+          mbar_wait(&empty_w[s], ph);
           mbar_expect_tx(&full_w[s], W_TILE);
           tma_load_2d_hint(w_ring + (size_t)s * W_TILE, &w_map, &full_w[s], (kb0 + i) * BK_ELEMS, n_tile * GEMM_BN, pol_w);
         }
-        // ... and, right after the prologue, pull the next `l2_ahead` weight tiles of this CTA's stream into L2 (tuning
-        // aid, default 0): HBM is idle while the predecessor drains
-        if (pi == 0 && i < npre && i + NP >= npre) {
-          const int pf_end = nk < npre + l2_ahead ? nk : npre + l2_ahead;
-          for (int q = npre; q < pf_end; ++q) tma_prefetch_l2_2d(&w_map, (kb0 + q) * BK_ELEMS, n_tile * GEMM_BN);
+        if (++s == nst) {
+          s = 0;
+          ph ^= 1;
         }
       }
     }
@@ -935,22 +944,25 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? WO_THREADS : DEC_THREADS, K
     }
     if (lane == 0) tc_commit(tfull);
     __syncwarp();
-  } else if (warp == AP_WARP || (NP == 2 && warp == AP_WARP + 1)) {
-    // ---- activation producer(s): everything they load was written by the previous kernel of the stream
-    const int pi = warp - AP_WARP;
+  } else if (warp == AP_WARP) {
+    // ---- activation producer: everything it loads was written by the previous kernel of the stream
     if (lane == 0 && nk > 0) {
       const uint64_t pol_a = policy_evict_last();  // activations are re-read by every tile
       griddep_wait();
-      if (pi == 0) B200_STAMP(1);
-      for (int i = pi; i < nk; i += NP) {
-        const int s = i % nst;
-        if (i >= nst) mbar_wait(&empty_a[s], (uint32_t)(i / nst - 1) & 1u);
+      B200_STAMP(1);
+      int s = 0, ph = 1;  // first pass over the ring: the stages are free (parity-1 wait on a fresh barrier returns at once)
+      for (int i = 0; i < nk; ++i) {
+        mbar_wait(&empty_a[s], ph);
         mbar_expect_tx(&full_a[s], A_TILE);
         tma_load_2d_hint(a_ring + (size_t)s * A_TILE, &a_map, &full_a[s], (kb0 + i) * BK_ELEMS, 0, pol_a);
+        if (++s == nst) {
+          s = 0;
+          ph ^= 1;
+        }
       }
     }
     __syncwarp();
-  } else if (WO && warp >= 6 && warp < AP_WARP) {
+  } else if (WO && warp >= 6) {
     // weight-only: the second converter group (odd k-blocks); see wo_convert below
     wo_convert<BM>(raw_ring, full_raw, empty_raw, full_w, empty_w, tmem_base + ACC_COLS, nk, nst, 1, warp & 3, lane);
   } else {
