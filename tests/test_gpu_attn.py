@@ -175,3 +175,34 @@ def test_prefill_last_row_equals_decode(ops):
     pre = ops.paged_attn_prefill(q, kd, vd, bt[0].cuda(), total - 100, 0.09)
     dec = ops.paged_attn_decode(q[-1:], kd, vd, bt.cuda(), torch.tensor([total], dtype=torch.int32, device="cuda"), 0.09)
     assert rel_err(pre[-1:].cpu(), dec.cpu()) < 1e-2
+
+
+def test_prefill_prefix_consistency_full_size(ops):
+    """Size-independent property at the headline head configuration (32 q heads, 8 kv heads, D = 128) and an 8k sequence,
+    where the CPU oracle would take minutes: computing the last 4096 tokens against a 4096-token CACHED prefix gives the
+    same rows as computing all 8192 tokens at once (different query tiles, kv-step counts and mask positions in the
+    tcgen05 kernel), and the last row of either equals a decode step at context 8192."""
+    g = torch.Generator().manual_seed(29)
+    hq, hkv, d, bs, total, cached = 32, 8, 128, 32, 8192, 4096
+    nblk = total // bs
+    kp, vp = _pools(nblk + 2, bs, hkv, d, g)
+    bt = make_block_tables(1, [total], bs, nblk + 2, nblk, g)
+    q = torch.randn(total, hq, d, generator=g).bfloat16().cuda()
+    kd, vd = logical_to_device_pool(kp).cuda(), logical_to_device_pool(vp).cuda()
+    scale = d**-0.5
+    full = ops.paged_attn_prefill(q, kd, vd, bt[0].cuda(), 0, scale)
+    tail = ops.paged_attn_prefill(q[cached:].contiguous(), kd, vd, bt[0].cuda(), cached, scale)
+    torch.cuda.synchronize()
+    assert torch.isfinite(full.float()).all() and torch.isfinite(tail.float()).all()
+    assert rel_err(tail.cpu(), full[cached:].cpu()) < 5e-3
+    dec = ops.paged_attn_decode(q[-1:], kd, vd, bt.cuda(), torch.tensor([total], dtype=torch.int32, device="cuda"), scale)
+    assert rel_err(full[-1:].cpu(), dec.cpu()) < 1e-2
+    # causality: row r must not depend on keys > r -- perturb the last block's K/V, the first 8160 rows stay bit-identical
+    kd2, vd2 = kd.clone(), vd.clone()
+    last_blk = int(bt[0, nblk - 1])
+    kd2[last_blk] += 1.0
+    vd2[last_blk] -= 1.0
+    full2 = ops.paged_attn_prefill(q, kd2, vd2, bt[0].cuda(), 0, scale)
+    torch.cuda.synchronize()
+    assert torch.equal(full2[: total - bs], full[: total - bs])
+    assert not torch.equal(full2[total - bs:], full[total - bs:])
