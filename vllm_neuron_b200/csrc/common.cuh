@@ -368,6 +368,10 @@ __device__ __forceinline__ uint8_t quant_byte(float y, float scale) {
     return (uint8_t)(int8_t)(int)r;
   }
 }
+// SiLU(g) = g * sigmoid(g) on the fast special-function path (ex2.approx + rcp.approx: relative error ~2^-21, far inside
+// the bf16 rounding every caller applies next); ONE definition for the fused GEMM epilogues and the stand-alone kernel,
+// which the tests require to agree bit for bit.  g -> -inf gives -0, g -> +inf gives g.
+__device__ __forceinline__ float silu_f32(float g) { return __fdividef(g, 1.f + __expf(-g)); }
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));

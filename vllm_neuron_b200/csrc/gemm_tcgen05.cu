@@ -146,8 +146,7 @@ __device__ __forceinline__ int span_owner(long long U, int P, long long x) { ret
 
 // SiLU(gate) * up for one channel; both inputs already rounded to bf16 like the unfused path (b200_gemm + b200_silu_mul)
 __device__ __forceinline__ float silu_mul_bf16(float g, float u) {
-  const float sg = __fdiv_rn(1.f, 1.f + expf(-g));
-  return __bfloat162float(__float2bfloat16_rn(g * sg * u));
+  return __bfloat162float(__float2bfloat16_rn(silu_f32(g) * u));
 }
 
 // Epilogue of one 16-token column chunk held in v[] by the lane that owns weight row n (EPI_LINEAR), or by the lane pair
@@ -333,19 +332,22 @@ __device__ __forceinline__ void epilogue_chunk_xpose(const GemmEpilogue& ep, con
       const int mm = (hi_half ? 8 : 0) + j;
       const bool ok = m_base + mm < M && n_ok;
       const float a = silu_mul_bf16(g, u);
-      xb[mm * 16 + (lane & 15)] = __float2bfloat16_rn(a);
-      float x = ok ? fabsf(a) : 0.f;  // max over the 16 channels of the group (one half-warp)
-#pragma unroll
-      for (int o = 1; o < 16; o <<= 1) x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, o));
-      if ((lane & 15) == 0 && ok) ep.group_amax[(int64_t)(m_base + mm) * n_groups + (n0w >> 5)] = x;
+      xb[mm * 16 + (lane & 15)] = __float2bfloat16_rn((m_base + mm < M && n_ok) ? a : 0.f);
     }
     __syncwarp();
     {
       const int mm = lane >> 1, c8 = (lane & 1) * 8;
       const int m = m_base + mm;
       const int ch = (n0w >> 5) * 16 + c8;
+      // the lane pair (2 mm, 2 mm + 1) holds the 16 channels of token mm: their maximum is the group's amax
+      const uint4 val = *reinterpret_cast<const uint4*>(xb + mm * 16 + c8);
+      const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&val);
+      float x = 0.f;
+#pragma unroll
+      for (int e = 0; e < 4; ++e) x = fmaxf(x, fmaxf(fabsf(__low2float(h2[e])), fabsf(__high2float(h2[e]))));
+      x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, 1));
       if (m < M && n0w < N) {  // N2 % 32 == 0: a 32-row group is inside N or outside as a whole
-        const uint4 val = *reinterpret_cast<const uint4*>(xb + mm * 16 + c8);
+        if ((lane & 1) == 0) ep.group_amax[(int64_t)m * n_groups + (n0w >> 5)] = x;
         __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(ep.out) + (int64_t)m * I + ch;
         if ((I & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0) {
           *reinterpret_cast<uint4*>(dst) = val;

@@ -266,8 +266,7 @@ __device__ __forceinline__ void silu_mul8(const uint4& g, const uint4& u, float 
   unpack8(u, uf);
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
-    float sg = __fdiv_rn(1.f, 1.f + expf(-gf[e]));
-    a[e] = bf16_round(gf[e] * sg * uf[e]);
+    a[e] = bf16_round(silu_f32(gf[e]) * uf[e]);
   }
 }
 
