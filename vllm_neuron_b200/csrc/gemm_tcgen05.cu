@@ -127,19 +127,6 @@ __device__ __forceinline__ float scaled_value(float acc, float a, float w, bool 
   if (has_res) y = __fadd_rn(y, r);
   return y;
 }
-__device__ __forceinline__ float linear_value(const GemmEpilogue& ep, float acc, int m, int n, int N) {
-  return scaled_value(acc, ep.a_scale ? ep.a_scale[m] : 1.f, ep.w_scale ? ep.w_scale[n] : 1.f, ep.bias != nullptr,
-                      ep.bias ? __bfloat162float(ep.bias[n]) : 0.f, ep.residual != nullptr,
-                      ep.residual ? __bfloat162float(ep.residual[(int64_t)m * N + n]) : 0.f);
-}
-__device__ __forceinline__ void store_out(const GemmEpilogue& ep, float acc, int m, int n, int N) {
-  float y = linear_value(ep, acc, m, n, N);
-  if (ep.out_f32)
-    reinterpret_cast<float*>(ep.out)[(int64_t)m * N + n] = y;
-  else
-    reinterpret_cast<__nv_bfloat16*>(ep.out)[(int64_t)m * N + n] = __float2bfloat16_rn(y);
-}
-
 // span of CTA c: units [U*c/P, U*(c+1)/P); owner(x) = the CTA whose span holds unit x
 __device__ __forceinline__ long long span_begin(long long U, int P, int c) { return U * c / P; }
 __device__ __forceinline__ int span_owner(long long U, int P, long long x) { return (int)(((x + 1) * P - 1) / U); }
@@ -149,50 +136,9 @@ __device__ __forceinline__ float silu_mul_bf16(float g, float u) {
   return __bfloat162float(__float2bfloat16_rn(silu_f32(g) * u));
 }
 
-// Epilogue of one 16-token column chunk held in v[] by the lane that owns weight row n (EPI_LINEAR), or by the lane pair
-// (l, l^16) that owns the gate and the up row of one channel (EPI_SILU_MUL; W rows interleaved 16 gate / 16 up per warp).
-template <int EPI>
-__device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, const float (&v)[16], int m_base, int M, int n,
-                                               bool n_ok, int N, int lane) {
-  if constexpr (EPI == EPI_LINEAR) {
-#pragma unroll
-    for (int j = 0; j < 16; ++j) {
-      const int m = m_base + j;
-      if (m < M && n_ok) store_out(ep, v[j], m, n, N);
-    }
-  } else {
-    // this lane's row: gate (lane < 16) or up (lane >= 16) of channel ch; both rounded to bf16 like the unfused path
-    const int I = N >> 1, n_groups = N >> 5;
-    const int ch = (n >> 5) * 16 + (lane & 15);
-    float mine[16];
-#pragma unroll
-    for (int j = 0; j < 16; ++j) {
-      const int m = m_base + j;
-      float y = 0.f;
-      if (m < M && n_ok) y = __bfloat162float(__float2bfloat16_rn(linear_value(ep, v[j], m, n, N)));
-      mine[j] = y;
-    }
-    // lanes < 16 finish tokens 0..7 of the chunk, lanes >= 16 finish tokens 8..15
-    const bool hi = lane >= 16;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float send = hi ? mine[j] : mine[j + 8];  // what the partner needs from me
-      const float got = __shfl_xor_sync(0xffffffffu, send, 16);
-      const float g = hi ? got : mine[j];
-      const float u = hi ? mine[j + 8] : got;
-      const int m = m_base + (hi ? 8 : 0) + j;
-      const bool ok = m < M && n_ok;
-      const float a = silu_mul_bf16(g, u);
-      if (ok) reinterpret_cast<__nv_bfloat16*>(ep.out)[(int64_t)m * I + ch] = __float2bfloat16_rn(a);
-      float x = ok ? fabsf(a) : 0.f;  // max over the 16 channels of the group (one half-warp)
-#pragma unroll
-      for (int o = 1; o < 16; o <<= 1) x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, o));
-      if ((lane & 15) == 0 && ok) ep.group_amax[(int64_t)m * n_groups + (n >> 5)] = x;
-    }
-  }
-}
-
-// Same, with every epilogue operand already staged: a_s[] per-token scales in shared memory, this lane's channel scale /
+// Decode-kernel epilogue of one 16-token column chunk held in v[] by the lane that owns weight row n (EPI_LINEAR), or by
+// the lane pair (l, l^16) that owns the gate and the up row of one channel (EPI_SILU_MUL; W rows interleaved 16 gate / 16
+// up per warp), with every epilogue operand already staged: a_s[] per-token scales in shared memory, this lane's channel scale /
 // bias in registers, the residual column of this lane in shared memory (resid[m * resid_stride]).
 template <int EPI>
 __device__ __forceinline__ void epilogue_chunk_staged(const GemmEpilogue& ep, const float (&v)[16], int m_base, int M, int n,
@@ -330,7 +276,6 @@ __device__ __forceinline__ void epilogue_chunk_xpose(const GemmEpilogue& ep, con
       const float g = hi_half ? got : mine[j];
       const float u = hi_half ? mine[j + 8] : got;
       const int mm = (hi_half ? 8 : 0) + j;
-      const bool ok = m_base + mm < M && n_ok;
       const float a = silu_mul_bf16(g, u);
       xb[mm * 16 + (lane & 15)] = __float2bfloat16_rn((m_base + mm < M && n_ok) ? a : 0.f);
     }
