@@ -234,6 +234,15 @@ int b200_allreduce_rmsnorm_nvls(const void* mc_buf, void* const* host_peer_flags
                                 void* x_out, const void* norm_w, void* out_bf16, void* out_q, float* out_scale, int T,
                                 int H, float eps, int q_dtype, void* stream);
 
+/* Greedy merge over the vocabulary shards of a TP group (the reference leaves sampling of the sharded logits to NxDI's
+ * on-device sampler, model_loader.py:367-382).  host_peer_vals[p] / host_peer_idxs[p]: rank p's [B] fp32 local maxima and
+ * [B] int64 GLOBAL indices inside peer-mapped memory, written by b200_argmax earlier on the stream; host_peer_flags[p]:
+ * rank p's [8] uint32 flag words (zero-initialised once); epoch: one local uint32 (zero-initialised once).
+ * out_ids[b] = index of the largest value over all ranks, ties to the lowest index; identical on every rank. */
+int b200_tp_argmax_merge(const void* const* host_peer_vals, const void* const* host_peer_idxs,
+                         void* const* host_peer_flags, uint32_t* epoch, int rank, int world, int64_t* out_ids, int B,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

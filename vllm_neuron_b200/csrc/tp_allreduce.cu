@@ -204,6 +204,56 @@ __global__ void __launch_bounds__(AR_THREADS)
   }
 }
 
+// Greedy merge across the vocabulary shards of a tensor-parallel group (replaces two NCCL all-gathers plus a handful of
+// eager element-wise kernels per step): every rank's argmax kernel has written its local (max logit, GLOBAL index) pairs
+// into its symmetric region (vals [B] fp32, idxs [B] int64); this kernel signals "my pairs of this step are written",
+// waits for every peer's signal, pulls the `world` pairs of each row and keeps the largest value, ties to the lowest
+// index -- the single-GPU argmax rule, so every rank computes the same token.  Same flag discipline as the exchange above
+// (relaxed system-scope epoch flags; the pairs were written by the PREVIOUS kernel of the stream).  One buffer suffices:
+// a rank rewrites its pairs one full decode step later, with dozens of all-rank exchange barriers in between.
+struct MergePeers {
+  const float* vals[AR_MAX_TP];
+  const long long* idxs[AR_MAX_TP];
+  uint32_t* flags[AR_MAX_TP];  // [AR_MAX_TP] epochs per rank, written by the peers
+};
+__global__ void __launch_bounds__(128)
+    tp_argmax_merge_kernel(MergePeers peers, uint32_t* __restrict__ epoch, int rank, int world, long long* __restrict__ out_ids,
+                           int B) {
+  griddep_launch();
+  griddep_wait();
+  if ((int)threadIdx.x < world) {
+    const int peer = threadIdx.x;
+    const uint32_t e = epoch[0] + 1;
+    __syncwarp((1u << world) - 1u);
+    st_flag_sys(peers.flags[peer] + rank, e);
+    const uint32_t* mine = peers.flags[rank] + peer;
+    const long long t0 = clock64();
+    while ((int32_t)(ld_flag_sys(mine) - e) < 0) {
+      if (clock64() - t0 > 6000000000LL) {
+        printf("b200: argmax merge barrier timeout rank %d peer %d epoch %u\n", rank, peer, e);
+        __trap();
+      }
+    }
+    if (peer == 0) epoch[0] = e;
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    float best = -INFINITY;
+    long long bi = 0x7fffffffffffffffLL;
+    for (int p = 0; p < world; ++p) {
+      float v;
+      long long i;
+      asm volatile("ld.volatile.global.f32 %0, [%1];\n" : "=f"(v) : "l"(peers.vals[p] + b) : "memory");
+      asm volatile("ld.volatile.global.s64 %0, [%1];\n" : "=l"(i) : "l"(peers.idxs[p] + b) : "memory");
+      if (v > best || (v == best && i < bi)) {
+        best = v;
+        bi = i;
+      }
+    }
+    out_ids[b] = bi;
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -259,4 +309,23 @@ extern "C" int b200_allreduce_rmsnorm_nvls(const void* mc_buf, void* const* host
   B200_REQUIRE(mc_buf, "allreduce_rmsnorm_nvls: null multicast pointer");
   return allreduce_common(nullptr, host_peer_flags, mc_buf, epoch, rank, world, x_out, norm_w, out_bf16, out_q, out_scale, T,
                           H, eps, q_dtype, stream);
+}
+
+extern "C" int b200_tp_argmax_merge(const void* const* host_peer_vals, const void* const* host_peer_idxs,
+                                    void* const* host_peer_flags, uint32_t* epoch, int rank, int world, int64_t* out_ids,
+                                    int B, void* stream) {
+  B200_REQUIRE(host_peer_vals && host_peer_idxs && host_peer_flags && epoch && out_ids, "tp_argmax_merge: null pointer");
+  B200_REQUIRE(world >= 1 && world <= AR_MAX_TP && rank >= 0 && rank < world, "tp_argmax_merge: bad rank %d / world %d", rank,
+               world);
+  if (B <= 0) return B200_OK;
+  MergePeers peers{};
+  for (int p = 0; p < world; ++p) {
+    B200_REQUIRE(host_peer_vals[p] && host_peer_idxs[p] && host_peer_flags[p], "tp_argmax_merge: null peer pointer %d", p);
+    peers.vals[p] = (const float*)host_peer_vals[p];
+    peers.idxs[p] = (const long long*)host_peer_idxs[p];
+    peers.flags[p] = (uint32_t*)host_peer_flags[p];
+  }
+  B200_CUDA_OK(launch_kernel(tp_argmax_merge_kernel, dim3(1), dim3(128), 0, (cudaStream_t)stream, peers, epoch, rank, world,
+                             (long long*)out_ids, B));
+  return B200_OK;
 }

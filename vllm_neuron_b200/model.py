@@ -381,6 +381,11 @@ class B200CausalLM:
             ids = ops.sample_candidates(cv, ci, samp[0], samp[1])
         elif self.tp_size == 1:
             ids = ops.argmax(logits)
+        elif self.tp_comm is not None and logits.shape[0] <= self.tp_comm.rows:
+            # per-shard (max, global index) straight into peer-mapped memory, merged by our kernel: no NCCL in the step
+            ops.argmax(logits, idx_offset=self.vocab_offset, want_val=True, out_val=self.tp_comm.merge_vals,
+                       out_idx=self.tp_comm.merge_idxs)
+            ids = self.tp_comm.merge_argmax(logits.shape[0])
         else:
             val, idx = ops.argmax(logits, idx_offset=self.vocab_offset, want_val=True)
             vals = torch.empty((self.tp_size, val.numel()), dtype=val.dtype, device=val.device)

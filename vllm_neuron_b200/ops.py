@@ -449,15 +449,24 @@ def embedding(tokens, table, out=None):
     return out
 
 
-def argmax(logits, idx_offset: int = 0, want_val: bool = False):
+def argmax(logits, idx_offset: int = 0, want_val: bool = False, out_val=None, out_idx=None):
     _cuda(logits)
     t, v = logits.shape
     assert logits.dtype == torch.float32 and logits.stride(1) == 1
-    idx = torch.empty((t,), dtype=torch.int64, device=logits.device)
-    val = torch.empty((t,), dtype=torch.float32, device=logits.device) if want_val else None
+    idx = torch.empty((t,), dtype=torch.int64, device=logits.device) if out_idx is None else out_idx[:t]
+    val = (torch.empty((t,), dtype=torch.float32, device=logits.device) if out_val is None else out_val[:t]) if want_val else None
     with _k("argmax"):
         check(_cabi.load().b200_argmax(_ptr(logits), logits.stride(0), _ptr(val), _ptr(idx), t, v, idx_offset, _stream()), "b200_argmax")
     return (val, idx) if want_val else idx
+
+
+def tp_argmax_merge(peer_vals, peer_idxs, peer_flags, epoch, rank, world, b):
+    """Greedy merge of the per-shard (max, global index) pairs over peer memory (tp_comm.TpComm.merge_argmax)."""
+    out = torch.empty((b,), dtype=torch.int64, device=epoch.device)
+    with _k("tp_argmax_merge"):
+        check(_cabi.load().b200_tp_argmax_merge(peer_vals, peer_idxs, peer_flags, _ptr(epoch), rank, world, _ptr(out), b,
+                                                _stream()), "b200_tp_argmax_merge")
+    return out
 
 
 SAMPLE_K = 256  # candidates per (row, vocab shard); the reference's _MAX_NEURON_SAMPLING_TOP_K (RUNNER:74)

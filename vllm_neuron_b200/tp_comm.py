@@ -26,7 +26,11 @@ class TpComm:
         part_bytes = rows * hidden * 2
         part_bytes = (part_bytes + 255) // 256 * 256
         flag_bytes = rows * self.FLAG_SLOTS * 4
-        self._region = symm_mem.empty((2 * part_bytes + flag_bytes,), dtype=torch.uint8, device=device)
+        # tail of the region: the greedy-merge exchange -- [rows] fp32 maxima | [rows] int64 indices | [8] uint32 flags
+        flag_bytes = (flag_bytes + 255) // 256 * 256
+        merge_off = 2 * part_bytes + flag_bytes
+        merge_bytes = (rows * 4 + 255) // 256 * 256 + rows * 8 + 256
+        self._region = symm_mem.empty((merge_off + merge_bytes,), dtype=torch.uint8, device=device)
         self._region.zero_()
         self._hdl = symm_mem.rendezvous(self._region, group)
         base = [int(p) for p in self._hdl.buffer_ptrs]
@@ -45,6 +49,15 @@ class TpComm:
         self.nvls = bool(mc) and use_nvls and world > 1
         self._mc_bufs = [mc + i * part_bytes if self.nvls else 0 for i in range(2)]
         self.epoch = torch.zeros((rows,), dtype=torch.int32, device=device)
+        v_off = merge_off
+        i_off = v_off + (rows * 4 + 255) // 256 * 256
+        f_off = i_off + rows * 8
+        self.merge_vals = self._region[v_off: v_off + rows * 4].view(torch.float32)
+        self.merge_idxs = self._region[i_off: i_off + rows * 8].view(torch.int64)
+        self._peer_mvals = arr(*[b + v_off for b in base])
+        self._peer_midxs = arr(*[b + i_off for b in base])
+        self._peer_mflags = arr(*[b + f_off for b in base])
+        self.merge_epoch = torch.zeros((1,), dtype=torch.int32, device=device)
         self._next = 0
         torch.cuda.synchronize(device)
         self._hdl.barrier()  # every rank has zeroed its flags before anyone signals
@@ -53,6 +66,13 @@ class TpComm:
         """The buffer the next row-parallel GEMM must write ([t, hidden] view); alternates A / B."""
         i = self._next
         return i, self.partials[i][:t]
+
+    def merge_argmax(self, b: int):
+        """Global greedy tokens [b] from the (max, index) pairs every rank's argmax wrote into merge_vals / merge_idxs."""
+        from . import ops
+
+        return ops.tp_argmax_merge(self._peer_mvals, self._peer_midxs, self._peer_mflags, self.merge_epoch, self.rank,
+                                   self.world, b)
 
     def exchange(self, i: int, t: int, norm_w, eps: float, quant):
         from . import ops
