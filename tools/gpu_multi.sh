@@ -18,7 +18,7 @@ run() { # name, timeout, cmd...
   grep -v "Warn\|^\*\*\*\|OMP_NUM\|^$" gpurun_out/$name.err | tail -4
 }
 [ -z "$SKIP_STRESS" ] && run tp_check_tp$N 400 $TR --master-port 29541 tools/tp_check.py --stress
-run bench_8b_bf16_tp$N 400 $TR --master-port 29545 bench.py --gpus $N --quant bf16 --steps 16 --warmup 3 --e2e-steps 4 $L
+[ -z "$SKIP_BF16" ] && run bench_8b_bf16_tp$N 400 $TR --master-port 29545 bench.py --gpus $N --quant bf16 --steps 16 --warmup 3 --e2e-steps 4 $L
 run bench_8b_fp8_tp$N 400 $TR --master-port 29542 bench.py --gpus $N --steps 32 --warmup 5 --e2e-steps 16 $L
 run bench_cfg4_qwen32b_int8wo_b128_tp$N 500 $TR --master-port 29543 bench.py --gpus $N --model qwen2.5-32b --quant int8_wo --batch 128 --ctx 2048 --steps $ST --warmup 3 --e2e-steps 8 $L
 run bench_cfg5_llama70b_fp8_sweep_tp$N 900 $TR --master-port 29544 bench.py --gpus $N --model llama-3.3-70b --quant fp8 --batch 64 --sweep-ctx $SW --steps $ST --warmup 3 --e2e-steps 4 $L
