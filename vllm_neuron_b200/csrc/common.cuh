@@ -201,8 +201,8 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
     if (++spins > (1u << 24)) {
-      printf("b200: mbarrier timeout block=(%d,%d,%d) thread=%d parity=%u\n", blockIdx.x, blockIdx.y, blockIdx.z,
-             threadIdx.x, parity);
+      printf("b200: mbarrier timeout block=(%d,%d,%d) thread=%d parity=%u smem=0x%x\n", blockIdx.x, blockIdx.y, blockIdx.z,
+             threadIdx.x, parity, smem_u32(bar));
       __trap();
     }
   }

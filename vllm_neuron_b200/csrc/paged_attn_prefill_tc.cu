@@ -8,29 +8,27 @@
 // for prompts / chunks of >= 64 new tokens (shorter ones keep the mma.sync kernel in paged_attn.cu).
 //
 // CTA = one 128-row query tile of TWO query heads that share a kv head (GQA), so every K/V byte fetched from L2 feeds two
-// tiles; a K/V step is 64 tokens = two 32-token blocks gathered through the block table by TMA (128B swizzle) straight
+// tiles; a K/V step is 128 tokens = four 32-token blocks gathered through the block table by TMA (128B swizzle) straight
 // into UMMA operand layout:
 //   S_t = Q_t K^T   : tcgen05.mma kind::f16, A = Q_t (smem, K-major), B = K step (smem, K-major: token rows)   -> TMEM fp32
 //   P_t = softmax   : one thread per query row (no shuffles): tcgen05.ld S, row max, exp2, row sum, bf16 P written back with
 //                     tcgen05.st INTO the columns S_t occupied (P aliases S, as in FlashAttention-4)
 //   O_t += P_t V    : tcgen05.mma, A = P_t FROM TENSOR MEMORY, B = V step (smem, MN-major: the TMA tile is already
 //                     [token][d]) -> TMEM fp32, accumulated over the whole K/V loop
-// TMEM: [S0a S0b | S1a S1b | O0 | O1] = 4 x 128 columns: every tile has TWO 64-column score buffers, so the score MMA of
-// step j + 2 is issued right behind PV(j) and the softmax of a tile never waits for its next scores (v3 of this kernel
-// had one 128-column buffer per tile: its softmax warps spent 37 % of their time on that barrier,
-// profiles/r02_prefill_tc_ncu_v1.md).  The running maximum is "lazy": O and l are rescaled only when a row's maximum
+// TMEM: S0 | S1 | O0 | O1 = 4 x 128 columns.  The running maximum is "lazy": O and l are rescaled only when a row's maximum
 // grew by more than 8 (in log2 units), so exp2 arguments stay <= 8 and the O read-modify-write is rare.
 // Warp roles (384 threads; setmaxnreg gives the softmax warpgroups 224 registers, the third warpgroup 56): warps 0-3 softmax of tile 0, warps 4-7 softmax of tile 1 (warp w owns TMEM lanes 32*(w%4)..),
 // warp 8 = MMA issuer + TMEM owner (+ Q loads), warp 9 = K producer, warp 10 = V producer (two issuing warps: one thread
 // sustains ~1 TMA box row per 5.5 clk, profiles/r02_tma_ingest_v1.txt).
-// MMA issue order per step j:  PV0(j)  S0(j+2)  PV1(j)  S1(j+2).
+// MMA issue order per step j:  PV0(j)  S0(j+1)  PV1(j)  S1(j+1)  -- tile 0's softmax of step j+1 overlaps tile 1's PV and
+// softmax of step j, and the other way round.
 #include "common.cuh"
 
 namespace b200 {
 
 constexpr int PF_BM = 128;   // query rows per tile
-constexpr int PF_BN = 64;    // kv tokens per step (two 32-token blocks)
-constexpr int PF_ST = 4;     // K / V stages
+constexpr int PF_BN = 128;   // kv tokens per step
+constexpr int PF_ST = 2;     // K / V stages
 constexpr int PF_THREADS = 256 + 4 * 32;  // two softmax warpgroups + the MMA / producer warpgroup (its 4th warp idles)
 constexpr int PF_BLK = 32;   // pa_block_size
 
@@ -77,18 +75,16 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
                                  __nv_bfloat16* __restrict__ out, int S_new, int computed_len, int Hq, int Hkv,
                                  float scale_log2) {
   constexpr int NH = D / 64;                 // 64-element (128 B) halves of the head dimension
-  constexpr int QHALF = PF_BM * 128;         // one [128 query rows x 128 B] half of a Q tile = 16 KB
-  constexpr int QTILE = NH * QHALF;
-  constexpr int HALF = PF_BN * 128;          // one [64 tokens x 128 B] half of a K / V step = 8 KB
-  constexpr int TILE = NH * HALF;            // K step / V step
+  constexpr int HALF = PF_BN * 128;          // one [128 rows x 128 B] half tile = 16 KB
+  constexpr int TILE = NH * HALF;            // Q tile / K step / V step
   constexpr uint32_t IDESC_S = umma_idesc(1, 1, PF_BM, PF_BN);
   constexpr uint32_t IDESC_PV = umma_idesc(1, 1, PF_BM, D) | (1u << 16);  // B (= V) is MN-major
   constexpr uint32_t TMEM_COLS = 512;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* q_s = smem;                               // [2 tiles][QTILE]
-  uint8_t* k_s = q_s + 2 * QTILE;                    // [PF_ST][TILE]
+  uint8_t* q_s = smem;                               // [2 tiles][TILE]
+  uint8_t* k_s = q_s + 2 * TILE;                     // [PF_ST][TILE]
   uint8_t* v_s = k_s + PF_ST * TILE;                 // [PF_ST][TILE]
   uint64_t* bars = reinterpret_cast<uint64_t*>(v_s + PF_ST * TILE);
   uint64_t* q_full = bars;                           // 1
@@ -96,11 +92,10 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
   uint64_t* k_empty = k_full + PF_ST;
   uint64_t* v_full = k_empty + PF_ST;
   uint64_t* v_empty = v_full + PF_ST;
-  uint64_t* s_full = v_empty + PF_ST;                // 4: [tile][score buffer]
-  uint64_t* p_ready = s_full + 4;                    // 2
+  uint64_t* s_full = v_empty + PF_ST;                // 2 (per tile)
+  uint64_t* p_ready = s_full + 2;                    // 2
   uint64_t* o_full = p_ready + 2;                    // 2
-  uint64_t* o_quiet = o_full + 2;                    // 2: PV_t(j) retired (one phase per step)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_quiet + 2);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int G = Hq / Hkv, pairs = (G + 1) >> 1;
@@ -127,11 +122,9 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
       mbar_init(&v_empty[s], 1);
     }
     for (int t = 0; t < 2; ++t) {
-      mbar_init(&s_full[2 * t], 1);
-      mbar_init(&s_full[2 * t + 1], 1);
+      mbar_init(&s_full[t], 1);
       mbar_init(&p_ready[t], 4);  // one arrival per softmax warp of the tile
       mbar_init(&o_full[t], 1);
-      mbar_init(&o_quiet[t], 1);
     }
     fence_mbar_init();
     fence_proxy_async();
@@ -177,59 +170,51 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
   } else if (warp == 8) {
     // ---------------------------------------------------------------- MMA issuer
     if (lane == 0) {
-      mbar_expect_tx(q_full, (uint32_t)(ntile * QTILE));
+      mbar_expect_tx(q_full, (uint32_t)(ntile * TILE));
       for (int t = 0; t < ntile; ++t)
 #pragma unroll
         for (int h = 0; h < NH; ++h)
-          tma_load_2d(q_s + t * QTILE + h * QHALF, &q_map, q_full, (head0 + t) * D + h * 64, q0);
-      // S_t(j) = Q_t K_j^T into score buffer (j & 1) of tile t
-      auto issue_s = [&](int t, int j) {
-        const uint32_t qa = smem_u32(q_s + t * QTILE), ka = smem_u32(k_s + (size_t)(j % PF_ST) * TILE);
-        const uint32_t sd = tmem_base + (uint32_t)t * 128u + (uint32_t)(j & 1) * 64u;
+          tma_load_2d(q_s + t * TILE + h * HALF, &q_map, q_full, (head0 + t) * D + h * 64, q0);
+      auto issue_s = [&](int t, int s) {
+        const uint32_t qa = smem_u32(q_s + t * TILE), ka = smem_u32(k_s + (size_t)s * TILE);
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
-          const uint32_t hq = (uint32_t)(kk >> 2), off = (uint32_t)(kk & 3) * 32;
-          umma_ss<KIND_F16>(sd, umma_desc_sw128(qa + hq * QHALF + off), umma_desc_sw128(ka + hq * HALF + off), IDESC_S,
+          const uint32_t off = (uint32_t)(kk >> 2) * HALF + (uint32_t)(kk & 3) * 32;
+          umma_ss<KIND_F16>(tmem_base + (uint32_t)t * 128u, umma_desc_sw128(qa + off), umma_desc_sw128(ka + off), IDESC_S,
                             (uint32_t)(kk != 0));
         }
-        tc_commit(&s_full[2 * t + (j & 1)]);
+        tc_commit(&s_full[t]);
       };
-      // O_t += P_t(j) V_j; P_t(j) sits in the first 32 columns of score buffer (j & 1)
-      auto issue_pv = [&](int t, int j) {
-        const uint32_t va = smem_u32(v_s + (size_t)(j % PF_ST) * TILE);
-        const uint32_t pa = tmem_base + (uint32_t)t * 128u + (uint32_t)(j & 1) * 64u;
+      auto issue_pv = [&](int t, int s, int j) {
+        const uint32_t va = smem_u32(v_s + (size_t)s * TILE);
 #pragma unroll
         for (int kk = 0; kk < PF_BN / 16; ++kk)  // 16 tokens per UMMA_K: two 8-row groups of the [token][d] tile
-          umma_ts_f16(tmem_base + 256u + (uint32_t)t * 128u, pa + (uint32_t)kk * 8u,
+          umma_ts_f16(tmem_base + 256u + (uint32_t)t * 128u, tmem_base + (uint32_t)t * 128u + (uint32_t)kk * 8u,
                       umma_desc_mn_sw128(va + kk * 2048, HALF, 1024), IDESC_PV, (uint32_t)((j | kk) != 0));
       };
       mbar_wait(q_full, 0);
-      // the score MMAs run TWO steps ahead of the softmax (two score buffers per tile): S(0), S(1) now, S(j + 2) right
-      // behind PV(j), which is the last reader of the buffer it overwrites
-      for (int jj = 0; jj < 2 && jj < nsteps; ++jj) {
-        mbar_wait(&k_full[jj % PF_ST], (uint32_t)(jj / PF_ST) & 1u);
-        tc_fence_after();
-        for (int t = 0; t < ntile; ++t) issue_s(t, jj);
-        tc_commit(&k_empty[jj % PF_ST]);
-      }
+      mbar_wait(&k_full[0], 0);
+      tc_fence_after();
+      for (int t = 0; t < ntile; ++t) issue_s(t, 0);
+      tc_commit(&k_empty[0]);
       for (int j = 0; j < nsteps; ++j) {
-        const int s = j % PF_ST, jn = j + 2;
-        const bool more = jn < nsteps;
+        const int s = j % PF_ST, sn = (j + 1) % PF_ST;
+        const bool more = j + 1 < nsteps;
         mbar_wait(&v_full[s], (uint32_t)(j / PF_ST) & 1u);
         for (int t = 0; t < ntile; ++t) {
           mbar_wait(&p_ready[t], (uint32_t)j & 1u);
           tc_fence_after();
-          issue_pv(t, j);
-          tc_commit(&o_quiet[t]);
+          issue_pv(t, s, j);
           if (t == ntile - 1) tc_commit(&v_empty[s]);
-          if (j == nsteps - 1) tc_commit(&o_full[t]);
           if (more) {
             if (t == 0) {
-              mbar_wait(&k_full[jn % PF_ST], (uint32_t)(jn / PF_ST) & 1u);
+              mbar_wait(&k_full[sn], (uint32_t)((j + 1) / PF_ST) & 1u);
               tc_fence_after();
             }
-            issue_s(t, jn);
-            if (t == ntile - 1) tc_commit(&k_empty[jn % PF_ST]);
+            issue_s(t, sn);
+            if (t == ntile - 1) tc_commit(&k_empty[sn]);
+          } else {
+            tc_commit(&o_full[t]);
           }
         }
       }
@@ -243,21 +228,22 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
     const int t = warp >> 2;
     const int row = (warp & 3) * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
-    const uint32_t s_tile = lane_base + (uint32_t)t * 128u;        // two 64-column score buffers; P over the first 32 of each
+    const uint32_t s_addr = lane_base + (uint32_t)t * 128u;        // S_t, and P_t over its first 64 columns
     const uint32_t o_addr = lane_base + 256u + (uint32_t)t * 128u;
     const int qpos = computed_len + q0 + row;
     float m_used = -INFINITY, l = 0.f;
     for (int j = 0; j < nsteps; ++j) {
-      mbar_wait(&s_full[2 * t + (j & 1)], (uint32_t)(j >> 1) & 1u);
+      mbar_wait(&s_full[t], (uint32_t)j & 1u);
       tc_fence_after();
-      const uint32_t s_addr = s_tile + (uint32_t)(j & 1) * 64u;
       const int k0 = j * PF_BN;
       const bool masked = k0 + PF_BN - 1 > computed_len + q0;  // some key of this step lies above some row's diagonal
-      // the whole score row of the step lives in registers: ONE pass over tensor memory, straight-line code after it
+      // the whole score row lives in registers: ONE pass over tensor memory, straight-line code after it
       uint32_t sv[PF_BN];
       auto load_scores = [&]() {
         tmem_ld_32x32b_x32(s_addr, *reinterpret_cast<uint32_t(*)[32]>(&sv[0]));
         tmem_ld_32x32b_x32(s_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&sv[32]));
+        tmem_ld_32x32b_x32(s_addr + 64, *reinterpret_cast<uint32_t(*)[32]>(&sv[64]));
+        tmem_ld_32x32b_x32(s_addr + 96, *reinterpret_cast<uint32_t(*)[32]>(&sv[96]));
         tmem_ld_wait();
         if (masked) {  // keys above the diagonal (and whatever stale bits a block past the sequence holds) -> -inf
 #pragma unroll
@@ -282,11 +268,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
         const float alpha = grow ? ex2_approx(m_used - m_new) : 1.f;  // m_used = -inf -> 0
         if (grow) m_used = m_new;
         l *= alpha;
-        if (j > 0) {
-          // O_t must be quiescent: the score MMAs run two steps ahead, so s_full(j) says nothing about PV_t(j - 1);
-          // o_quiet completes one phase per retired PV of this tile (PV_t(j) cannot be issued before our p_ready)
-          mbar_wait(&o_quiet[t], (uint32_t)(j - 1) & 1u);
-          tc_fence_after();
+        if (j > 0) {  // rare after the first steps: the score registers are given up for the O tile and loaded again
 #pragma unroll 1
           for (int c = 0; c < D / 32; ++c) {
             uint32_t v[32];
@@ -297,9 +279,10 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
             tmem_st_32x32b_x32(o_addr + c * 32, v);
           }
           tmem_st_wait();
+          load_scores();
         }
       }
-      // p = 2^(s*scale - m), row sum on four independent chains, bf16 P over the first 32 columns of the score buffer
+      // p = 2^(s*scale - m), row sum on four independent chains, bf16 P over the first 64 columns S occupied
       float l4[4] = {0.f, 0.f, 0.f, 0.f};
       const float neg_m = -m_used;
       uint32_t pk[PF_BN / 2];
@@ -318,6 +301,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1)
       }
       l += (l4[0] + l4[1]) + (l4[2] + l4[3]);
       tmem_st_32x32b_x32(s_addr, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+      tmem_st_32x32b_x32(s_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -357,7 +341,7 @@ template <int D>
 static int launch_tc(const CUtensorMap& km, const CUtensorMap& vm, const CUtensorMap& qm, const int32_t* bt_row, void* out,
                      int S_new, int computed_len, int Hq, int Hkv, float scale, cudaStream_t stream) {
   auto kern = paged_attn_prefill_tc_kernel<D>;
-  constexpr size_t smem = (size_t)(D / 64) * (2 * PF_BM + 2 * PF_ST * PF_BN) * 128 + 256 + 1024;
+  constexpr size_t smem = (size_t)(2 + 2 * PF_ST) * (D / 64) * PF_BN * 128 + 256 + 1024;
   static bool attr_done = false;
   if (!attr_done) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
