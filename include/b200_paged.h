@@ -158,6 +158,15 @@ int b200_gemm_int8_wo(const void* a_bf16, const void* w_int8, void* out, const f
 int b200_gemm_silu_mul(const void* a, const void* w_gu, void* out_act, const float* a_scale, const float* w_scale,
                        const void* bias, float* group_amax, int M, int N2, int K, int ab_dtype, int split_k,
                        void* workspace, size_t workspace_bytes, void* stream);
+/* The same gate/up GEMM + SiLU*mul with the dynamic per-token quantisation of its result (the down_proj input) done in the
+ * SAME launch: out_q [M][N2/2] e4m3 / int8, out_scale [M].  The CTAs agree on each token's amax through a grid-wide
+ * barrier; `state` is 1040 bytes of device memory, zero-initialised ONCE and then owned by the library (any number of
+ * launches on one stream).  Bit-identical to b200_gemm_silu_mul + b200_quantize_per_token.  Decode schedule only:
+ * returns B200_ERR_UNSUPPORTED (nothing launched) when M > 128 or when the shape does not run as one resident wave of
+ * one CTA per weight tile -- the caller then uses the two-call form. */
+int b200_gemm_silu_mul_quant(const void* a, const void* w_gu, void* out_q, float* out_scale, const float* a_scale,
+                             const float* w_scale, const void* bias, void* state, int M, int N2, int K, int ab_dtype,
+                             void* stream);
 
 /* qkv projection with RoPE and the KV-cache write fused into its epilogue: b200_gemm (bf16 out, no residual) followed by
  * b200_rope_kv_write on its output, in ONE launch when the decode schedule splits K over a cluster (the token's owner

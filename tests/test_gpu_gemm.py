@@ -255,3 +255,30 @@ def test_gemm_rope_kv_write_matches_two_launches(ops, kind, m, hq, hkv, d, k, sp
     assert torch.equal(got.view(torch.int16), ref.view(torch.int16))
     assert torch.equal(kp2.view(torch.int16), kp1.view(torch.int16)) and torch.equal(vp2.view(torch.int16), vp1.view(torch.int16))
     assert kp1.abs().sum().item() > 0 and (kp2[0] == 0).all()
+
+
+@pytest.mark.parametrize("kind", ["fp8", "int8"])
+@pytest.mark.parametrize("m,i,k", [(64, 14336, 4096), (1, 512, 256), (33, 1792, 512), (128, 3584, 1024), (17, 7168, 2048)])
+def test_gemm_silu_mul_quant_fused_equals_two_calls(ops, kind, m, i, k):
+    """b200_gemm_silu_mul_quant (SiLU*mul + per-token quantisation inside the gate/up GEMM, CTAs meeting at a grid barrier)
+    == b200_gemm_silu_mul + b200_quantize_per_token, bit for bit, launch after launch on the same state buffer."""
+    g = torch.Generator().manual_seed(m * 7 + i)
+    x = (torch.randn(m, k, generator=g) * 0.7).bfloat16()
+    w = (torch.randn(2 * i, k, generator=g) * 0.05).bfloat16()
+    xq, xs = quant_ref.quantize_act_per_token(x, kind)
+    wq, ws = quant_ref.quantize_weight_per_channel(w, kind)
+    wi, si = ops.interleave_gate_up(wq.cuda(), ws.cuda())
+    state = torch.zeros(1040, dtype=torch.uint8, device="cuda")
+    act, gam = ops.gemm_silu_mul(xq.cuda(), wi, xs.cuda(), si)
+    want_q, want_s = ops.quantize_per_token(act, kind, group_amax=gam)
+    for rep in range(3):  # the state carries over: the epoch-tagged maxima of earlier launches must never leak
+        xin = xq.cuda() if rep != 1 else torch.zeros_like(xq).cuda()
+        got = ops.gemm_silu_mul_quant(xin, wi, xs.cuda(), si, None, state, kind)
+        if got is None:
+            pytest.skip("shape does not run as one resident wave")
+        torch.cuda.synchronize()
+        if rep == 1:
+            assert torch.all(got[1] == 1.0) and torch.all(got[0].view(torch.uint8).int() % 128 == 0)  # all-zero rows: scale 1
+            continue
+        assert torch.equal(got[1], want_s)
+        assert torch.equal(got[0].view(torch.uint8), want_q.view(torch.uint8))

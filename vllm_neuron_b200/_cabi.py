@@ -59,6 +59,7 @@ SIGNATURES = {
     "b200_row_lse": (_i, [_p, _i64, _p, _p, _i, _i, _p]),
     "b200_gather_logprobs": (_i, [_p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _p]),
     "b200_allreduce_rmsnorm": (_i, [_p, _p, _p, _i, _i, _p, _p, _p, _p, _p, _i, _i, _f, _i, _p]),
+    "b200_gemm_silu_mul_quant": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p]),
     "b200_tp_argmax_merge": (_i, [_p, _p, _p, _p, _i, _i, _p, _i, _p]),
     "b200_allreduce_rmsnorm_nvls": (_i, [_p, _p, _p, _i, _i, _p, _p, _p, _p, _p, _i, _i, _f, _i, _p]),
 }

@@ -94,7 +94,9 @@ __device__ __forceinline__ void widen_w_tile(const uint8_t* __restrict__ raw, ui
 
 // EPI_ROPE: EPI_LINEAR whose split-K owner epilogue also rotates q/k and scatters k/v (decode kernel, S > 1 only); its own
 // instantiation so the plain linears keep their register budget (80 vs 137)
-enum { EPI_LINEAR = 0, EPI_SILU_MUL = 1, EPI_ROPE = 2 };
+// EPI_SILU_QUANT: EPI_SILU_MUL whose CTAs also agree on the per-token amax through a grid-wide barrier and write the
+// quantised activation themselves (decode kernel, S == 1, all CTAs co-resident; b200_gemm_silu_mul_quant)
+enum { EPI_LINEAR = 0, EPI_SILU_MUL = 1, EPI_ROPE = 2, EPI_SILU_QUANT = 3 };
 
 struct GemmEpilogue {
   const float* a_scale;
@@ -104,6 +106,11 @@ struct GemmEpilogue {
   void* out;
   int out_f32;
   float* group_amax;  // EPI_SILU_MUL: [M][N/32] max |act| over the 16 channels of each interleaved row group
+  // EPI_SILU_QUANT: `out` is the quantised activation [M][N/2] (one byte per element), out_scale [M] its per-token scale;
+  // fq_state = { uint64 tok_amax[128] (epoch << 32 | float bits), uint32 arrive counter, uint32 epoch }: zero once, then
+  // self-maintaining (the epoch only grows, so stale maxima of earlier launches always lose the 64-bit atomicMax)
+  float* out_scale;
+  unsigned long long* fq_state;
   // EPI_ROPE (decode kernel with a split-K cluster only; b200_gemm_rope_kv_write): the output row is a packed qkv row
   // [Hq*D | Hkv*D | Hkv*D]; the token's owner rotates q and k (rotate-half, same roundings as rope_kv_write_kernel)
   // and scatters k, v into the block-KV pools by slot.
@@ -965,7 +972,103 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? WO_THREADS : DEC_THREADS, K
     tc_fence_after();
     if (et == 0) B200_STAMP(3);
     const uint32_t acc = tmem_base + ((uint32_t)(lg * 32) << 16);
-    if (S == 1) {
+    if constexpr (EPI == EPI_SILU_QUANT) {
+      // ---- gate/up GEMM + SiLU*mul + dynamic per-token quantisation in ONE kernel (host guarantees S == 1 and that the
+      // whole grid is resident).  Every lane keeps its 8 activations per 16-token chunk in registers; the CTAs agree on
+      // the per-token amax with one 64-bit atomicMax per token and a grid-wide barrier; then each lane quantises what it
+      // holds.  Same bits as b200_gemm_silu_mul + b200_quantize_per_token (max of the same bf16 values, same division).
+      constexpr int QD = KIND == KIND_I8 ? (int)B200_INT8 : (int)B200_FP8_E4M3;
+      unsigned long long* tok_amax = ep.fq_state;
+      unsigned int* bar_cnt = reinterpret_cast<unsigned int*>(ep.fq_state + 128);
+      unsigned int* bar_epoch = bar_cnt + 1;
+      unsigned int* s_amax = reinterpret_cast<unsigned int*>(smem);  // [BM] (+ the epoch at [BM]); the rings are dead
+      float* s_scale = reinterpret_cast<float*>(smem) + BM + 4;       // [BM]
+      const int n = n0 + nl;
+      const bool n_ok = n < N;
+      const int I = N >> 1;
+      const int ch = (n >> 5) * 16 + (lane & 15);
+      const bool hi = lane >= 16;
+      const bool hb = ep.bias != nullptr;
+      if (et < BM) s_amax[et] = 0u;
+      if (et == 0) s_amax[BM] = *reinterpret_cast<volatile unsigned int*>(bar_epoch);  // stable until THIS CTA has arrived
+      named_bar_sync(1, 128);
+      float areg[BM / 16][8];
+#pragma unroll
+      for (int cc = 0; cc < BM / 16; ++cc) {
+        uint32_t v[16];
+        tmem_ld_32x32b_x16(acc + cc * 16, v);
+        tmem_ld_wait();
+        float mine[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int m = cc * 16 + j;
+          const float a0 = KIND == KIND_I8 ? (float)(int32_t)v[j] : __uint_as_float(v[j]);
+          mine[j] = (m < M && n_ok)
+                        ? __bfloat162float(__float2bfloat16_rn(scaled_value(a0, a_s[m], w_sc, hb, bias_v, false, 0.f)))
+                        : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float send = hi ? mine[j] : mine[j + 8];
+          const float got = __shfl_xor_sync(0xffffffffu, send, 16);
+          const float a = silu_mul_bf16(hi ? got : mine[j], hi ? mine[j + 8] : got);
+          const int m = cc * 16 + (hi ? 8 : 0) + j;
+          const bool ok = m < M && n_ok;
+          areg[cc][j] = ok ? a : 0.f;
+          float x = ok ? fabsf(a) : 0.f;
+#pragma unroll
+          for (int o = 1; o < 16; o <<= 1) x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, o));
+          if ((lane & 15) == 0 && m < BM) atomicMax(&s_amax[m], __float_as_uint(x));  // x >= 0: uint order = float order
+        }
+      }
+      named_bar_sync(1, 128);
+      const unsigned int e0 = s_amax[BM];
+      if (et < M)
+        atomicMax(&tok_amax[et], ((unsigned long long)(e0 + 1u) << 32) | (unsigned long long)s_amax[et]);
+      __threadfence();
+      named_bar_sync(1, 128);
+      if (et == 0) {
+        const unsigned int old = atomicAdd(bar_cnt, 1u);
+        if (old == gridDim.x - 1) {
+          atomicExch(bar_cnt, 0u);
+          __threadfence();
+          atomicAdd(bar_epoch, 1u);
+        } else {
+          const long long t0 = clock64();
+          unsigned int e;
+          do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(e) : "l"(bar_epoch) : "memory");
+            if (clock64() - t0 > 4000000000LL) {  // ~2 s: a grid that is not fully resident must not hang the box
+              printf("b200: silu-quant grid barrier timeout block %d epoch %u\n", blockIdx.x, e0);
+              __trap();
+            }
+          } while (e == e0);
+        }
+        __threadfence();
+      }
+      named_bar_sync(1, 128);
+      if (et < BM) {
+        float sc = 1.f;
+        if (et < M) {
+          const unsigned long long tv = __ldcg(&tok_amax[et]);
+          const float amax = __uint_as_float((unsigned int)tv);
+          const float qmax = QD == B200_FP8_E4M3 ? 448.f : 127.f;
+          sc = amax > 0.f ? __fdiv_rn(amax, qmax) : 1.f;
+          if (blockIdx.x == 0) ep.out_scale[et] = sc;
+        }
+        s_scale[et] = sc;
+      }
+      named_bar_sync(1, 128);
+      uint8_t* oq = reinterpret_cast<uint8_t*>(ep.out);
+#pragma unroll
+      for (int cc = 0; cc < BM / 16; ++cc) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int m = cc * 16 + (hi ? 8 : 0) + j;
+          if (m < M && n_ok) oq[(int64_t)m * I + ch] = quant_byte<QD>(areg[cc][j], s_scale[m]);
+        }
+      }
+    } else if (S == 1) {
       const int n = n0 + nl;
 #pragma unroll 1
       for (int cc = 0; cc < BM / 16; ++cc) {
@@ -975,7 +1078,7 @@ __global__ void __launch_bounds__(KIND == KIND_WO8 ? WO_THREADS : DEC_THREADS, K
         float f[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) f[j] = KIND == KIND_I8 ? (float)(int32_t)v[j] : __uint_as_float(v[j]);
-        epilogue_chunk_staged<EPI == EPI_ROPE ? (int)EPI_LINEAR : EPI>(ep, f, cc * 16, M, n, n < N, N, lane, a_s, w_sc, bias_v,
+        epilogue_chunk_staged<(EPI == EPI_ROPE || EPI == EPI_SILU_QUANT) ? (int)EPI_LINEAR : EPI>(ep, f, cc * 16, M, n, n < N, N, lane, a_s, w_sc, bias_v,
                                                                         resid_s + nl, GEMM_BN);
       }
     } else {
@@ -1406,6 +1509,32 @@ int query_plan(DecodeCfg& c, int bm, int M, int n_tiles, int num_kb, int split_k
 }
 }  // namespace
 
+namespace {
+// gate/up GEMM + SiLU*mul + per-token quantisation in one launch (decode schedule, W8A8 kinds).  Returns
+// B200_ERR_UNSUPPORTED -- and the caller runs b200_gemm_silu_mul + b200_quantize_per_token -- unless the planner's own
+// choice for this shape is one CTA per weight tile (S == 1) with the whole grid resident at once: the CTAs meet at a
+// grid-wide barrier, which must never wait for a CTA that has not been scheduled.
+template <int KIND>
+static int launch_silu_quant(const CUtensorMap& wm, const CUtensorMap& am, const GemmEpilogue& ep, int M, int N,
+                             const GemmPlan& p, cudaStream_t s) {
+  DecodeCfg c;
+  int rc = p.bm == 32   ? plan_decode<KIND, 32, EPI_SILU_QUANT>(c, M, p.n_tiles, p.num_kb, 0, false)
+           : p.bm == 64 ? plan_decode<KIND, 64, EPI_SILU_QUANT>(c, M, p.n_tiles, p.num_kb, 0, false)
+                        : plan_decode<KIND, 128, EPI_SILU_QUANT>(c, M, p.n_tiles, p.num_kb, 0, false);
+  if (rc) return rc;
+  const int per_sm = c.smem > SMEM_TWO_PER_SM ? 1 : 2;
+  if (c.S != 1 || p.n_tiles > c.cap_ctas * per_sm) {
+    set_last_error("gemm_silu_mul_quant: plan S=%d, %d tiles, capacity %d: not one resident wave", c.S, p.n_tiles,
+                   c.cap_ctas * per_sm);
+    return B200_ERR_UNSUPPORTED;
+  }
+  if (p.bm == 32) return launch_decode<KIND, 32, EPI_SILU_QUANT>(wm, am, ep, M, N, p, 0, s);
+  if (p.bm == 64) return launch_decode<KIND, 64, EPI_SILU_QUANT>(wm, am, ep, M, N, p, 0, s);
+  return launch_decode<KIND, 128, EPI_SILU_QUANT>(wm, am, ep, M, N, p, 0, s);
+}
+
+}  // namespace
+
 extern "C" {
 
 void b200_gemm_set_trace(void* buf) { g_trace = (unsigned long long*)buf; }
@@ -1495,6 +1624,31 @@ int b200_gemm_int8_wo(const void* a_bf16, const void* w_int8, void* out, const f
                       size_t workspace_bytes, void* stream) {
   return b200_gemm(a_bf16, w_int8, out, nullptr, w_scale, bias, residual, M, N, K, B200_INT8_WO, out_dtype, split_k, workspace,
                    workspace_bytes, stream);
+}
+
+int b200_gemm_silu_mul_quant(const void* a, const void* w_gu, void* out_q, float* out_scale, const float* a_scale,
+                             const float* w_scale, const void* bias, void* state, int M, int N2, int K, int ab_dtype,
+                             void* stream) {
+  B200_REQUIRE(a && w_gu && out_q && out_scale && a_scale && w_scale && state, "gemm_silu_mul_quant: null pointer");
+  B200_REQUIRE(ab_dtype == B200_FP8_E4M3 || ab_dtype == B200_INT8, "gemm_silu_mul_quant: W8A8 dtypes only (got %d)", ab_dtype);
+  B200_REQUIRE(N2 % 32 == 0 && M > 0 && K > 0 && K % 16 == 0, "gemm_silu_mul_quant: bad shape M=%d N2=%d K=%d", M, N2, K);
+  if (M > 128) {
+    set_last_error("gemm_silu_mul_quant: decode schedule only (M <= 128), got %d", M);
+    return B200_ERR_UNSUPPORTED;
+  }
+  GemmPlan p;
+  int rc = plan_gemm(p, M, N2, K, ab_dtype, 0);
+  if (rc) return rc;
+  GemmEpilogue ep{a_scale, w_scale, (const __nv_bfloat16*)bias, nullptr, out_q, 0, nullptr, out_scale,
+                  (unsigned long long*)state};
+  CUtensorMap wm, am;
+  rc = make_tmap_2d(&wm, w_gu, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)K, (uint64_t)N2, (uint64_t)K, GEMM_BK_BYTES, GEMM_BN);
+  if (rc) return rc;
+  rc = make_tmap_2d(&am, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)K, (uint64_t)M, (uint64_t)K, GEMM_BK_BYTES, p.bm);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (ab_dtype == B200_FP8_E4M3) return launch_silu_quant<KIND_F8F6F4>(wm, am, ep, M, N2, p, s);
+  return launch_silu_quant<KIND_I8>(wm, am, ep, M, N2, p, s);
 }
 
 int b200_gemm_silu_mul(const void* a, const void* w_gu, void* out_act, const float* a_scale, const float* w_scale,

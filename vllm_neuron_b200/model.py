@@ -267,6 +267,10 @@ class B200CausalLM:
         self._prefill_meta = None
         self.last_logprobs = None
         self._alloc_workspaces()
+        # state of the fused gate/up + quantise kernel (token maxima, grid-barrier counter and epoch): zeroed once
+        self._fq_state = torch.zeros(1040, dtype=torch.uint8, device=dev)
+        import os as _os
+        self._fuse_silu_quant = _os.environ.get("B200_NO_SILU_QUANT_FUSION") is None
         # TP exchange over NVLink peer memory (our kernel); NCCL stays for prefill-sized batches and the greedy merge
         self.tp_comm = None
         if tp_size > 1 and use_peer_exchange:
@@ -346,11 +350,18 @@ class B200CausalLM:
             x, h2, h2s = self._row_parallel(L["o"], a[0], a[1], x, L["post_norm"])
             gu = L["gu"]
             # gate/up GEMM with SiLU(gate)*up in the epilogue; the per-group maxima feed the per-token quantisation
-            act, group_amax = ops.gemm_silu_mul(h2, gu.w, h2s, gu.scale, gu.bias, workspace=self.gemm_ws)
-            if q is None:
-                aq, a_s = act, None
+            fused = None
+            if q is not None and t <= 128 and self._fuse_silu_quant:
+                # decode-sized batches: SiLU*mul AND the per-token quantisation of its result in the GEMM's own launch
+                fused = ops.gemm_silu_mul_quant(h2, gu.w, h2s, gu.scale, gu.bias, self._fq_state, q)
+            if fused is not None:
+                aq, a_s = fused
             else:
-                aq, a_s = ops.quantize_per_token(act, q, group_amax=group_amax)
+                act, group_amax = ops.gemm_silu_mul(h2, gu.w, h2s, gu.scale, gu.bias, workspace=self.gemm_ws)
+                if q is None:
+                    aq, a_s = act, None
+                else:
+                    aq, a_s = ops.quantize_per_token(act, q, group_amax=group_amax)
             nxt = self.layers[li + 1]["input_norm"] if li + 1 < n_layers else None
             x, h, hs = self._row_parallel(L["down"], aq, a_s, x, nxt)
         return x

@@ -381,6 +381,32 @@ def gemm_silu_mul(a, w_gu_interleaved, a_scale=None, w_scale=None, bias=None, sp
     return act, group_amax
 
 
+_UNSUPPORTED = -4  # B200_ERR_UNSUPPORTED
+
+
+def gemm_silu_mul_quant(a, w_gu_interleaved, a_scale, w_scale, bias, state, quant: str):
+    """gate/up GEMM + SiLU*mul + per-token quantisation in ONE launch (b200_gemm_silu_mul_quant): returns (q [M, I], scale [M])
+    or None when the shape does not run as one resident wave of one CTA per weight tile (the caller then uses gemm_silu_mul
+    + quantize_per_token, which produce the same bits).  `state`: 1040-byte uint8 device tensor, zeroed once."""
+    _cuda(a, w_gu_interleaved, a_scale, w_scale, bias, state)
+    m, k = a.shape
+    n2, k2 = w_gu_interleaved.shape
+    assert k == k2 and a.is_contiguous() and w_gu_interleaved.is_contiguous() and n2 % 32 == 0 and state.numel() >= 1040
+    if m > 128:
+        return None
+    dt = _gemm_dtype(a, w_gu_interleaved)
+    qd = _QDT[quant]
+    q = torch.empty((m, n2 // 2), dtype=_TORCH_Q[qd], device=a.device)
+    sc = torch.empty((m,), dtype=torch.float32, device=a.device)
+    with _k(f"gemm_silu_mul_quant_{_DTN[dt]}[{m}x{n2}x{k}]"):
+        rc = _cabi.load().b200_gemm_silu_mul_quant(_ptr(a), _ptr(w_gu_interleaved), _ptr(q), _ptr(sc), _ptr(a_scale), _ptr(w_scale),
+                                                   _ptr(bias), _ptr(state), m, n2, k, dt, _stream())
+    if rc == _UNSUPPORTED:
+        return None
+    check(rc, "b200_gemm_silu_mul_quant")
+    return q, sc
+
+
 # ------------------------------------------------------------------ glue
 def rmsnorm(x, w, eps, quant=None, out_bf16=None, want_bf16=None):
     """Returns bf16 y, or (q, scale) for quant in {"fp8","int8"} (plus y when want_bf16)."""
