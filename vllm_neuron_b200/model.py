@@ -267,10 +267,13 @@ class B200CausalLM:
         self._prefill_meta = None
         self.last_logprobs = None
         self._alloc_workspaces()
-        # state of the fused gate/up + quantise kernel (token maxima, grid-barrier counter and epoch): zeroed once
+        # state of the fused gate/up + quantise kernel (token maxima, grid-barrier counter and epoch): zeroed once.
+        # OFF by default: measured on the headline workload the one-launch form is SLOWER (5.83 vs 5.58 ms per step) --
+        # CTAs that wait at the grid barrier keep their SM slots, so the down_proj GEMM can no longer become resident and
+        # prefetch its weights while the gate/up GEMM drains (profiles/r02_summary_v1.md).  B200_SILU_QUANT_FUSION=1 enables.
         self._fq_state = torch.zeros(1040, dtype=torch.uint8, device=dev)
         import os as _os
-        self._fuse_silu_quant = _os.environ.get("B200_NO_SILU_QUANT_FUSION") is None
+        self._fuse_silu_quant = _os.environ.get("B200_SILU_QUANT_FUSION") == "1"
         # TP exchange over NVLink peer memory (our kernel); NCCL stays for prefill-sized batches and the greedy merge
         self.tp_comm = None
         if tp_size > 1 and use_peer_exchange:
