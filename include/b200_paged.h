@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 7
+#define B200_ABI_VERSION 8
 
 enum {
   B200_OK = 0,
@@ -112,6 +112,32 @@ int b200_paged_attn_decode(const void* q, int64_t q_token_stride, const void* k_
                            const int32_t* ctx_lens, void* out, void* out_q, float* out_scale, int q_dtype, void* workspace,
                            size_t workspace_bytes, int B, int Hq, int Hkv, int D, int block_size, int max_blocks,
                            int min_quota, float scale, void* stream);
+/* Decode attention for callers that cannot allocate device memory.  (No counterpart in the reference: NxDI owns all of
+ * its device buffers, so vllm-neuron never faces the question.)
+ * b200_paged_attn_decode wants a workspace for its flash-decoding partials.  Not every caller can produce one: a binding
+ * from a language runtime that may only pass along tensors its framework already holds, a plugin loaded into a serving
+ * process after the device-memory budget was handed out (vLLM gives what is left after the weights to the KV pool), or
+ * any host that is not allowed to call cudaMalloc.  This variant takes the same inputs and outputs but no workspace: the
+ * partials go into an array of B200_DECODE_STATIC_SCRATCH_BYTES that is part of the library image, so EVERY GPU that loads
+ * the library gives up that much memory until the process exits, whether or not this entry point is ever called.
+ *   - Limit: a shape whose b200_paged_attn_decode_workspace_bytes(...) exceeds the array is refused with
+ *     B200_ERR_WORKSPACE (the message gives both numbers) and nothing is launched.  The headline shape (B=64, Hq=32,
+ *     Hkv=8, D=128, 64 blocks per sequence) needs 18.1 MB; a larger min_quota shrinks the need.
+ *   - It calls no cudaMalloc / cudaFree and no allocating library routine, and does not synchronise.
+ *   - First call on each device: the library looks up the array's device address (cudaGetSymbolAddress, with that device
+ *     current) and keeps it.  Make that first call on every device you use BEFORE you start capturing a stream.
+ *   - There is ONE array per device and every call uses it.  Two calls that can overlap on the same GPU (different
+ *     streams, or different host threads feeding different streams) corrupt each other's partials; keep them on one
+ *     stream or order them with events.  The array keeps whatever the last call left there; nothing in it needs to be
+ *     zero, the kernels overwrite every entry they later read.
+ * Results are bit-identical to b200_paged_attn_decode with the same arguments. */
+#define B200_DECODE_STATIC_SCRATCH_BYTES (32u << 20)
+size_t b200_paged_attn_decode_static_max_bytes(void);
+int b200_paged_attn_decode_static(const void* q, int64_t q_token_stride, const void* k_pool, const void* v_pool,
+                                  int num_blocks, const int32_t* block_table, int64_t bt_row_stride, const int32_t* row_ids,
+                                  const int32_t* ctx_lens, void* out, void* out_q, float* out_scale, int q_dtype, int B,
+                                  int Hq, int Hkv, int D, int block_size, int max_blocks, int min_quota, float scale,
+                                  void* stream);
 /* Prefix-cached prefill, one sequence: queries for absolute positions computed_len .. computed_len+S_new-1,
  * causal over cached prefix + new tokens, all K/V already in the pools. */
 int b200_paged_attn_prefill(const void* q, int64_t q_token_stride, const void* k_pool, const void* v_pool, int num_blocks,

@@ -34,7 +34,7 @@ def test_header_and_binding_agree(lib):
 
 def test_abi_version(lib):
     from vllm_neuron_b200 import _cabi
-    assert lib.b200_abi_version() == _cabi.ABI_VERSION == 7
+    assert lib.b200_abi_version() == _cabi.ABI_VERSION == 8
 
 
 def test_no_device_is_an_error_not_a_fallback(lib):

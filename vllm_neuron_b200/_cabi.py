@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200_paged.so")
 
 OK = 0
-ABI_VERSION = 7
+ABI_VERSION = 8
 BF16, FP8_E4M3, INT8, F32 = 0, 1, 2, 3
 
 _p = C.c_void_p
@@ -39,6 +39,11 @@ SIGNATURES = {
     "b200_paged_attn_decode": (
         _i,
         [_p, _i64, _p, _p, _i, _p, _i64, _p, _p, _p, _p, _p, _i, _p, _sz, _i, _i, _i, _i, _i, _i, _i, _f, _p],
+    ),
+    "b200_paged_attn_decode_static_max_bytes": (_sz, []),
+    "b200_paged_attn_decode_static": (
+        _i,
+        [_p, _i64, _p, _p, _i, _p, _i64, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _f, _p],
     ),
     "b200_paged_attn_prefill": (_i, [_p, _i64, _p, _p, _i, _p, _p, _i, _i, _i, _i, _i, _i, _f, _p]),
     "b200_gemm_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),

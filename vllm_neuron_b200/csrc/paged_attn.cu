@@ -791,3 +791,77 @@ int b200_paged_attn_prefill(const void* q, int64_t q_token_stride, const void* k
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------- decode attention for callers that cannot allocate
+// The flash-decoding partials normally live in a caller-supplied workspace.  Some hosts have no way to get one: a
+// foreign-language binding that can only hand over the tensors its framework already owns, a plugin running inside a
+// serving process whose device-memory budget was fixed (and fully claimed by the KV pool) before the plugin was loaded,
+// or code that runs where cudaMalloc is forbidden.  For them the partials go into the array below, which belongs to the
+// loaded library image: every GPU that loads libb200_paged.so carries these bytes until the process exits.
+constexpr size_t DECODE_STATIC_BYTES = (size_t)B200_DECODE_STATIC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_decode_static_scratch[DECODE_STATIC_BYTES];
+
+namespace {
+constexpr int STATIC_MAX_DEVICES = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[STATIC_MAX_DEVICES] = {};  // device address of g_decode_static_scratch, per device ordinal
+
+// In host code `g_decode_static_scratch` is only a handle for the runtime's symbol table, not memory a kernel can touch:
+// ask the runtime for the array's address on the CURRENT device (each device has its own copy), once per device.
+int static_scratch_for_current_device(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0) {
+    (void)cudaGetLastError();
+    set_last_error("paged_attn_decode_static: no current CUDA device (%s)", cudaGetErrorString(e));
+    return B200_ERR_NO_DEVICE;
+  }
+  B200_REQUIRE(dev < STATIC_MAX_DEVICES, "paged_attn_decode_static: device ordinal %d >= %d", dev, STATIC_MAX_DEVICES);
+  std::lock_guard<std::mutex> g(g_static_mu);
+  if (!g_static_ptr[dev]) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_decode_static_scratch);
+    if (e != cudaSuccess || !ptr) {
+      (void)cudaGetLastError();
+      set_last_error("paged_attn_decode_static: cudaGetSymbolAddress failed on device %d (%s)", dev, cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : B200_ERR_DRIVER;
+    }
+    g_static_ptr[dev] = ptr;
+  }
+  *out = g_static_ptr[dev];
+  return B200_OK;
+}
+}  // namespace
+
+extern "C" {
+
+size_t b200_paged_attn_decode_static_max_bytes(void) { return DECODE_STATIC_BYTES; }
+
+int b200_paged_attn_decode_static(const void* q, int64_t q_token_stride, const void* k_pool, const void* v_pool,
+                                  int num_blocks, const int32_t* block_table, int64_t bt_row_stride, const int32_t* row_ids,
+                                  const int32_t* ctx_lens, void* out, void* out_q, float* out_scale, int q_dtype, int B,
+                                  int Hq, int Hkv, int D, int block_size, int max_blocks, int min_quota, float scale,
+                                  void* stream) {
+  // the size check needs no device, so an oversized shape is refused the same way on every machine
+  if (B > 0 && Hq > 0 && Hkv > 0 && D > 0 && max_blocks > 0) {
+    const size_t need = plan_decode(B, Hq, Hkv, D, max_blocks, min_quota).ws_bytes;
+    if (need > DECODE_STATIC_BYTES) {
+      set_last_error(
+          "paged_attn_decode_static: this shape needs %zu bytes of scratch but the built-in array holds %zu "
+          "(B200_DECODE_STATIC_SCRATCH_BYTES); raise min_quota, split the batch, or use b200_paged_attn_decode with "
+          "your own workspace",
+          need, DECODE_STATIC_BYTES);
+      return B200_ERR_WORKSPACE;
+    }
+  }
+  void* scratch = nullptr;
+  int rc = static_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  // Nothing in the scratch has to start at zero: the decode kernel writes every partial and every part count that the merge
+  // kernel reads for this call's shapes, and entries left over from earlier calls lie beyond those counts.
+  return b200_paged_attn_decode(q, q_token_stride, k_pool, v_pool, num_blocks, block_table, bt_row_stride, row_ids, ctx_lens,
+                                out, out_q, out_scale, q_dtype, scratch, DECODE_STATIC_BYTES, B, Hq, Hkv, D, block_size,
+                                max_blocks, min_quota, scale, stream);
+}
+
+}  // extern "C"
