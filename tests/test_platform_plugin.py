@@ -153,3 +153,29 @@ def test_device_communicator_class_resolves(platform):
     mod, _, name = platform.get_device_communicator_cls().rpartition(".")
     cls = getattr(importlib.import_module(mod), name)
     assert hasattr(cls, "all_reduce") and hasattr(cls, "all_gather")
+
+
+def test_validate_request_refuses_what_the_device_sampler_lacks(platform):
+    """vLLM's input processor calls Platform.validate_request(processed_inputs, params) per request in the front end:
+    the place where a ValueError reaches one client instead of the engine core."""
+    from vllm import SamplingParams
+    from vllm.pooling_params import PoolingParams
+
+    platform.validate_request({}, SamplingParams(temperature=0.8, top_k=40, top_p=0.9, seed=1, logprobs=5, min_tokens=2))
+    platform.validate_request({}, SamplingParams())
+    platform.validate_request({}, PoolingParams())  # not a sampling request: nothing to say
+    for kw, word in (({"repetition_penalty": 1.1}, "repetition_penalty=1.1"), ({"presence_penalty": 0.5}, "presence_penalty"),
+                     ({"frequency_penalty": 0.5}, "frequency_penalty"), ({"min_p": 0.1}, "min_p"),
+                     ({"logit_bias": {3: 1.0}}, "logit_bias"), ({"allowed_token_ids": [1, 2]}, "allowed_token_ids"),
+                     ({"prompt_logprobs": 1}, "prompt_logprobs"), ({"logprobs": 300}, "logprobs=300")):
+        with pytest.raises(ValueError, match=word):
+            platform.validate_request({}, SamplingParams(**kw))
+
+
+def test_input_processor_reaches_the_platform_hook():
+    """The installed vLLM really calls the hook from its input processor (otherwise the refusal above is dead code)."""
+    import inspect
+
+    from vllm.v1.engine import input_processor
+
+    assert "current_platform.validate_request(" in inspect.getsource(input_processor)

@@ -106,3 +106,22 @@ def test_all_greedy_batch_takes_the_argmax_path_and_seeded_draws_repeat():
     assert rows[0] == (1.0, 1.0, 1.0) and rows[1] == (50.0, 0.9, 0.8) and u[0] == 0.0 and 0.0 <= u[1] < 1.0
     _, u2 = r._sampling_inputs([b])
     assert u2[0] == u[1]  # same SamplingParams.seed -> same stream of uniforms
+
+
+def test_unsupported_sampling_params_do_not_take_the_step_down(caplog):
+    """A worker exception ends every in-flight request (vLLM v1 engine core), so the runner must not raise on a request
+    whose parameters the device sampler lacks: it warns, keeps the row bookkeeping consistent and samples from
+    (top_k, top_p, temperature) alone, like the reference's device path (RUNNER:1106-1140).  Refusal happens at the front
+    end (tests/test_platform_plugin.py::test_validate_request_refuses_what_the_device_sampler_lacks)."""
+    import logging
+
+    from vllm import SamplingParams
+
+    r = _runner(mns=2)
+    so = sched_output(new_reqs=[("a", [1, 2, 3], [4], 0)])
+    so.scheduled_new_reqs[0].sampling_params = SamplingParams(repetition_penalty=1.1, logit_bias={5: 2.0}, temperature=0.7)
+    with caplog.at_level(logging.WARNING):
+        upd = r._update_states(so)
+    assert upd == [(0, 0, 4)] and r.req_to_row == {"a": 0} and r.free_rows == {1}
+    assert any("repetition_penalty=1.1" in m and "logit_bias" in m for m in caplog.messages)
+    assert r.requests["a"].sampling_params.temperature == 0.7

@@ -109,6 +109,18 @@ class B200Platform(Platform):
                 assert cache_config.block_size is not None, "When prefix caching is enabled, block_size must be set."
 
     @classmethod
+    def validate_request(cls, processed_inputs=None, params=None, *args, **kwargs) -> None:
+        """Front-end admission (vLLM's input processor calls this once per request, in the API process): refuse sampling
+        parameters the device sampler cannot apply, so that only the offending client gets an error.  The reference has
+        no such hook: its device path drops those parameters silently (RUNNER:1106-1140), its CPU path applies them
+        (RUNNER:1142-1239); there is no CPU path here."""
+        if params is None or not hasattr(params, "temperature"):  # PoolingParams and the like: not this platform's call
+            return
+        from .admission import check_sampling_params
+
+        check_sampling_params(params, getattr(processed_inputs, "request_id", None) or "?")
+
+    @classmethod
     def get_attn_backend_cls(cls, selected_backend=None, *args, **kwargs) -> str:
         return ATTN_BACKEND_CLS  # one backend; no dispatch
 

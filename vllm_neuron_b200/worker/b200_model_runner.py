@@ -22,6 +22,7 @@ from dataclasses import dataclass, field
 import torch
 
 from .. import ops
+from ..admission import check_sampling_params, unsupported_sampling_params  # noqa: F401 (re-exported)
 from ..config import B200Config, ModelShape, build_config
 from ..model import B200CausalLM, bucket_batch, bucket_ctx_blocks
 
@@ -58,32 +59,6 @@ def _first_group(block_ids):
         assert len(block_ids) == 1, "exactly one KV cache group is supported"
         return list(block_ids[0])
     return list(block_ids)
-
-
-def check_sampling_params(sp, req_id="?") -> None:
-    """Admission check.  The device sampler implements what the reference's on-device sampler takes -- (top_k, top_p,
-    temperature) rows with top_k <= 256 (RUNNER:1106-1140) -- plus seeds, min_tokens / stop handling in the scheduler, and
-    log-probabilities.  Everything else vLLM's CPU Sampler would apply on the reference's CPU path (RUNNER:1142-1239) has
-    no device implementation here; a request asking for it is REJECTED instead of being sampled without it."""
-    if sp is None:
-        return
-    bad = []
-    for name, neutral in (("repetition_penalty", 1.0), ("presence_penalty", 0.0), ("frequency_penalty", 0.0), ("min_p", 0.0)):
-        v = getattr(sp, name, neutral)
-        if v is not None and float(v) != neutral:
-            bad.append(f"{name}={v}")
-    for name in ("logit_bias", "bad_words", "allowed_token_ids", "logits_processors", "structured_outputs", "guided_decoding"):
-        v = getattr(sp, name, None)
-        if v:
-            bad.append(name)
-    if getattr(sp, "prompt_logprobs", None) is not None:
-        bad.append("prompt_logprobs")
-    lp = getattr(sp, "logprobs", None)
-    if lp is not None and not (0 <= int(lp) <= _MAX_SAMPLING_TOP_K):
-        bad.append(f"logprobs={lp} (0..{_MAX_SAMPLING_TOP_K})")
-    if bad:
-        raise ValueError(f"request {req_id}: sampling parameters not supported by the B200 device sampler: {', '.join(bad)} "
-                         "(supported: temperature, top_k <= 256, top_p, seed, min_tokens, stop conditions, logprobs <= 256)")
 
 
 def _logprob_bucket(n: int) -> int:
@@ -274,11 +249,18 @@ class B200ModelRunner:
         for nr in so.scheduled_new_reqs:
             assert nr.req_id not in self.req_to_row, "Encountered an existing request ID while prefilling a new request"
             assert self.free_rows, "No free sequence ID available!"
+            # Unsupported sampling parameters are refused by the front end (B200Platform.validate_request).  A request that
+            # reaches the worker anyway (an engine driven without the input processor) must not take the step down -- an
+            # exception here would end every in-flight request -- so it is sampled from (top_k, top_p, temperature) alone,
+            # exactly what the reference's device path does with it (RUNNER:1106-1140), and says so.
+            bad = unsupported_sampling_params(getattr(nr, "sampling_params", None))
+            if bad:
+                logger.warning("request %s: ignoring sampling parameters without a device implementation: %s",
+                               nr.req_id, ", ".join(bad))
             row = min(self.free_rows)
             self.free_rows.discard(row)
             self.req_to_row[nr.req_id] = row
             blocks = _first_group(nr.block_ids) or []
-            check_sampling_params(getattr(nr, "sampling_params", None), nr.req_id)
             st = CachedRequest(nr.req_id, list(nr.prompt_token_ids), [], blocks, nr.num_computed_tokens, row,
                                getattr(nr, "sampling_params", None))
             self.requests[nr.req_id] = st
