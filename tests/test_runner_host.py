@@ -125,3 +125,29 @@ def test_unsupported_sampling_params_do_not_take_the_step_down(caplog):
     assert upd == [(0, 0, 4)] and r.req_to_row == {"a": 0} and r.free_rows == {1}
     assert any("repetition_penalty=1.1" in m and "logit_bias" in m for m in caplog.messages)
     assert r.requests["a"].sampling_params.temperature == 0.7
+
+
+def test_logprob_rows_of_a_mixed_step_hold_only_real_token_ids():
+    """A prefill part that asked for 1 log-probability (2 columns) next to a decode part that asked for 5 (6 columns), plus
+    a part nobody asked for: every id handed to vLLM must be detokenisable (>= 0), the filler is the row's sampled token
+    at -inf, and the columns a request asked for are untouched."""
+    import numpy as np
+
+    narrow = (torch.tensor([[7, 9]], dtype=torch.int32), torch.tensor([[-0.5, -0.25]]), torch.tensor([2], dtype=torch.int32))
+    wide_ids = torch.tensor([[3, 3, 8, 1, 4, 6], [5, 2, 5, -1, -1, -1]], dtype=torch.int32)  # 2nd row: 3-token vocabulary
+    wide_lp = torch.tensor([[-0.125, -0.125, -2.5, -3.0, -4.0, -5.0], [-1.0, -0.5, -1.0, -np.inf, -np.inf, -np.inf]])
+    wide = (wide_ids, wide_lp, torch.tensor([1, 2], dtype=torch.int32))
+    out = B200ModelRunner._logprobs_lists([(1, narrow), (2, wide), (3, None)])
+    ids, lps, ranks = np.asarray(out[0]), np.asarray(out[1]), np.asarray(out[2])
+    assert ids.shape == lps.shape == (6, 6) and (ids >= 0).all()
+    assert ids[0].tolist() == [7, 9, 7, 7, 7, 7] and lps[0, :2].tolist() == [-0.5, -0.25] and np.isinf(lps[0, 2:]).all()
+    assert ids[1].tolist() == [3, 3, 8, 1, 4, 6]
+    assert ids[2].tolist() == [5, 2, 5, 5, 5, 5] and lps[2].tolist() == [-1.0, -0.5, -1.0, -1.0, -1.0, -1.0]
+    assert (ids[3:] == 0).all() and np.isinf(lps[3:]).all()
+    assert ranks.tolist() == [2, 1, 2, 0, 0, 0]
+    # what vLLM's front end does with a row: detokenise all ids, then keep num_logprobs + 1 entries
+    from vllm.logprobs import append_logprobs_for_next_position
+
+    acc = []
+    append_logprobs_for_next_position(acc, ids[0].tolist(), lps[0].tolist(), [None] * 6, int(ranks[0]), 1)
+    assert {k: v.logprob for k, v in acc[0].items()} == {7: -0.5, 9: -0.25}

@@ -382,8 +382,14 @@ class B200ModelRunner:
 
     @staticmethod
     def _logprobs_lists(parts):
-        """vLLM's LogprobsLists over the step's sampled rows (RUNNER:347-349 `logprobs_tensors.tolists()`); parts that
-        did not compute log-probabilities contribute -inf rows (their requests did not ask)."""
+        """vLLM's LogprobsLists over the step's sampled rows (RUNNER:347-349 `logprobs_tensors.tolists()`).  A mixed step
+        has parts of different widths (a prefill that asked for 1 log-probability next to a decode batch that asked for 20);
+        all are widened to the widest.  vLLM's front end detokenises EVERY id of a row before it cuts the row down to what
+        the request asked for, so the filler must be a real token id: the row's own sampled token (column 0) with
+        log-probability -inf -- never -1, which fast tokenizers refuse.  The same goes for the -1 ids the gather kernel
+        leaves when a vocabulary has fewer tokens than columns; those repeat column 0 outright (id and log-probability), so
+        a duplicate key cannot change the sampled token's entry.  Parts that computed no log-probabilities (nobody in them
+        asked, nobody reads them) are rows of token 0 at -inf."""
         if parts is None:
             return None
         import numpy as np
@@ -392,12 +398,17 @@ class B200ModelRunner:
         width = max(h[0].shape[1] for _, h in parts if h is not None)
         ids, lps, rks = [], [], []
         for rows, h in parts:
-            i = np.full((rows, width), -1, dtype=np.int32)
+            i = np.zeros((rows, width), dtype=np.int32)
             l = np.full((rows, width), -np.inf, dtype=np.float32)
             r = np.zeros((rows,), dtype=np.int32)
             if h is not None:
                 w = h[0].shape[1]
                 i[:, :w], l[:, :w], r[:] = h[0].numpy(), h[1].numpy(), h[2].numpy()
+                i[:, w:] = i[:, :1]
+                short = i < 0  # only inside [:, :w]: the candidate list ran out (vocabulary smaller than the bucket)
+                if short.any():
+                    i = np.where(short, i[:, :1], i)
+                    l = np.where(short, l[:, :1], l)
             ids.append(i); lps.append(l); rks.append(r)
         return LogprobsLists(np.concatenate(ids), np.concatenate(lps), np.concatenate(rks))
 
