@@ -238,14 +238,17 @@ __global__ void __launch_bounds__(128)
   }
   __syncthreads();
   for (int b = threadIdx.x; b < B; b += blockDim.x) {
-    float best = -INFINITY;
-    long long bi = 0x7fffffffffffffffLL;
+    // Start from rank 0's pair, so that out_ids is always an index some rank's argmax wrote (b200_argmax never writes one
+    // outside its shard) -- also for a row whose maxima are all NaN, where no comparison below is true.  A NaN maximum
+    // loses to any number; among numbers the largest wins, ties to the lowest index.
+    float best = 0.f;
+    long long bi = 0;
     for (int p = 0; p < world; ++p) {
       float v;
       long long i;
       asm volatile("ld.volatile.global.f32 %0, [%1];\n" : "=f"(v) : "l"(peers.vals[p] + b) : "memory");
       asm volatile("ld.volatile.global.s64 %0, [%1];\n" : "=l"(i) : "l"(peers.idxs[p] + b) : "memory");
-      if (v > best || (v == best && i < bi)) {
+      if (p == 0 || v > best || (v == best && i < bi) || (best != best && v == v)) {
         best = v;
         bi = i;
       }
