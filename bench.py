@@ -284,6 +284,10 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
       deep (n = all layers, or as many as fit beside rank 0's shard and KV pool), depth-aware bar -- two differently
         rounded computations decorrelate like sqrt(n): measured 0.42 std (8B fp8, 32 layers), 0.63 (70B fp8, 78 layers),
         0.08 (32B weight-only, 64 layers) at TP=8; bar = min(1.0, 1.6 x base x sqrt(n / 2)), base 0.10 (W8A8) / 0.012 (0.016 with the NVLS exchange).
+        For W8A8 that bar is 0.64 std at 32 layers and 1.0 std at 78, where two UNRELATED logit vectors sit at 1.41 std: it
+        cannot catch a wrong shard, so the W8A8 deep pass is reported (`"gate": "informational"`) and does not decide the
+        exit status -- only a non-finite distance fails it.  The gates are the shallow pass (any quantisation) and the deep
+        pass of bf16 / weight-only models.
     In both passes the TP=N sampled ids must equal TP=1's wherever TP=1's own top-2 margin is outside 8x the measured rms
     difference.  On failure every rank exits with status 3.  Returns the record that goes into the JSON line."""
     import math
@@ -336,6 +340,7 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
     for n_chk, bar in ((n_shallow, tight), (n_fit, max(tight, min(1.0, 1.6 * base * math.sqrt(n_fit / 2))))):
         if rec["passes"] and n_chk == rec["passes"][0]["layers_checked"]:
             break
+        gating = not (w8a8 and rec["passes"])  # the deep W8A8 pass is a record, not a gate (docstring)
         model.layers, model.kv = all_layers[:n_chk], all_kv[:n_chk]
         ref = None
         if rank == 0:
@@ -344,8 +349,8 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
             fill_kv_pools(ref, shape, 0, 1, blocks=blocks)
             ref.block_table[:b].copy_(bt[:, :ref.max_blocks])
         tok = torch.randint(0, shape.vocab, (b,), generator=torch.Generator().manual_seed(4321)).to(dev)
-        pr = {"layers_checked": n_chk, "bar_frac_of_std": round(bar, 3), "tokens_compared": 0, "tokens_equal": 0,
-              "logit_rms_err": [], "logit_std": []}
+        pr = {"layers_checked": n_chk, "gate": "pass/fail" if gating else "informational",
+              "bar_frac_of_std": round(bar, 3), "tokens_compared": 0, "tokens_equal": 0, "logit_rms_err": [], "logit_std": []}
         rec["passes"].append(pr)
         for st in range(steps):
             bufs.tokens.copy_(tok)
@@ -368,7 +373,7 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
                 pr["tokens_equal"] += int((got == want).sum().item())
                 pr["logit_rms_err"].append(round(err, 5))
                 pr["logit_std"].append(round(std, 4))
-                if bad.any() or not err < bar * std:
+                if (bad.any() or not err < bar * std) if gating else not math.isfinite(err):
                     status[0] = 3
                     rec["tp_check"] = (f"FAILED ({n_chk} layers) at step {st}: {int(bad.sum().item())} tokens differ outside the "
                                        f"margin guard, logit rms err {err:.3e} vs std {std:.3f} (bar {bar:.2f} std)")
@@ -385,6 +390,23 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
     model.layers, model.kv = all_layers, all_kv
     rec["layers_checked"] = rec["passes"][-1]["layers_checked"]
     return rec
+
+
+def parity_summary(rec) -> str:
+    """The TP parity record in one short string for the `data` field (the full record is the line's `parity` object, which
+    a reader that keeps only the head of the line loses): per pass `<layers>L <worst rms distance>/<bar> std <equal>/<compared>
+    tok`, the bar replaced by `info` for a pass that does not gate."""
+    if not rec:
+        return "tp parity: n/a (1 GPU)"
+    if "passes" not in rec:
+        return f"tp parity: {rec.get('tp_check', '?')[:60]}"
+    parts = []
+    for p in rec["passes"]:
+        fr = max((e / s for e, s in zip(p["logit_rms_err"], p["logit_std"]) if s > 0), default=float("nan"))
+        bar = f"{p['bar_frac_of_std']:.2f}" if p.get("gate", "pass/fail") == "pass/fail" else "info"
+        parts.append(f"{p['layers_checked']}L {fr:.3f}/{bar} std {p['tokens_equal']}/{p['tokens_compared']} tok")
+    head = "ok" if rec.get("tp_check") == "ok" else "FAILED"
+    return f"tp parity vs TP=1 {head} ({rec.get('exchange', '?')}): " + "; ".join(parts)
 
 
 def measure_at(args, shape, model, bufs, bt_host, dev, rank, world, local, group, barrier, parity, max_model_len, num_blocks,
@@ -480,7 +502,7 @@ def measure_at(args, shape, model, bufs, bt_host, dev, rank, world, local, group
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": k_steps, "warmup": w_steps,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": args.quant, "data": "synthetic (random-init weights, N(0,1) KV pool, random tokens, permuted block ids)",
+        "dtype": args.quant, "data": "synthetic (random-init weights, N(0,1) KV pool, random tokens, permuted block ids); " + parity_summary(parity),
         "config": workload_config(args, shape, world),  # the same dict the reference arm prints
         "run": {"mean_context_in_timed_region": mean_ctx, "max_model_len": max_model_len, "num_blocks": num_blocks,
                 "cuda_graph": True},

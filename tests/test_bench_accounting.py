@@ -44,3 +44,19 @@ def test_context_bucket_bounds():
         got = bucket_ctx_blocks(n, 1031)
         assert n <= got <= min(1031, max(8, int(n * 1.125) + 8)), (n, got)
     assert [bucket_batch(b, 64) for b in (1, 2, 3, 5, 33, 64)] == [1, 2, 4, 8, 64, 64]
+
+
+def test_parity_summary_fits_the_head_of_the_line():
+    """The one-line TP parity summary that goes into `data`: worst distance per pass over its bar, `info` for the W8A8 deep
+    pass (reported, not gating), token agreement; short enough to survive a reader that truncates the JSON line."""
+    b = _bench()
+    assert b.parity_summary(None) == "tp parity: n/a (1 GPU)"
+    assert b.parity_summary({"tp_check": "off"}) == "tp parity: off"
+    rec = {"tp_check": "ok", "exchange": "nvls", "passes": [
+        {"layers_checked": 2, "gate": "pass/fail", "bar_frac_of_std": 0.3, "tokens_compared": 256, "tokens_equal": 240,
+         "logit_rms_err": [0.01, 0.011], "logit_std": [0.1, 0.1]},
+        {"layers_checked": 32, "gate": "informational", "bar_frac_of_std": 0.64, "tokens_compared": 256, "tokens_equal": 61,
+         "logit_rms_err": [0.043, 0.04], "logit_std": [0.1, 0.1]}]}
+    s = b.parity_summary(rec)
+    assert s == "tp parity vs TP=1 ok (nvls): 2L 0.110/0.30 std 240/256 tok; 32L 0.430/info std 61/256 tok"
+    assert len(s) < 120
