@@ -189,7 +189,10 @@ int b200_gemm_silu_mul(const void* a, const void* w_gu, void* out_act, const flo
  * barrier; `state` is 1040 bytes of device memory, zero-initialised ONCE and then owned by the library (any number of
  * launches on one stream).  Bit-identical to b200_gemm_silu_mul + b200_quantize_per_token.  Decode schedule only:
  * returns B200_ERR_UNSUPPORTED (nothing launched) when M > 128 or when the shape does not run as one resident wave of
- * one CTA per weight tile -- the caller then uses the two-call form. */
+ * one CTA per weight tile -- the caller then uses the two-call form.  "Resident" is worked out from the occupancy
+ * query for a GPU that runs nothing else: if another stream or process holds SM slots while this kernel starts, CTAs wait
+ * at the barrier for peers that cannot be scheduled and the kernel traps after about 2 s.  Use it only where this library's
+ * stream owns the GPU; the product path keeps it off (B200_FUSE_SILU_QUANT unset) and uses the two-call form. */
 int b200_gemm_silu_mul_quant(const void* a, const void* w_gu, void* out_q, float* out_scale, const float* a_scale,
                              const float* w_scale, const void* bias, void* state, int M, int N2, int K, int ab_dtype,
                              void* stream);

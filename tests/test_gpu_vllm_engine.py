@@ -78,6 +78,12 @@ def _oracle_check(res, quant, band, widen_once=False):
     return checked, near_ties, bad
 
 
+# Committed floors on the number of engine tokens that ARE the oracle's argmax (the rest must sit inside the error band).
+# Two or three below the lowest count ever measured: room for a near-tie flipping with the CPU oracle's thread count,
+# none for a real regression.
+EXACT_FLOOR = {"bf16": 102, "fp8": 82, "native": 101, "cfg1": 236, "tp2": 101}
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("quant,band", [("bf16", 0.05), ("fp8", 0.6)])
 def test_vllm_engine_greedy_tokens_match_oracle(tmp_path, quant, band):
@@ -93,7 +99,12 @@ def test_vllm_engine_greedy_tokens_match_oracle(tmp_path, quant, band):
     total = sum(want_len.values())
     print(f"[{quant}] engine tokens: {checked} equal to the oracle's argmax, {near_ties} inside the error band, {len(bad)} outside")
     assert not bad, bad
-    assert checked >= (0.9 if quant == "bf16" else 0.7) * total
+    # north_star asks for identical greedy tokens; on random-init weights the oracle's own top-2 gap is often inside the
+    # rounding noise, so "identical" is stated as a committed floor on the exact-match count instead of a loose
+    # fraction.  Measured on B200 (104 tokens): bf16 104 / 104 / 103, fp8 85 / 86 over rounds 2-3 (the CPU oracle's thread
+    # count moves a near-tie or two between hosts).  A drop below the floor is a regression, not noise.
+    assert total == 104
+    assert checked >= EXACT_FLOOR[quant], (checked, EXACT_FLOOR[quant])
     # "d" repeats a's first 64 tokens: vLLM's prefix cache must have served two full blocks
     nc = res["num_cached_tokens"].get("d")
     assert nc is None or nc >= 64, res["num_cached_tokens"]
@@ -109,7 +120,8 @@ def test_vllm_engine_native_scheduler_chunked_prefill(tmp_path):
     checked, near_ties, bad = _oracle_check(res, "bf16", 0.05)
     print(f"[native scheduler] engine tokens: {checked} equal to the oracle's argmax, {near_ties} inside the band, {len(bad)} outside")
     assert not bad, bad
-    assert checked >= 0.9 * sum(len(v) for v in res["outputs"].values())
+    assert sum(len(v) for v in res["outputs"].values()) == 104
+    assert checked >= EXACT_FLOOR["native"], (checked, EXACT_FLOOR["native"])  # measured 103 / 103
 
 
 @pytest.mark.gpu
@@ -125,7 +137,7 @@ def test_vllm_engine_cfg1_tinyllama_64_greedy_steps(tmp_path):
     checked, near_ties, bad = _oracle_check(res, "bf16", 0.10, widen_once=True)
     print(f"[cfg1] engine tokens: {checked} equal to the oracle's argmax, {near_ties} inside the band, {len(bad)} outside")
     assert not bad, bad
-    assert checked >= 0.9 * 256
+    assert checked >= EXACT_FLOOR["cfg1"], (checked, EXACT_FLOOR["cfg1"])  # measured 238 / 248 / 245 of 256 over rounds 1-3
 
 
 @pytest.mark.gpu
@@ -140,4 +152,5 @@ def test_vllm_engine_tensor_parallel_2(tmp_path):
     checked, near_ties, bad = _oracle_check(res, "bf16", 0.05)
     print(f"[tp2] engine tokens: {checked} equal to the oracle's argmax, {near_ties} inside the band, {len(bad)} outside")
     assert not bad, bad
-    assert checked >= 0.9 * sum(len(v) for v in res["outputs"].values())
+    assert sum(len(v) for v in res["outputs"].values()) == 104
+    assert checked >= EXACT_FLOOR["tp2"], (checked, EXACT_FLOOR["tp2"])
