@@ -215,7 +215,7 @@ def run_reference(args, shape):
     budget_s, t_layer, t_head, done = args.cpu_budget_s, [], [], 0
     t_start = time.perf_counter()
     for _ in range(args.steps):
-        if done >= 3 and time.perf_counter() - t_start > budget_s:
+        if done >= 4 and time.perf_counter() - t_start > budget_s:  # at least 4 layers' worth, whatever the budget
             break
         t0 = time.perf_counter()
         x = layer_once()
@@ -225,11 +225,16 @@ def run_reference(args, shape):
         t_layer.append(t1 - t0)
         t_head.append(t2 - t1)
         done += 1
-    step_s = shape.layers * statistics.mean(t_layer) + statistics.mean(t_head)
+    # MEDIAN of the timed layers (a shared host's stragglers moved the mean by +-25 % between runs), and the time actually
+    # spent next to the extrapolated one, so that a reader can check the line against a wall clock
+    step_s = shape.layers * statistics.median(t_layer) + statistics.median(t_head)
     value = args.batch / step_s
+    timed_s = sum(t_layer) + sum(t_head)
     sample = (f"each step = 1 of {shape.layers} decoder layers on the full batch ({args.batch} seqs, ctx {args.ctx}) + "
               f"lm_head/argmax, extrapolated x{shape.layers}; {done} of {args.steps} steps timed inside a "
-              f"{budget_s:.0f} s budget (mean used); torch-CPU oracle (oracle/llama_ref.py), fp64-accumulate GEMMs")
+              f"{budget_s:.0f} s budget (median used; {timed_s:.1f} s actually timed, layer min/median/max "
+              f"{min(t_layer):.3f}/{statistics.median(t_layer):.3f}/{max(t_layer):.3f} s); torch-CPU oracle "
+              f"(oracle/llama_ref.py), fp64-accumulate GEMMs")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "strong",
@@ -238,6 +243,9 @@ def run_reference(args, shape):
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        # ms_per_step is the EXTRAPOLATED full step; this is what the clock saw
+        "timed": {"timed_s": round(timed_s, 3), "steps_timed": done, "layers_per_step_timed": 1,
+                  "extrapolation_factor_layers": shape.layers},
     }
     print(json.dumps(line), flush=True)
 
@@ -392,6 +400,17 @@ def tp_parity_check(args, shape, model, bufs, rank, world, dev, group, steps=4, 
     return rec
 
 
+def traffic_capture(args, shape, b, world):
+    """What the committed `ncu --set full` capture behind roofline.traffic measured: DRAM bytes of one launch, the
+    algorithmic bytes of THAT launch (its context differs from the timed one's by a few tokens) and their ratio."""
+    cap = getattr(args, "attn_traffic_capture", None)
+    if not (cap and cap.get("algorithmic_bytes") and args.attn_traffic
+            and shape.name == "Llama-3.1-8B" and b == 64 and args.ctx == 2048 and world == 1):
+        return None
+    return {"dram_bytes": args.attn_traffic, "algorithmic_bytes": cap["algorithmic_bytes"],
+            "dram_over_algorithmic": round(args.attn_traffic / cap["algorithmic_bytes"], 4), "source": cap["source"]}
+
+
 def parity_summary(rec) -> str:
     """The TP parity record in one short string for the `data` field (the full record is the line's `parity` object, which
     a reader that keeps only the head of the line loses): per pass `<layers>L <worst rms distance>/<bar> std <equal>/<compared>
@@ -481,6 +500,9 @@ def measure_at(args, shape, model, bufs, bt_host, dev, rank, world, local, group
         "peak": hbm_peak, "unit": "GB/s", "frac": round(achieved / hbm_peak, 4),
         # the committed ncu --set full capture is of the headline shape (8B, B=64, 2k, TP=1) only
         "traffic": args.attn_traffic if (shape.name == "Llama-3.1-8B" and b == 64 and args.ctx == 2048 and world == 1) else None,
+        # `traffic` is an ncu capture of an EARLIER launch of the same kernel at a slightly shorter context than the one timed
+        # here: compare it with the capture's own algorithmic bytes (traffic_capture), not with algorithmic_bytes_per_launch
+        "traffic_capture": traffic_capture(args, shape, b, world),
         "peak_source": peak_src, "algorithmic_bytes_per_launch": int(attn_bytes), "mean_us_per_launch": round(attn_ms * 1e3, 2),
         "timing": f"CUDA events around {attn_launches} graph-replayed launches (one per layer's KV pool per replay)",
         "mean_us_per_launch_eager": round(attn_ms_eager * 1e3, 2),
@@ -706,7 +728,10 @@ def main():
     if args.attn_traffic is None:
         try:
             with open(os.path.join(ROOT, "profiles", "attn_traffic.json")) as f:
-                args.attn_traffic = json.load(f).get("dram_bytes_per_launch")
+                cap = json.load(f)
+            args.attn_traffic = cap.get("dram_bytes_per_launch")
+            args.attn_traffic_capture = {"algorithmic_bytes": cap.get("algorithmic_bytes_same_launch"),
+                                         "source": cap.get("source")}
         except Exception:
             pass
     if args.impl == "reference":

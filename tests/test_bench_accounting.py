@@ -60,3 +60,20 @@ def test_parity_summary_fits_the_head_of_the_line():
     s = b.parity_summary(rec)
     assert s == "tp parity vs TP=1 ok (nvls): 2L 0.110/0.30 std 240/256 tok; 32L 0.430/info std 61/256 tok"
     assert len(s) < 120
+
+
+def test_traffic_is_paired_with_the_capture_it_came_from():
+    """roofline.traffic comes from one committed ncu capture; the line must carry that capture's own algorithmic bytes so
+    that nobody divides it by the (different) launch timed in the bench."""
+    from types import SimpleNamespace
+
+    b = _bench()
+    from vllm_neuron_b200.config import PRESETS
+
+    args = SimpleNamespace(attn_traffic=542090000, ctx=2048,
+                           attn_traffic_capture={"algorithmic_bytes": 538700000, "source": "profiles/x.json"})
+    got = b.traffic_capture(args, PRESETS["llama-3.1-8b"], 64, 1)
+    assert got == {"dram_bytes": 542090000, "algorithmic_bytes": 538700000, "dram_over_algorithmic": 1.0063,
+                   "source": "profiles/x.json"}
+    assert b.traffic_capture(args, PRESETS["llama-3.1-8b"], 64, 2) is None      # capture is of the TP=1 headline shape only
+    assert b.traffic_capture(SimpleNamespace(attn_traffic=None, ctx=2048), PRESETS["llama-3.1-8b"], 64, 1) is None
