@@ -21,6 +21,13 @@ try:
 except Exception:
     pass
 HBM = PEAKS.get("hbm_gbs", 6650.0)
+# dense FP8 peak measured by tools/fp8_peak.py on this pool (cuBLASLt e4m3, sustained); None until that file is committed
+FP8_PEAK = None
+try:
+    FP8_PEAK = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles",
+                                           "fp8_peak.json"))).get("fp8_tflops_sustained")
+except Exception:
+    pass
 
 
 def time_calls(fns, iters=3, warmup=1, graph=True):
@@ -185,6 +192,8 @@ def bench_prefill(attn_only=False):
                 tf = 2 * m * n * k / ms / 1e9
                 res.append({"kernel": f"gemm_streamk_{kind}", "linear": name, "M": m, "N": n, "K": k, "us": round(ms * 1e3, 1),
                             "TFLOPs": round(tf, 1), "frac_bf16_sustained_peak": round(tf / tf_peak, 3)})
+                if kind == "fp8" and FP8_PEAK:  # an FP8 GEMM is judged against the FP8 tensor peak, not the bf16 one
+                    res[-1]["frac_fp8_sustained_peak"] = round(tf / FP8_PEAK, 3)
                 print(res[-1], flush=True)
     hq, hkv, d, bs = 32, 8, 128, 32
     cases = ((2048, 0), (2048, 1024), (8192, 0), (8192, 4096), (32768, 0))
