@@ -19,6 +19,7 @@ Runs in this (GPU-less) authoring container with transformers 5.5.0; takes a few
 from __future__ import annotations
 
 import argparse
+import dataclasses
 import json
 import os
 import sys
@@ -39,7 +40,13 @@ CASES = [
     ("tiny-test", "tiny-test", 3, 0.05, None, 40, ("plain", "int8_wo", "fp8", "int8")),
     ("tiny-qwen", "tiny-qwen", 5, 0.05, None, 37, ("plain", "int8_wo", "fp8", "int8")),
     ("tinyllama-1.1b", "tinyllama-1.1b", 3, 0.02, None, 48, ("plain",)),
+    # Llama-3.1's frequency scaling (rope_type "llama3", what the headline 8B / 70B models run): the tiny shape with the
+    # 3.1 factors and an original context of 64, so that positions 0..153 cross all three branches of the rule (wavelength
+    # < 16 untouched, > 64 divided by 8, smooth in between) -- with the real 8192 a short golden sequence would not see it
+    ("tiny-llama3rope", "tiny-test", 7, 0.05, None, 90, ("plain",)),
 ]
+ROPE_SCALING = {"tiny-llama3rope": {"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0, "high_freq_factor": 4.0,
+                                    "original_max_position_embeddings": 64}}
 
 
 def fake_quant_rows(x: torch.Tensor, kind: str) -> torch.Tensor:
@@ -66,7 +73,8 @@ def build_hf(shape, weights, mode: str):
               num_key_value_heads=shape.num_kv_heads, intermediate_size=shape.intermediate, vocab_size=shape.vocab,
               rms_norm_eps=shape.rms_eps, rope_theta=shape.rope_theta, max_position_embeddings=4096,
               tie_word_embeddings=False, hidden_act="silu", attn_implementation="eager")
-    assert shape.rope_scaling is None, "golden shapes use plain RoPE"
+    if shape.rope_scaling is not None:
+        kw["rope_scaling"] = dict(shape.rope_scaling)
     if shape.qkv_bias:
         assert shape.head_dim * shape.num_q_heads == shape.hidden
         cfg, cls = Qwen2Config(**kw), Qwen2ForCausalLM
@@ -138,10 +146,12 @@ def main():
         if only and key not in only:
             continue
         shape = PRESETS[preset]
+        if key in ROPE_SCALING:
+            shape = dataclasses.replace(shape, rope_scaling=ROPE_SCALING[key])
         weights = random_init_full_weights(shape, seed=seed, std=std, resid_std=resid_std)
         g = torch.Generator().manual_seed(1000 + seed)
         prompt = torch.randint(3, shape.vocab, (plen,), generator=g).tolist()
-        golden[key] = {"preset": preset, "seed": seed, "std": std, "resid_std": resid_std, "prompt": prompt,
+        golden[key] = {"rope_scaling": shape.rope_scaling, "preset": preset, "seed": seed, "std": std, "resid_std": resid_std, "prompt": prompt,
                        "arch": "Qwen2ForCausalLM" if shape.qkv_bias else "LlamaForCausalLM", "modes": {}}
         for mode in modes:
             rec = run_case(shape, weights, mode, prompt)

@@ -12,6 +12,7 @@ Three gates per case:
  3. ROUNDING NOISE: the oracle as the GPU tests use it (bf16 activations) against the same HF vectors -- the distance is
     bf16 rounding noise; it is measured, bounded, and tokens must agree wherever HF's own top-2 margin exceeds it.
 """
+import dataclasses
 import json
 import os
 
@@ -24,6 +25,7 @@ from vllm_neuron_b200.model import random_init_full_weights
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "hf_golden.json")
 BS = 32
+rope_scaling_override = {}  # {"value": None} makes _oracle drop a case's rope scaling (sensitivity check below)
 
 
 def _golden():
@@ -33,6 +35,8 @@ def _golden():
 
 def _oracle(case, mode, act_dtype, total_len):
     shape = PRESETS[case["preset"]]
+    if case.get("rope_scaling"):
+        shape = dataclasses.replace(shape, rope_scaling=rope_scaling_override.get("value", case["rope_scaling"]))
     w = random_init_full_weights(shape, seed=case["seed"], std=case["std"], resid_std=case["resid_std"])
     nblk = -(-total_len // BS)
     mml = nblk * BS
@@ -179,3 +183,28 @@ def test_oracle_tinyllama_shape_matches_hf_fp32():
     worst, same, must = _compare(logits, rec, 5e-4, "tinyllama-1.1b")
     print(f"[tinyllama-1.1b] fp32 oracle vs HF: max top-8 logit diff {worst:.2e} of spread, {same}/64 tokens equal")
     assert same == 64
+
+
+def test_oracle_llama3_rope_scaling_matches_hf_fp32():
+    """Llama-3.1 frequency scaling (rope_type "llama3"), which the headline 8B / 70B models run and the plain-RoPE cases above
+    never touch: HF's own LlamaRotaryEmbedding supplies the frequencies (28 of 32 scaled at this shape: untouched, smooth and
+    divided-by-8 branches all present), the oracle's kv_ref.rope_table must land on the same logits to fp32 noise, through
+    the block-KV prefill path over positions 0..153.  And the pin is not vacuous: the same oracle WITHOUT the scaling is far
+    outside the bar."""
+    case = _golden()["tiny-llama3rope"]
+    assert case["rope_scaling"]["rope_type"] == "llama3"
+    logits, rec = _replay_prefill(case, "plain", torch.float32)
+    worst, same, must = _compare(logits, rec, 2e-4, "tiny-llama3rope prefill path")
+    print(f"[tiny-llama3rope] fp32 oracle vs HF: max top-8 logit diff {worst:.2e} of spread, {same}/64 tokens equal")
+    assert same == 64
+    full = torch.tensor(rec["logits0"])
+    assert ((logits[0] - full).abs().max() / rec["logit_std"][0]).item() <= 2e-4
+    rope_scaling_override["value"] = None
+    try:
+        plain, _ = _replay_prefill(case, "plain", torch.float32)
+    finally:
+        rope_scaling_override.clear()
+    drift = max(((plain[i][torch.tensor(rec["top_ids"][i])] - torch.tensor(rec["top_vals"][i])).abs().max()
+                 / rec["logit_std"][i]).item() for i in range(plain.shape[0]))
+    print(f"[tiny-llama3rope] the same oracle with plain RoPE is {drift:.3f} of the spread away")
+    assert drift > 50 * 2e-4
